@@ -1,0 +1,185 @@
+/*
+ * soda_b200.h - C ABI of the B200-native SODa hot path (libsoda_b200.so).
+ *
+ * The reference (KirillHit/snn_for_object_detection) has NO native/FFI boundary: its operator
+ * interface is a Python protocol.  The entry points below are therefore the
+ * device-side halves of the reference *call sites* they replace; each cites the reference
+ * file:line whose arithmetic it reproduces.  The Python host side
+ * (snn_for_object_detection_b200/) keeps the reference's LayerGen / BlockGen / SODa API on top.
+ *
+ * Conventions (all entry points):
+ *   - plain C types only: device pointers, int/int64_t sizes, float parameters, a CUDA stream
+ *     passed as void* (cudaStream_t);
+ *   - returns 0 on success, a soda_status_t > 0 otherwise; soda_last_error() gives the
+ *     thread-local message.  Never throws, never allocates device memory, never synchronises:
+ *     work is enqueued on the caller's stream and every buffer is caller-owned;
+ *   - activations are fp32, "pixel-major" (N, H, W, C) = torch channels_last, addressed as
+ *         elem(n, y, x, c) = base[n * batch_stride + (y * W + x) * pix_stride + c]
+ *     (strides in elements) so a layer can read or write a channel slice of a concat buffer;
+ *   - there is no CPU implementation behind any of them.
+ */
+#ifndef SODA_B200_H
+#define SODA_B200_H
+
+#include <stdint.h>
+
+#if defined(__GNUC__)
+#define SODA_API __attribute__((visibility("default")))
+#else
+#define SODA_API
+#endif
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+typedef enum {
+  SODA_OK = 0,
+  SODA_ERR_BAD_ARG = 1,      /* null pointer / non-positive size / misaligned buffer */
+  SODA_ERR_UNSUPPORTED = 2,  /* shape or flag combination this build has no kernel for */
+  SODA_ERR_CUDA = 3          /* a CUDA runtime/driver call failed (message has the code) */
+} soda_status_t;
+
+#define SODA_ABI_VERSION 1
+
+SODA_API int soda_abi_version(void);
+SODA_API const char* soda_last_error(void);
+/* Number of kernels launched by this library in this process (all threads). */
+SODA_API int64_t soda_launch_count(void);
+
+/* ---------------------------------------------------------------------------------------------
+ * Event decode + occupancy binning  (K7)
+ *   replaces: prophesee_toolbox/src/io/dat_events_tools.py:100-108 (Event2D unpack:
+ *             x = w & 0x3FFF, y = (w >> 14) & 0x3FFF, p = (w >> 28) & 1) followed by
+ *             utils/datasets.py:420-433 (ST) / :326-336 (MT):  ts = (t - t0) / step_us ;
+ *             features[ts, p, y, x] = 1   (binary occupancy, duplicates idempotent).
+ *   events        : device, n_total little-endian 8-byte records {u32 t_us, i32 w}, samples
+ *                   concatenated; sample b owns records [sample_offsets[b], sample_offsets[b+1])
+ *   sample_offsets: device int64[B+1]
+ *   t0_us         : device int64[B]; events with t < t0 are dropped (datasets.py:416); events
+ *                   whose bin is >= T are dropped (the reference never produces them: its loader
+ *                   slices by time first, psee_loader.py:123-165)
+ *   clip_x        : 1 = clamp x to W-1 as datasets.py:426 (ST); 0 = MT behaviour.  Events with
+ *                   y >= H (or x >= W when !clip_x) raise IndexError in the reference; here they
+ *                   are dropped and counted in *n_dropped (device int32, may be NULL).
+ *   frames        : device fp32, element (t, b, p, y, x) at
+ *                   frames[t*stride_t + b*stride_b + (p*H + y)*W + x]; every element of the
+ *                   [T,B,2,H,W] block is written (0.0f or 1.0f) - no pre-zeroing needed.
+ *   sorted_by_time: 1 = records of each sample are non-decreasing in t (the .dat contract that
+ *                   psee_loader.py:157 itself relies on) -> single-pass shared-memory bitmap
+ *                   kernel; 0 = any order -> clear + scatter kernels.
+ * ------------------------------------------------------------------------------------------- */
+SODA_API int soda_bin_events(const void* events, const int64_t* sample_offsets, const int64_t* t0_us,
+                    int B, int64_t step_us, int T, int H, int W, int clip_x, int sorted_by_time,
+                    float* frames, int64_t stride_t, int64_t stride_b, int* n_dropped,
+                    void* stream);
+
+/* ---------------------------------------------------------------------------------------------
+ * Convolution (K1) with the per-channel affine of inference BatchNorm (K2), residual add and
+ * concat-slice store (K6) in the epilogue.
+ *   replaces: models/modules/layer_gen.py:129-136  nn.Conv2d(Cin, Cout, k, padding=k/2,
+ *             stride, bias=False); :211-214 nn.BatchNorm2d in eval mode;
+ *             models/generator.py:146 (Residual = sum of branches) and :158 (Dense = cat(dim=1)).
+ *   y[n,oy,ox,co] = scale[co] * sum_{ky,kx,ci} x[n, oy*s+ky-k/2, ox*s+kx-k/2, ci] * w[co,ci,ky,kx]
+ *                   + shift[co] (+ residual[n,oy,ox,co])
+ *
+ * Two steps, so that the weight re-layout and the BatchNorm fold are paid once per weight
+ * update and not once per call:
+ *   soda_conv_pack_weights : weight in the reference's own layout [Cout, Cin, k, k] (the
+ *       state_dict tensor) * scale[Cout] (NULL = 1) -> an opaque packed buffer of
+ *       soda_conv_packed_elems() floats owned by the caller.
+ *   soda_conv2d_fwd        : consumes the packed buffer.
+ *   kind: SODA_CONV_FP32 = FP32-pipe implicit GEMM, fp32-exact products (any shape);
+ *         SODA_CONV_TC   = TMA-fed tcgen05/TMEM implicit GEMM, 3xTF32 split (fp32-level
+ *                          accuracy); needs Cin % 32 == 0 and pixel-major input.
+ *   shift, residual : may be NULL.
+ *   in_nchw: 1 = input is plain NCHW-contiguous [N,Cin,H,W] (the event frames); strides ignored
+ * ------------------------------------------------------------------------------------------- */
+#define SODA_CONV_FP32 0
+#define SODA_CONV_TC 1
+
+typedef struct {
+  int N, H, W, Cin, Cout, k, stride;
+  int in_nchw;
+  int kind;
+  int64_t in_batch_stride, in_pix_stride;
+  int64_t out_batch_stride, out_pix_stride;
+  int64_t res_batch_stride, res_pix_stride;
+} soda_conv_desc_t;
+
+SODA_API int64_t soda_conv_packed_elems(int Cout, int Cin, int k, int kind);
+SODA_API int soda_conv_pack_weights(const float* weight, const float* scale, int Cout, int Cin, int k,
+                           int kind, float* packed, void* stream);
+SODA_API int soda_conv2d_fwd(const soda_conv_desc_t* d, const float* x, const float* packed,
+                    const float* shift, const float* residual, float* y, void* stream);
+
+/* ---------------------------------------------------------------------------------------------
+ * LIF / LI scans over T time steps (K3, K4)
+ *   replaces: models/modules/layer_gen.py:233 norse.torch.LIFCell() and :253 LICell() (norse
+ *             1.1.0, third-party, restated in oracle/norse_restated.py), called once per time
+ *             step by models/generator.py:190-193; optional Tanh of layer_gen.py:283-284.
+ *   x        : [T, n] input currents, time-major, any element order inside a step
+ *   v0, i0   : [n] incoming state or NULL (= initial state v = v_leak, i = 0)
+ *   out      : [T, n]  LIF: spikes {0,1};  LI: membrane potential (tanh applied if apply_tanh)
+ *   v_out,i_out : [n] state after the last step (never NULL)
+ *   v_dec_trace : NULL or [T, n], pre-reset membrane v_decayed (saved for backward)
+ *   v_trace,i_trace : NULL or [T, n], per-step new state (what StateStorage records,
+ *                     models/modules/common.py:117-122)
+ *   Arithmetic is op-for-op that of the restatement (no FMA contraction), so results are
+ *   bit-identical to it for identical inputs.  jump_first: 1 = norse 1.1.0 order (default).
+ * ------------------------------------------------------------------------------------------- */
+typedef struct {
+  float dt_tau_mem; /* fp32(dt) * fp32(tau_mem_inv) = 0.1f  */
+  float dt_tau_syn; /* fp32(dt) * fp32(tau_syn_inv) = 0.2f  */
+  float v_leak, v_th, v_reset;
+  float alpha;      /* SuperSpike steepness (backward only) */
+  int jump_first;
+  int detach_reset; /* backward only */
+} soda_neuron_params_t;
+
+SODA_API int soda_lif_fwd(const soda_neuron_params_t* p, const float* x, const float* v0, const float* i0,
+                 int T, int64_t n, float* out, float* v_out, float* i_out, float* v_dec_trace,
+                 float* v_trace, float* i_trace, void* stream);
+
+SODA_API int soda_li_fwd(const soda_neuron_params_t* p, const float* x, const float* v0, const float* i0,
+                int T, int64_t n, int apply_tanh, float* out, float* v_out, float* i_out,
+                float* i_trace, void* stream);
+
+/* Surrogate-gradient LIF backward (K8): fused reverse scan over T.
+ *   replaces: autograd through T calls of LIFCell incl. norse SuperSpike.backward
+ *             (g / (alpha*|v_dec - v_th| + 1)^2), models/soda.py:146-158.
+ *   grad_out : [T, n] dL/dz ;  grad_v_T, grad_i_T : [n] or NULL (grad wrt final state)
+ *   v_dec_trace : [T, n] from the forward
+ *   grad_x : [T, n] ; grad_v0, grad_i0 : [n] or NULL */
+SODA_API int soda_lif_bwd(const soda_neuron_params_t* p, const float* grad_out, const float* grad_v_T,
+                 const float* grad_i_T, const float* v_dec_trace, int T, int64_t n, float* grad_x,
+                 float* grad_v0, float* grad_i0, void* stream);
+
+/* LI backward: out_t = v_t (pre-tanh; tanh' is applied by the caller's grad_out). */
+SODA_API int soda_li_bwd(const soda_neuron_params_t* p, const float* grad_out, const float* grad_v_T,
+                const float* grad_i_T, int T, int64_t n, float* grad_x, float* grad_v0,
+                float* grad_i0, void* stream);
+
+/* ---------------------------------------------------------------------------------------------
+ * Pooling (K5)
+ *   replaces: models/modules/common.py:45-49 SumPool2d (avg_pool2d * k * k) and
+ *             layer_gen.py:163-168 AvgPool2d / MaxPool2d (floor mode, no padding).
+ *   mode: 0 = sum, 1 = average, 2 = max.  Pixel-major in and out (see conventions).
+ * ------------------------------------------------------------------------------------------- */
+SODA_API int soda_pool2d_fwd(const float* x, int N, int H, int W, int C, int k, int stride, int mode,
+                    int64_t in_batch_stride, int64_t in_pix_stride, float* y,
+                    int64_t out_batch_stride, int64_t out_pix_stride, void* stream);
+
+/* Per-channel affine on pixel-major data (stand-alone eval BatchNorm, layer_gen.py:211-214, for
+ * generated nets where Norm does not follow a Conv) and strided copy into a concat slice. */
+SODA_API int soda_channel_affine(const float* x, int64_t n_pix, int C, int64_t in_pix_stride,
+                        const float* scale, const float* shift, float* y, int64_t out_pix_stride,
+                        void* stream);
+
+/* Sum of k pixel-major tensors of equal shape (Residual merge, generator.py:146). */
+SODA_API int soda_add_n(const float* const* xs, int k, int64_t n, float* y, void* stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* SODA_B200_H */

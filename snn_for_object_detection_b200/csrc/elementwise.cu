@@ -1,0 +1,178 @@
+// Pooling, per-channel affine and n-ary add on pixel-major fp32 tensors (HBM-bound glue kernels).
+//
+// Reference arithmetic: models/modules/common.py:45-49 (SumPool2d = avg_pool2d * k * k),
+// layer_gen.py:163-168 (Avg/Max pool), layer_gen.py:211-214 (eval BatchNorm as a stand-alone
+// layer), models/generator.py:146 (Residual sum) / :158 (Dense concat via strided copy).
+#include <float.h>
+
+#include "common.cuh"
+
+namespace soda {
+
+// mode: 0 = sum (computed as avg * k * k like the reference), 1 = avg, 2 = max
+template <int V>
+__global__ void __launch_bounds__(256)
+pool2d_kernel(const float* __restrict__ x, int N, int H, int W, int C, int k, int stride, int mode,
+              int Ho, int Wo, int64_t in_bs, int64_t in_ps, float* __restrict__ y, int64_t out_bs,
+              int64_t out_ps) {
+  const int cv = C / V;
+  const int64_t total = (int64_t)N * Ho * Wo * cv;
+  const float inv = 1.0f / (float)(k * k);
+  for (int64_t idx = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; idx < total;
+       idx += (int64_t)gridDim.x * blockDim.x) {
+    const int c = (int)(idx % cv) * V;
+    int64_t r = idx / cv;
+    const int ox = (int)(r % Wo);
+    r /= Wo;
+    const int oy = (int)(r % Ho);
+    const int n = (int)(r / Ho);
+    float acc[V];
+#pragma unroll
+    for (int q = 0; q < V; ++q) acc[q] = (mode == 2) ? -FLT_MAX : 0.0f;
+    for (int ky = 0; ky < k; ++ky)
+      for (int kx = 0; kx < k; ++kx) {
+        const float* src = x + (int64_t)n * in_bs + ((int64_t)(oy * stride + ky) * W + ox * stride + kx) * in_ps + c;
+        float v[V];
+        if constexpr (V == 4) {
+          const float4 t = __ldg(reinterpret_cast<const float4*>(src));
+          v[0] = t.x, v[1] = t.y, v[2] = t.z, v[3] = t.w;
+        } else {
+          v[0] = __ldg(src);
+        }
+#pragma unroll
+        for (int q = 0; q < V; ++q) acc[q] = (mode == 2) ? fmaxf(acc[q], v[q]) : acc[q] + v[q];
+      }
+    float o[V];
+#pragma unroll
+    for (int q = 0; q < V; ++q) {
+      if (mode == 2) o[q] = acc[q];
+      else if (mode == 1) o[q] = acc[q] * inv;
+      else o[q] = __fmul_rn(__fmul_rn(__fmul_rn(acc[q], inv), (float)k), (float)k);
+    }
+    float* dst = y + (int64_t)n * out_bs + ((int64_t)oy * Wo + ox) * out_ps + c;
+    if constexpr (V == 4) *reinterpret_cast<float4*>(dst) = make_float4(o[0], o[1], o[2], o[3]);
+    else *dst = o[0];
+  }
+}
+
+template <int V>
+__global__ void __launch_bounds__(256)
+channel_affine_kernel(const float* __restrict__ x, int64_t n_pix, int C, int64_t in_ps,
+                      const float* __restrict__ scale, const float* __restrict__ shift,
+                      float* __restrict__ y, int64_t out_ps) {
+  const int cv = C / V;
+  const int64_t total = n_pix * cv;
+  for (int64_t idx = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; idx < total;
+       idx += (int64_t)gridDim.x * blockDim.x) {
+    const int c = (int)(idx % cv) * V;
+    const int64_t pix = idx / cv;
+    float v[V];
+    if constexpr (V == 4) {
+      const float4 t = __ldg(reinterpret_cast<const float4*>(x + pix * in_ps + c));
+      v[0] = t.x, v[1] = t.y, v[2] = t.z, v[3] = t.w;
+    } else {
+      v[0] = __ldg(x + pix * in_ps + c);
+    }
+#pragma unroll
+    for (int q = 0; q < V; ++q) {
+      const float s = scale ? __ldg(scale + c + q) : 1.0f;
+      const float b = shift ? __ldg(shift + c + q) : 0.0f;
+      v[q] = __fadd_rn(__fmul_rn(v[q], s), b);
+    }
+    float* dst = y + pix * out_ps + c;
+    if constexpr (V == 4) *reinterpret_cast<float4*>(dst) = make_float4(v[0], v[1], v[2], v[3]);
+    else *dst = v[0];
+  }
+}
+
+struct AddPtrs {
+  const float* p[8];
+};
+
+template <int V>
+__global__ void __launch_bounds__(256) add_n_kernel(AddPtrs xs, int k, int64_t n, float* __restrict__ y) {
+  for (int64_t e = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) * V; e < n;
+       e += (int64_t)gridDim.x * blockDim.x * V) {
+    float acc[V];
+#pragma unroll
+    for (int q = 0; q < V; ++q) acc[q] = 0.0f;
+    for (int j = 0; j < k; ++j) {
+      if constexpr (V == 4) {
+        const float4 t = __ldg(reinterpret_cast<const float4*>(xs.p[j] + e));
+        acc[0] = j ? __fadd_rn(acc[0], t.x) : t.x, acc[1] = j ? __fadd_rn(acc[1], t.y) : t.y;
+        acc[2] = j ? __fadd_rn(acc[2], t.z) : t.z, acc[3] = j ? __fadd_rn(acc[3], t.w) : t.w;
+      } else {
+        const float t = __ldg(xs.p[j] + e);
+        acc[0] = j ? __fadd_rn(acc[0], t) : t;
+      }
+    }
+    if constexpr (V == 4) *reinterpret_cast<float4*>(y + e) = make_float4(acc[0], acc[1], acc[2], acc[3]);
+    else y[e] = acc[0];
+  }
+}
+
+static unsigned grid_for(int64_t work_items) {
+  int64_t b = ceil_div(work_items, 256);
+  const int64_t cap = (int64_t)kNumSMs * 16;
+  return (unsigned)(b < 1 ? 1 : (b > cap ? cap : b));
+}
+
+}  // namespace soda
+
+extern "C" int soda_pool2d_fwd(const float* x, int N, int H, int W, int C, int k, int stride,
+                               int mode, int64_t in_bs, int64_t in_ps, float* y, int64_t out_bs,
+                               int64_t out_ps, void* stream) {
+  using namespace soda;
+  if (!x || !y) return fail(SODA_ERR_BAD_ARG, "pool2d: null pointer");
+  if (N <= 0 || C <= 0 || k <= 0 || stride <= 0 || mode < 0 || mode > 2)
+    return fail(SODA_ERR_BAD_ARG, "pool2d: bad size or mode");
+  const int Ho = (H - k) / stride + 1, Wo = (W - k) / stride + 1;
+  if (H < k || W < k || Ho <= 0 || Wo <= 0) return fail(SODA_ERR_BAD_ARG, "pool2d: window larger than input");
+  cudaStream_t st = (cudaStream_t)stream;
+  const bool vec = (C % 4 == 0) && (in_ps % 4 == 0) && (in_bs % 4 == 0) && (out_ps % 4 == 0) &&
+                   (out_bs % 4 == 0) && ((reinterpret_cast<uintptr_t>(x) & 15) == 0) &&
+                   ((reinterpret_cast<uintptr_t>(y) & 15) == 0);
+  if (vec)
+    pool2d_kernel<4><<<grid_for((int64_t)N * Ho * Wo * (C / 4)), 256, 0, st>>>(
+        x, N, H, W, C, k, stride, mode, Ho, Wo, in_bs, in_ps, y, out_bs, out_ps);
+  else
+    pool2d_kernel<1><<<grid_for((int64_t)N * Ho * Wo * C), 256, 0, st>>>(
+        x, N, H, W, C, k, stride, mode, Ho, Wo, in_bs, in_ps, y, out_bs, out_ps);
+  return after_launch("pool2d_kernel");
+}
+
+extern "C" int soda_channel_affine(const float* x, int64_t n_pix, int C, int64_t in_ps,
+                                   const float* scale, const float* shift, float* y,
+                                   int64_t out_ps, void* stream) {
+  using namespace soda;
+  if (!x || !y) return fail(SODA_ERR_BAD_ARG, "channel_affine: null pointer");
+  if (n_pix <= 0 || C <= 0) return fail(SODA_ERR_BAD_ARG, "channel_affine: non-positive size");
+  cudaStream_t st = (cudaStream_t)stream;
+  const bool vec = (C % 4 == 0) && (in_ps % 4 == 0) && (out_ps % 4 == 0) &&
+                   ((reinterpret_cast<uintptr_t>(x) & 15) == 0) &&
+                   ((reinterpret_cast<uintptr_t>(y) & 15) == 0);
+  if (vec)
+    channel_affine_kernel<4><<<grid_for(n_pix * (C / 4)), 256, 0, st>>>(x, n_pix, C, in_ps, scale,
+                                                                      shift, y, out_ps);
+  else
+    channel_affine_kernel<1><<<grid_for(n_pix * C), 256, 0, st>>>(x, n_pix, C, in_ps, scale, shift,
+                                                                y, out_ps);
+  return after_launch("channel_affine_kernel");
+}
+
+extern "C" int soda_add_n(const float* const* xs, int k, int64_t n, float* y, void* stream) {
+  using namespace soda;
+  if (!xs || !y) return fail(SODA_ERR_BAD_ARG, "add_n: null pointer");
+  if (k <= 0 || k > 8 || n <= 0) return fail(SODA_ERR_BAD_ARG, "add_n: need 1..8 inputs and n > 0");
+  AddPtrs ap;
+  bool vec = (n % 4 == 0) && ((reinterpret_cast<uintptr_t>(y) & 15) == 0);
+  for (int j = 0; j < k; ++j) {
+    if (!xs[j]) return fail(SODA_ERR_BAD_ARG, "add_n: null input");
+    ap.p[j] = xs[j];
+    vec = vec && ((reinterpret_cast<uintptr_t>(xs[j]) & 15) == 0);
+  }
+  cudaStream_t st = (cudaStream_t)stream;
+  if (vec) add_n_kernel<4><<<grid_for(n / 4), 256, 0, st>>>(ap, k, n, y);
+  else add_n_kernel<1><<<grid_for(n), 256, 0, st>>>(ap, k, n, y);
+  return after_launch("add_n_kernel");
+}

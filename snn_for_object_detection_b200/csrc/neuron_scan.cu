@@ -1,0 +1,312 @@
+// LIF / LI forward scans over T and the fused surrogate-gradient reverse scans.
+//
+// Reference arithmetic: norse 1.1.0 lif_feed_forward_step / li_feed_forward_step as restated in
+// oracle/norse_restated.py (reference call sites models/modules/layer_gen.py:233,253).  The
+// forward uses explicit round-to-nearest intrinsics op-for-op (no FMA contraction) so that for
+// identical inputs the state and the spikes are bit-identical to the fp32 restatement.
+//
+// HBM-bound elementwise work: the state (v, i) lives in registers for all T steps; per
+// neuron-step the forward moves 4 B in + 4 B out (+4 B per optional trace).  The time loop is
+// unrolled so that kUnroll independent 16-byte loads are in flight per thread.
+#include "common.cuh"
+
+namespace soda {
+
+constexpr int kUnroll = 4;
+
+struct NP {
+  float a, s, v_leak, v_th, v_reset, alpha;
+  int jump_first, detach_reset;
+};
+
+__device__ __forceinline__ void lif_step(const NP& p, float x, float& v, float& i, float& z,
+                                         float& v_dec) {
+  float i_src;
+  if (p.jump_first) {
+    i_src = __fadd_rn(i, x);  // i_new = i + x
+  } else {
+    i_src = i;
+  }
+  const float dv = __fmul_rn(p.a, __fadd_rn(__fsub_rn(p.v_leak, v), i_src));
+  v_dec = __fadd_rn(v, dv);
+  const float di = __fmul_rn(-p.s, i_src);
+  float i_dec = __fadd_rn(i_src, di);
+  if (!p.jump_first) i_dec = __fadd_rn(i_dec, x);
+  z = (__fsub_rn(v_dec, p.v_th) > 0.0f) ? 1.0f : 0.0f;
+  v = __fadd_rn(__fmul_rn(__fsub_rn(1.0f, z), v_dec), __fmul_rn(z, p.v_reset));
+  i = i_dec;
+}
+
+__device__ __forceinline__ void li_step(const NP& p, float x, float& v, float& i) {
+  const float i_src = p.jump_first ? __fadd_rn(i, x) : i;
+  const float dv = __fmul_rn(p.a, __fadd_rn(__fsub_rn(p.v_leak, v), i_src));
+  v = __fadd_rn(v, dv);
+  const float di = __fmul_rn(-p.s, i_src);
+  float i_dec = __fadd_rn(i_src, di);
+  if (!p.jump_first) i_dec = __fadd_rn(i_dec, x);
+  i = i_dec;
+}
+
+template <int V>
+struct Vec;
+template <>
+struct Vec<4> {
+  using T = float4;
+};
+template <>
+struct Vec<1> {
+  using T = float;
+};
+
+template <int V>
+__device__ __forceinline__ void vload(float (&r)[V], const float* p) {
+  if constexpr (V == 4) {
+    const float4 t = __ldcs(reinterpret_cast<const float4*>(p));
+    r[0] = t.x, r[1] = t.y, r[2] = t.z, r[3] = t.w;
+  } else {
+    r[0] = __ldcs(p);
+  }
+}
+template <int V>
+__device__ __forceinline__ void vstore(float* p, const float (&r)[V]) {
+  if constexpr (V == 4) {
+    *reinterpret_cast<float4*>(p) = make_float4(r[0], r[1], r[2], r[3]);
+  } else {
+    *p = r[0];
+  }
+}
+
+// kMode: 0 = LIF, 1 = LI, 2 = LI + tanh
+template <int V, int kMode>
+__global__ void __launch_bounds__(256)
+neuron_fwd_kernel(NP p, const float* __restrict__ x, const float* __restrict__ v0,
+                  const float* __restrict__ i0, int T, int64_t n, float* __restrict__ out,
+                  float* __restrict__ v_out, float* __restrict__ i_out,
+                  float* __restrict__ v_dec_trace, float* __restrict__ v_trace,
+                  float* __restrict__ i_trace) {
+  const int64_t e = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) * V;
+  if (e >= n) return;
+  float v[V], i[V];
+  if (v0 != nullptr) {
+    vload<V>(v, v0 + e);
+  } else {
+#pragma unroll
+    for (int k = 0; k < V; ++k) v[k] = p.v_leak;
+  }
+  if (i0 != nullptr) {
+    vload<V>(i, i0 + e);
+  } else {
+#pragma unroll
+    for (int k = 0; k < V; ++k) i[k] = 0.0f;
+  }
+
+  int t = 0;
+  for (; t + kUnroll <= T; t += kUnroll) {
+    float xs[kUnroll][V];
+#pragma unroll
+    for (int u = 0; u < kUnroll; ++u) vload<V>(xs[u], x + (int64_t)(t + u) * n + e);
+#pragma unroll
+    for (int u = 0; u < kUnroll; ++u) {
+      float o[V], vd[V];
+#pragma unroll
+      for (int k = 0; k < V; ++k) {
+        if constexpr (kMode == 0) {
+          lif_step(p, xs[u][k], v[k], i[k], o[k], vd[k]);
+        } else {
+          li_step(p, xs[u][k], v[k], i[k]);
+          o[k] = (kMode == 2) ? tanhf(v[k]) : v[k];
+        }
+      }
+      const int64_t off = (int64_t)(t + u) * n + e;
+      vstore<V>(out + off, o);
+      if constexpr (kMode == 0) {
+        if (v_dec_trace != nullptr) vstore<V>(v_dec_trace + off, vd);
+      }
+      if (v_trace != nullptr) vstore<V>(v_trace + off, v);
+      if (i_trace != nullptr) vstore<V>(i_trace + off, i);
+    }
+  }
+  for (; t < T; ++t) {
+    float xs[V], o[V], vd[V];
+    vload<V>(xs, x + (int64_t)t * n + e);
+#pragma unroll
+    for (int k = 0; k < V; ++k) {
+      if constexpr (kMode == 0) {
+        lif_step(p, xs[k], v[k], i[k], o[k], vd[k]);
+      } else {
+        li_step(p, xs[k], v[k], i[k]);
+        o[k] = (kMode == 2) ? tanhf(v[k]) : v[k];
+      }
+    }
+    const int64_t off = (int64_t)t * n + e;
+    vstore<V>(out + off, o);
+    if constexpr (kMode == 0) {
+      if (v_dec_trace != nullptr) vstore<V>(v_dec_trace + off, vd);
+    }
+    if (v_trace != nullptr) vstore<V>(v_trace + off, v);
+    if (i_trace != nullptr) vstore<V>(i_trace + off, i);
+  }
+  vstore<V>(v_out + e, v);
+  vstore<V>(i_out + e, i);
+}
+
+// Reverse scan.  kLif: uses v_dec_trace, surrogate gradient and the (non-detached) reset path.
+template <int V, bool kLif>
+__global__ void __launch_bounds__(256)
+neuron_bwd_kernel(NP p, const float* __restrict__ gout, const float* __restrict__ gvT,
+                  const float* __restrict__ giT, const float* __restrict__ v_dec_trace, int T,
+                  int64_t n, float* __restrict__ gx, float* __restrict__ gv0,
+                  float* __restrict__ gi0) {
+  const int64_t e = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) * V;
+  if (e >= n) return;
+  float gv[V], gi[V];
+  if (gvT != nullptr) {
+    vload<V>(gv, gvT + e);
+  } else {
+#pragma unroll
+    for (int k = 0; k < V; ++k) gv[k] = 0.0f;
+  }
+  if (giT != nullptr) {
+    vload<V>(gi, giT + e);
+  } else {
+#pragma unroll
+    for (int k = 0; k < V; ++k) gi[k] = 0.0f;
+  }
+  const float one_m_a = 1.0f - p.a, one_m_s = 1.0f - p.s;
+
+  for (int t0 = T; t0 > 0; t0 -= kUnroll) {
+    const int cnt = t0 >= kUnroll ? kUnroll : t0;
+    float go[kUnroll][V], vd[kUnroll][V];
+#pragma unroll
+    for (int u = 0; u < kUnroll; ++u) {
+      if (u < cnt) {
+        const int64_t off = (int64_t)(t0 - 1 - u) * n + e;
+        vload<V>(go[u], gout + off);
+        if constexpr (kLif) vload<V>(vd[u], v_dec_trace + off);
+      }
+    }
+#pragma unroll
+    for (int u = 0; u < kUnroll; ++u) {
+      if (u < cnt) {
+        float g[V];
+#pragma unroll
+        for (int k = 0; k < V; ++k) {
+          float gvd;
+          if constexpr (kLif) {
+            const float u_th = vd[u][k] - p.v_th;
+            const float z = u_th > 0.0f ? 1.0f : 0.0f;
+            float gz = go[u][k];
+            if (!p.detach_reset) gz += gv[k] * (p.v_reset - vd[u][k]);
+            const float den = p.alpha * fabsf(u_th) + 1.0f;
+            gvd = gv[k] * (1.0f - z) + gz / (den * den);
+          } else {
+            gvd = go[u][k] + gv[k];
+          }
+          gv[k] = gvd * one_m_a;
+          if (p.jump_first) {
+            gi[k] = gvd * p.a + gi[k] * one_m_s;
+            g[k] = gi[k];
+          } else {
+            g[k] = gi[k];
+            gi[k] = gvd * p.a + gi[k] * one_m_s;
+          }
+        }
+        vstore<V>(gx + (int64_t)(t0 - 1 - u) * n + e, g);
+      }
+    }
+  }
+  if (gv0 != nullptr) vstore<V>(gv0 + e, gv);
+  if (gi0 != nullptr) vstore<V>(gi0 + e, gi);
+}
+
+static NP to_np(const soda_neuron_params_t* q) {
+  NP p;
+  p.a = q->dt_tau_mem, p.s = q->dt_tau_syn, p.v_leak = q->v_leak, p.v_th = q->v_th;
+  p.v_reset = q->v_reset, p.alpha = q->alpha, p.jump_first = q->jump_first;
+  p.detach_reset = q->detach_reset;
+  return p;
+}
+
+static bool all_aligned16(std::initializer_list<const void*> ptrs) {
+  for (const void* q : ptrs)
+    if (q != nullptr && (reinterpret_cast<uintptr_t>(q) & 15) != 0) return false;
+  return true;
+}
+
+template <int kMode>
+static int launch_fwd(const soda_neuron_params_t* q, const float* x, const float* v0,
+                      const float* i0, int T, int64_t n, float* out, float* v_out, float* i_out,
+                      float* v_dec_trace, float* v_trace, float* i_trace, void* stream,
+                      const char* name) {
+  if (!q || !x || !out || !v_out || !i_out) return fail(SODA_ERR_BAD_ARG, "neuron fwd: null pointer");
+  if (T <= 0 || n <= 0) return fail(SODA_ERR_BAD_ARG, "neuron fwd: non-positive size");
+  const NP p = to_np(q);
+  cudaStream_t st = (cudaStream_t)stream;
+  const bool vec = (n % 4 == 0) &&
+                   all_aligned16({x, v0, i0, out, v_out, i_out, v_dec_trace, v_trace, i_trace});
+  if (vec) {
+    const int64_t blocks = ceil_div(n / 4, 256);
+    neuron_fwd_kernel<4, kMode><<<(unsigned)blocks, 256, 0, st>>>(
+        p, x, v0, i0, T, n, out, v_out, i_out, v_dec_trace, v_trace, i_trace);
+  } else {
+    const int64_t blocks = ceil_div(n, 256);
+    neuron_fwd_kernel<1, kMode><<<(unsigned)blocks, 256, 0, st>>>(
+        p, x, v0, i0, T, n, out, v_out, i_out, v_dec_trace, v_trace, i_trace);
+  }
+  return after_launch(name);
+}
+
+template <bool kLif>
+static int launch_bwd(const soda_neuron_params_t* q, const float* gout, const float* gvT,
+                      const float* giT, const float* v_dec_trace, int T, int64_t n, float* gx,
+                      float* gv0, float* gi0, void* stream, const char* name) {
+  if (!q || !gout || !gx || (kLif && !v_dec_trace))
+    return fail(SODA_ERR_BAD_ARG, "neuron bwd: null pointer");
+  if (T <= 0 || n <= 0) return fail(SODA_ERR_BAD_ARG, "neuron bwd: non-positive size");
+  const NP p = to_np(q);
+  cudaStream_t st = (cudaStream_t)stream;
+  const bool vec = (n % 4 == 0) && all_aligned16({gout, gvT, giT, v_dec_trace, gx, gv0, gi0});
+  if (vec) {
+    neuron_bwd_kernel<4, kLif><<<(unsigned)ceil_div(n / 4, 256), 256, 0, st>>>(
+        p, gout, gvT, giT, v_dec_trace, T, n, gx, gv0, gi0);
+  } else {
+    neuron_bwd_kernel<1, kLif><<<(unsigned)ceil_div(n, 256), 256, 0, st>>>(
+        p, gout, gvT, giT, v_dec_trace, T, n, gx, gv0, gi0);
+  }
+  return after_launch(name);
+}
+
+}  // namespace soda
+
+extern "C" int soda_lif_fwd(const soda_neuron_params_t* p, const float* x, const float* v0,
+                            const float* i0, int T, int64_t n, float* out, float* v_out,
+                            float* i_out, float* v_dec_trace, float* v_trace, float* i_trace,
+                            void* stream) {
+  return soda::launch_fwd<0>(p, x, v0, i0, T, n, out, v_out, i_out, v_dec_trace, v_trace, i_trace,
+                             stream, "lif_fwd");
+}
+
+extern "C" int soda_li_fwd(const soda_neuron_params_t* p, const float* x, const float* v0,
+                           const float* i0, int T, int64_t n, int apply_tanh, float* out,
+                           float* v_out, float* i_out, float* i_trace, void* stream) {
+  if (apply_tanh)
+    return soda::launch_fwd<2>(p, x, v0, i0, T, n, out, v_out, i_out, nullptr, nullptr, i_trace,
+                               stream, "li_tanh_fwd");
+  return soda::launch_fwd<1>(p, x, v0, i0, T, n, out, v_out, i_out, nullptr, nullptr, i_trace,
+                             stream, "li_fwd");
+}
+
+extern "C" int soda_lif_bwd(const soda_neuron_params_t* p, const float* grad_out,
+                            const float* grad_v_T, const float* grad_i_T, const float* v_dec_trace,
+                            int T, int64_t n, float* grad_x, float* grad_v0, float* grad_i0,
+                            void* stream) {
+  return soda::launch_bwd<true>(p, grad_out, grad_v_T, grad_i_T, v_dec_trace, T, n, grad_x,
+                                grad_v0, grad_i0, stream, "lif_bwd");
+}
+
+extern "C" int soda_li_bwd(const soda_neuron_params_t* p, const float* grad_out,
+                           const float* grad_v_T, const float* grad_i_T, int T, int64_t n,
+                           float* grad_x, float* grad_v0, float* grad_i0, void* stream) {
+  return soda::launch_bwd<false>(p, grad_out, grad_v_T, grad_i_T, nullptr, T, n, grad_x, grad_v0,
+                                 grad_i0, stream, "li_bwd");
+}
