@@ -1,0 +1,376 @@
+"""Model generation tools: recursive net builder + layer-major executor.
+
+Public surface of the reference's ``models/generator.py``: ``ListGen`` / ``ListState`` types,
+``BlockGen`` (:35-198), ``ModelGen`` (:206-275), ``BackboneGen`` (:283-295), ``NeckGen`` (:303-351),
+``Head`` (:359-457), ``HeadGen`` (:465-538) with the same constructor arguments, ``forward``
+signatures, module tree (hence ``state_dict`` keys) and state nesting.
+
+What is different underneath: the network has no inter-layer recurrence (every state is private to
+one cell), so besides the per-step protocol ``forward(X, state)`` every generator also has
+``forward_seq(X, T, state)`` which takes all T time steps at once, folded time-major into the batch
+dimension (``X[T*B, C, H, W]``).  A layer then runs ONCE over all T steps: convolutions see a batch
+of T*B images, neuron cells scan T steps inside one kernel with the membrane state in registers.
+``forward(X, state)`` is ``forward_seq(X, 1, state)``.
+"""
+
+from __future__ import annotations
+
+import inspect
+from typing import List, Optional, Tuple, Union
+
+import torch
+from torch import nn
+
+from . import ops
+from .modules import *  # noqa: F401,F403
+from .modules.cells import LICell, LIFCell, SNNCell
+from .modules.common import SodaBatchNorm2d, SodaConv2d, StateStorage, Storage
+from .modules.layer_gen import Dense, LayerGen, Residual, Return
+from .utils.anchors import AnchorGenerator
+
+ListGen = List[Union[LayerGen, "ListGen"]]
+ListState = List[Union[torch.Tensor, None, "ListState"]]
+
+__all__ = ["ListGen", "ListState", "BlockGen", "ModelGen", "BackboneGen", "NeckGen", "Head", "HeadGen"]
+
+
+def _is_module_stateful(module: nn.Module) -> bool:
+    """A module is stateful iff its ``forward`` takes a ``state`` argument (norse utils/state.py)."""
+    return "state" in inspect.signature(module.forward).parameters or isinstance(module, nn.RNNBase)
+
+
+def _has_state(block: "BlockGen") -> bool:
+    for flags, branch in zip(block.branch_state, block.net):
+        for f, layer in zip(flags, branch):
+            if f and (not isinstance(layer, BlockGen) or _has_state(layer)):
+                return True
+    return False
+
+
+def _copy_into(src: torch.Tensor, dst: torch.Tensor) -> None:
+    """Strided pixel-major copy on our own kernel (concat-slice store, generator.py:158)."""
+    ops.channel_affine(src, None, None, out=dst)
+
+
+class BlockGen(nn.Module):
+    """Block generator: inner lists are sequential, outer lists are parallel branches merged by the
+    list type (plain = first branch, ``Residual`` = sum, ``Dense`` = channel concat)."""
+
+    def __init__(self, in_channels: int, cfgs: ListGen):
+        super().__init__()
+        branch_list: List[nn.ModuleList] = []
+        self.branch_state: List[List[bool]] = []
+        self.out_channels = 0
+        if isinstance(cfgs, Residual):
+            self.merge = "residual"
+        elif isinstance(cfgs, Dense):
+            self.merge = "dense"
+        else:
+            self.merge = "forward"
+            cfgs = [cfgs]
+        self.branch_channels: List[int] = []
+        for branch_cfg in cfgs:
+            layer_list, state_layers, out_channels = self._make_branch(in_channels, branch_cfg)
+            branch_list.append(layer_list)
+            self.branch_state.append(state_layers)
+            self.branch_channels.append(out_channels)
+            self._channels_calc(out_channels)
+        self.net = nn.ModuleList(branch_list)
+
+    def _channels_calc(self, channels: int) -> None:
+        if self.merge == "dense":
+            self.out_channels += channels
+        elif self.merge == "residual":
+            if not self.out_channels:
+                self.out_channels = channels
+            elif self.out_channels != channels:
+                raise RuntimeError(
+                    "[ERROR]: The number of channels in the residual "
+                    "network does not match! Check the configuration settings."
+                )
+        else:
+            self.out_channels = channels
+
+    def _make_branch(self, in_channels: int, cfg: ListGen) -> Tuple[nn.ModuleList, List[bool], int]:
+        state_layers: List[bool] = []
+        layer_list: List[nn.Module] = []
+        channels = in_channels
+        for layer_gen in cfg:
+            if isinstance(layer_gen, list):
+                layer = BlockGen(channels, layer_gen)
+                channels = layer.out_channels
+            else:
+                layer, channels = layer_gen.get(channels)
+            layer_list.append(layer)
+            state_layers.append(_is_module_stateful(layer))
+        return nn.ModuleList(layer_list), state_layers, channels
+
+    # ------------------------------------------------------------------------------------------
+    def forward(self, X: torch.Tensor, state: Optional[ListState] = None) -> Tuple[torch.Tensor, ListState]:
+        """Per-step protocol of the reference (generator.py:169-198)."""
+        return self.forward_seq(X, 1, state)
+
+    def forward_seq(
+        self, X: torch.Tensor, T: int, state: Optional[ListState] = None, out: Optional[torch.Tensor] = None
+    ) -> Tuple[torch.Tensor, ListState]:
+        """All T steps of the block; ``X`` is ``[T*B, C, H, W]`` time-major.  ``out``: optional
+        pre-allocated (possibly channel-sliced) destination for the block's result."""
+        outs = []
+        out_state = []
+        state = [None] * len(self.net) if state is None else state
+        dense_buf = None
+        if self.merge == "dense":
+            Ho, Wo = self.out_hw(X.shape[2], X.shape[3])
+            dense_buf = out if out is not None else ops.empty_pixel_major(
+                X.shape[0], self.out_channels, Ho, Wo, X.device
+            )
+        c0 = 0
+        for bi, (branch, flags, branch_state) in enumerate(zip(self.net, self.branch_state, state)):
+            branch_state = [None] * len(branch) if branch_state is None else list(branch_state)
+            dst = None
+            if self.merge == "dense":
+                dst = dense_buf[:, c0 : c0 + self.branch_channels[bi]]
+                c0 += self.branch_channels[bi]
+            elif self.merge == "forward":
+                dst = out
+            outs.append(self._run_branch(X, T, branch, flags, branch_state, dst))
+            out_state.append(branch_state)
+        if self.merge == "dense":
+            return dense_buf, out_state
+        if self.merge == "residual":
+            Y = ops.add_n(outs)
+            if out is not None:
+                _copy_into(Y, out)
+                Y = out
+            return Y, out_state
+        return outs[0], out_state
+
+    def out_hw(self, H: int, W: int) -> Tuple[int, int]:
+        """Spatial size of the block's output for an ``H x W`` input (first branch decides)."""
+        for layer in self.net[0]:
+            if isinstance(layer, nn.Conv2d):
+                H, W = ops.conv_out_hw(H, W, layer.kernel_size[0], layer.stride[0])
+            elif isinstance(layer, BlockGen):
+                H, W = layer.out_hw(H, W)
+            elif isinstance(layer, nn.Upsample):
+                H, W = int(H * layer.scale_factor), int(W * layer.scale_factor)
+            elif hasattr(layer, "kernel_size") and hasattr(layer, "stride"):  # pooling modules
+                k, s = layer.kernel_size, layer.stride
+                H, W = (H - k) // s + 1, (W - k) // s + 1
+        return H, W
+
+    def _run_branch(self, X, T, branch, flags, branch_state, dst):
+        """Runs one branch; fuses Conv+Norm(eval) and LI+Tanh; the branch's last layer writes
+        straight into ``dst`` (concat slice / caller's buffer) when it can."""
+        n = len(branch)
+        Y = X
+        idx = 0
+        while idx < n:
+            layer = branch[idx]
+            if isinstance(layer, SodaConv2d):
+                norm = None
+                last = idx
+                if idx + 1 < n and isinstance(branch[idx + 1], SodaBatchNorm2d) and not branch[idx + 1].training:
+                    norm = branch[idx + 1]
+                    last = idx + 1
+                o = dst if last == n - 1 else None
+                Y = layer(Y, norm=norm, out=o)
+                idx = last + 1
+                if o is not None:
+                    return Y
+                continue
+            if isinstance(layer, BlockGen):
+                o = dst if idx == n - 1 else None
+                Y, branch_state[idx] = layer.forward_seq(Y, T, branch_state[idx], out=o)
+                idx += 1
+                if o is not None:
+                    return Y
+                continue
+            if isinstance(layer, (SNNCell, StateStorage)):
+                fuse = (
+                    isinstance(layer, LICell)
+                    and idx + 1 < n
+                    and isinstance(branch[idx + 1], nn.Tanh)
+                    and not torch.is_grad_enabled()
+                )
+                if fuse:
+                    Y, branch_state[idx] = layer.forward_seq(Y, T, branch_state[idx], fuse_tanh=True)
+                    idx += 2
+                else:
+                    Y, branch_state[idx] = layer.forward_seq(Y, T, branch_state[idx])
+                    idx += 1
+                continue
+            if flags[idx]:
+                # unknown stateful module: per-step protocol, one call per time step
+                if T == 1:
+                    Y, branch_state[idx] = layer(Y, branch_state[idx])
+                else:
+                    B = Y.shape[0] // T
+                    ys, s = [], branch_state[idx]
+                    for t in range(T):
+                        y, s = layer(Y[t * B : (t + 1) * B], s)
+                        ys.append(y)
+                    Y, branch_state[idx] = torch.cat(ys), s
+            else:
+                Y = layer(Y)
+            idx += 1
+        if dst is not None and dst.data_ptr() != Y.data_ptr():
+            _copy_into(Y, dst)
+            Y = dst
+        return Y
+
+
+class ModelGen(nn.Module):
+    """Base class of the model generators (reference models/generator.py:206-275)."""
+
+    def __init__(self, cfg, in_channels: int = 2, init_weights: bool = True) -> None:
+        super().__init__()
+        self.out_channels = 0
+        self.net_cfg = self._load_cfg(cfg)
+        self._net_generator(in_channels)
+        if init_weights:
+            for m in self.modules():
+                if isinstance(m, nn.Conv2d):
+                    nn.init.kaiming_normal_(m.weight, mode="fan_out", nonlinearity="relu")
+                    if m.bias is not None:
+                        nn.init.constant_(m.bias, 0)
+                elif isinstance(m, nn.BatchNorm2d):
+                    nn.init.constant_(m.weight, 1)
+                    if m.bias is not None:
+                        nn.init.constant_(m.bias, 0)
+
+    def _net_generator(self, in_channels: int) -> None:
+        self.net = BlockGen(in_channels, self.net_cfg)
+        self.out_channels = self.net.out_channels
+
+    def _load_cfg(self, cfg) -> ListGen:
+        raise NotImplementedError
+
+    def forward(self, X: torch.Tensor, state: Optional[ListState] = None):
+        raise NotImplementedError
+
+
+class BackboneGen(ModelGen):
+    """Returns the tensor from the last layer of the network."""
+
+    def _load_cfg(self, cfg) -> ListGen:
+        return cfg()
+
+    def forward(self, X: torch.Tensor, state: Optional[ListState] = None) -> Tuple[torch.Tensor, ListState]:
+        return self.net(X, state)
+
+    def forward_seq(self, X: torch.Tensor, T: int, state: Optional[ListState] = None):
+        return self.net.forward_seq(X, T, state)
+
+
+class NeckGen(ModelGen):
+    """Returns the list of tensors recorded by the ``Return`` taps, in module order."""
+
+    def __init__(self, cfg, in_channels: int = 2, init_weights: bool = False):
+        super().__init__(cfg, in_channels, init_weights)
+        self.out_shape = self._search_out(self.net_cfg)
+
+    def _search_out(self, cfg) -> List[int]:
+        out: List[int] = []
+        for module in cfg:
+            if isinstance(module, Return):
+                out.append(module.out_channels)
+            elif isinstance(module, list):
+                out += self._search_out(module)
+        return out
+
+    def _load_cfg(self, cfg) -> ListGen:
+        return cfg()
+
+    def _taps(self) -> List[torch.Tensor]:
+        return [m.get_storage() for m in self.net.modules() if isinstance(m, Storage)]
+
+    def forward(self, X: torch.Tensor, state: Optional[ListState] = None):
+        _, state = self.net(X, state)
+        return self._taps(), state
+
+    def forward_seq(self, X: torch.Tensor, T: int, state: Optional[ListState] = None):
+        _, state = self.net.forward_seq(X, T, state)
+        return self._taps(), state
+
+
+class Head(nn.Module):
+    """One ``HeadGen`` + ``AnchorGenerator`` per pyramid level; flattens and concatenates the
+    per-level predictions (reference models/generator.py:359-457)."""
+
+    def __init__(self, cfg, num_classes: int, in_shape: List[int], init_weights: bool = True) -> None:
+        super().__init__()
+        self.num_classes = num_classes
+        hi, lo, size_per_pix = 0.75, 0.08, 3
+        sizes = torch.arange(lo, hi, (hi - lo) / (len(in_shape) * size_per_pix), dtype=torch.float32)
+        sizes = sizes.reshape((-1, size_per_pix))
+        ratios = torch.tensor((0.5, 1.0, 2), dtype=torch.float32)
+        num_anchors = size_per_pix * len(ratios)
+        num_class_out = num_anchors * (self.num_classes + 1)
+        num_box_out = num_anchors * 4
+        self.num_levels = len(in_shape)
+        for idx, channels in enumerate(in_shape):
+            setattr(self, f"anchor_gen_{idx}", AnchorGenerator(sizes=sizes[idx], ratios=ratios))
+            setattr(self, f"model_{idx}", HeadGen(cfg, num_box_out, num_class_out, channels, init_weights))
+
+    def forward(self, X: List[torch.Tensor], state: Optional[ListState] = None):
+        return self.forward_seq(X, 1, state)
+
+    def forward_seq(self, X: List[torch.Tensor], T: int, state: Optional[ListState] = None):
+        """Predictions of the LAST of the T steps (the only ones the detector observes,
+        models/soda.py:141-144) + the head state after all T steps."""
+        state = [None] * len(X) if state is None else list(state)
+        anchors, cls_preds, bbox_preds = [], [], []
+        for idx, fmap in enumerate(X):
+            anchors.append(getattr(self, f"anchor_gen_{idx}")(fmap))
+            boxes, classes, state[idx] = getattr(self, f"model_{idx}").forward_seq(fmap, T, state[idx])
+            bbox_preds.append(boxes)
+            cls_preds.append(classes)
+        anchors = torch.cat(anchors)
+        cls_preds = self._concat_preds(cls_preds)
+        cls_preds = cls_preds.reshape(cls_preds.shape[0], -1, self.num_classes + 1)
+        bbox_preds = self._concat_preds(bbox_preds)
+        bbox_preds = bbox_preds.reshape(bbox_preds.shape[0], -1, 4)
+        return anchors, cls_preds, bbox_preds, state
+
+    def _flatten_pred(self, pred: torch.Tensor) -> torch.Tensor:
+        # pixel-major storage makes permute(0,2,3,1) + flatten a view, not a copy
+        return torch.flatten(torch.permute(pred, (0, 2, 3, 1)), start_dim=1)
+
+    def _concat_preds(self, preds: List[torch.Tensor]) -> torch.Tensor:
+        return torch.cat([self._flatten_pred(p) for p in preds], dim=1)
+
+
+class HeadGen(ModelGen):
+    """Head for one pyramid level: ``[prepare, box, cls]`` lists (reference generator.py:465-538)."""
+
+    def __init__(self, cfg, box_out: int, cls_out: int, in_channels: int = 2, init_weights=False):
+        self.box_out = box_out
+        self.cls_out = cls_out
+        super().__init__(cfg, in_channels, init_weights)
+
+    def _net_generator(self, in_channels: int) -> None:
+        self.base_net = BlockGen(in_channels, [self.net_cfg[0]])
+        self.box_net = BlockGen(self.base_net.out_channels, [self.net_cfg[1]])
+        self.cls_net = BlockGen(self.base_net.out_channels, [self.net_cfg[2]])
+
+    def _load_cfg(self, cfg) -> ListGen:
+        return cfg(self.box_out, self.cls_out)
+
+    def forward(self, X: torch.Tensor, state: Optional[ListState] = None):
+        return self.forward_seq(X, 1, state)
+
+    def forward_seq(self, X: torch.Tensor, T: int, state: Optional[ListState] = None):
+        state = [None] * 3 if state is None else list(state)
+        Y, state[0] = self.base_net.forward_seq(X, T, state[0])
+        B = Y.shape[0] // T
+        outs = []
+        for k, net in ((1, self.box_net), (2, self.cls_net)):
+            if T > 1 and not _has_state(net):
+                # stateless prediction nets: only the last step is observable
+                o, state[k] = net.forward_seq(Y[(T - 1) * B :], 1, state[k])
+            else:
+                o, state[k] = net.forward_seq(Y, T, state[k])
+                o = o[(T - 1) * B :]
+            outs.append(o)
+        return outs[0], outs[1], state

@@ -1,0 +1,163 @@
+"""LIF / LI neuron cells backed by the fused CUDA scans.
+
+These take the place of ``norse.torch.LIFCell()`` / ``norse.torch.LICell()`` as the reference
+instantiates them (models/modules/layer_gen.py:233,253): same call protocol
+``forward(x, state=None) -> (out, new_state)``, same state tuples with ``.v`` / ``.i`` fields, same
+default parameters, same initial state (v = v_leak, i = 0).  On top of the per-step protocol each
+cell has ``forward_seq(x, T, state)`` which advances T time steps in ONE kernel with the state
+held in registers (layer-major execution).
+"""
+
+from __future__ import annotations
+
+from typing import NamedTuple, Optional, Tuple
+
+import torch
+from torch import nn
+
+from .. import ops
+from ..ops import NeuronConst
+
+__all__ = ["LIFParameters", "LIParameters", "LIFFeedForwardState", "LIState", "SNNCell", "LIFCell", "LICell"]
+
+
+class LIFParameters(NamedTuple):
+    tau_syn_inv: float = 1.0 / 5e-3
+    tau_mem_inv: float = 1.0 / 1e-2
+    v_leak: float = 0.0
+    v_th: float = 1.0
+    v_reset: float = 0.0
+    method: str = "super"
+    alpha: float = 100.0
+
+
+class LIParameters(NamedTuple):
+    tau_syn_inv: float = 1.0 / 5e-3
+    tau_mem_inv: float = 1.0 / 1e-2
+    v_leak: float = 0.0
+
+
+class LIFFeedForwardState(NamedTuple):
+    v: torch.Tensor
+    i: torch.Tensor
+
+
+class LIState(NamedTuple):
+    v: torch.Tensor
+    i: torch.Tensor
+
+
+def _f32(x: float) -> float:
+    return float(torch.tensor(x, dtype=torch.float32))
+
+
+def _const(p, dt: float, jump_first: bool = True, detach_reset: bool = False) -> NeuronConst:
+    # torch evaluates ``dt * tau_inv_tensor`` in fp32: fp32(dt) * fp32(tau_inv), rounded to fp32
+    a = float(torch.tensor(dt, dtype=torch.float32) * torch.tensor(p.tau_mem_inv, dtype=torch.float32))
+    s = float(torch.tensor(dt, dtype=torch.float32) * torch.tensor(p.tau_syn_inv, dtype=torch.float32))
+    return NeuronConst(
+        dt_tau_mem=a,
+        dt_tau_syn=s,
+        v_leak=_f32(p.v_leak),
+        v_th=_f32(getattr(p, "v_th", 1.0)),
+        v_reset=_f32(getattr(p, "v_reset", 0.0)),
+        alpha=_f32(getattr(p, "alpha", 100.0)),
+        jump_first=int(jump_first),
+        detach_reset=int(detach_reset),
+    )
+
+
+class _LIFScanFn(torch.autograd.Function):
+    """Forward scan + fused surrogate-gradient reverse scan (soda_lif_fwd / soda_lif_bwd)."""
+
+    @staticmethod
+    def forward(ctx, x, v0, i0, T, const):
+        z, v, i, vd, _, _ = ops.lif_scan(x, T, v0, i0, const, want_v_dec=True)
+        ctx.save_for_backward(vd)
+        ctx.T, ctx.const = T, const
+        ctx.has_state = v0 is not None
+        return z, v, i
+
+    @staticmethod
+    def backward(ctx, gz, gv, gi):
+        (vd,) = ctx.saved_tensors
+        if gz is None:
+            gz = torch.zeros_like(vd)
+        gx, gv0, gi0 = ops.lif_scan_bwd(gz.contiguous(memory_format=torch.preserve_format), gv, gi, vd, ctx.T,
+                                        ctx.const)
+        if not ctx.has_state:
+            gv0 = gi0 = None
+        return gx, gv0, gi0, None, None
+
+
+class _LIScanFn(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, x, v0, i0, T, const):
+        out, v, i, _ = ops.li_scan(x, T, v0, i0, const, apply_tanh=False)
+        ctx.T, ctx.const = T, const
+        ctx.has_state = i0 is not None
+        return out, v, i
+
+    @staticmethod
+    def backward(ctx, gout, gv, gi):
+        if gout is None:
+            gout = torch.zeros_like(gv).repeat(ctx.T, *([1] * (gv.dim() - 1)))
+        gx, gv0, gi0 = ops.li_scan_bwd(gout, gv, gi, ctx.T, ctx.const)
+        if not ctx.has_state:
+            gv0 = gi0 = None
+        return gx, gv0, gi0, None, None
+
+
+class SNNCell(nn.Module):
+    """Base of the stateful neuron cells (role of ``norse.torch.module.snn.SNNCell``)."""
+
+    def __init__(self, p, dt: float = 0.001, jump_first: bool = True, detach_reset: bool = False):
+        super().__init__()
+        self.p = p
+        self.dt = dt
+        self.jump_first = jump_first
+        self.detach_reset = detach_reset
+        self._const = _const(p, dt, jump_first, detach_reset)
+
+    def forward(self, input_tensor: torch.Tensor, state=None):
+        return self.forward_seq(input_tensor, 1, state)
+
+    def forward_seq(self, x: torch.Tensor, T: int, state=None, want_trace: bool = False):
+        raise NotImplementedError
+
+
+class LIFCell(SNNCell):
+    """Leaky integrate-and-fire cell; returns ``(spikes, LIFFeedForwardState(v, i))``."""
+
+    def __init__(self, p: LIFParameters = LIFParameters(), **kwargs):
+        super().__init__(p, **kwargs)
+
+    def forward_seq(self, x, T, state=None, want_trace=False):
+        v0, i0 = (None, None) if state is None else (state.v, state.i)
+        if torch.is_grad_enabled() and (x.requires_grad or (v0 is not None and v0.requires_grad)):
+            z, v, i = _LIFScanFn.apply(x, v0, i0, T, self._const)
+            return z, LIFFeedForwardState(v, i)
+        z, v, i, _, vt, it = ops.lif_scan(x, T, v0, i0, self._const, want_trace=want_trace)
+        if want_trace:
+            return z, LIFFeedForwardState(v, i), LIFFeedForwardState(vt, it)
+        return z, LIFFeedForwardState(v, i)
+
+
+class LICell(SNNCell):
+    """Leaky integrator cell; returns ``(v, LIState(v, i))``.  ``fuse_tanh`` folds a following Tanh."""
+
+    def __init__(self, p: LIParameters = LIParameters(), **kwargs):
+        super().__init__(p, **kwargs)
+
+    def forward_seq(self, x, T, state=None, want_trace=False, fuse_tanh=False):
+        v0, i0 = (None, None) if state is None else (state.v, state.i)
+        if torch.is_grad_enabled() and (x.requires_grad or (i0 is not None and i0.requires_grad)):
+            out, v, i = _LIScanFn.apply(x, v0, i0, T, self._const)
+            if fuse_tanh:
+                out = torch.tanh(out)
+            return out, LIState(v, i)
+        out, v, i, it = ops.li_scan(x, T, v0, i0, self._const, apply_tanh=fuse_tanh, want_trace=want_trace)
+        if want_trace:
+            # per-step v is the (pre-tanh) output itself
+            return out, LIState(v, i), LIState(out if not fuse_tanh else None, it)
+        return out, LIState(v, i)

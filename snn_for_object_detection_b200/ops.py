@@ -1,0 +1,451 @@
+"""Torch-facing wrappers of the C ABI (``include/soda_b200.h``).
+
+Each function takes CUDA tensors, derives plain pointers / sizes / strides from them and enqueues
+the kernel on torch's current stream.  Nothing here computes on the CPU: a non-CUDA tensor raises.
+
+Layout convention (see the header): activations are fp32 "pixel-major" — logical shape
+``[N, C, H, W]`` with ``torch.channels_last`` strides — so that a channel slice of a concat buffer
+is addressable as (batch_stride, pix_stride) without a copy.
+"""
+
+from __future__ import annotations
+
+import ctypes as C
+from typing import NamedTuple, Optional, Sequence, Tuple
+
+import torch
+
+from . import _lib
+from ._lib import ConvDesc, NeuronParams, check, lib
+
+__all__ = [
+    "NeuronConst",
+    "LIF_DEFAULT",
+    "LI_DEFAULT",
+    "bin_events",
+    "PackedConv",
+    "pack_conv",
+    "conv2d",
+    "lif_scan",
+    "li_scan",
+    "lif_scan_bwd",
+    "li_scan_bwd",
+    "pool2d",
+    "channel_affine",
+    "add_n",
+    "to_pixel_major",
+    "empty_pixel_major",
+]
+
+
+def _stream() -> int:
+    return torch.cuda.current_stream().cuda_stream
+
+
+def _need_cuda(*ts: Optional[torch.Tensor]) -> None:
+    for t in ts:
+        if t is not None and not t.is_cuda:
+            raise RuntimeError(
+                "snn_for_object_detection_b200 runs on CUDA (sm_100a) only; got a "
+                f"{t.device} tensor.  There is no CPU fallback."
+            )
+
+
+def _ptr(t: Optional[torch.Tensor]) -> Optional[int]:
+    return None if t is None else t.data_ptr()
+
+
+# --------------------------------------------------------------------------------------------
+# layout helpers
+# --------------------------------------------------------------------------------------------
+def empty_pixel_major(n: int, c: int, h: int, w: int, device, dtype=torch.float32) -> torch.Tensor:
+    return torch.empty((n, c, h, w), device=device, dtype=dtype, memory_format=torch.channels_last)
+
+
+def _pm_strides(x: torch.Tensor) -> Optional[Tuple[int, int]]:
+    """(batch_stride, pix_stride) if ``x`` ([N,C,H,W]) is pixel-major addressable, else None."""
+    n, c, h, w = x.shape
+    sn, sc, sh, sw = x.stride()
+    if c > 1 and sc != 1:
+        return None
+    ps = sw if w > 1 else (sh if h > 1 else c)
+    if ps < c:
+        return None
+    if h > 1 and w > 1 and sh != w * ps:
+        return None
+    if w == 1 and h > 1:
+        ps = sh
+    bs = sn if n > 1 else h * w * ps
+    return bs, ps
+
+
+def to_pixel_major(x: torch.Tensor) -> torch.Tensor:
+    if _pm_strides(x) is not None:
+        return x
+    return x.contiguous(memory_format=torch.channels_last)
+
+
+def _is_dense(x: torch.Tensor) -> bool:
+    return x.is_contiguous() or x.is_contiguous(memory_format=torch.channels_last)
+
+
+# --------------------------------------------------------------------------------------------
+# event binning (K7)
+# --------------------------------------------------------------------------------------------
+def bin_events(
+    events: torch.Tensor,
+    sample_offsets: torch.Tensor,
+    t0_us: torch.Tensor,
+    step_us: int,
+    T: int,
+    H: int,
+    W: int,
+    clip_x: bool = True,
+    sorted_by_time: bool = True,
+    out: Optional[torch.Tensor] = None,
+    n_dropped: Optional[torch.Tensor] = None,
+) -> torch.Tensor:
+    """Event2D records -> occupancy frames ``[T, B, 2, H, W]`` fp32 {0,1}.
+
+    ``events``: CUDA tensor holding the raw 8-byte little-endian records (uint8 ``[n*8]`` or
+    int64/uint64 ``[n]``), samples concatenated; ``sample_offsets`` int64 ``[B+1]``; ``t0_us`` int64 ``[B]``.
+    Reference: prophesee_toolbox/src/io/dat_events_tools.py:100-108 + utils/datasets.py:420-433.
+    """
+    _need_cuda(events, sample_offsets, t0_us, out)
+    B = t0_us.numel()
+    if sample_offsets.dtype != torch.int64 or t0_us.dtype != torch.int64:
+        raise TypeError("sample_offsets and t0_us must be int64")
+    if sample_offsets.numel() != B + 1:
+        raise ValueError("sample_offsets must have B+1 entries")
+    if out is None:
+        out = torch.empty((T, B, 2, H, W), device=events.device, dtype=torch.float32)
+    else:
+        if out.shape != (T, B, 2, H, W) or out.dtype != torch.float32:
+            raise ValueError("out must be fp32 [T,B,2,H,W]")
+        if out.stride()[2:] != (H * W, W, 1):
+            raise ValueError("out frames must be contiguous in (p, y, x)")
+    st, sb = out.stride(0), out.stride(1)
+    if T == 1:
+        st = B * 2 * H * W
+    if B == 1:
+        sb = 2 * H * W
+    check(
+        lib.soda_bin_events(
+            events.data_ptr(), sample_offsets.data_ptr(), t0_us.data_ptr(), B, int(step_us), T, H, W,
+            int(bool(clip_x)), int(bool(sorted_by_time)), out.data_ptr(), st, sb, _ptr(n_dropped), _stream(),
+        ),
+        "soda_bin_events",
+    )
+    return out
+
+
+# --------------------------------------------------------------------------------------------
+# convolution (K1, K2, K6)
+# --------------------------------------------------------------------------------------------
+class PackedConv(NamedTuple):
+    packed: torch.Tensor
+    shift: Optional[torch.Tensor]
+    Cout: int
+    Cin: int
+    k: int
+    stride: int
+    kind: int
+
+
+def pack_conv(
+    weight: torch.Tensor,
+    stride: int,
+    scale: Optional[torch.Tensor] = None,
+    shift: Optional[torch.Tensor] = None,
+    kind: int = _lib.SODA_CONV_FP32,
+) -> PackedConv:
+    """Re-layout ``weight [Cout,Cin,k,k]`` (the state_dict tensor) for the kernels; fold ``scale``."""
+    _need_cuda(weight, scale, shift)
+    Cout, Cin, k, k2 = weight.shape
+    if k != k2:
+        raise ValueError("square kernels only")
+    w = weight.detach().contiguous().float()
+    n = lib.soda_conv_packed_elems(Cout, Cin, k, kind)
+    if n <= 0:
+        raise _lib.SodaError(f"soda_conv_packed_elems: unsupported conv {Cout}x{Cin}x{k} kind {kind}")
+    packed = torch.empty(n, device=w.device, dtype=torch.float32)
+    sc = None if scale is None else scale.detach().contiguous().float()
+    check(
+        lib.soda_conv_pack_weights(w.data_ptr(), _ptr(sc), Cout, Cin, k, kind, packed.data_ptr(), _stream()),
+        "soda_conv_pack_weights",
+    )
+    sh = None if shift is None else shift.detach().contiguous().float()
+    return PackedConv(packed, sh, Cout, Cin, k, int(stride), kind)
+
+
+def conv_out_hw(H: int, W: int, k: int, stride: int) -> Tuple[int, int]:
+    pad = k // 2
+    return (H + 2 * pad - k) // stride + 1, (W + 2 * pad - k) // stride + 1
+
+
+def conv2d(
+    x: torch.Tensor,
+    pc: PackedConv,
+    residual: Optional[torch.Tensor] = None,
+    out: Optional[torch.Tensor] = None,
+) -> torch.Tensor:
+    """``conv(x, W*scale) + shift (+ residual)``; x ``[N,Cin,H,W]``; out may be a channel slice.
+
+    Reference: nn.Conv2d(bias=False, padding=k//2) models/modules/layer_gen.py:129-136 with the
+    eval BatchNorm affine (:211-214) and the Residual sum (models/generator.py:146) fused.
+    """
+    _need_cuda(x, residual, out)
+    if x.dtype != torch.float32:
+        raise TypeError("conv2d: fp32 activations only")
+    N, Cin, H, W = x.shape
+    if Cin != pc.Cin:
+        raise ValueError(f"conv2d: input has {Cin} channels, weights expect {pc.Cin}")
+    Ho, Wo = conv_out_hw(H, W, pc.k, pc.stride)
+    d = ConvDesc()
+    d.N, d.H, d.W, d.Cin, d.Cout, d.k, d.stride, d.kind = N, H, W, Cin, pc.Cout, pc.k, pc.stride, pc.kind
+    if x.is_contiguous() and not (Cin == 1 or (H == 1 and W == 1)):
+        d.in_nchw = 1  # plain NCHW frames (the binned events)
+    else:
+        x = to_pixel_major(x)
+        d.in_nchw = 0
+        d.in_batch_stride, d.in_pix_stride = _pm_strides(x)
+    if out is None:
+        out = empty_pixel_major(N, pc.Cout, Ho, Wo, x.device)
+    elif out.shape != (N, pc.Cout, Ho, Wo):
+        raise ValueError(f"conv2d: out has shape {tuple(out.shape)}, expected {(N, pc.Cout, Ho, Wo)}")
+    os_ = _pm_strides(out)
+    if os_ is None:
+        raise ValueError("conv2d: out must be pixel-major (channels_last) addressable")
+    d.out_batch_stride, d.out_pix_stride = os_
+    if residual is not None:
+        if residual.shape != out.shape:
+            raise ValueError("conv2d: residual shape mismatch")
+        residual = to_pixel_major(residual)
+        d.res_batch_stride, d.res_pix_stride = _pm_strides(residual)
+    check(
+        lib.soda_conv2d_fwd(C.byref(d), x.data_ptr(), pc.packed.data_ptr(), _ptr(pc.shift), _ptr(residual),
+                            out.data_ptr(), _stream()),
+        "soda_conv2d_fwd",
+    )
+    return out
+
+
+# --------------------------------------------------------------------------------------------
+# neuron scans (K3, K4, K8)
+# --------------------------------------------------------------------------------------------
+class NeuronConst(NamedTuple):
+    """fp32 constants exactly as torch forms them for ``python_float * fp32_tensor``."""
+
+    dt_tau_mem: float = 0.1  # fp32(0.001 * 100.0)
+    dt_tau_syn: float = 0.2  # fp32(0.001 * 200.0)
+    v_leak: float = 0.0
+    v_th: float = 1.0
+    v_reset: float = 0.0
+    alpha: float = 100.0
+    jump_first: int = 1
+    detach_reset: int = 0
+
+    def c(self) -> NeuronParams:
+        return NeuronParams(self.dt_tau_mem, self.dt_tau_syn, self.v_leak, self.v_th, self.v_reset,
+                            self.alpha, self.jump_first, self.detach_reset)
+
+
+LIF_DEFAULT = NeuronConst()
+LI_DEFAULT = NeuronConst()
+
+
+def _flat_T(x: torch.Tensor, T: int) -> Tuple[torch.Tensor, int]:
+    if not _is_dense(x):
+        x = x.contiguous(memory_format=torch.channels_last) if x.dim() == 4 else x.contiguous()
+    total = x.numel()
+    if total % T:
+        raise ValueError("leading dimension is not a multiple of T")
+    return x, total // T
+
+
+def lif_scan(
+    x: torch.Tensor,
+    T: int,
+    v0: Optional[torch.Tensor] = None,
+    i0: Optional[torch.Tensor] = None,
+    p: NeuronConst = LIF_DEFAULT,
+    want_v_dec: bool = False,
+    want_trace: bool = False,
+):
+    """T steps of norse LIFCell on ``x`` whose leading dim is ``T*B`` (time-major blocks).
+
+    Returns ``(z, v_T, i_T, v_dec_trace|None, v_trace|None, i_trace|None)``; z and the traces have
+    x's shape and memory layout; v_T, i_T have the shape of one time block.
+    """
+    _need_cuda(x, v0, i0)
+    x, n = _flat_T(x, T)
+    blk_shape = (x.shape[0] // T,) + tuple(x.shape[1:])
+    z = torch.empty_like(x)
+    v = torch.empty_like(x[: blk_shape[0]])
+    i = torch.empty_like(v)
+    if v0 is not None:
+        v0 = _like_block(v0, v)
+        i0 = _like_block(i0, v)
+    vd = torch.empty_like(x) if want_v_dec else None
+    vt = torch.empty_like(x) if want_trace else None
+    it = torch.empty_like(x) if want_trace else None
+    pc = p.c()
+    check(
+        lib.soda_lif_fwd(C.byref(pc), x.data_ptr(), _ptr(v0), _ptr(i0), T, n, z.data_ptr(), v.data_ptr(),
+                         i.data_ptr(), _ptr(vd), _ptr(vt), _ptr(it), _stream()),
+        "soda_lif_fwd",
+    )
+    return z, v, i, vd, vt, it
+
+
+def _like_block(s: torch.Tensor, ref: torch.Tensor) -> torch.Tensor:
+    """State tensor with the same shape and strides as one time block of the activation."""
+    if s.shape != ref.shape:
+        if s.numel() == 1:  # norse LICell initial v is a scalar tensor
+            return torch.full_like(ref, float(s))
+        raise ValueError(f"state shape {tuple(s.shape)} does not match activation block {tuple(ref.shape)}")
+    if s.stride() != ref.stride() or s.dtype != torch.float32:
+        t = torch.empty_like(ref)
+        t.copy_(s)
+        return t
+    return s
+
+
+def li_scan(
+    x: torch.Tensor,
+    T: int,
+    v0: Optional[torch.Tensor] = None,
+    i0: Optional[torch.Tensor] = None,
+    p: NeuronConst = LI_DEFAULT,
+    apply_tanh: bool = False,
+    want_trace: bool = False,
+):
+    """T steps of norse LICell (+ optional Tanh).  Returns ``(out, v_T, i_T, i_trace|None)``."""
+    _need_cuda(x, v0, i0)
+    x, n = _flat_T(x, T)
+    out = torch.empty_like(x)
+    v = torch.empty_like(x[: x.shape[0] // T])
+    i = torch.empty_like(v)
+    if i0 is not None:
+        i0 = _like_block(i0, v)
+        v0 = _like_block(v0, v)
+    it = torch.empty_like(x) if want_trace else None
+    pc = p.c()
+    check(
+        lib.soda_li_fwd(C.byref(pc), x.data_ptr(), _ptr(v0), _ptr(i0), T, n, int(apply_tanh), out.data_ptr(),
+                        v.data_ptr(), i.data_ptr(), _ptr(it), _stream()),
+        "soda_li_fwd",
+    )
+    return out, v, i, it
+
+
+def lif_scan_bwd(grad_out, grad_vT, grad_iT, v_dec, T: int, p: NeuronConst = LIF_DEFAULT):
+    """Fused reverse scan: returns ``(grad_x, grad_v0, grad_i0)``."""
+    _need_cuda(grad_out, grad_vT, grad_iT, v_dec)
+    if grad_out.stride() != v_dec.stride():
+        g = torch.empty_like(v_dec)
+        g.copy_(grad_out)
+        grad_out = g
+    n = v_dec.numel() // T
+    blk = v_dec[: v_dec.shape[0] // T]
+    gx = torch.empty_like(v_dec)
+    gv0 = torch.empty_like(blk)
+    gi0 = torch.empty_like(blk)
+    if grad_vT is not None:
+        grad_vT = _like_block(grad_vT, blk)
+    if grad_iT is not None:
+        grad_iT = _like_block(grad_iT, blk)
+    pc = p.c()
+    check(
+        lib.soda_lif_bwd(C.byref(pc), grad_out.data_ptr(), _ptr(grad_vT), _ptr(grad_iT), v_dec.data_ptr(), T, n,
+                         gx.data_ptr(), gv0.data_ptr(), gi0.data_ptr(), _stream()),
+        "soda_lif_bwd",
+    )
+    return gx, gv0, gi0
+
+
+def li_scan_bwd(grad_out, grad_vT, grad_iT, T: int, p: NeuronConst = LI_DEFAULT):
+    _need_cuda(grad_out, grad_vT, grad_iT)
+    if not _is_dense(grad_out):
+        grad_out = grad_out.contiguous()
+    n = grad_out.numel() // T
+    blk = grad_out[: grad_out.shape[0] // T]
+    gx = torch.empty_like(grad_out)
+    gv0 = torch.empty_like(blk)
+    gi0 = torch.empty_like(blk)
+    if grad_vT is not None:
+        grad_vT = _like_block(grad_vT, blk)
+    if grad_iT is not None:
+        grad_iT = _like_block(grad_iT, blk)
+    pc = p.c()
+    check(
+        lib.soda_li_bwd(C.byref(pc), grad_out.data_ptr(), _ptr(grad_vT), _ptr(grad_iT), T, n, gx.data_ptr(),
+                        gv0.data_ptr(), gi0.data_ptr(), _stream()),
+        "soda_li_bwd",
+    )
+    return gx, gv0, gi0
+
+
+# --------------------------------------------------------------------------------------------
+# glue kernels (K5, K6)
+# --------------------------------------------------------------------------------------------
+_POOL_MODES = {"S": 0, "A": 1, "M": 2}
+
+
+def pool2d(x: torch.Tensor, k: int, stride: int, mode: str, out: Optional[torch.Tensor] = None) -> torch.Tensor:
+    """Sum / average / max pooling, floor mode, no padding (models/modules/common.py:45-49)."""
+    _need_cuda(x, out)
+    x = to_pixel_major(x)
+    N, Cc, H, W = x.shape
+    Ho, Wo = (H - k) // stride + 1, (W - k) // stride + 1
+    if out is None:
+        out = empty_pixel_major(N, Cc, Ho, Wo, x.device)
+    ibs, ips = _pm_strides(x)
+    obs, ops_ = _pm_strides(out)
+    check(
+        lib.soda_pool2d_fwd(x.data_ptr(), N, H, W, Cc, k, stride, _POOL_MODES[mode], ibs, ips, out.data_ptr(), obs,
+                            ops_, _stream()),
+        "soda_pool2d_fwd",
+    )
+    return out
+
+
+def channel_affine(x: torch.Tensor, scale: Optional[torch.Tensor], shift: Optional[torch.Tensor],
+                   out: Optional[torch.Tensor] = None) -> torch.Tensor:
+    """``y = x * scale[c] + shift[c]`` on pixel-major data; also the strided copy into a concat slice."""
+    _need_cuda(x, scale, shift, out)
+    x = to_pixel_major(x)
+    N, Cc, H, W = x.shape
+    if out is None:
+        out = empty_pixel_major(N, Cc, H, W, x.device)
+    ibs, ips = _pm_strides(x)
+    obs, ops_ = _pm_strides(out)
+    if N > 1 and (ibs != H * W * ips or obs != H * W * ops_):
+        for b in range(N):  # batch-strided slices: one launch per image keeps the kernel 2-D
+            channel_affine(x[b : b + 1], scale, shift, out[b : b + 1])
+        return out
+    check(
+        lib.soda_channel_affine(x.data_ptr(), N * H * W, Cc, ips, _ptr(scale), _ptr(shift), out.data_ptr(), ops_,
+                                _stream()),
+        "soda_channel_affine",
+    )
+    return out
+
+
+def add_n(xs: Sequence[torch.Tensor]) -> torch.Tensor:
+    """Residual merge: elementwise sum in list order (models/generator.py:146)."""
+    _need_cuda(*xs)
+    ref = xs[0] if _is_dense(xs[0]) else xs[0].contiguous(memory_format=torch.channels_last)
+    ys = [ref]
+    for t in xs[1:]:
+        if t.shape != ref.shape:
+            raise RuntimeError("residual branches differ in shape")
+        if t.stride() != ref.stride():
+            u = torch.empty_like(ref)
+            u.copy_(t)
+            t = u
+        ys.append(t)
+    out = torch.empty_like(ref)
+    arr = (C.c_void_p * len(ys))(*[t.data_ptr() for t in ys])
+    check(lib.soda_add_n(arr, len(ys), ref.numel(), out.data_ptr(), _stream()), "soda_add_n")
+    return out

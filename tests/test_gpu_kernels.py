@@ -1,0 +1,286 @@
+"""GPU parity: each CUDA entry point (through the C ABI) against the CPU oracle.
+
+Bars (BASELINE.json north_star): event binning bit-exact; LIF/LI forward bit-exact against the fp32
+restatement (same op order, no FMA contraction); conv within 2e-6 relative of an fp64 reference
+(fp32 products, fp32 accumulation); pooling / merges bit-exact.
+"""
+import numpy as np
+import pytest
+import torch
+import torch.nn.functional as F
+
+from helpers import golden
+from oracle import binning as ob
+from oracle import norse_restated as nr
+
+pytestmark = pytest.mark.gpu
+DEV = "cuda"
+
+
+def _pkg():
+    import snn_for_object_detection_b200 as pkg
+
+    return pkg
+
+
+def _unpack(bits, shape):
+    return np.unpackbits(bits)[: int(np.prod(shape))].reshape(shape).astype(np.float32)
+
+
+# ----------------------------------------------------------------------------------------------
+# event binning
+# ----------------------------------------------------------------------------------------------
+def _bin(samples, t0, step, T, H, W, clip_x=True, sorted_by_time=True, out=None, count_dropped=False):
+    pkg = _pkg()
+    ev, offs = pkg.events.pack_samples(samples)
+    nd = torch.zeros(1, dtype=torch.int32, device=DEV) if count_dropped else None
+    f = pkg.ops.bin_events(ev.to(DEV), offs.to(DEV), torch.tensor(t0, dtype=torch.int64, device=DEV), step, T, H, W,
+                           clip_x=clip_x, sorted_by_time=sorted_by_time, out=out, n_dropped=nd)
+    return (f, int(nd.item())) if count_dropped else f
+
+
+def test_bin_golden_st_bit_exact():
+    g = golden("binning_st.npz")
+    T, H, W = int(g["T"]), int(g["H"]), int(g["W"])
+    ref = _unpack(g["features_bits"], (T, 2, H, W))
+    for srt in (True, False):
+        f = _bin([g["records"]], [int(g["first_event_time_us"])], int(g["step_us"]), T, H, W, True, srt)
+        assert np.array_equal(f[:, 0].cpu().numpy(), ref)
+
+
+def test_bin_golden_mt_bit_exact():
+    g = golden("binning_mt.npz")
+    T, H, W, step = int(g["T"]), int(g["H"]), int(g["W"]), int(g["step_us"])
+    ref = _unpack(g["features_bits"], (2, T, 2, H, W))
+    # both windows as one batch of two samples reading the same record stream
+    f = _bin([g["records"], g["records"]], [0, T * step], step, T, H, W, clip_x=False)
+    assert np.array_equal(f[:, 0].cpu().numpy(), ref[0])
+    assert np.array_equal(f[:, 1].cpu().numpy(), ref[1])
+
+
+@pytest.mark.parametrize("H,W", [(240, 304), (37, 51), (8, 4), (720, 1280)])
+@pytest.mark.parametrize("srt", [True, False])
+def test_bin_random_ragged_batches(H, W, srt):
+    rng = np.random.default_rng(H * 1000 + W)
+    T, step = 5, 16000
+    counts = [0, 1, 777, 20000, 3]
+    t0 = [0, 100, 5000, 16000, 7]
+    samples = [ob.make_records(rng, n, 0, (T + 2) * step, H, W) for n in counts]
+    f = _bin(samples, t0, step, T, H, W, clip_x=True, sorted_by_time=srt)
+    ref = ob.bin_batch(samples, t0, step, T, H, W, clip_x=True)
+    assert np.array_equal(f.cpu().numpy(), ref)
+    assert set(np.unique(ref)) <= {0.0, 1.0}
+
+
+def test_bin_out_of_frame_events_clip_and_drop():
+    rng = np.random.default_rng(9)
+    T, step, H, W = 3, 16000, 40, 64
+    rec = ob.make_records(rng, 5000, 0, T * step, H, W, x_overflow=5)
+    f = _bin([rec], [0], step, T, H, W, clip_x=True)
+    assert np.array_equal(f.cpu().numpy(), ob.bin_batch([rec], [0], step, T, H, W, clip_x=True))
+    f2, nd = _bin([rec], [0], step, T, H, W, clip_x=False, count_dropped=True)
+    assert np.array_equal(f2.cpu().numpy(), ob.bin_batch([rec], [0], step, T, H, W, clip_x=False))
+    x = rec[:, 1] & 16383
+    assert nd == int((x >= W).sum())
+
+
+def test_bin_writes_every_element_and_strided_out():
+    rng = np.random.default_rng(2)
+    T, B, step, H, W = 4, 3, 16000, 24, 32
+    samples = [ob.make_records(rng, 900, 0, T * step, H, W) for _ in range(B)]
+    big = torch.full((T, B + 2, 2, H, W), 7.0, device=DEV)
+    out = big[:, 1 : 1 + B]
+    _bin(samples, [0] * B, step, T, H, W, out=out)
+    assert np.array_equal(out.cpu().numpy(), ob.bin_batch(samples, [0] * B, step, T, H, W))
+    assert float(big[:, 0].min()) == 7.0 and float(big[:, -1].min()) == 7.0
+
+
+def test_bin_full_size_property_gen1_and_1mpx():
+    """BASELINE sizes: ones == number of distinct (t-bin, p, y, x); idempotent on duplicated input."""
+    for (H, W, n_per_step, B) in ((240, 304, 10000, 5), (720, 1280, 150000, 2)):
+        rng = np.random.default_rng(H)
+        T, step = 32, 16000
+        samples = [ob.make_records(rng, n_per_step * T, 0, T * step, H, W) for _ in range(B)]
+        f = _bin(samples, [0] * B, step, T, H, W)
+        for b in range(B):
+            t = samples[b][:, 0].astype(np.int64) // step
+            key = (t << 29) | (samples[b][:, 1].astype(np.int64) & 0x1FFFFFFF)
+            assert int(f[:, b].sum().item()) == np.unique(key).size
+        dup = [np.concatenate([s, s])[np.argsort(np.concatenate([s[:, 0], s[:, 0]]), kind="stable")] for s in samples]
+        f2 = _bin(dup, [0] * B, step, T, H, W)
+        assert torch.equal(f, f2)
+
+
+# ----------------------------------------------------------------------------------------------
+# LIF / LI scans
+# ----------------------------------------------------------------------------------------------
+def _oracle_scan(cell, x, state=None):
+    outs, vs, is_ = [], [], []
+    for t in range(x.shape[0]):
+        o, state = cell(x[t], state)
+        outs.append(o), vs.append(state.v), is_.append(state.i)
+    return torch.stack(outs), torch.stack(vs), torch.stack(is_), state
+
+
+@pytest.mark.parametrize("n", [1, 5, 1024, 4099])
+@pytest.mark.parametrize("with_state", [False, True])
+def test_lif_scan_bit_exact(n, with_state):
+    pkg = _pkg()
+    torch.manual_seed(n)
+    T = 9
+    x = torch.randn(T, n) * 3
+    state = nr.LIFFeedForwardState(torch.rand(n), torch.randn(n)) if with_state else None
+    with torch.no_grad():
+        zo, vo, io, so = _oracle_scan(nr.LIFCell(), x, state)
+    xs = x.to(DEV).reshape(T * 1, n)
+    v0 = state.v.to(DEV).reshape(1, n) if with_state else None
+    i0 = state.i.to(DEV).reshape(1, n) if with_state else None
+    z, v, i, vd, vt, it = pkg.ops.lif_scan(xs, T, v0, i0, want_v_dec=True, want_trace=True)
+    assert zo.sum() > 0
+    assert torch.equal(z.cpu().reshape(T, n), zo)
+    assert torch.equal(vt.cpu().reshape(T, n), vo) and torch.equal(it.cpu().reshape(T, n), io)
+    assert torch.equal(v.cpu().reshape(n), so.v.detach()) and torch.equal(i.cpu().reshape(n), so.i)
+
+
+@pytest.mark.parametrize("tanh", [False, True])
+def test_li_scan(tanh):
+    pkg = _pkg()
+    torch.manual_seed(1)
+    T, n = 8, 1003
+    x = torch.randn(T, n)
+    with torch.no_grad():
+        vo, _, io, so = _oracle_scan(nr.LICell(), x)
+    out, v, i, it = pkg.ops.li_scan(x.to(DEV), T, apply_tanh=tanh, want_trace=True)
+    assert torch.equal(it.cpu(), io) and torch.equal(v.cpu().reshape(n), so.v.detach().reshape(n))
+    if tanh:
+        assert torch.allclose(out.cpu(), torch.tanh(vo), rtol=0, atol=2e-7)
+    else:
+        assert torch.equal(out.cpu(), vo)
+
+
+def test_lif_decay_first_order_switch():
+    pkg = _pkg()
+    torch.manual_seed(4)
+    T, n = 6, 300
+    x = torch.randn(T, n) * 3
+    nr.ORDER = "decay_first"
+    try:
+        with torch.no_grad():
+            zo, vo, io, _ = _oracle_scan(nr.LIFCell(), x)
+    finally:
+        nr.ORDER = "jump_first"
+    p = pkg.ops.LIF_DEFAULT._replace(jump_first=0)
+    z, v, i, _, vt, it = pkg.ops.lif_scan(x.to(DEV), T, p=p, want_trace=True)
+    assert torch.equal(z.cpu(), zo) and torch.equal(vt.cpu(), vo) and torch.equal(it.cpu(), io)
+
+
+@pytest.mark.parametrize("detach", [False, True])
+def test_lif_backward_matches_oracle_autograd(detach):
+    """fp32 reverse scan vs fp64 autograd through the restated cell (SuperSpike, alpha=100)."""
+    from snn_for_object_detection_b200.modules.cells import LIFCell, LIFFeedForwardState
+
+    torch.manual_seed(3)
+    T, n = 7, 515
+    x = (torch.randn(T, n) * 2).double()
+    v0, i0 = torch.rand(n).double(), torch.randn(n).double()
+    gz = torch.randn(T, n).double()
+    gv, gi = torch.randn(n).double(), torch.randn(n).double()
+    xo, v0o, i0o = (t.clone().requires_grad_(True) for t in (x, v0, i0))
+    nr.DETACH_RESET = detach
+    try:
+        state = nr.LIFFeedForwardState(v0o, i0o)
+        zs = []
+        for t in range(T):
+            z, state = nr.lif_feed_forward_step(xo[t], state)
+            zs.append(z)
+        loss = (torch.stack(zs) * gz).sum() + (state.v * gv).sum() + (state.i * gi).sum()
+        loss.backward()
+    finally:
+        nr.DETACH_RESET = False
+    cell = LIFCell(detach_reset=detach)
+    xc = x.float().to(DEV).requires_grad_(True)
+    v0c = v0.float().to(DEV).reshape(1, n).requires_grad_(True)
+    i0c = i0.float().to(DEV).reshape(1, n).requires_grad_(True)
+    z, st = cell.forward_seq(xc.reshape(T, n), T, LIFFeedForwardState(v0c, i0c))
+    ((z * gz.float().to(DEV)).sum() + (st.v * gv.float().to(DEV)).sum() + (st.i * gi.float().to(DEV)).sum()).backward()
+    for got, want in ((xc.grad, xo.grad), (v0c.grad.reshape(n), v0o.grad), (i0c.grad.reshape(n), i0o.grad)):
+        err = (got.cpu().double() - want).abs().max() / want.abs().max()
+        assert float(err) < 2e-5, float(err)
+
+
+# ----------------------------------------------------------------------------------------------
+# convolution, pooling, merges
+# ----------------------------------------------------------------------------------------------
+CONV_CASES = [
+    # N, Cin, H, W, Cout, k, stride, nchw_input
+    (3, 2, 24, 32, 8, 3, 1, True),
+    (2, 2, 30, 38, 64, 3, 2, True),
+    (2, 32, 15, 19, 64, 3, 2, False),
+    (2, 64, 15, 19, 27, 1, 1, False),
+    (2, 64, 8, 10, 36, 1, 1, False),
+    (1, 48, 9, 7, 40, 3, 1, False),
+    (2, 8, 12, 16, 32, 3, 1, False),
+    (1, 128, 8, 10, 256, 3, 2, False),
+    (2, 256, 4, 5, 128, 1, 1, False),
+]
+
+
+@pytest.mark.parametrize("case", CONV_CASES)
+def test_conv2d_against_fp64(case):
+    pkg = _pkg()
+    N, Cin, H, W, Cout, k, s, nchw = case
+    torch.manual_seed(Cin * 7 + Cout)
+    x = torch.randn(N, Cin, H, W)
+    w = torch.randn(Cout, Cin, k, k) / (Cin * k * k) ** 0.5
+    scale, shift = torch.rand(Cout) + 0.5, torch.randn(Cout)
+    ref = F.conv2d(x.double(), (w * scale.view(-1, 1, 1, 1)).double(), stride=s, padding=k // 2) + shift.double().view(1, -1, 1, 1)
+    xd = x.to(DEV) if nchw else x.to(DEV).contiguous(memory_format=torch.channels_last)
+    pc = pkg.ops.pack_conv(w.to(DEV), s, scale.to(DEV), shift.to(DEV))
+    y = pkg.ops.conv2d(xd, pc)
+    assert y.shape == ref.shape
+    err = (y.cpu().double() - ref).abs().max() / ref.abs().max()
+    assert float(err) < 2e-6, float(err)
+    # residual + channel-slice destination
+    res = torch.randn_like(ref).float()
+    buf = torch.zeros(N, Cout + 16, *ref.shape[2:], device=DEV).contiguous(memory_format=torch.channels_last)
+    out = buf[:, 8 : 8 + Cout]
+    pkg.ops.conv2d(xd, pc, residual=res.to(DEV).contiguous(memory_format=torch.channels_last), out=out)
+    err = (out.cpu().double() - (ref + res.double())).abs().max() / ref.abs().max()
+    assert float(err) < 2e-6
+    assert float(buf[:, :8].abs().max()) == 0.0 and float(buf[:, 8 + Cout :].abs().max()) == 0.0
+
+
+@pytest.mark.parametrize("mode", ["S", "A", "M"])
+@pytest.mark.parametrize("shape", [(2, 8, 24, 32), (1, 5, 9, 11), (3, 32, 15, 19)])
+def test_pool2d(mode, shape):
+    pkg = _pkg()
+    torch.manual_seed(0)
+    x = torch.randint(0, 2, shape).float() if mode == "S" else torch.randn(shape)
+    if mode == "S":
+        ref = F.avg_pool2d(x, 2, 2, 0) * 2 * 2
+    elif mode == "A":
+        ref = F.avg_pool2d(x, 2, 2)
+    else:
+        ref = F.max_pool2d(x, 2, 2)
+    y = pkg.ops.pool2d(x.to(DEV).contiguous(memory_format=torch.channels_last), 2, 2, mode)
+    if mode == "A":
+        assert torch.allclose(y.cpu(), ref, rtol=1e-6, atol=1e-7)
+    else:
+        assert torch.equal(y.cpu(), ref)
+
+
+def test_add_n_and_channel_affine():
+    pkg = _pkg()
+    torch.manual_seed(0)
+    a, b = torch.randn(2, 12, 5, 7), torch.randn(2, 12, 5, 7)
+    y = pkg.ops.add_n([a.to(DEV).contiguous(memory_format=torch.channels_last), b.to(DEV)])
+    assert torch.equal(y.cpu(), torch.stack([a, b]).sum(0))
+    sc, sh = torch.randn(12), torch.randn(12)
+    z = pkg.ops.channel_affine(a.to(DEV), sc.to(DEV), sh.to(DEV))
+    assert torch.equal(z.cpu(), a * sc.view(1, -1, 1, 1) + sh.view(1, -1, 1, 1))
+
+
+def test_cpu_tensor_is_rejected_not_computed():
+    pkg = _pkg()
+    with pytest.raises(RuntimeError, match="no CPU fallback"):
+        pkg.ops.lif_scan(torch.zeros(4, 8), 4)

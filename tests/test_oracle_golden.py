@@ -1,0 +1,107 @@
+"""CPU: the oracle restatements against the golden vectors produced by the reference's own Python
+(oracle/make_golden.py).  Bit-exact unless stated."""
+import numpy as np
+import torch
+
+from helpers import golden, tiny_yolo_from_golden, vgg_block_from_golden
+from oracle import binning as ob
+from oracle import net_restated as onr
+
+
+def _unpack(bits, shape):
+    n = int(np.prod(shape))
+    return np.unpackbits(bits)[:n].reshape(shape).astype(np.float32)
+
+
+def test_binning_st_matches_reference_parse_data():
+    g = golden("binning_st.npz")
+    T, H, W = int(g["T"]), int(g["H"]), int(g["W"])
+    rec = g["records"]
+    # the reference loads events with t < load_until (psee_loader.load_delta_t) before binning
+    rec = rec[rec[:, 0] < int(g["load_until_us"])]
+    f = ob.bin_st(rec, int(g["first_event_time_us"]), int(g["step_us"]), T, H, W)
+    ref = _unpack(g["features_bits"], (T, 2, H, W))
+    assert int(ref.sum()) == int(g["n_ones"])
+    assert np.array_equal(f, ref)
+    # batched contract of the CUDA entry point (drops t >= t0 + T*step itself)
+    fb = ob.bin_batch([g["records"]], [int(g["first_event_time_us"])], int(g["step_us"]), T, H, W, clip_x=True)
+    assert np.array_equal(fb[:, 0], ref)
+
+
+def test_binning_mt_matches_reference_parse_data():
+    g = golden("binning_mt.npz")
+    T, H, W, step = int(g["T"]), int(g["H"]), int(g["W"]), int(g["step_us"])
+    ref = _unpack(g["features_bits"], (2, T, 2, H, W))
+    rec = g["records"]
+    for win in range(2):
+        lo, hi = win * T * step, (win + 1) * T * step
+        sl = rec[(rec[:, 0] >= lo) & (rec[:, 0] < hi)]
+        assert np.array_equal(ob.bin_mt(sl, win * T, step, T, H, W), ref[win])
+        fb = ob.bin_batch([rec], [lo], step, T, H, W, clip_x=False)
+        assert np.array_equal(fb[:, 0], ref[win])
+
+
+def test_dat_roundtrip_and_decode():
+    rng = np.random.default_rng(5)
+    rec = ob.make_records(rng, 500, 10, 5000, 240, 304)
+    back, ev_type, ev_size, hw = ob.split_dat(ob.dat_bytes(rec, 240, 304))
+    assert (ev_type, ev_size, hw) == (0, 8, (240, 304))
+    assert np.array_equal(back, rec)
+    t, x, y, p = ob.decode_events(rec)
+    assert x.max() < 304 and y.max() < 240 and set(np.unique(p)) <= {0, 1}
+    assert np.all(np.diff(t) >= 0)
+
+
+def test_oracle_executor_matches_reference_blockgen_vgg():
+    block, g = vgg_block_from_golden()
+    X = torch.from_numpy(g["X"]).float()
+    Y, state = onr.seq_block_forward(block, X)
+    assert torch.equal(Y, torch.from_numpy(g["Y"]))
+    last = [s for s in state[0] if s is not None][-1]
+    assert torch.equal(last.v, torch.from_numpy(g["v_final"]))
+    assert torch.equal(last.i, torch.from_numpy(g["i_final"]))
+    assert 0.02 < float(Y.mean()) < 0.5  # not a dead net
+
+
+def test_oracle_executor_matches_reference_tiny_yolo():
+    model, X, g, digest_ok = tiny_yolo_from_golden()
+    assert [k for k in model.state_dict().keys()] == [str(k) for k in g["keys"]], "state_dict keys differ from the reference's"
+    assert digest_ok, "seeded weights differ from the reference's (torch RNG / construction order changed)"
+    (anchors, cls, bbox), _ = onr.soda_forward(model, X)
+    assert torch.equal(anchors, torch.from_numpy(g["anchors"]))
+    assert torch.equal(cls, torch.from_numpy(g["cls"]))
+    assert torch.equal(bbox, torch.from_numpy(g["bbox"]))
+    assert float(np.min(g["rates"])) > 0.03
+
+
+def test_box_utils_match_reference():
+    from snn_for_object_detection_b200.utils import box
+    from snn_for_object_detection_b200.utils.anchors import AnchorGenerator
+
+    g = golden("box.npz")
+    gen = AnchorGenerator(torch.from_numpy(g["sizes"]), torch.from_numpy(g["ratios"]))
+    anchors = gen(torch.zeros(1, 4, int(g["fh"]), int(g["fw"])))
+    assert torch.equal(anchors, torch.from_numpy(g["anchors"]))
+    det = box.multibox_detection(torch.from_numpy(g["cls_probs"]), torch.from_numpy(g["offsets"]), anchors)
+    assert torch.equal(det, torch.from_numpy(g["det"]))
+
+
+def test_norse_restatement_known_answers():
+    """PARITY UNPINNED (norse absent): hand-computed known answers of the published update rule."""
+    from oracle import norse_restated as nr
+
+    cell = nr.LIFCell()
+    x = torch.tensor([6.0, 0.0])
+    z, s = cell(x)  # i=6 -> v = 0.1*6 = 0.6 ; i' = 4.8
+    assert torch.equal(z, torch.zeros(2))
+    assert torch.allclose(s.v, torch.tensor([0.6, 0.0])) and torch.allclose(s.i, torch.tensor([4.8, 0.0]))
+    z, s = cell(torch.zeros(2), s)  # v = 0.6 + 0.1*(4.8-0.6) = 1.02 > 1 -> spike, reset
+    assert torch.equal(z, torch.tensor([1.0, 0.0]))
+    assert float(s.v[0]) == 0.0 and abs(float(s.i[0]) - 3.84) < 1e-6
+    li = nr.LICell()
+    v, s = li(torch.tensor([1.0]))
+    assert abs(float(v) - 0.1) < 1e-7 and abs(float(s.i) - 0.8) < 1e-7
+    # surrogate gradient: 1 / (100*|v-1| + 1)^2
+    xg = torch.tensor([0.5], requires_grad=True)
+    nr.threshold(xg, "super", 100.0).backward()
+    assert abs(float(xg.grad) - 1.0 / (100 * 0.5 + 1) ** 2) < 1e-9
