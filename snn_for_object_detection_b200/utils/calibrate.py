@@ -1,0 +1,41 @@
+"""Synthetic-weight calibration on the CUDA path.
+
+There are no trained weights for the reference (its checkpoint is a git-LFS pointer) and with its
+raw initialisation (kaiming conv, BatchNorm = identity) every LIF layer is silent.
+``calibrate`` runs one layer-major pass in which every ``Conv -> Norm`` pair first measures the
+per-channel statistics of its own convolution output and stores them as the BatchNorm running
+statistics, with gamma = ``gain``: LIF inputs become ~N(0, gain^2) and every layer fires.
+Only the statistics reduction uses a stock torch op (``var_mean``); the convolutions run on the
+package's kernels.
+"""
+
+from __future__ import annotations
+
+import torch
+
+from .. import ops
+from ..modules.common import SodaConv2d
+
+
+@torch.no_grad()
+def calibrate(model: torch.nn.Module, X: torch.Tensor, gain: float = 5.0) -> None:
+    """``X[T,B,2,H,W]`` on the model's CUDA device.  Mutates BatchNorm buffers / gamma in place."""
+    orig = SodaConv2d.forward
+
+    def measuring_forward(self, x, norm=None, residual=None, out=None):
+        if norm is not None:
+            raw = ops.conv2d(x, ops.pack_conv(self.weight, self.stride[0]))
+            var, mean = torch.var_mean(raw, dim=(0, 2, 3), unbiased=False)
+            norm.running_mean.copy_(mean)
+            norm.running_var.copy_(var.clamp_min(1e-12))
+            norm.weight.fill_(gain)
+        return orig(self, x, norm=norm, residual=residual, out=out)
+
+    was_training = model.training
+    model.eval()
+    SodaConv2d.forward = measuring_forward
+    try:
+        model(X)
+    finally:
+        SodaConv2d.forward = orig
+        model.train(was_training)
