@@ -38,6 +38,30 @@ __all__ = [
 ]
 
 
+# When set to a dict, every op records a (start, end) CUDA-event pair on the launching stream under
+# its family name: bench.py uses it for the per-kernel-family device time of one eager step.
+PROFILE = None
+CONV_KERNEL_NAME = "conv_ffma_kernel"
+
+
+def _prof(name):
+    def deco(fn):
+        def wrapped(*a, **k):
+            if PROFILE is None:
+                return fn(*a, **k)
+            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            e0.record()
+            r = fn(*a, **k)
+            e1.record()
+            PROFILE.setdefault(name, []).append((e0, e1))
+            return r
+
+        wrapped.__name__, wrapped.__doc__ = fn.__name__, fn.__doc__
+        return wrapped
+
+    return deco
+
+
 def _stream() -> int:
     return torch.cuda.current_stream().cuda_stream
 
@@ -92,6 +116,7 @@ def _is_dense(x: torch.Tensor) -> bool:
 # --------------------------------------------------------------------------------------------
 # event binning (K7)
 # --------------------------------------------------------------------------------------------
+@_prof("bin_events")
 def bin_events(
     events: torch.Tensor,
     sample_offsets: torch.Tensor,
@@ -183,6 +208,7 @@ def conv_out_hw(H: int, W: int, k: int, stride: int) -> Tuple[int, int]:
     return (H + 2 * pad - k) // stride + 1, (W + 2 * pad - k) // stride + 1
 
 
+@_prof("conv2d")
 def conv2d(
     x: torch.Tensor,
     pc: PackedConv,
@@ -263,6 +289,7 @@ def _flat_T(x: torch.Tensor, T: int) -> Tuple[torch.Tensor, int]:
     return x, total // T
 
 
+@_prof("lif_scan")
 def lif_scan(
     x: torch.Tensor,
     T: int,
@@ -311,6 +338,7 @@ def _like_block(s: torch.Tensor, ref: torch.Tensor) -> torch.Tensor:
     return s
 
 
+@_prof("li_scan")
 def li_scan(
     x: torch.Tensor,
     T: int,
@@ -392,6 +420,7 @@ def li_scan_bwd(grad_out, grad_vT, grad_iT, T: int, p: NeuronConst = LI_DEFAULT)
 _POOL_MODES = {"S": 0, "A": 1, "M": 2}
 
 
+@_prof("pool2d")
 def pool2d(x: torch.Tensor, k: int, stride: int, mode: str, out: Optional[torch.Tensor] = None) -> torch.Tensor:
     """Sum / average / max pooling, floor mode, no padding (models/modules/common.py:45-49)."""
     _need_cuda(x, out)
@@ -410,6 +439,7 @@ def pool2d(x: torch.Tensor, k: int, stride: int, mode: str, out: Optional[torch.
     return out
 
 
+@_prof("channel_affine")
 def channel_affine(x: torch.Tensor, scale: Optional[torch.Tensor], shift: Optional[torch.Tensor],
                    out: Optional[torch.Tensor] = None) -> torch.Tensor:
     """``y = x * scale[c] + shift[c]`` on pixel-major data; also the strided copy into a concat slice."""
@@ -432,6 +462,7 @@ def channel_affine(x: torch.Tensor, scale: Optional[torch.Tensor], shift: Option
     return out
 
 
+@_prof("add_n")
 def add_n(xs: Sequence[torch.Tensor]) -> torch.Tensor:
     """Residual merge: elementwise sum in list order (models/generator.py:146)."""
     _need_cuda(*xs)
