@@ -97,11 +97,15 @@ SODA_API int soda_bin_events(const void* events, const int64_t* sample_offsets, 
  * ------------------------------------------------------------------------------------------- */
 #define SODA_CONV_FP32 0
 #define SODA_CONV_TC 1
+/* flags: the input tensor holds only values exactly representable in TF32 (spikes {0,1}, pooled
+ * spike counts, event frames): the tensor-core kernel then skips the A-operand split pass. */
+#define SODA_CONV_FLAG_INPUT_EXACT_TF32 1
 
 typedef struct {
   int N, H, W, Cin, Cout, k, stride;
   int in_nchw;
   int kind;
+  int flags;
   int64_t in_batch_stride, in_pix_stride;
   int64_t out_batch_stride, out_pix_stride;
   int64_t res_batch_stride, res_pix_stride;
@@ -110,6 +114,8 @@ typedef struct {
 SODA_API int64_t soda_conv_packed_elems(int Cout, int Cin, int k, int kind);
 SODA_API int soda_conv_pack_weights(const float* weight, const float* scale, int Cout, int Cin, int k,
                            int kind, float* packed, void* stream);
+/* 1 if the SODA_CONV_TC kernel takes this descriptor / input pointer, else 0 (use SODA_CONV_FP32). */
+SODA_API int soda_conv_tc_supported(const soda_conv_desc_t* d, const float* x);
 SODA_API int soda_conv2d_fwd(const soda_conv_desc_t* d, const float* x, const float* packed,
                     const float* shift, const float* residual, float* y, void* stream);
 

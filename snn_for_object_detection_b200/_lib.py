@@ -16,6 +16,7 @@ LIB_PATH = os.path.join(_HERE, "libsoda_b200.so")
 
 SODA_CONV_FP32 = 0
 SODA_CONV_TC = 1
+SODA_CONV_FLAG_INPUT_EXACT_TF32 = 1
 
 
 class SodaError(RuntimeError):
@@ -33,6 +34,7 @@ class ConvDesc(C.Structure):
         ("stride", C.c_int),
         ("in_nchw", C.c_int),
         ("kind", C.c_int),
+        ("flags", C.c_int),
         ("in_batch_stride", C.c_int64),
         ("in_pix_stride", C.c_int64),
         ("out_batch_stride", C.c_int64),
@@ -65,6 +67,7 @@ SIGNATURES = {
     "soda_bin_events": (_i, [_vp, _vp, _vp, _i, _i64, _i, _i, _i, _i, _i, _vp, _i64, _i64, _vp, _vp]),
     "soda_conv_packed_elems": (_i64, [_i, _i, _i, _i]),
     "soda_conv_pack_weights": (_i, [_vp, _vp, _i, _i, _i, _i, _vp, _vp]),
+    "soda_conv_tc_supported": (_i, [C.POINTER(ConvDesc), _vp]),
     "soda_conv2d_fwd": (_i, [C.POINTER(ConvDesc), _vp, _vp, _vp, _vp, _vp, _vp]),
     "soda_lif_fwd": (_i, [C.POINTER(NeuronParams), _vp, _vp, _vp, _i, _i64, _vp, _vp, _vp, _vp, _vp, _vp, _vp]),
     "soda_li_fwd": (_i, [C.POINTER(NeuronParams), _vp, _vp, _vp, _i, _i64, _i, _vp, _vp, _vp, _vp, _vp]),

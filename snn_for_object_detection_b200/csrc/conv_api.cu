@@ -13,6 +13,7 @@ int conv_tc_pack(const float* w, const float* scale, int Cout, int Cin, int k, f
 int conv_tc_dispatch(const soda_conv_desc_t* d, const float* x, const float* packed,
                      const float* shift, const float* residual, float* y, void* stream);
 
+bool conv_tc_supported(const soda_conv_desc_t* d, const float* x);
 static inline int cout_pad_of(int Cout) { return (Cout + 31) / 32 * 32; }
 }  // namespace soda
 
@@ -43,4 +44,9 @@ extern "C" int soda_conv2d_fwd(const soda_conv_desc_t* d, const float* x, const 
   if (d->kind == SODA_CONV_TC) return conv_tc_dispatch(d, x, packed, shift, residual, y, stream);
   if (d->kind != SODA_CONV_FP32) return fail(SODA_ERR_UNSUPPORTED, "conv2d: unknown kind");
   return conv_ffma_dispatch(d, x, packed, cout_pad_of(d->Cout), shift, residual, y, stream);
+}
+
+extern "C" int soda_conv_tc_supported(const soda_conv_desc_t* d, const float* x) {
+  if (!d || !x) return 0;
+  return soda::conv_tc_supported(d, x) ? 1 : 0;
 }

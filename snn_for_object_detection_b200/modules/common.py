@@ -38,24 +38,22 @@ class SodaConv2d(nn.Conv2d):
     The packed / BatchNorm-folded weight is a cache keyed on the parameter versions.
     """
 
-    conv_kind = _lib.SODA_CONV_FP32
-
     def __init__(self, *args, **kwargs):
         super().__init__(*args, **kwargs)
-        self._pack_key = None
-        self._packed = None
+        self._pack_cache = {}
 
-    def packed(self, norm: Optional["SodaBatchNorm2d"] = None) -> ops.PackedConv:
-        key = (self.weight.data_ptr(), self.weight._version, self.weight.device, self.conv_kind)
+    def packed(self, norm: Optional["SodaBatchNorm2d"] = None, kind: int = _lib.SODA_CONV_FP32) -> ops.PackedConv:
+        key = (self.weight.data_ptr(), self.weight._version, self.weight.device)
         scale = shift = None
         if norm is not None:
             key = key + norm.fold_key()
-        if key != self._pack_key:
+        hit = self._pack_cache.get(kind)
+        if hit is None or hit[0] != key:
             if norm is not None:
                 scale, shift = norm.fold()
-            self._packed = ops.pack_conv(self.weight, self.stride[0], scale, shift, self.conv_kind)
-            self._pack_key = key
-        return self._packed
+            hit = (key, ops.pack_conv(self.weight, self.stride[0], scale, shift, kind))
+            self._pack_cache[kind] = hit
+        return hit[1]
 
     def forward(self, x: torch.Tensor, norm: Optional["SodaBatchNorm2d"] = None, residual=None, out=None):
         if self.bias is not None or self.groups != 1 or self.dilation != (1, 1):
@@ -64,7 +62,8 @@ class SodaConv2d(nn.Conv2d):
             from ..autograd import conv2d_autograd  # training route (dgrad / wgrad kernels)
 
             return conv2d_autograd(self, x, norm, residual, out)
-        return ops.conv2d(x, self.packed(norm), residual=residual, out=out)
+        kind = ops.conv_kind_for(x, self.in_channels, self.kernel_size[0], self.stride[0])
+        return ops.conv2d(x, self.packed(norm, kind), residual=residual, out=out)
 
 
 class SodaBatchNorm2d(nn.BatchNorm2d):

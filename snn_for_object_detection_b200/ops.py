@@ -11,6 +11,7 @@ is addressable as (batch_stride, pix_stride) without a copy.
 from __future__ import annotations
 
 import ctypes as C
+import os
 from typing import NamedTuple, Optional, Sequence, Tuple
 
 import torch
@@ -41,7 +42,7 @@ __all__ = [
 # When set to a dict, every op records a (start, end) CUDA-event pair on the launching stream under
 # its family name: bench.py uses it for the per-kernel-family device time of one eager step.
 PROFILE = None
-CONV_KERNEL_NAME = "conv_ffma_kernel"
+CONV_KERNEL_NAME = "conv_tc_kernel (tcgen05 3xTF32) + conv_ffma_kernel (Cin % 32 != 0)"
 
 
 def _prof(name):
@@ -203,6 +204,31 @@ def pack_conv(
     return PackedConv(packed, sh, Cout, Cin, k, int(stride), kind)
 
 
+def conv_kind_for(x: torch.Tensor, Cin: int, k: int, stride: int) -> int:
+    """SODA_CONV_TC (tcgen05 implicit GEMM) when the shape/layout qualifies, else the FP32-pipe kernel.
+    ``SODA_CONV_KIND=fp32`` in the environment forces the FP32-pipe kernel (cross-check runs)."""
+    if os.environ.get("SODA_CONV_KIND", "") == "fp32":
+        return _lib.SODA_CONV_FP32
+    if Cin % 32 != 0 or k not in (1, 3) or stride not in (1, 2):
+        return _lib.SODA_CONV_FP32
+    st = _pm_strides(x)
+    if st is None:
+        return _lib.SODA_CONV_TC  # will be made pixel-major by conv2d
+    if st[0] % 4 or st[1] % 4 or x.data_ptr() % 16:
+        return _lib.SODA_CONV_FP32
+    return _lib.SODA_CONV_TC
+
+
+def mark_exact(t: torch.Tensor) -> torch.Tensor:
+    """Tags a tensor whose values are exactly representable in TF32 (spikes, pooled spike counts)."""
+    t._soda_exact = True
+    return t
+
+
+def is_exact(t: torch.Tensor) -> bool:
+    return bool(getattr(t, "_soda_exact", False))
+
+
 def conv_out_hw(H: int, W: int, k: int, stride: int) -> Tuple[int, int]:
     pad = k // 2
     return (H + 2 * pad - k) // stride + 1, (W + 2 * pad - k) // stride + 1
@@ -229,7 +255,8 @@ def conv2d(
     Ho, Wo = conv_out_hw(H, W, pc.k, pc.stride)
     d = ConvDesc()
     d.N, d.H, d.W, d.Cin, d.Cout, d.k, d.stride, d.kind = N, H, W, Cin, pc.Cout, pc.k, pc.stride, pc.kind
-    if x.is_contiguous() and not (Cin == 1 or (H == 1 and W == 1)):
+    d.flags = _lib.SODA_CONV_FLAG_INPUT_EXACT_TF32 if is_exact(x) else 0
+    if pc.kind == _lib.SODA_CONV_FP32 and x.is_contiguous() and not (Cin == 1 or (H == 1 and W == 1)):
         d.in_nchw = 1  # plain NCHW frames (the binned events)
     else:
         x = to_pixel_major(x)
@@ -307,7 +334,7 @@ def lif_scan(
     _need_cuda(x, v0, i0)
     x, n = _flat_T(x, T)
     blk_shape = (x.shape[0] // T,) + tuple(x.shape[1:])
-    z = torch.empty_like(x)
+    z = mark_exact(torch.empty_like(x))
     v = torch.empty_like(x[: blk_shape[0]])
     i = torch.empty_like(v)
     if v0 is not None:
@@ -436,6 +463,8 @@ def pool2d(x: torch.Tensor, k: int, stride: int, mode: str, out: Optional[torch.
                             ops_, _stream()),
         "soda_pool2d_fwd",
     )
+    if mode in ("S", "M") and is_exact(x):
+        mark_exact(out)
     return out
 
 

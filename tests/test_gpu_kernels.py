@@ -225,29 +225,65 @@ CONV_CASES = [
 ]
 
 
-@pytest.mark.parametrize("case", CONV_CASES)
-def test_conv2d_against_fp64(case):
+def _conv_case(case, kind, exact_input=False):
     pkg = _pkg()
     N, Cin, H, W, Cout, k, s, nchw = case
     torch.manual_seed(Cin * 7 + Cout)
-    x = torch.randn(N, Cin, H, W)
+    x = torch.randint(0, 5, (N, Cin, H, W)).float() if exact_input else torch.randn(N, Cin, H, W)
     w = torch.randn(Cout, Cin, k, k) / (Cin * k * k) ** 0.5
     scale, shift = torch.rand(Cout) + 0.5, torch.randn(Cout)
     ref = F.conv2d(x.double(), (w * scale.view(-1, 1, 1, 1)).double(), stride=s, padding=k // 2) + shift.double().view(1, -1, 1, 1)
     xd = x.to(DEV) if nchw else x.to(DEV).contiguous(memory_format=torch.channels_last)
-    pc = pkg.ops.pack_conv(w.to(DEV), s, scale.to(DEV), shift.to(DEV))
+    if exact_input:
+        pkg.ops.mark_exact(xd)
+    pc = pkg.ops.pack_conv(w.to(DEV), s, scale.to(DEV), shift.to(DEV), kind=kind)
     y = pkg.ops.conv2d(xd, pc)
     assert y.shape == ref.shape
-    err = (y.cpu().double() - ref).abs().max() / ref.abs().max()
-    assert float(err) < 2e-6, float(err)
+    err = float((y.cpu().double() - ref).abs().max() / ref.abs().max())
     # residual + channel-slice destination
     res = torch.randn_like(ref).float()
     buf = torch.zeros(N, Cout + 16, *ref.shape[2:], device=DEV).contiguous(memory_format=torch.channels_last)
     out = buf[:, 8 : 8 + Cout]
     pkg.ops.conv2d(xd, pc, residual=res.to(DEV).contiguous(memory_format=torch.channels_last), out=out)
-    err = (out.cpu().double() - (ref + res.double())).abs().max() / ref.abs().max()
-    assert float(err) < 2e-6
+    err2 = float((out.cpu().double() - (ref + res.double())).abs().max() / ref.abs().max())
     assert float(buf[:, :8].abs().max()) == 0.0 and float(buf[:, 8 + Cout :].abs().max()) == 0.0
+    return max(err, err2)
+
+
+@pytest.mark.parametrize("case", CONV_CASES)
+def test_conv2d_fp32_pipe_against_fp64(case):
+    assert _conv_case(case, 0) < 2e-6
+
+
+TC_CASES = [c for c in CONV_CASES if c[1] % 32 == 0 and not c[7]] + [
+    (2, 64, 30, 38, 64, 3, 1, False),
+    (3, 32, 17, 23, 32, 1, 1, False),
+    (2, 96, 16, 16, 64, 1, 1, False),
+    (1, 128, 30, 38, 128, 3, 1, False),
+    (2, 64, 60, 76, 128, 3, 2, False),
+    (2, 384, 8, 10, 256, 1, 1, False),
+]
+
+
+@pytest.mark.parametrize("exact_input", [False, True])
+@pytest.mark.parametrize("case", TC_CASES)
+def test_conv2d_tcgen05_against_fp64(case, exact_input):
+    """3xTF32 split on the tensor pipe: fp32-level accuracy (bar: 1e-5 relative to the output scale)."""
+    err = _conv_case(case, 1, exact_input)
+    print(f"tcgen05 conv {case} exact_input={exact_input}: max rel err {err:.2e}")
+    assert err < 1e-5, err
+
+
+def test_conv2d_tcgen05_channel_slice_input():
+    """Input is a channel slice of a wider concat buffer (pix stride > Cin)."""
+    pkg = _pkg()
+    torch.manual_seed(0)
+    big = torch.randn(2, 96, 15, 19, device=DEV).contiguous(memory_format=torch.channels_last)
+    x = big[:, 32:64]
+    w = torch.randn(64, 32, 3, 3, device=DEV) * 0.1
+    ref = F.conv2d(x.double(), w.double(), padding=1)
+    y = pkg.ops.conv2d(x, pkg.ops.pack_conv(w, 1, kind=1))
+    assert float((y.double() - ref).abs().max() / ref.abs().max()) < 1e-5
 
 
 @pytest.mark.parametrize("mode", ["S", "A", "M"])
