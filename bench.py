@@ -261,7 +261,11 @@ def run_gpu_arm(args):
         step_device()
         torch.cuda.synchronize()
         pkg.ops.PROFILE = None
+        tags = prof.pop("conv2d_tags", [])
         fam = {k: sum(a.elapsed_time(b) for a, b in v) for k, v in prof.items()}
+        if args.per_layer:
+            for tag, (a, b) in zip(tags, prof.get("conv2d", [])):
+                sys.stderr.write(f"conv {a.elapsed_time(b):8.3f} ms  {tag}\n")
         n_conv = len(prof.get("conv2d", []))
         rate = float((g_cls.abs() > 0).float().mean())
 
@@ -323,6 +327,7 @@ def main():
     ap.add_argument("--batch", type=int, default=BATCH)
     ap.add_argument("--no-graph", action="store_true")
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--per-layer", action="store_true", help="print per-conv device times to stderr")
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3) if args.impl == "b200" else args.warmup
     if args.impl == "reference":

@@ -53,6 +53,8 @@ def block_forward(block, X, state=None, taps: Optional[dict] = None):
         Y = X
         for idx, (layer, is_state) in enumerate(zip(branch, flags)):
             name = _kind(layer)
+            if taps is not None and name != "BlockGen":
+                taps.setdefault(("in", id(layer)), []).append(Y)
             if name == "BlockGen":
                 Y, branch_state[idx] = block_forward(layer, Y, branch_state[idx], taps)
             elif name in ("LIFCell", "LICell", "StateStorage"):

@@ -14,14 +14,17 @@
 //   of pixels (box 32 x 128).
 // * B tiles (BN output channels x 32 input channels) come from the packed weights.
 // * Precision: fp32-level results from the TF32 tensor pipe by operand splitting.  The packed
-//   weights hold hi = tf32(w) and lo = w - hi; a transform warpgroup splits each A tile in shared
-//   memory the same way; D += A_hi*B_hi + A_lo*B_hi + A_hi*B_lo with fp32 accumulation in TMEM
+//   weights hold hi = tf32(w) and lo = w - hi; each A tile is split the same way; D += A_hi*B_hi + A_lo*B_hi + A_hi*B_lo with fp32 accumulation in TMEM
 //   ("3xTF32").  When the caller declares the input exactly representable in TF32 (spikes, pooled
 //   spike counts) the A split and the A_lo pass are skipped (2 passes).
+// * The A operand of the MMAs lives in TENSOR MEMORY (tcgen05.mma "TS" form): a transform
+//   warpgroup reads each fp32 A tile from shared memory once, splits it into tf32 hi / lo and
+//   writes both to TMEM with tcgen05.st.  The 12 MMAs of a K block then read A from TMEM and only
+//   B from shared memory, which keeps small-N layers (Cout 32/64) off the shared-memory roof.
 // * Persistent, warp-specialised: warp 0 = TMA producer, warp 1 = MMA issuer (single thread) and
-//   TMEM owner, warps 2-5 = A-split transform, warps 6-9 = epilogue (tcgen05.ld -> +shift
-//   -> +residual -> global store).  Two TMEM accumulator stages let the epilogue of tile i overlap
-//   the main loop of tile i+1.
+//   TMEM owner, warps 2-5 = A split -> TMEM, warps 6-9 = epilogue (tcgen05.ld -> +shift
+//   -> +residual -> global store).  For BN <= 64 two TMEM accumulator stages let the epilogue of
+//   tile i overlap the main loop of tile i+1.
 #include "common.cuh"
 #include "tc_common.cuh"
 
@@ -52,25 +55,30 @@ struct TcParams {
 template <int BN>
 struct TcSmem {
   static constexpr int B_BYTES = BN * TC_BK * 4;
-  static constexpr int STAGE_BYTES = 2 * TC_A_BYTES + 2 * B_BYTES;  // A, A_lo, B_hi, B_lo
-  static constexpr int STAGES = (200 * 1024) / STAGE_BYTES > 6 ? 6 : (200 * 1024) / STAGE_BYTES;
+  static constexpr int STAGE_BYTES = TC_A_BYTES + 2 * B_BYTES;  // A (fp32), B_hi, B_lo
+  static constexpr int STAGES = 4;                              // = A-operand stages in TMEM
   static constexpr int BYTES = STAGES * STAGE_BYTES + 1024 /*align*/ + 256 /*barriers*/;
 };
+
+// TMEM map (512 columns): [0,256) accumulators, [256,512) A operand, 4 stages x (hi 32 | lo 32).
+// Accumulator stage a: main at a*2*BN, correction at a*2*BN + BN.  BN=128 -> one stage.
+constexpr uint32_t TC_TMEM_COLS = 512;
+constexpr uint32_t TC_TMEM_A0 = 256;
 
 template <int BN>
 __global__ void __launch_bounds__(TC_THREADS, 1)
 conv_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB, TcParams p) {
   using S = TcSmem<BN>;
   constexpr int STAGES = S::STAGES;
-  constexpr uint32_t TMEM_COLS = 2 * BN < 32 ? 32 : 2 * BN;
+  constexpr int ACC_STAGES = BN == 128 ? 1 : 2;
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
   uint64_t* bars = reinterpret_cast<uint64_t*>(smem + STAGES * S::STAGE_BYTES);
-  uint64_t* full_bar = bars;                 // TMA bytes landed            [STAGES]
-  uint64_t* ready_bar = bars + STAGES;       // A split done (transform)    [STAGES]
-  uint64_t* empty_bar = bars + 2 * STAGES;   // MMAs reading the stage done [STAGES]
-  uint64_t* acc_full = bars + 3 * STAGES;    // accumulator complete        [2]
-  uint64_t* acc_empty = bars + 3 * STAGES + 2;  // accumulator drained      [2]
+  uint64_t* full_bar = bars;                 // TMA bytes landed                  [STAGES]
+  uint64_t* ready_bar = bars + STAGES;       // A split written to TMEM           [STAGES]
+  uint64_t* empty_bar = bars + 2 * STAGES;   // MMAs reading the stage completed  [STAGES]
+  uint64_t* acc_full = bars + 3 * STAGES;    // accumulator complete              [2]
+  uint64_t* acc_empty = bars + 3 * STAGES + 2;  // accumulator drained            [2]
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 3 * STAGES + 4);
 
   const int warp = threadIdx.x >> 5;
@@ -92,16 +100,15 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
     }
     fence_barrier_init();
   }
-  if (warp == 1) tmem_alloc(tmem_slot, TMEM_COLS);
+  if (warp == 1) tmem_alloc(tmem_slot, TC_TMEM_COLS);
   tc_fence_before();
   __syncthreads();
   tc_fence_after();
   const uint32_t tmem_base = *tmem_slot;
 
   auto stage_a = [&](int s) { return smem + s * S::STAGE_BYTES; };
-  auto stage_alo = [&](int s) { return smem + s * S::STAGE_BYTES + TC_A_BYTES; };
-  auto stage_bhi = [&](int s) { return smem + s * S::STAGE_BYTES + 2 * TC_A_BYTES; };
-  auto stage_blo = [&](int s) { return smem + s * S::STAGE_BYTES + 2 * TC_A_BYTES + S::B_BYTES; };
+  auto stage_bhi = [&](int s) { return smem + s * S::STAGE_BYTES + TC_A_BYTES; };
+  auto stage_blo = [&](int s) { return smem + s * S::STAGE_BYTES + TC_A_BYTES + S::B_BYTES; };
 
   if (warp == 0) {
     // ================================ TMA producer ============================================
@@ -142,26 +149,29 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
       uint32_t ph = 0;
       int local = 0;
       for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x, ++local) {
-        const int acc = local & 1;
-        const uint32_t acc_ph = (local >> 1) & 1;
+        const int acc = local % ACC_STAGES;
+        const uint32_t acc_ph = (local / ACC_STAGES) & 1;
         mbar_wait(&acc_empty[acc], acc_ph ^ 1);
         tc_fence_after();
-        const uint32_t d_tmem = tmem_base + acc * BN;
+        const uint32_t d_main = tmem_base + acc * 2 * BN;  // sum of A_hi*B_hi
+        const uint32_t d_corr = d_main + BN;               // sum of the 2^-11-sized split terms
         for (int kb = 0; kb < kblocks; ++kb) {
-          mbar_wait(&full_bar[s], ph);                     // B (and A) bytes landed
-          if (!p.a_exact) mbar_wait(&ready_bar[s], ph);   // A split written
+          mbar_wait(&full_bar[s], ph);    // B tiles landed
+          mbar_wait(&ready_bar[s], ph);   // A_hi / A_lo written to TMEM
           tc_fence_after();
-          const uint64_t a_hi = smem_desc_sw128(smem_u32(stage_a(s)));
-          const uint64_t a_lo = smem_desc_sw128(smem_u32(stage_alo(s)));
+          const uint32_t a_hi = tmem_base + TC_TMEM_A0 + s * 64;
+          const uint32_t a_lo = a_hi + 32;
           const uint64_t b_hi = smem_desc_sw128(smem_u32(stage_bhi(s)));
           const uint64_t b_lo = smem_desc_sw128(smem_u32(stage_blo(s)));
 #pragma unroll
           for (int kk = 0; kk < TC_BK / 8; ++kk) {
             const uint64_t adv = (uint64_t)((kk * 32) >> 4);  // 8 tf32 = 32 B along K inside the 128 B row
-            // small terms first, the hi*hi term last
-            mma_tf32_ss(d_tmem, a_hi + adv, b_lo + adv, idesc, (kb | kk) != 0);
-            if (!p.a_exact) mma_tf32_ss(d_tmem, a_lo + adv, b_hi + adv, idesc, 1);
-            mma_tf32_ss(d_tmem, a_hi + adv, b_hi + adv, idesc, 1);
+            // The tensor pipe truncates the fp32 accumulator on every accumulation, so the error
+            // grows with (#MMAs into an accumulator) x ulp(|accumulator|): the small split terms
+            // get their own accumulator and are added to the main one once, in the epilogue.
+            mma_tf32_ts(d_corr, a_hi + kk * 8, b_lo + adv, idesc, (kb | kk) != 0);
+            if (!p.a_exact) mma_tf32_ts(d_corr, a_lo + kk * 8, b_hi + adv, idesc, 1);
+            mma_tf32_ts(d_main, a_hi + kk * 8, b_hi + adv, idesc, (kb | kk) != 0);
           }
           mma_commit(&empty_bar[s]);
           if (kb == kblocks - 1) mma_commit(&acc_full[acc]);
@@ -170,33 +180,37 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
       }
     }
   } else if (warp < 6) {
-    // ================================ A split (transform) =====================================
-    if (!p.a_exact) {
-      const int t = threadIdx.x - 64;  // 0..127
-      int s = 0;
-      uint32_t ph = 0;
-      for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
-        for (int kb = 0; kb < kblocks; ++kb) {
-          mbar_wait(&full_bar[s], ph);
-          float4* a = reinterpret_cast<float4*>(stage_a(s));
-          float4* alo = reinterpret_cast<float4*>(stage_alo(s));
+    // ============== A operand: shared memory (fp32) -> tf32 hi / lo split -> tensor memory =======
+    const int q = warp & 3;            // TMEM lane quarter this warp may access
+    const int row = q * 32 + lane;     // tile row = TMEM lane
+    int s = 0;
+    uint32_t ph = 0;
+    for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
+      for (int kb = 0; kb < kblocks; ++kb) {
+        mbar_wait(&full_bar[s], ph);
+        const uint8_t* arow = stage_a(s) + row * 128;
+        uint32_t hi[32], lo[32];
 #pragma unroll
-          for (int j = 0; j < TC_A_BYTES / 16 / 128; ++j) {
-            const int idx = j * 128 + t;
-            const float4 v = a[idx];
-            float4 hi, lo;
-            hi.x = __uint_as_float(__float_as_uint(v.x) & 0xFFFFE000u);
-            hi.y = __uint_as_float(__float_as_uint(v.y) & 0xFFFFE000u);
-            hi.z = __uint_as_float(__float_as_uint(v.z) & 0xFFFFE000u);
-            hi.w = __uint_as_float(__float_as_uint(v.w) & 0xFFFFE000u);
-            lo.x = v.x - hi.x, lo.y = v.y - hi.y, lo.z = v.z - hi.z, lo.w = v.w - hi.w;
-            a[idx] = hi;
-            alo[idx] = lo;
+        for (int c = 0; c < 8; ++c) {
+          // SWIZZLE_128B: 16-byte chunk c of row r lives at chunk position c ^ (r & 7)
+          const float4 v = *reinterpret_cast<const float4*>(arow + ((c ^ (row & 7)) << 4));
+          const float f[4] = {v.x, v.y, v.z, v.w};
+#pragma unroll
+          for (int e = 0; e < 4; ++e) {
+            const uint32_t h = __float_as_uint(f[e]) & 0xFFFFE000u;
+            hi[c * 4 + e] = h;
+            lo[c * 4 + e] = __float_as_uint(f[e] - __uint_as_float(h));
           }
-          fence_proxy_async_smem();
-          mbar_arrive(&ready_bar[s]);
-          if (++s == STAGES) s = 0, ph ^= 1;
         }
+        // stage s of the previous round has been consumed: the producer only refilled the shared
+        // memory stage after the MMAs reading TMEM stage s committed (empty_bar)
+        const uint32_t t_a = tmem_base + ((uint32_t)(q * 32) << 16) + TC_TMEM_A0 + s * 64;
+        tmem_st_32x32(t_a, hi);
+        if (!p.a_exact) tmem_st_32x32(t_a + 32, lo);
+        tmem_st_wait();
+        tc_fence_before();
+        mbar_arrive(&ready_bar[s]);
+        if (++s == STAGES) s = 0, ph ^= 1;
       }
     }
   } else {
@@ -205,8 +219,8 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
     const int row = q * 32 + lane;
     int local = 0;
     for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x, ++local) {
-      const int acc = local & 1;
-      const uint32_t acc_ph = (local >> 1) & 1;
+      const int acc = local % ACC_STAGES;
+      const uint32_t acc_ph = (local / ACC_STAGES) & 1;
       const int nt = tile % p.num_n_tiles;
       const int mt = tile / p.num_n_tiles;
       // output pixel of this thread
@@ -232,12 +246,20 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
       }
       mbar_wait(&acc_full[acc], acc_ph);
       tc_fence_after();
-      const uint32_t t_row = tmem_base + ((uint32_t)(q * 32) << 16) + acc * BN;
+      const uint32_t t_row = tmem_base + ((uint32_t)(q * 32) << 16) + acc * 2 * BN;
 #pragma unroll 1
       for (int c0 = 0; c0 < BN; c0 += 32) {
-        uint32_t r[32];
+        uint32_t r[32], rc[32];
         tmem_ld_32x32(t_row + c0, r);
+        tmem_ld_32x32(t_row + BN + c0, rc);
         tmem_ld_wait();
+        if (c0 + 32 >= BN) {
+          // last TMEM read of this tile: hand the accumulator back before the global stores
+          tc_fence_before();
+          mbar_arrive(&acc_empty[acc]);
+        }
+#pragma unroll
+        for (int j = 0; j < 32; ++j) r[j] = __float_as_uint(__uint_as_float(r[j]) + __uint_as_float(rc[j]));
         const int co0 = nt * BN + c0;
         if (valid && co0 < p.Cout) {
           float* dst = p.y + out_off + co0;
@@ -274,8 +296,6 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
           }
         }
       }
-      tc_fence_before();
-      mbar_arrive(&acc_empty[acc]);
     }
   }
 
@@ -283,10 +303,9 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
   __syncthreads();
   if (warp == 1) {
     tc_fence_after();
-    tmem_dealloc(tmem_base, TMEM_COLS);
+    tmem_dealloc(tmem_base, TC_TMEM_COLS);
   }
 }
-
 
 // ------------------------------------------------------------------------------------------------
 // host side: weight packing, tensor maps, dispatch

@@ -55,6 +55,10 @@ def _prof(name):
             r = fn(*a, **k)
             e1.record()
             PROFILE.setdefault(name, []).append((e0, e1))
+            if name == "conv2d":
+                x, pc = a[0], a[1]
+                PROFILE.setdefault("conv2d_tags", []).append(
+                    f"{tuple(x.shape)}->{pc.Cout} k{pc.k} s{pc.stride} kind{pc.kind} exact{int(is_exact(x))}")
             return r
 
         wrapped.__name__, wrapped.__doc__ = fn.__name__, fn.__doc__
