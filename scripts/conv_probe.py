@@ -1,0 +1,82 @@
+"""Times single convolution shapes of the TinyYolo GEN1 forward through the C ABI (CUDA events,
+rotating input buffers so every launch misses L2) and checks each against an fp64 reference.
+
+  python scripts/conv_probe.py                 # the default shape list
+  python scripts/conv_probe.py 160,32,120,152,32,3,1[,exact] ...
+"""
+import os
+import sys
+
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+import torch
+import torch.nn.functional as F
+
+import snn_for_object_detection_b200 as pkg
+from snn_for_object_detection_b200 import _lib, ops
+
+DEFAULT = [
+    "160,32,120,152,32,3,1",
+    "160,64,60,76,64,3,1",
+    "160,128,30,38,128,3,1",
+    "160,64,120,152,128,3,2",
+    "160,128,60,76,256,3,2",
+    "160,128,120,152,64,1,1",
+    "160,64,120,152,64,1,1,exact",
+    "160,320,60,76,128,1,1",
+    "160,768,30,38,256,1,1",
+]
+
+
+def run(spec, iters=10, check=True):
+    parts = spec.split(",")
+    N, Cin, H, W, Cout, k, s = map(int, parts[:7])
+    exact = len(parts) > 7 and parts[7] == "exact"
+    dev = "cuda"
+    g = torch.Generator(device=dev).manual_seed(1)
+    nbuf = max(2, int(400e6 // (N * Cin * H * W * 4)) + 1)
+    nbuf = min(nbuf, 6)
+    xs = []
+    for _ in range(nbuf):
+        x = torch.randn(N, Cin, H, W, device=dev, generator=g)
+        if exact:
+            x = (x > 1.0).float()
+        x = x.contiguous(memory_format=torch.channels_last)
+        if exact:
+            ops.mark_exact(x)
+        xs.append(x)
+    w = torch.randn(Cout, Cin, k, k, device=dev, generator=g) / (Cin * k * k) ** 0.5
+    kind = ops.conv_kind_for(xs[0], Cin, k, s)
+    pc = ops.pack_conv(w, s, None, None, kind)
+    Ho, Wo = ops.conv_out_hw(H, W, k, s)
+    out = ops.empty_pixel_major(N, Cout, Ho, Wo, dev)
+    for i in range(3):
+        ops.conv2d(xs[i % nbuf], pc, out=out)
+    torch.cuda.synchronize()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for i in range(iters):
+        ops.conv2d(xs[i % nbuf], pc, out=out)
+    e1.record()
+    torch.cuda.synchronize()
+    ms = e0.elapsed_time(e1) / iters
+    flops = 2.0 * N * Ho * Wo * Cout * Cin * k * k
+    byts = 4.0 * (N * Cin * H * W + N * Cout * Ho * Wo)
+    err = float("nan")
+    if check:
+        nchk = min(N, 2)
+        ops.conv2d(xs[0], pc, out=out)
+        ref = F.conv2d(xs[0][:nchk].double(), w.double(), padding=k // 2, stride=s)
+        err = float((out[:nchk].double() - ref).abs().max() / ref.abs().max())
+    print(f"{spec:38s} kind{kind} {ms:8.4f} ms  {flops / ms / 1e9:8.1f} TFLOP/s  {byts / ms / 1e6:8.1f} GB/s  relerr {err:.2e}",
+          flush=True)
+
+
+if __name__ == "__main__":
+    specs = [a for a in sys.argv[1:] if not a.startswith("--")] or DEFAULT
+    iters = 10
+    for a in sys.argv[1:]:
+        if a.startswith("--iters="):
+            iters = int(a.split("=")[1])
+    with torch.no_grad():
+        for sp in specs:
+            run(sp, iters=iters, check="--nocheck" not in sys.argv)

@@ -9,43 +9,11 @@
 // neuron-step the forward moves 4 B in + 4 B out (+4 B per optional trace).  The time loop is
 // unrolled so that kUnroll independent 16-byte loads are in flight per thread.
 #include "common.cuh"
+#include "neuron.cuh"
 
 namespace soda {
 
 constexpr int kUnroll = 4;
-
-struct NP {
-  float a, s, v_leak, v_th, v_reset, alpha;
-  int jump_first, detach_reset;
-};
-
-__device__ __forceinline__ void lif_step(const NP& p, float x, float& v, float& i, float& z,
-                                         float& v_dec) {
-  float i_src;
-  if (p.jump_first) {
-    i_src = __fadd_rn(i, x);  // i_new = i + x
-  } else {
-    i_src = i;
-  }
-  const float dv = __fmul_rn(p.a, __fadd_rn(__fsub_rn(p.v_leak, v), i_src));
-  v_dec = __fadd_rn(v, dv);
-  const float di = __fmul_rn(-p.s, i_src);
-  float i_dec = __fadd_rn(i_src, di);
-  if (!p.jump_first) i_dec = __fadd_rn(i_dec, x);
-  z = (__fsub_rn(v_dec, p.v_th) > 0.0f) ? 1.0f : 0.0f;
-  v = __fadd_rn(__fmul_rn(__fsub_rn(1.0f, z), v_dec), __fmul_rn(z, p.v_reset));
-  i = i_dec;
-}
-
-__device__ __forceinline__ void li_step(const NP& p, float x, float& v, float& i) {
-  const float i_src = p.jump_first ? __fadd_rn(i, x) : i;
-  const float dv = __fmul_rn(p.a, __fadd_rn(__fsub_rn(p.v_leak, v), i_src));
-  v = __fadd_rn(v, dv);
-  const float di = __fmul_rn(-p.s, i_src);
-  float i_dec = __fadd_rn(i_src, di);
-  if (!p.jump_first) i_dec = __fadd_rn(i_dec, x);
-  i = i_dec;
-}
 
 template <int V>
 struct Vec;
@@ -217,14 +185,6 @@ neuron_bwd_kernel(NP p, const float* __restrict__ gout, const float* __restrict_
   }
   if (gv0 != nullptr) vstore<V>(gv0 + e, gv);
   if (gi0 != nullptr) vstore<V>(gi0 + e, gi);
-}
-
-static NP to_np(const soda_neuron_params_t* q) {
-  NP p;
-  p.a = q->dt_tau_mem, p.s = q->dt_tau_syn, p.v_leak = q->v_leak, p.v_th = q->v_th;
-  p.v_reset = q->v_reset, p.alpha = q->alpha, p.jump_first = q->jump_first;
-  p.detach_reset = q->detach_reset;
-  return p;
 }
 
 static bool all_aligned16(std::initializer_list<const void*> ptrs) {
