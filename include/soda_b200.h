@@ -42,6 +42,8 @@ typedef enum {
 
 #define SODA_ABI_VERSION 1
 
+struct soda_neuron_params_s; /* defined below (LIF / LI section) */
+
 SODA_API int soda_abi_version(void);
 SODA_API const char* soda_last_error(void);
 /* Number of kernels launched by this library in this process (all threads). */
@@ -90,8 +92,9 @@ SODA_API int soda_bin_events(const void* events, const int64_t* sample_offsets, 
  *       soda_conv_packed_elems() floats owned by the caller.
  *   soda_conv2d_fwd        : consumes the packed buffer.
  *   kind: SODA_CONV_FP32 = FP32-pipe implicit GEMM, fp32-exact products (any shape);
- *         SODA_CONV_TC   = TMA-fed tcgen05/TMEM implicit GEMM, 3xTF32 split (fp32-level
- *                          accuracy); needs Cin % 32 == 0 and pixel-major input.
+ *         SODA_CONV_TC   = TMA-fed tcgen05/TMEM implicit GEMM, tf32 main pass + bf16 correction
+ *                          pass on split operands (fp32-level accuracy); needs Cin % 32 == 0 and
+ *                          pixel-major input.
  *   shift, residual : may be NULL.
  *   in_nchw: 1 = input is plain NCHW-contiguous [N,Cin,H,W] (the event frames); strides ignored
  * ------------------------------------------------------------------------------------------- */
@@ -120,6 +123,24 @@ SODA_API int soda_conv2d_fwd(const soda_conv_desc_t* d, const float* x, const fl
                     const float* shift, const float* residual, float* y, void* stream);
 
 /* ---------------------------------------------------------------------------------------------
+ * Fused Conv -> BatchNorm(eval) -> LIF over T time steps (K1 + K2 + K3 + K6 in one kernel)
+ *   replaces: the Conv / Norm / LIF triple emitted by models/tiny_yolo.py:53-58 (_conv) as executed
+ *             once per time step by models/generator.py:184-198, including the Residual sum with
+ *             the Pass branch of a bottleneck (models/tiny_yolo.py:60-65, generator.py:146).
+ *   x        : [T*B, H, W, Cin] pixel-major, time-major frames (frame t*B + b); d->N = T*B
+ *   y        : spikes {0,1} (+ residual), same frame order, written through out strides
+ *   v0, i0   : [B, Ho, Wo, Cout] dense pixel-major incoming state, or both NULL (v = v_leak, i = 0)
+ *   v_out, i_out : state after step T-1, same layout (never NULL)
+ *   The work item of the kernel is (sample, pixel tile, channel chunk) and t runs inside it, so the
+ *   membrane state lives in registers for all T steps.  LIF arithmetic is op-for-op soda_lif_fwd's.
+ *   Needs d->kind == SODA_CONV_TC and Cout % 16 == 0.
+ * ------------------------------------------------------------------------------------------- */
+SODA_API int soda_conv_lif_fwd(const soda_conv_desc_t* d, const float* x, const float* packed,
+                      const float* shift, const float* residual, int T,
+                      const struct soda_neuron_params_s* np, const float* v0, const float* i0,
+                      float* y, float* v_out, float* i_out, void* stream);
+
+/* ---------------------------------------------------------------------------------------------
  * LIF / LI scans over T time steps (K3, K4)
  *   replaces: models/modules/layer_gen.py:233 norse.torch.LIFCell() and :253 LICell() (norse
  *             1.1.0, third-party, restated in oracle/norse_restated.py), called once per time
@@ -134,7 +155,7 @@ SODA_API int soda_conv2d_fwd(const soda_conv_desc_t* d, const float* x, const fl
  *   Arithmetic is op-for-op that of the restatement (no FMA contraction), so results are
  *   bit-identical to it for identical inputs.  jump_first: 1 = norse 1.1.0 order (default).
  * ------------------------------------------------------------------------------------------- */
-typedef struct {
+typedef struct soda_neuron_params_s {
   float dt_tau_mem; /* fp32(dt) * fp32(tau_mem_inv) = 0.1f  */
   float dt_tau_syn; /* fp32(dt) * fp32(tau_syn_inv) = 0.2f  */
   float v_leak, v_th, v_reset;

@@ -71,6 +71,37 @@ def run(spec, iters=10, check=True):
           flush=True)
 
 
+def run_lif(spec, T=8, iters=5):
+    """Fused conv+LIF vs conv2d followed by the stand-alone scan (same kernels' arithmetic)."""
+    parts = spec.split(",")
+    N, Cin, H, W, Cout, k, s = map(int, parts[:7])
+    res = len(parts) > 7 and parts[7] == "res"
+    dev = "cuda"
+    g = torch.Generator(device=dev).manual_seed(2)
+    x = (torch.randn(N, Cin, H, W, device=dev, generator=g) * 0.8).contiguous(memory_format=torch.channels_last)
+    w = torch.randn(Cout, Cin, k, k, device=dev, generator=g) / (Cin * k * k) ** 0.5
+    shift = torch.randn(Cout, device=dev, generator=g) * 0.1
+    pc = ops.pack_conv(w, s, None, shift, _lib.SODA_CONV_TC)
+    B = N // T
+    y0 = ops.conv2d(x, pc)
+    z0, v0, i0, _, _, _ = ops.lif_scan(y0, T)
+    if res:
+        z0 = z0 + x
+    z1, v1, i1 = ops.conv_lif(x, pc, T, ops.LIF_DEFAULT, residual=x if res else None)
+    torch.cuda.synchronize()
+    mism = float((z0 != z1).float().mean())
+    dv = float((v0 - v1).abs().max())
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for _ in range(iters):
+        ops.conv_lif(x, pc, T, ops.LIF_DEFAULT, residual=x if res else None)
+    e1.record()
+    torch.cuda.synchronize()
+    ms = e0.elapsed_time(e1) / iters
+    print(f"LIF {spec:34s} T={T} B={B} {ms:8.4f} ms  rate {float(z1.mean() if not res else (z1 - x).mean()):.3f} "
+          f"mismatch {mism:.2e} dv {dv:.2e}", flush=True)
+
+
 if __name__ == "__main__":
     specs = [a for a in sys.argv[1:] if not a.startswith("--")] or DEFAULT
     iters = 10
@@ -79,4 +110,8 @@ if __name__ == "__main__":
             iters = int(a.split("=")[1])
     with torch.no_grad():
         for sp in specs:
-            run(sp, iters=iters, check="--nocheck" not in sys.argv)
+            if sp.startswith("lif:"):
+                run_lif(sp[4:])
+            else:
+                run(sp, iters=iters, check="--nocheck" not in sys.argv)
+

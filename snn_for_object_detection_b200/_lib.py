@@ -69,6 +69,8 @@ SIGNATURES = {
     "soda_conv_pack_weights": (_i, [_vp, _vp, _i, _i, _i, _i, _vp, _vp]),
     "soda_conv_tc_supported": (_i, [C.POINTER(ConvDesc), _vp]),
     "soda_conv2d_fwd": (_i, [C.POINTER(ConvDesc), _vp, _vp, _vp, _vp, _vp, _vp]),
+    "soda_conv_lif_fwd": (_i, [C.POINTER(ConvDesc), _vp, _vp, _vp, _vp, _i, C.POINTER(NeuronParams), _vp, _vp, _vp,
+                                _vp, _vp, _vp]),
     "soda_lif_fwd": (_i, [C.POINTER(NeuronParams), _vp, _vp, _vp, _i, _i64, _vp, _vp, _vp, _vp, _vp, _vp, _vp]),
     "soda_li_fwd": (_i, [C.POINTER(NeuronParams), _vp, _vp, _vp, _i, _i64, _i, _vp, _vp, _vp, _vp, _vp]),
     "soda_lif_bwd": (_i, [C.POINTER(NeuronParams), _vp, _vp, _vp, _vp, _i, _i64, _vp, _vp, _vp, _vp]),

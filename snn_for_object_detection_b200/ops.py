@@ -27,6 +27,7 @@ __all__ = [
     "PackedConv",
     "pack_conv",
     "conv2d",
+    "conv_lif",
     "lif_scan",
     "li_scan",
     "lif_scan_bwd",
@@ -42,7 +43,7 @@ __all__ = [
 # When set to a dict, every op records a (start, end) CUDA-event pair on the launching stream under
 # its family name: bench.py uses it for the per-kernel-family device time of one eager step.
 PROFILE = None
-CONV_KERNEL_NAME = "conv_tc_kernel (tcgen05 3xTF32) + conv_ffma_kernel (Cin % 32 != 0)"
+CONV_KERNEL_NAME = "conv_tc2_kernel (tcgen05: tf32 main + bf16 correction pass) + conv_ffma_kernel (Cin % 32 != 0)"
 
 
 def _prof(name):
@@ -285,6 +286,70 @@ def conv2d(
         "soda_conv2d_fwd",
     )
     return out
+
+
+def conv_lif_supported(x: torch.Tensor, pc: "PackedConv") -> bool:
+    """The fused Conv->BN->LIF kernel takes tensor-core convolutions with Cout % 16 == 0."""
+    return pc.kind == _lib.SODA_CONV_TC and pc.Cout % 16 == 0 and os.environ.get("SODA_FUSE_LIF", "1") != "0"
+
+
+@_prof("conv_lif")
+def conv_lif(
+    x: torch.Tensor,
+    pc: "PackedConv",
+    T: int,
+    p: "NeuronConst",
+    v0: Optional[torch.Tensor] = None,
+    i0: Optional[torch.Tensor] = None,
+    residual: Optional[torch.Tensor] = None,
+    out: Optional[torch.Tensor] = None,
+):
+    """Fused ``LIF_T(conv(x, W*scale) + shift) (+ residual)`` over ``x [T*B, Cin, H, W]``.
+
+    Returns ``(y, v_T, i_T)``; the membrane state never leaves the SM between time steps.
+    Reference: the Conv / Norm / LIF triple of models/tiny_yolo.py:53-58 run T times by
+    models/generator.py:184-198 (+ the Residual sum of :146).
+    """
+    _need_cuda(x, v0, i0, residual, out)
+    N, Cin, H, W = x.shape
+    if N % T:
+        raise ValueError("conv_lif: leading dimension is not a multiple of T")
+    B = N // T
+    Ho, Wo = conv_out_hw(H, W, pc.k, pc.stride)
+    d = ConvDesc()
+    d.N, d.H, d.W, d.Cin, d.Cout, d.k, d.stride, d.kind = N, H, W, Cin, pc.Cout, pc.k, pc.stride, pc.kind
+    d.flags = _lib.SODA_CONV_FLAG_INPUT_EXACT_TF32 if is_exact(x) else 0
+    x = to_pixel_major(x)
+    d.in_nchw = 0
+    d.in_batch_stride, d.in_pix_stride = _pm_strides(x)
+    if out is None:
+        out = empty_pixel_major(N, pc.Cout, Ho, Wo, x.device)
+    elif out.shape != (N, pc.Cout, Ho, Wo):
+        raise ValueError(f"conv_lif: out has shape {tuple(out.shape)}, expected {(N, pc.Cout, Ho, Wo)}")
+    os_ = _pm_strides(out)
+    if os_ is None:
+        raise ValueError("conv_lif: out must be pixel-major (channels_last) addressable")
+    d.out_batch_stride, d.out_pix_stride = os_
+    if residual is not None:
+        if residual.shape != out.shape:
+            raise ValueError("conv_lif: residual shape mismatch")
+        residual = to_pixel_major(residual)
+        d.res_batch_stride, d.res_pix_stride = _pm_strides(residual)
+    v = empty_pixel_major(B, pc.Cout, Ho, Wo, x.device)
+    i = torch.empty_like(v)
+    if v0 is not None:
+        v0 = _like_block(v0, v)
+        i0 = _like_block(i0, v)
+    npar = p.c()
+    check(
+        lib.soda_conv_lif_fwd(C.byref(d), x.data_ptr(), pc.packed.data_ptr(), _ptr(pc.shift), _ptr(residual), T,
+                              C.byref(npar), _ptr(v0), _ptr(i0), out.data_ptr(), v.data_ptr(), i.data_ptr(),
+                              _stream()),
+        "soda_conv_lif_fwd",
+    )
+    if residual is None:
+        mark_exact(out)
+    return out, v, i
 
 
 # --------------------------------------------------------------------------------------------
