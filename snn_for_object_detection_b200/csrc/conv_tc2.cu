@@ -33,8 +33,9 @@
 //   the epilogue warps' registers for all T steps and never touch HBM; spikes (+ the Residual's Pass
 //   branch) are what is stored.
 //
-// Persistent, warp-specialised, 20 warps: w0 A producer (TMA), w1 MMA issuer + TMEM owner, w2 B producer
-// (TMA), w3 idle, w4-11 transform, w12-19 epilogue.
+// Persistent, warp-specialised, 20 warps: w0-7 transform, w8-15 epilogue, w16 A producer (TMA), w17 main-pass
+// MMA issuer + TMEM owner, w18 B producer (TMA), w19 correction-pass MMA issuer.
+#include <stdlib.h>
 #include <string.h>
 
 #include <algorithm>
@@ -53,6 +54,8 @@ constexpr int T2_THREADS = 640;
 constexpr int T2_TA_STAGES = 4;          // A-operand stages in tensor memory, 64 columns each
 constexpr uint32_t T2_TMEM_COLS = 512;
 constexpr uint32_t T2_TMEM_A0 = 256;
+constexpr int T2_W_PROD_A = 16, T2_W_MMA_MAIN = 17, T2_W_PROD_B = 18, T2_W_MMA_CORR = 19;  // highest warp ids:
+// the SM's issue arbiter favours them, and these four single-instruction-stream roles pace everyone else
 constexpr int T2_MAX_RING = 8;           // max stages of the A / B shared-memory rings
 constexpr int T2_SMEM_LIMIT = 232448 - 1024 /*alignment slack*/ - 512 /*barriers*/;
 
@@ -64,6 +67,9 @@ struct Tc2Params {
   int mode;                      // 0 = HALO (one A stage per 32-channel slab, `taps` k-blocks), 1 = TAP
   int flat;                      // 1x1 stride-1 over the flattened pixel list
   int a_exact;
+  int presplit;                  // HALO 3x3: split each halo slab once in shared memory, taps only copy
+  int halo_rows;                 // pixels in one halo slab
+  uint32_t a_lb_off;             // offset of the bf16(lo) rows inside an A stage (presplit)
   int nch;                       // output-channel chunks of BN
   int n_outer, T_inner, Bsz;     // work items = nch * n_spatial * n_outer, each walks T_inner frames
   int n_items;
@@ -75,6 +81,8 @@ struct Tc2Params {
   const float* shift;
   const float* residual;
   float* y;
+  long long* dbg_out;            // per-role wait-cycle counters of CTA 0 (debug)
+  int dbg;                       // SODA_TC2_DBG timing experiments (results are garbage when set)
   int lif;
   NP np;
   const float* v0;
@@ -82,6 +90,18 @@ struct Tc2Params {
   float* v_out;
   float* i_out;
 };
+
+// debug timing: accumulate the clocks a role spends inside a wait
+#define T2_TIMED(slot, stmt)                           \
+  do {                                                 \
+    if (p.dbg_out != nullptr) {                        \
+      const long long _t0 = clock64();                 \
+      stmt;                                            \
+      dbg_acc[slot] += clock64() - _t0;                \
+    } else {                                           \
+      stmt;                                            \
+    }                                                  \
+  } while (0)
 
 struct Tc2Item {
   int chunk, sp, outer;
@@ -93,6 +113,84 @@ __device__ __forceinline__ Tc2Item tc2_item(const Tc2Params& p, int item) {
   it.sp = r % p.n_spatial;
   it.outer = r / p.n_spatial;
   return it;
+}
+
+// ================================ MMA issuers ===================================================
+// Two issuing warps, one per accumulator: one issues the tf32 main pass, the other the bf16 correction
+// pass.  The two streams never touch the same accumulator, so they need no ordering between them.  What
+// bounds small-N tiles is not the tensor pipe (N/2 clocks per MMA, measured) but the instructions the
+// issuing warp spends per k-block (barrier wait, descriptor arithmetic, commits), so this loop is kept
+// warp-uniform, specialised at compile time, and split over the two warps.
+template <int BN, bool CORR>
+__device__ __forceinline__ void tc2_mma_role(const Tc2Params& p, uint32_t tmem_base, uint32_t smem_b_u32,
+                                             uint64_t* ta_ready, uint64_t* ta_empty, uint64_t* b_full,
+                                             uint64_t* b_empty, uint64_t* acc_full, uint64_t* acc_empty) {
+  constexpr uint32_t B_TILE = BN * 128, B_STAGE = 2 * B_TILE;
+  constexpr int ACC_STAGES = BN == 128 ? 1 : 2;
+  constexpr uint32_t ACC_STRIDE = BN == 128 ? 256 : 128;
+  constexpr uint32_t idesc = CORR ? idesc_bf16(T2_BM, BN) : idesc_tf32(T2_BM, BN);
+  const uint32_t a_col0 = tmem_base + T2_TMEM_A0 + (CORR ? 32u : 0u);
+  const uint64_t desc0 = smem_desc_sw128(smem_b_u32 + (CORR ? B_TILE : 0u));  // + (bytes >> 4) moves the start address
+  const bool half = CORR && p.a_exact;   // exact inputs have no lo(a) half
+  const bool stat = p.b_stationary != 0;
+  const int n_o = p.mode == 0 ? p.cblocks : p.taps;
+  const int n_i = p.mode == 0 ? p.taps : p.cblocks;
+  // resident weights are stored (tap, cb); HALO walks (cb outer, tap inner)
+  const uint32_t step_o = ((p.mode == 0 ? 1u : (uint32_t)p.cblocks) * B_STAGE) >> 4;
+  const uint32_t step_i = ((p.mode == 0 ? (uint32_t)p.cblocks : 1u) * B_STAGE) >> 4;
+  uint32_t sa = 0, pa = 0;    // TMEM A stage / parity
+  uint32_t sb = 0, pb = 0;    // B ring stage / parity (streamed B)
+  uint32_t acc = 0, acc_ph = 0;
+  long long dbg_acc[2] = {0, 0};
+  const long long _role0 = clock64();
+  if (stat) mbar_wait(&b_full[0], 0);
+  for (int item = blockIdx.x; item < p.n_items; item += gridDim.x) {
+    for (int t = 0; t < p.T_inner; ++t) {
+      T2_TIMED(0, mbar_wait(&acc_empty[acc], acc_ph ^ 1));
+      tc_fence_after();
+      const uint32_t d_acc = tmem_base + acc * ACC_STRIDE + (CORR ? (uint32_t)BN : 0u);
+      uint32_t accum = 0;
+      for (int o = 0; o < n_o; ++o) {
+        uint64_t b_desc = desc0 + (uint64_t)((uint32_t)o * step_o);
+        for (int i = 0; i < n_i; ++i, b_desc += step_i) {
+          if (!stat) {
+            mbar_wait(&b_full[sb], pb);
+            b_desc = desc0 + (uint64_t)(sb * (B_STAGE >> 4));
+          }
+          T2_TIMED(1, mbar_wait(&ta_ready[sa], pa));
+          tc_fence_after();
+          if (elect_one()) {
+            const uint32_t a_t = a_col0 + sa * 64;
+            // 32 bytes along the 128-byte row = 8 tf32 / 16 bf16 K elements; descriptor unit is 16 B
+            if (CORR) {
+              mma_bf16_ts(d_acc, a_t, b_desc, idesc, accum);
+              mma_bf16_ts(d_acc, a_t + 8, b_desc + 2, idesc, 1);
+              if (!half) {
+                mma_bf16_ts(d_acc, a_t + 16, b_desc + 4, idesc, 1);
+                mma_bf16_ts(d_acc, a_t + 24, b_desc + 6, idesc, 1);
+              }
+            } else {
+              mma_tf32_ts(d_acc, a_t, b_desc, idesc, accum);
+              mma_tf32_ts(d_acc, a_t + 8, b_desc + 2, idesc, 1);
+              mma_tf32_ts(d_acc, a_t + 16, b_desc + 4, idesc, 1);
+              mma_tf32_ts(d_acc, a_t + 24, b_desc + 6, idesc, 1);
+            }
+            mma_commit(&ta_empty[sa]);
+            if (!stat) mma_commit(&b_empty[sb]);
+          }
+          accum = 1;
+          if (++sa == T2_TA_STAGES) sa = 0, pa ^= 1;
+          if (!stat && ++sb == (uint32_t)p.b_stages) sb = 0, pb ^= 1;
+        }
+      }
+      if (elect_one()) mma_commit(&acc_full[acc]);
+      if (++acc == ACC_STAGES) acc = 0, acc_ph ^= 1;
+    }
+  }
+  if (p.dbg_out != nullptr && blockIdx.x == 0 && (threadIdx.x & 31) == 0) {
+    const int b = CORR ? 9 : 6;
+    p.dbg_out[b] = dbg_acc[0], p.dbg_out[b + 1] = dbg_acc[1], p.dbg_out[b + 2] = clock64() - _role0;
+  }
 }
 
 template <int BN, bool LIF>
@@ -120,26 +218,26 @@ conv_tc2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__
   const int warp = threadIdx.x >> 5;
   const int lane = threadIdx.x & 31;
 
-  if (warp == 0 && lane == 0) {
+  if (warp == T2_W_PROD_A && lane == 0) {
     prefetch_tmap(&tmA);
     prefetch_tmap(&tmB);
     for (int s = 0; s < T2_MAX_RING; ++s) {
       mbar_init(&a_full[s], 1);
-      mbar_init(&a_empty[s], 256);
+      mbar_init(&a_empty[s], 8);      // one arrival per transform warp
       mbar_init(&b_full[s], 1);
-      mbar_init(&b_empty[s], 1);
+      mbar_init(&b_empty[s], 2);
     }
     for (int s = 0; s < T2_TA_STAGES; ++s) {
-      mbar_init(&ta_ready[s], 128);
-      mbar_init(&ta_empty[s], 1);
+      mbar_init(&ta_ready[s], 4);     // one arrival per warp of the filling warpgroup
+      mbar_init(&ta_empty[s], 2);
     }
     for (int a = 0; a < 2; ++a) {
-      mbar_init(&acc_full[a], 1);
-      mbar_init(&acc_empty[a], 256);
+      mbar_init(&acc_full[a], 2);
+      mbar_init(&acc_empty[a], 8);    // one arrival per epilogue warp
     }
     fence_barrier_init();
   }
-  if (warp == 1) tmem_alloc(tmem_slot, T2_TMEM_COLS);
+  if (warp == T2_W_MMA_MAIN) tmem_alloc(tmem_slot, T2_TMEM_COLS);
   tc_fence_before();
   __syncthreads();
   tc_fence_after();
@@ -151,9 +249,10 @@ conv_tc2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__
   // registers and a tcgen05.mma / TMA issue costs a handful of instructions.  (Issued from inside an
   // `if (lane == 0)` branch every such instruction is wrapped in a divergence loop, and the single
   // issuing thread - not the tensor pipe - bounds the kernel.)
-  if (warp == 0) {
+  if (warp == T2_W_PROD_A) {
     // ================================ A producer (TMA) =========================================
     uint32_t s = 0, ph = 0;  // ring position / parity
+    long long dbg_acc[1] = {0};
     const uint32_t smem_a_u32 = smem_u32(smem_a);
     for (int item = blockIdx.x; item < p.n_items; item += gridDim.x) {
       const Tc2Item it = tc2_item(p, item);
@@ -171,7 +270,7 @@ conv_tc2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__
         int ky = 0, kx = 0;
         for (int tap = 0; tap < n_tap; ++tap) {
           for (int cb = 0; cb < p.cblocks; ++cb) {
-            mbar_wait(&a_empty[s], ph ^ 1);
+            T2_TIMED(0, mbar_wait(&a_empty[s], ph ^ 1));
             if (elect_one()) {
               mbar_expect_tx(&a_full[s], p.a_tx_bytes);
               tma_load_4d_s(smem_a_u32 + s * p.a_stage_bytes, &tmA, &a_full[s], cb * T2_BK, x0 + kx, y0 + ky, img);
@@ -183,7 +282,8 @@ conv_tc2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__
         }
       }
     }
-  } else if (warp == 2) {
+    if (p.dbg_out != nullptr && blockIdx.x == 0 && lane == 0) p.dbg_out[12] = dbg_acc[0];
+  } else if (warp == T2_W_PROD_B) {
     // ================================ B producer (TMA) =========================================
     const uint32_t smem_b_u32 = smem_u32(smem_b);
     if (p.b_stationary) {
@@ -220,67 +320,18 @@ conv_tc2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__
         }
       }
     }
-  } else if (warp == 1) {
-    // ================================ MMA issuer ================================================
-    constexpr uint32_t id_tf32 = idesc_tf32(T2_BM, BN);
-    constexpr uint32_t id_bf16 = idesc_bf16(T2_BM, BN);
-    const uint32_t smem_b_u32 = smem_u32(smem_b);
-    const int n_o = p.mode == 0 ? p.cblocks : p.taps;
-    const int n_i = p.mode == 0 ? p.taps : p.cblocks;
-    uint32_t sa = 0, pa = 0;    // TMEM A stage / parity
-    uint32_t sb = 0, pb = 0;    // B ring stage / parity (streamed B)
-    uint32_t acc = 0, acc_ph = 0;
-    if (p.b_stationary) mbar_wait(&b_full[0], 0);
-    for (int item = blockIdx.x; item < p.n_items; item += gridDim.x) {
-      for (int t = 0; t < p.T_inner; ++t) {
-        mbar_wait(&acc_empty[acc], acc_ph ^ 1);
-        tc_fence_after();
-        const uint32_t d_main = tmem_base + acc * ACC_STRIDE;
-        const uint32_t d_corr = d_main + BN;
-        uint32_t first = 0;
-        for (int o = 0; o < n_o; ++o) {
-          for (int i = 0; i < n_i; ++i) {
-            uint32_t b_addr;
-            if (p.b_stationary) {
-              // resident weights are stored (tap, cb)
-              const int bi = p.mode == 0 ? i * p.cblocks + o : o * p.cblocks + i;
-              b_addr = smem_b_u32 + (uint32_t)bi * B_STAGE;
-            } else {
-              mbar_wait(&b_full[sb], pb);
-              b_addr = smem_b_u32 + sb * B_STAGE;
-            }
-            mbar_wait(&ta_ready[sa], pa);
-            tc_fence_after();
-            if (elect_one()) {
-              const uint32_t a_t = tmem_base + T2_TMEM_A0 + sa * 64;
-              const uint64_t b_hi = smem_desc_sw128(b_addr);
-              const uint64_t b_cr = smem_desc_sw128(b_addr + B_TILE);
-#pragma unroll
-              for (int kk = 0; kk < 4; ++kk) {
-                // 32 bytes along the 128-byte row = 8 tf32 / 16 bf16 K elements
-                const uint64_t adv = (uint64_t)((kk * 32) >> 4);
-                if (kk < 2 || !p.a_exact) mma_bf16_ts(d_corr, a_t + 32 + kk * 8, b_cr + adv, id_bf16, first | kk);
-                mma_tf32_ts(d_main, a_t + kk * 8, b_hi + adv, id_tf32, first | kk);
-              }
-              mma_commit(&ta_empty[sa]);
-              if (!p.b_stationary) mma_commit(&b_empty[sb]);
-              if (o == n_o - 1 && i == n_i - 1) mma_commit(&acc_full[acc]);
-            }
-            __syncwarp();
-            first = 1;
-            if (++sa == T2_TA_STAGES) sa = 0, pa ^= 1;
-            if (!p.b_stationary && ++sb == (uint32_t)p.b_stages) sb = 0, pb ^= 1;
-          }
-        }
-        if (++acc == ACC_STAGES) acc = 0, acc_ph ^= 1;
-      }
-    }
-  } else if (warp >= 4 && warp < 12) {
+  } else if (warp == T2_W_MMA_MAIN) {
+    tc2_mma_role<BN, false>(p, tmem_base, smem_u32(smem_b), ta_ready, ta_empty, b_full, b_empty, acc_full, acc_empty);
+  } else if (warp == T2_W_MMA_CORR) {
+    tc2_mma_role<BN, true>(p, tmem_base, smem_u32(smem_b), ta_ready, ta_empty, b_full, b_empty, acc_full, acc_empty);
+  } else if (warp < 8) {
     // ============ A operand: shared memory (fp32) -> tf32 hi | bf16 hi | bf16 lo -> tensor memory =======
     // The two warpgroups alternate k-blocks (j even / odd); TMEM stage (j & 3) therefore always belongs
     // to the same warpgroup.  Every thread waits for and releases EVERY shared-memory A stage, used or
-    // not, so that no thread can run a full ring ahead of the others on the 256-arrival barrier.
-    const int g = (warp - 4) >> 2;
+    // not, so that no warp can run a full ring ahead of the others on the 8-arrival barrier.
+    long long dbg_acc[4] = {0, 0, 0, 0};
+    const long long _role0 = clock64();
+    const int g = warp >> 2;
     const int q = warp & 3;            // TMEM lane quarter this warp may access
     const int row = q * 32 + lane;     // tile row = TMEM lane
     const int kb_per_stage = p.mode == 0 ? p.taps : 1;
@@ -294,8 +345,33 @@ conv_tc2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__
       for (int t = 0; t < p.T_inner; ++t) {
         for (int st = 0; st < stages_per_tile; ++st, ++hs) {
           const uint32_t s = hs % p.a_stages, ph = (hs / p.a_stages) & 1;
-          mbar_wait(&a_full[s], ph);
+          T2_TIMED(0, mbar_wait(&a_full[s], ph));
           const uint32_t stage = smem_a_u32 + s * p.a_stage_bytes;
+          const long long _ps0 = clock64();
+          if (p.presplit && !p.a_exact) {
+            // Split the slab ONCE (not once per tap): tf32 hi overwrites the raw values in place,
+            // bf16(lo) goes to 64-byte rows behind them (16-byte chunk j of pixel P at j ^ ((P >> 1) & 3)).
+            for (int task = (int)threadIdx.x; task < p.halo_rows * 4; task += 256) {
+              const uint32_t P = (uint32_t)task >> 2, qd = (uint32_t)task & 3u, sw = P & 7u;
+              const uint32_t a0 = stage + P * 128u + (((2u * qd) ^ sw) << 4);
+              const uint32_t a1 = stage + P * 128u + (((2u * qd + 1u) ^ sw) << 4);
+              const float4 v0 = lds128(a0), v1 = lds128(a1);
+              const float f[8] = {v0.x, v0.y, v0.z, v0.w, v1.x, v1.y, v1.z, v1.w};
+              float fh[8], fl[8];
+#pragma unroll
+              for (int e = 0; e < 8; ++e) {
+                fh[e] = __uint_as_float(__float_as_uint(f[e]) & 0xFFFFE000u);
+                fl[e] = f[e] - fh[e];
+              }
+              sts128(a0, fh[0], fh[1], fh[2], fh[3]);
+              sts128(a1, fh[4], fh[5], fh[6], fh[7]);
+              sts128(stage + p.a_lb_off + P * 64u + ((qd ^ ((P >> 1) & 3u)) << 4),
+                     __uint_as_float(pack_bf16x2(fl[0], fl[1])), __uint_as_float(pack_bf16x2(fl[2], fl[3])),
+                     __uint_as_float(pack_bf16x2(fl[4], fl[5])), __uint_as_float(pack_bf16x2(fl[6], fl[7])));
+            }
+            asm volatile("bar.sync 1, 256;" ::: "memory");
+          }
+          dbg_acc[1] += clock64() - _ps0;
           for (int tp = 0; tp < kb_per_stage; ++tp, ++j) {
             if ((int)(j & 1) != g) continue;
             int r = r0;
@@ -307,50 +383,89 @@ conv_tc2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__
             const uint32_t sw = (uint32_t)r & 7u;
             const uint32_t sa = j & (T2_TA_STAGES - 1), pa = (j / T2_TA_STAGES) & 1;
             const uint32_t t_a = t_lane + sa * 64;
+            if (p.presplit) {
+              // operands are already split (or exact): gather the tap's rows and copy them to TMEM
+              uint32_t hi[32], hb[16];
 #pragma unroll
-            for (int h = 0; h < 2; ++h) {
-              uint32_t hi[16], hb[8], lb[8];
+              for (int c = 0; c < 8; ++c) {
+                float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
+                if (!(p.dbg & 1)) v = lds128(arow + (((uint32_t)c ^ sw) << 4));
+                hi[c * 4 + 0] = __float_as_uint(v.x), hi[c * 4 + 1] = __float_as_uint(v.y);
+                hi[c * 4 + 2] = __float_as_uint(v.z), hi[c * 4 + 3] = __float_as_uint(v.w);
+              }
 #pragma unroll
-              for (int c = 0; c < 4; ++c) {
-                // SWIZZLE_128B: 16-byte chunk c of row r lives at chunk position c ^ (r & 7)
-                const float4 v = lds128(arow + (((uint32_t)(h * 4 + c) ^ sw) << 4));
-                const float f[4] = {v.x, v.y, v.z, v.w};
-                float fh[4], fl[4];
+              for (int e = 0; e < 16; ++e) hb[e] = __byte_perm(hi[2 * e], hi[2 * e + 1], 0x7632);  // bf16 by truncation
+              T2_TIMED(2, mbar_wait(&ta_empty[sa], pa ^ 1));
+              tc_fence_after();
+              if (!(p.dbg & 2)) tmem_st_32x32(t_a, hi);
+              if (!(p.dbg & 2)) tmem_st_32x16(t_a + 32, hb);
+              if (!p.a_exact && !(p.dbg & 3)) {
+                uint32_t lb[16];
+                const uint32_t lrow = stage + p.a_lb_off + (uint32_t)r * 64u;
+                const uint32_t lsw = ((uint32_t)r >> 1) & 3u;
 #pragma unroll
-                for (int e = 0; e < 4; ++e) {
-                  const uint32_t hbits = __float_as_uint(f[e]) & 0xFFFFE000u;
-                  hi[c * 4 + e] = hbits;
-                  fh[e] = __uint_as_float(hbits);
-                  fl[e] = f[e] - fh[e];
+                for (int c = 0; c < 4; ++c) {
+                  const float4 v = lds128(lrow + (((uint32_t)c ^ lsw) << 4));
+                  lb[c * 4 + 0] = __float_as_uint(v.x), lb[c * 4 + 1] = __float_as_uint(v.y);
+                  lb[c * 4 + 2] = __float_as_uint(v.z), lb[c * 4 + 3] = __float_as_uint(v.w);
                 }
-                hb[c * 2 + 0] = pack_bf16x2(fh[0], fh[1]);
-                hb[c * 2 + 1] = pack_bf16x2(fh[2], fh[3]);
-                lb[c * 2 + 0] = pack_bf16x2(fl[0], fl[1]);
-                lb[c * 2 + 1] = pack_bf16x2(fl[2], fl[3]);
+                tmem_st_32x16(t_a + 48, lb);
               }
-              if (h == 0) {
-                // the MMAs that read this TMEM stage four k-blocks ago must have completed
-                mbar_wait(&ta_empty[sa], pa ^ 1);
-                tc_fence_after();
+            } else {
+#pragma unroll
+              for (int h = 0; h < 2; ++h) {
+                uint32_t hi[16], hb[8], lb[8];
+#pragma unroll
+                for (int c = 0; c < 4; ++c) {
+                  // SWIZZLE_128B: 16-byte chunk c of row r lives at chunk position c ^ (r & 7)
+                  const float4 v = lds128(arow + (((uint32_t)(h * 4 + c) ^ sw) << 4));
+                  const float f[4] = {v.x, v.y, v.z, v.w};
+                  float fh[4], fl[4];
+#pragma unroll
+                  for (int e = 0; e < 4; ++e) {
+                    const uint32_t hbits = __float_as_uint(f[e]) & 0xFFFFE000u;
+                    hi[c * 4 + e] = hbits;
+                    fh[e] = __uint_as_float(hbits);
+                    fl[e] = f[e] - fh[e];
+                  }
+                  hb[c * 2 + 0] = pack_bf16x2(fh[0], fh[1]);
+                  hb[c * 2 + 1] = pack_bf16x2(fh[2], fh[3]);
+                  lb[c * 2 + 0] = pack_bf16x2(fl[0], fl[1]);
+                  lb[c * 2 + 1] = pack_bf16x2(fl[2], fl[3]);
+                }
+                if (h == 0) {
+                  // the MMAs that read this TMEM stage four k-blocks ago must have completed
+                  mbar_wait(&ta_empty[sa], pa ^ 1);
+                  tc_fence_after();
+                }
+                tmem_st_32x16(t_a + h * 16, hi);
+                tmem_st_32x8(t_a + 32 + h * 8, hb);
+                if (!p.a_exact) tmem_st_32x8(t_a + 48 + h * 8, lb);
               }
-              tmem_st_32x16(t_a + h * 16, hi);
-              tmem_st_32x8(t_a + 32 + h * 8, hb);
-              if (!p.a_exact) tmem_st_32x8(t_a + 48 + h * 8, lb);
             }
-            tmem_st_wait();
+            // 32 same-address mbarrier arrivals serialise: one elected arrival per warp instead
+            T2_TIMED(3, tmem_st_wait());
             tc_fence_before();
-            mbar_arrive(&ta_ready[sa]);
+            __syncwarp();
+            if (lane == 0) mbar_arrive(&ta_ready[sa]);
           }
-          mbar_arrive(&a_empty[s]);
+          if (p.presplit && !p.a_exact) fence_proxy_async_smem();  // generic writes to the stage before TMA refills it
+          __syncwarp();
+          if (lane == 0) mbar_arrive(&a_empty[s]);
         }
       }
     }
-  } else if (warp >= 12) {
+    if (p.dbg_out != nullptr && blockIdx.x == 0 && threadIdx.x == 0) {
+      for (int d = 0; d < 4; ++d) p.dbg_out[d] = dbg_acc[d];
+      p.dbg_out[4] = clock64() - _role0;
+    }
+  } else if (warp < 16) {
     // ================================ epilogue ================================================
     // Two warps per TMEM lane quarter; warpgroup e owns columns [e*BN/2, (e+1)*BN/2) of the tile.
     constexpr int NCOL = BN / 2;
     static_assert(!LIF || NCOL <= 32, "fused LIF keeps 2*NCOL state registers per thread");
-    const int e = (warp - 12) >> 2;
+    long long dbg_acc[1] = {0};
+    const int e = (warp - 8) >> 2;
     const int q = warp & 3;
     const int row = q * 32 + lane;
     const int64_t hw = (int64_t)p.Ho * p.Wo;
@@ -395,7 +510,7 @@ conv_tc2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__
         const int64_t frame = frame0 + (int64_t)t * p.Bsz;
         const int64_t out_off = frame * p.out_bs + rr * p.out_ps;
         const int64_t res_off = frame * p.res_bs + rr * p.res_ps;
-        mbar_wait(&acc_full[acc], acc_ph);
+        T2_TIMED(0, mbar_wait(&acc_full[acc], acc_ph));
         tc_fence_after();
         const uint32_t t_row = tmem_base + ((uint32_t)(q * 32) << 16) + acc * ACC_STRIDE + e * NCOL;
 #pragma unroll
@@ -407,7 +522,8 @@ conv_tc2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__
           if (c0 + 16 >= NCOL) {
             // last TMEM read of this tile: hand the accumulator back before the global traffic
             tc_fence_before();
-            mbar_arrive(&acc_empty[acc]);
+            __syncwarp();
+            if (lane == 0) mbar_arrive(&acc_empty[acc]);
           }
           const int co0 = co_base + c0;
           const bool live = valid && co0 < p.Cout;
@@ -435,7 +551,7 @@ conv_tc2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__
               o[jj] = z;
             }
           }
-          if (live) {
+          if (live && !(p.dbg & 8)) {
             float* dst = p.y + out_off + co0;
             const float* rs = p.residual ? p.residual + res_off + co0 : nullptr;
             const int nvalid = min(16, p.Cout - co0);
@@ -475,11 +591,12 @@ conv_tc2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__
         }
       }
     }
+    if (p.dbg_out != nullptr && blockIdx.x == 0 && threadIdx.x == 256) p.dbg_out[5] = dbg_acc[0];
   }
 
   tc_fence_before();
   __syncthreads();
-  if (warp == 1) {
+  if (warp == T2_W_MMA_MAIN) {
     tc_fence_after();
     tmem_dealloc(tmem_base, T2_TMEM_COLS);
   }
@@ -586,6 +703,20 @@ static int launch_tc2(const CUtensorMap& tmA, const CUtensorMap& tmB, const Tc2P
     }
     attr_set = true;
   }
+  if (p.dbg & 16) {
+    Tc2Params q = p;
+    cudaMalloc(&q.dbg_out, 16 * sizeof(long long));
+    cudaMemset(q.dbg_out, 0, 16 * sizeof(long long));
+    conv_tc2_kernel<BN, LIF><<<grid, T2_THREADS, smem, st>>>(tmA, tmB, q);
+    long long h[16];
+    cudaMemcpy(h, q.dbg_out, sizeof(h), cudaMemcpyDeviceToHost);
+    cudaFree(q.dbg_out);
+    fprintf(stderr,
+            "tc2 dbg cta0: transform[a_full %lld presplit %lld ta_empty %lld st_wait %lld total %lld] epi[acc_full %lld] "
+            "mma_main[acc_empty %lld ta_ready %lld total %lld] mma_corr[acc_empty %lld ta_ready %lld total %lld] prodA[a_empty %lld]\n",
+            h[0], h[1], h[2], h[3], h[4], h[5], h[6], h[7], h[8], h[9], h[10], h[11], h[12]);
+    return after_launch("conv_tc2_kernel");
+  }
   conv_tc2_kernel<BN, LIF><<<grid, T2_THREADS, smem, st>>>(tmA, tmB, p);
   return after_launch("conv_tc2_kernel");
 }
@@ -615,6 +746,10 @@ int conv_tc2_dispatch(const soda_conv_desc_t* d, const float* x, const float* pa
                 "conv_tc: needs pixel-major input, Cin % 32 == 0, 16-byte aligned strides, k in {1,3}, stride in {1,2}");
   Tc2Params p;
   memset(&p, 0, sizeof(p));
+  {
+    const char* e = getenv("SODA_TC2_DBG");
+    p.dbg = e ? atoi(e) : 0;
+  }
   p.H = d->H, p.W = d->W, p.Cin = d->Cin, p.Cout = d->Cout, p.k = d->k, p.stride = d->stride;
   p.pad = d->k / 2;
   p.Ho = (d->H + 2 * p.pad - d->k) / d->stride + 1;
@@ -681,6 +816,12 @@ int conv_tc2_dispatch(const soda_conv_desc_t* d, const float* x, const float* pa
       const int HH = p.BH + 2 * p.pad;
       p.a_tx_bytes = (uint32_t)(p.WW * HH * 128);
       p.a_stage_bytes = (p.a_tx_bytes + 1023u) & ~1023u;
+      p.halo_rows = p.WW * HH;
+      if (p.k == 3) {
+        p.presplit = 1;
+        p.a_lb_off = p.a_stage_bytes;
+        if (!p.a_exact) p.a_stage_bytes += ((uint32_t)p.halo_rows * 64u + 1023u) & ~1023u;
+      }
       const cuuint32_t box[4] = {T2_BK, (cuuint32_t)p.WW, (cuuint32_t)HH, 1};
       const cuuint32_t es[4] = {1, 1, 1, 1};
       int rc = encode_map2(&tmA, x, 4, dims, str, box, es);
