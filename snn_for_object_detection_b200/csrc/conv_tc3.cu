@@ -1,0 +1,749 @@
+// tcgen05 / TMEM / TMA implicit-GEMM convolution (soda_conv2d_fwd kind SODA_CONV_TC and the fused
+// soda_conv_lif_fwd).
+//
+// Reference arithmetic: nn.Conv2d(bias=False, padding=k/2) models/modules/layer_gen.py:129-136, the eval
+// BatchNorm affine (:211-214), norse LIFCell (:233), Residual sum (models/generator.py:146) and the
+// concat-slice store (:158) in the epilogue.
+//
+//   D[m, co] = sum_{tap, ci} A_tap[m, ci] * W[tap][co][ci]          m = output pixel, 128 per tile
+//
+// Design (each point is a measured fact about B200, see DESIGN.md and scripts/microbench/):
+//
+// * "im2col by descriptor".  The swizzle of a SWIZZLE_128B shared-memory matrix descriptor is a function of
+//   the absolute shared-memory address, so a descriptor may start at any 128-byte row and its 8-row groups
+//   may be any multiple of 16 B apart.  A tile is 16 x 8 output pixels; TMA loads its 18 x 10 input halo
+//   ONCE per 32-channel slab (out-of-bounds = the convolution's zero padding) as 180 rows of 128 B, and the
+//   A operand of filter tap (ky, kx) is simply the descriptor {start = slab + (ky*10 + kx)*128 B, group
+//   stride = 10*128 B}: the nine taps read the same slab, nothing is gathered or copied.  1x1 layers load
+//   the tile itself; stride-2 layers load one dense tap tile per filter tap through the tensor map's element
+//   strides (2.25x the input instead of 9x).
+// * Precision: "tf32 + bf16 correction", 2 tensor passes instead of 3xTF32's 3:
+//       a*b ~= hi(a)*hi(b)            kind::tf32, exact products, fp32 accumulate  -> main accumulator
+//            + bf16(hi a)*bf16(lo b)
+//            + bf16(lo a)*bf16(hi b)  kind::f16, K-stacked in one 128-byte row     -> correction accumulator
+//   The correction terms are 2^-11 of the main term, so 8 mantissa bits on them keep ~2^-20 overall.
+//   Each slab is split ONCE in shared memory by 8 split warps (tf32 hi in place + a second plane of
+//   [bf16 hi | bf16 lo] rows with the same row addressing), not once per tap.  Inputs declared exactly
+//   representable (spikes, pooled spike counts) skip the lo(a) half.
+// * All synchronisation is per slab (9 k-blocks = 72 MMAs for a 3x3 layer), not per k-block: an mbarrier
+//   round trip costs several hundred clocks, a k-block of a 32-channel tile only 128.
+// * B (weights: tf32 hi plane + bf16 [lo|hi] plane, BatchNorm scale folded) is SHARED-MEMORY RESIDENT for
+//   the whole kernel when one output-channel chunk of it fits; otherwise it streams through its own ring.
+// * Two MMA issuer warps, one per accumulator (main / correction): independent instruction streams.
+// * Epilogue: 8 warps (two per TMEM lane quarter, splitting the columns): main + correction + shift
+//   (+ residual) -> global / concat slice.  LIF variant: the work item is (sample, tile, channel chunk)
+//   and the kernel walks t = 0..T-1 INSIDE the item, so membrane potential and synaptic current stay in
+//   the epilogue warps' registers for all T steps and never touch HBM.
+//
+// Persistent, warp-specialised, 20 warps: w0-7 split, w8-15 epilogue, w16 A producer (TMA), w17 main-pass MMA
+// issuer + TMEM owner, w18 B producer (TMA), w19 correction-pass MMA issuer.
+#include <stdlib.h>
+#include <string.h>
+
+#include <algorithm>
+
+#include "common.cuh"
+#include "neuron.cuh"
+#include "tc_common.cuh"
+
+namespace soda {
+
+using namespace tc;
+
+constexpr int T3_BM = 128;
+constexpr int T3_BK = 32;
+constexpr int T3_BH = 16, T3_BW = 8;     // spatial tile (one 8-row descriptor group per output row)
+constexpr int T3_THREADS = 640;
+constexpr int T3_W_PROD_A = 16, T3_W_MMA_MAIN = 17, T3_W_PROD_B = 18, T3_W_MMA_CORR = 19;
+constexpr int T3_MAX_RING = 8;           // max stages of the A / B shared-memory rings
+constexpr int T3_SMEM_LIMIT = 232448 - 1024 /*alignment slack*/ - 512 /*barriers*/;
+
+struct Tc3Params {
+  int H, W, Cin, Cout, k, stride, pad, Ho, Wo;
+  int tiles_x, tiles_y, n_spatial;
+  int taps, cblocks, kblocks;
+  int mode;                      // 0 = HALO (one A stage per 32-channel slab, `taps` k-blocks), 1 = TAP
+  int flat;                      // 1x1 stride-1 over the flattened pixel list
+  int a_exact;
+  int rows;                      // 128-byte rows in one A plane (180 halo pixels, or 128)
+  int WW;                        // halo row pitch in pixels
+  uint32_t sbo;                  // bytes between the 8-row groups of the A operand
+  uint32_t plane_bytes;          // hi plane size = offset of the correction plane inside a stage
+  int nch;                       // output-channel chunks of BN
+  int n_outer, T_inner, Bsz;     // work items = nch * n_spatial * n_outer, each walks T_inner frames
+  int n_items;
+  int b_stationary, b_stages;
+  int a_stages;
+  uint32_t a_stage_bytes, a_tx_bytes, b_region_bytes;
+  int64_t total_pix;
+  int64_t out_bs, out_ps, res_bs, res_ps;
+  const float* shift;
+  const float* residual;
+  float* y;
+  int dbg;                       // SODA_TC_DBG timing experiments (results are garbage when set)
+  int lif;
+  NP np;
+  const float* v0;
+  const float* i0;
+  float* v_out;
+  float* i_out;
+};
+
+struct Tc3Item {
+  int chunk, sp, outer;
+};
+__device__ __forceinline__ Tc3Item tc3_item(const Tc3Params& p, int item) {
+  Tc3Item it;
+  it.chunk = item % p.nch;
+  const int r = item / p.nch;
+  it.sp = r % p.n_spatial;
+  it.outer = r / p.n_spatial;
+  return it;
+}
+
+// ================================ MMA issuers ===================================================
+// One warp per accumulator.  CORR = false: tf32 main pass over the hi planes; CORR = true: bf16 correction
+// pass over the [bf16 hi | bf16 lo] x [bf16 lo | bf16 hi] planes.  Warp-uniform control flow; one elected
+// lane issues, so descriptors live in uniform registers.
+template <int BN, bool CORR>
+__device__ __forceinline__ void tc3_mma_role(const Tc3Params& p, uint32_t tmem_base, uint32_t smem_a_u32,
+                                             uint32_t smem_b_u32, uint64_t* a_ready, uint64_t* a_empty,
+                                             uint64_t* b_full, uint64_t* b_empty, uint64_t* acc_full,
+                                             uint64_t* acc_empty) {
+  constexpr uint32_t B_TILE = BN * 128, B_STAGE = 2 * B_TILE;
+  constexpr uint32_t idesc = CORR ? idesc_bf16(T3_BM, BN) : idesc_tf32(T3_BM, BN);
+  // + (bytes >> 4) on a descriptor moves its start address
+  const uint64_t a_desc0 = smem_desc_sw128_sbo(smem_a_u32 + (CORR ? p.plane_bytes : 0u), p.sbo);
+  const uint64_t b_desc0 = smem_desc_sw128(smem_b_u32 + (CORR ? B_TILE : 0u));
+  const bool half = CORR && p.a_exact;   // exact inputs have no lo(a) half
+  const bool stat = p.b_stationary != 0;
+  const bool halo3 = p.mode == 0 && p.k == 3;
+  const int stages_per_tile = p.mode == 0 ? p.cblocks : p.kblocks;
+  const int kb_per_stage = p.mode == 0 ? p.taps : 1;
+  const uint32_t a_stage16 = p.a_stage_bytes >> 4;
+  uint32_t sa = 0, pa = 0;    // A ring stage / parity
+  uint32_t sb = 0, pb = 0;    // B ring stage / parity (streamed B)
+  uint32_t acc = 0, acc_ph = 0;
+  if (stat) mbar_wait(&b_full[0], 0);
+  for (int item = blockIdx.x; item < p.n_items; item += gridDim.x) {
+    for (int t = 0; t < p.T_inner; ++t) {
+      mbar_wait(&acc_empty[acc], acc_ph ^ 1);
+      tc_fence_after();
+      const uint32_t d_acc = tmem_base + acc * (2 * BN) + (CORR ? (uint32_t)BN : 0u);
+      uint32_t accum = 0;
+      for (int st = 0; st < stages_per_tile; ++st) {
+        mbar_wait(&a_ready[sa], pa);
+        tc_fence_after();
+        const uint64_t a_st = a_desc0 + (uint64_t)(sa * a_stage16);
+        int ky = 0, kx = 0;
+        for (int tp = 0; tp < kb_per_stage; ++tp) {
+          // resident weights are stored (tap, cb); HALO stage = channel slab st, k-block = tap tp
+          uint64_t b_desc;
+          if (stat) {
+            const int bi = p.mode == 0 ? tp * p.cblocks + st : st;
+            b_desc = b_desc0 + (uint64_t)((uint32_t)bi * (B_STAGE >> 4));
+          } else {
+            mbar_wait(&b_full[sb], pb);
+            tc_fence_after();
+            b_desc = b_desc0 + (uint64_t)(sb * (B_STAGE >> 4));
+          }
+          // tap (ky, kx) of the halo = the same slab, started (ky * WW + kx) rows further
+          const uint64_t a_desc = a_st + (uint64_t)(halo3 ? (uint32_t)(ky * p.WW + kx) * 8u : 0u);
+          if (elect_one()) {
+            // 32 bytes along the 128-byte row = 8 tf32 / 16 bf16 K elements; descriptor unit is 16 B
+            if (!(p.dbg & 4)) {
+              if (CORR) {
+                mma_bf16_ss(d_acc, a_desc, b_desc, idesc, accum);
+                mma_bf16_ss(d_acc, a_desc + 2, b_desc + 2, idesc, 1);
+                if (!half) {
+                  mma_bf16_ss(d_acc, a_desc + 4, b_desc + 4, idesc, 1);
+                  mma_bf16_ss(d_acc, a_desc + 6, b_desc + 6, idesc, 1);
+                }
+              } else {
+                mma_tf32_ss(d_acc, a_desc, b_desc, idesc, accum);
+                mma_tf32_ss(d_acc, a_desc + 2, b_desc + 2, idesc, 1);
+                mma_tf32_ss(d_acc, a_desc + 4, b_desc + 4, idesc, 1);
+                mma_tf32_ss(d_acc, a_desc + 6, b_desc + 6, idesc, 1);
+              }
+            }
+            if (!stat) mma_commit(&b_empty[sb]);
+          }
+          accum = 1;
+          if (++kx == 3) kx = 0, ++ky;
+          if (!stat && ++sb == (uint32_t)p.b_stages) sb = 0, pb ^= 1;
+        }
+        if (elect_one()) mma_commit(&a_empty[sa]);
+        if (++sa == (uint32_t)p.a_stages) sa = 0, pa ^= 1;
+      }
+      if (elect_one()) mma_commit(&acc_full[acc]);
+      if (++acc == 2) acc = 0, acc_ph ^= 1;
+    }
+  }
+}
+
+template <int BN, bool LIF>
+__global__ void __launch_bounds__(T3_THREADS, 1)
+conv_tc3_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB, Tc3Params p) {
+  constexpr uint32_t B_TILE = BN * 128;        // one plane of one k-block: BN rows x 128 B
+  constexpr uint32_t B_STAGE = 2 * B_TILE;     // tf32 hi plane + bf16 [lo|hi] plane
+  constexpr uint32_t TMEM_COLS = 4 * BN;       // two accumulator stages of (main | correction)
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+  uint8_t* smem_b = smem;
+  uint8_t* smem_a = smem + p.b_region_bytes;
+  uint64_t* bars = reinterpret_cast<uint64_t*>(smem_a + (size_t)p.a_stages * p.a_stage_bytes);
+  uint64_t* a_full = bars;                        // TMA bytes of an A stage landed            [8]
+  uint64_t* a_ready = bars + 8;                   // stage split (hi in place + correction plane) [8]
+  uint64_t* a_empty = bars + 16;                  // both MMA streams done with the stage     [8]
+  uint64_t* b_full = bars + 24;                   // [8]
+  uint64_t* b_empty = bars + 32;                  // [8]
+  uint64_t* acc_full = bars + 40;                 // [2]
+  uint64_t* acc_empty = bars + 42;                // [2]
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 44);
+
+  const int warp = threadIdx.x >> 5;
+  const int lane = threadIdx.x & 31;
+
+  if (warp == T3_W_PROD_A && lane == 0) {
+    prefetch_tmap(&tmA);
+    prefetch_tmap(&tmB);
+    for (int s = 0; s < T3_MAX_RING; ++s) {
+      mbar_init(&a_full[s], 1);
+      mbar_init(&a_ready[s], 8);      // one arrival per split warp
+      mbar_init(&a_empty[s], 2);      // one commit per MMA stream
+      mbar_init(&b_full[s], 1);
+      mbar_init(&b_empty[s], 2);
+    }
+    for (int a = 0; a < 2; ++a) {
+      mbar_init(&acc_full[a], 2);
+      mbar_init(&acc_empty[a], 8);    // one arrival per epilogue warp
+    }
+    fence_barrier_init();
+  }
+  if (warp == T3_W_MMA_MAIN) tmem_alloc(tmem_slot, TMEM_COLS);
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = *tmem_slot;
+  const int my_chunk = blockIdx.x % p.nch;   // gridDim.x is a multiple of nch: fixed per CTA
+
+  // Roles 16-19 run warp-uniform control flow and elect one lane only around the asynchronous instructions
+  // themselves: descriptors, coordinates and barrier addresses then live in uniform registers.
+  if (warp == T3_W_PROD_A) {
+    // ================================ A producer (TMA) =========================================
+    uint32_t s = 0, ph = 0;  // ring position / parity
+    const uint32_t smem_a_u32 = smem_u32(smem_a);
+    for (int item = blockIdx.x; item < p.n_items; item += gridDim.x) {
+      const Tc3Item it = tc3_item(p, item);
+      int x0 = 0, y0 = 0;
+      if (p.flat) {
+        x0 = it.sp * T3_BM;
+      } else {
+        const int ty = it.sp / p.tiles_x, tx = it.sp - ty * p.tiles_x;
+        y0 = ty * T3_BH * p.stride - p.pad;
+        x0 = tx * T3_BW * p.stride - p.pad;
+      }
+      for (int t = 0; t < p.T_inner; ++t) {
+        const int img = p.flat ? 0 : t * p.Bsz + it.outer;
+        const int n_tap = p.mode == 0 ? 1 : p.taps;   // HALO: one stage per channel slab
+        int ky = 0, kx = 0;
+        for (int tap = 0; tap < n_tap; ++tap) {
+          for (int cb = 0; cb < p.cblocks; ++cb) {
+            mbar_wait(&a_empty[s], ph ^ 1);
+            if (elect_one()) {
+              mbar_expect_tx(&a_full[s], p.a_tx_bytes);
+              tma_load_4d_s(smem_a_u32 + s * p.a_stage_bytes, &tmA, &a_full[s], cb * T3_BK, x0 + kx, y0 + ky, img);
+            }
+            __syncwarp();
+            if (++s == (uint32_t)p.a_stages) s = 0, ph ^= 1;
+          }
+          if (++kx == p.k) kx = 0, ++ky;
+        }
+      }
+    }
+  } else if (warp == T3_W_PROD_B) {
+    // ================================ B producer (TMA) =========================================
+    const uint32_t smem_b_u32 = smem_u32(smem_b);
+    if (p.b_stationary) {
+      if (elect_one()) mbar_expect_tx(&b_full[0], (uint32_t)p.kblocks * B_STAGE);
+      __syncwarp();
+      for (int tap = 0; tap < p.taps; ++tap)
+        for (int cb = 0; cb < p.cblocks; ++cb) {
+          const uint32_t dst = smem_b_u32 + (uint32_t)(tap * p.cblocks + cb) * B_STAGE;
+          if (elect_one()) {
+            tma_load_3d_s(dst, &tmB, &b_full[0], cb * T3_BK, my_chunk * BN, tap);
+            tma_load_3d_s(dst + B_TILE, &tmB, &b_full[0], cb * T3_BK, my_chunk * BN, p.taps + tap);
+          }
+          __syncwarp();
+        }
+    } else {
+      uint32_t s = 0, ph = 0;
+      const int n_o = p.mode == 0 ? p.cblocks : p.taps;   // HALO walks (cb, tap), TAP walks (tap, cb)
+      const int n_i = p.mode == 0 ? p.taps : p.cblocks;
+      for (int item = blockIdx.x; item < p.n_items; item += gridDim.x) {
+        for (int t = 0; t < p.T_inner; ++t) {
+          for (int o = 0; o < n_o; ++o)
+            for (int i = 0; i < n_i; ++i) {
+              const int tap = p.mode == 0 ? i : o, cb = p.mode == 0 ? o : i;
+              mbar_wait(&b_empty[s], ph ^ 1);
+              if (elect_one()) {
+                mbar_expect_tx(&b_full[s], B_STAGE);
+                const uint32_t dst = smem_b_u32 + s * B_STAGE;
+                tma_load_3d_s(dst, &tmB, &b_full[s], cb * T3_BK, my_chunk * BN, tap);
+                tma_load_3d_s(dst + B_TILE, &tmB, &b_full[s], cb * T3_BK, my_chunk * BN, p.taps + tap);
+              }
+              __syncwarp();
+              if (++s == (uint32_t)p.b_stages) s = 0, ph ^= 1;
+            }
+        }
+      }
+    }
+  } else if (warp == T3_W_MMA_MAIN) {
+    tc3_mma_role<BN, false>(p, tmem_base, smem_u32(smem_a), smem_u32(smem_b), a_ready, a_empty, b_full, b_empty,
+                            acc_full, acc_empty);
+  } else if (warp == T3_W_MMA_CORR) {
+    tc3_mma_role<BN, true>(p, tmem_base, smem_u32(smem_a), smem_u32(smem_b), a_ready, a_empty, b_full, b_empty,
+                           acc_full, acc_empty);
+  } else if (warp < 8) {
+    // ============ split: fp32 slab -> tf32 hi (in place) + [bf16 hi | bf16 lo] correction plane =========
+    // Task = (pixel row P, 8 channels q).  SWIZZLE_128B: logical 16-byte chunk c of row P sits at chunk
+    // position c ^ (P & 7) in both planes (TMA wrote the hi plane that way; the correction plane copies the
+    // convention so that one descriptor arithmetic serves both).
+    const uint32_t smem_a_u32 = smem_u32(smem_a);
+    const int n_task = p.rows * 4;
+    const int stages_per_tile = p.mode == 0 ? p.cblocks : p.kblocks;
+    uint32_t s = 0, ph = 0;
+    for (int item = blockIdx.x; item < p.n_items; item += gridDim.x) {
+      for (int t = 0; t < p.T_inner; ++t) {
+        for (int st = 0; st < stages_per_tile; ++st) {
+          mbar_wait(&a_full[s], ph);
+          const uint32_t hi_pl = smem_a_u32 + s * p.a_stage_bytes;
+          const uint32_t cr_pl = hi_pl + p.plane_bytes;
+          if (!(p.dbg & 1)) {
+            for (int task = (int)threadIdx.x; task < n_task; task += 256) {
+              const uint32_t P = (uint32_t)task >> 2, q = (uint32_t)task & 3u, sw = P & 7u;
+              const uint32_t a0 = hi_pl + P * 128u + (((2u * q) ^ sw) << 4);
+              const uint32_t a1 = hi_pl + P * 128u + (((2u * q + 1u) ^ sw) << 4);
+              const float4 v0 = lds128(a0), v1 = lds128(a1);
+              const float f[8] = {v0.x, v0.y, v0.z, v0.w, v1.x, v1.y, v1.z, v1.w};
+              float fh[8], fl[8];
+#pragma unroll
+              for (int e = 0; e < 8; ++e) {
+                fh[e] = __uint_as_float(__float_as_uint(f[e]) & 0xFFFFE000u);
+                fl[e] = f[e] - fh[e];
+              }
+              const uint32_t cr = cr_pl + P * 128u;
+              sts128(cr + ((q ^ sw) << 4), __uint_as_float(pack_bf16x2(fh[0], fh[1])),
+                     __uint_as_float(pack_bf16x2(fh[2], fh[3])), __uint_as_float(pack_bf16x2(fh[4], fh[5])),
+                     __uint_as_float(pack_bf16x2(fh[6], fh[7])));
+              if (!p.a_exact) {
+                sts128(a0, fh[0], fh[1], fh[2], fh[3]);
+                sts128(a1, fh[4], fh[5], fh[6], fh[7]);
+                sts128(cr + (((4u + q) ^ sw) << 4), __uint_as_float(pack_bf16x2(fl[0], fl[1])),
+                       __uint_as_float(pack_bf16x2(fl[2], fl[3])), __uint_as_float(pack_bf16x2(fl[4], fl[5])),
+                       __uint_as_float(pack_bf16x2(fl[6], fl[7])));
+              }
+            }
+          }
+          // generic-proxy writes must be visible to the tensor core's (async proxy) operand reads
+          fence_proxy_async_smem();
+          __syncwarp();
+          if (lane == 0) mbar_arrive(&a_ready[s]);
+          if (++s == (uint32_t)p.a_stages) s = 0, ph ^= 1;
+        }
+      }
+    }
+  } else if (warp < 16) {
+    // ================================ epilogue ================================================
+    // Two warps per TMEM lane quarter; warpgroup e owns columns [e*BN/2, (e+1)*BN/2) of the tile.
+    constexpr int NCOL = BN / 2;
+    static_assert(!LIF || NCOL <= 32, "fused LIF keeps 2*NCOL state registers per thread");
+    const int e = (warp - 8) >> 2;
+    const int q = warp & 3;
+    const int row = q * 32 + lane;
+    const int64_t hw = (int64_t)p.Ho * p.Wo;
+    uint32_t local = 0;
+    for (int item = blockIdx.x; item < p.n_items; item += gridDim.x) {
+      const Tc3Item it = tc3_item(p, item);
+      bool valid;
+      int64_t rr;      // pixel index inside its frame
+      int64_t frame0;  // frame of step t = 0
+      if (p.flat) {
+        const int64_t pix = (int64_t)it.sp * T3_BM + row;
+        valid = pix < p.total_pix;
+        frame0 = pix / hw;
+        rr = pix - frame0 * hw;
+      } else {
+        const int ty = it.sp / p.tiles_x, tx = it.sp - ty * p.tiles_x;
+        const int oy = ty * T3_BH + (row >> 3);
+        const int ox = tx * T3_BW + (row & 7);
+        valid = oy < p.Ho && ox < p.Wo;
+        rr = (int64_t)oy * p.Wo + ox;
+        frame0 = it.outer;
+      }
+      const int co_base = it.chunk * BN + e * NCOL;
+      float sv[LIF ? NCOL : 1], si[LIF ? NCOL : 1];
+      if constexpr (LIF) {
+        const int64_t soff = ((int64_t)it.outer * hw + rr) * p.Cout + co_base;
+#pragma unroll
+        for (int c = 0; c < NCOL; c += 4) {
+          float4 a = make_float4(p.np.v_leak, p.np.v_leak, p.np.v_leak, p.np.v_leak);
+          float4 b = make_float4(0.f, 0.f, 0.f, 0.f);
+          if (valid && p.v0 != nullptr && co_base + c < p.Cout) {
+            a = __ldg(reinterpret_cast<const float4*>(p.v0 + soff + c));
+            b = __ldg(reinterpret_cast<const float4*>(p.i0 + soff + c));
+          }
+          sv[c] = a.x, sv[c + 1] = a.y, sv[c + 2] = a.z, sv[c + 3] = a.w;
+          si[c] = b.x, si[c + 1] = b.y, si[c + 2] = b.z, si[c + 3] = b.w;
+        }
+      }
+      for (int t = 0; t < p.T_inner; ++t, ++local) {
+        const uint32_t acc = local & 1u;
+        const uint32_t acc_ph = (local >> 1) & 1u;
+        const int64_t frame = frame0 + (int64_t)t * p.Bsz;
+        const int64_t out_off = frame * p.out_bs + rr * p.out_ps;
+        const int64_t res_off = frame * p.res_bs + rr * p.res_ps;
+        mbar_wait(&acc_full[acc], acc_ph);
+        tc_fence_after();
+        const uint32_t t_row = tmem_base + ((uint32_t)(q * 32) << 16) + acc * (2 * BN) + e * NCOL;
+#pragma unroll
+        for (int c0 = 0; c0 < NCOL; c0 += 16) {
+          uint32_t r[16], rc[16];
+          tmem_ld_32x16(t_row + c0, r);
+          tmem_ld_32x16(t_row + BN + c0, rc);
+          tmem_ld_wait();
+          if (c0 + 16 >= NCOL) {
+            // last TMEM read of this tile: hand the accumulator back before the global traffic
+            tc_fence_before();
+            __syncwarp();
+            if (lane == 0) mbar_arrive(&acc_empty[acc]);
+          }
+          const int co0 = co_base + c0;
+          const bool live = valid && co0 < p.Cout;
+          float o[16];
+#pragma unroll
+          for (int jj = 0; jj < 16; ++jj) o[jj] = __uint_as_float(r[jj]) + __uint_as_float(rc[jj]);
+          if (p.shift != nullptr && co0 < p.Cout) {
+            if (co0 + 16 <= p.Cout) {
+#pragma unroll
+              for (int jj = 0; jj < 16; jj += 4) {
+                const float4 sh = __ldg(reinterpret_cast<const float4*>(p.shift + co0 + jj));
+                o[jj] += sh.x, o[jj + 1] += sh.y, o[jj + 2] += sh.z, o[jj + 3] += sh.w;
+              }
+            } else {
+#pragma unroll
+              for (int jj = 0; jj < 16; ++jj)
+                if (co0 + jj < p.Cout) o[jj] += __ldg(p.shift + co0 + jj);
+            }
+          }
+          if constexpr (LIF) {
+#pragma unroll
+            for (int jj = 0; jj < 16; ++jj) {
+              float z, vd;
+              lif_step(p.np, o[jj], sv[c0 + jj], si[c0 + jj], z, vd);
+              o[jj] = z;
+            }
+          }
+          if (live && !(p.dbg & 8)) {
+            float* dst = p.y + out_off + co0;
+            const float* rs = p.residual ? p.residual + res_off + co0 : nullptr;
+            const int nvalid = min(16, p.Cout - co0);
+            const bool vec = nvalid == 16 && ((reinterpret_cast<uintptr_t>(dst) & 15) == 0) &&
+                             (rs == nullptr || (reinterpret_cast<uintptr_t>(rs) & 15) == 0);
+            if (vec) {
+#pragma unroll
+              for (int jj = 0; jj < 16; jj += 4) {
+                float4 ov = make_float4(o[jj], o[jj + 1], o[jj + 2], o[jj + 3]);
+                if (rs) {
+                  const float4 rv = __ldg(reinterpret_cast<const float4*>(rs + jj));
+                  ov.x += rv.x, ov.y += rv.y, ov.z += rv.z, ov.w += rv.w;
+                }
+                *reinterpret_cast<float4*>(dst + jj) = ov;
+              }
+            } else {
+#pragma unroll
+              for (int jj = 0; jj < 16; ++jj) {
+                if (jj < nvalid) {
+                  float ov = o[jj];
+                  if (rs) ov += __ldg(rs + jj);
+                  dst[jj] = ov;
+                }
+              }
+            }
+          }
+        }
+      }
+      if constexpr (LIF) {
+        if (valid && co_base < p.Cout) {
+          const int64_t soff = ((int64_t)it.outer * hw + rr) * p.Cout + co_base;
+#pragma unroll
+          for (int c = 0; c < NCOL; c += 4) {
+            *reinterpret_cast<float4*>(p.v_out + soff + c) = make_float4(sv[c], sv[c + 1], sv[c + 2], sv[c + 3]);
+            *reinterpret_cast<float4*>(p.i_out + soff + c) = make_float4(si[c], si[c + 1], si[c + 2], si[c + 3]);
+          }
+        }
+      }
+    }
+  }
+
+  tc_fence_before();
+  __syncthreads();
+  if (warp == T3_W_MMA_MAIN) {
+    tc_fence_after();
+    tmem_dealloc(tmem_base, TMEM_COLS);
+  }
+}
+
+// ------------------------------------------------------------------------------------------------
+// host side: weight packing, tensor maps, configuration, dispatch
+// ------------------------------------------------------------------------------------------------
+static inline int tc3_bn_for(int Cout, bool lif) {
+  if (Cout <= 32) return 32;
+  if (Cout <= 64 || lif) return 64;
+  return 128;
+}
+// The packed layout pads Cout to a multiple of 128 (or to 32 / 64 below that) so that every BN the
+// dispatcher may pick (plain and LIF launches share one packed buffer) addresses whole tiles.
+static inline int tc3_cout_pad(int Cout) {
+  if (Cout <= 32) return 32;
+  if (Cout <= 64) return 64;
+  return (Cout + 127) / 128 * 128;
+}
+
+int64_t conv_tc3_packed_elems(int Cout, int Cin, int k) {
+  if (Cin % T3_BK != 0) return 0;
+  return 2LL * k * k * tc3_cout_pad(Cout) * Cin;
+}
+
+__device__ __forceinline__ uint16_t tc3_bf16_bits(float f) {
+  return (uint16_t)(pack_bf16x2(f, 0.0f) & 0xFFFFu);
+}
+
+// [Cout, Cin, k, k] -> plane 0: [tap][Cout_pad][Cin] tf32 hi of (w * scale)
+//                      plane 1: [tap][Cout_pad][Cin/32] rows of 128 B = bf16 lo[32] | bf16 hi[32]
+__global__ void pack_weights_tc3_kernel(const float* __restrict__ w, const float* __restrict__ scale, int Cout,
+                                        int Cin, int taps, int Cout_pad, float* __restrict__ wp) {
+  const int64_t plane = (int64_t)taps * Cout_pad * Cin;
+  uint16_t* corr = reinterpret_cast<uint16_t*>(wp + plane);
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < plane;
+       i += (int64_t)gridDim.x * blockDim.x) {
+    const int ci = (int)(i % Cin);
+    const int64_t r = i / Cin;
+    const int co = (int)(r % Cout_pad);
+    const int tap = (int)(r / Cout_pad);
+    float v = 0.f;
+    if (co < Cout) {
+      v = w[((int64_t)co * Cin + ci) * taps + tap];
+      if (scale != nullptr) v = __fmul_rn(v, scale[co]);
+    }
+    const float hi = __uint_as_float(__float_as_uint(v) & 0xFFFFE000u);
+    wp[i] = hi;
+    const int64_t row16 = (r * Cin + (ci & ~31)) * 2;  // start of this 128-byte row, in uint16
+    corr[row16 + (ci & 31)] = tc3_bf16_bits(v - hi);
+    corr[row16 + 32 + (ci & 31)] = tc3_bf16_bits(hi);
+  }
+}
+
+int conv_tc3_pack(const float* w, const float* scale, int Cout, int Cin, int k, float* packed, cudaStream_t st) {
+  if (Cin % T3_BK != 0) return fail(SODA_ERR_UNSUPPORTED, "conv_tc: Cin must be a multiple of 32");
+  const int64_t plane = (int64_t)k * k * tc3_cout_pad(Cout) * Cin;
+  pack_weights_tc3_kernel<<<(unsigned)std::min<int64_t>(ceil_div(plane, 256), 4096), 256, 0, st>>>(
+      w, scale, Cout, Cin, k * k, tc3_cout_pad(Cout), packed);
+  return after_launch("pack_weights_tc3_kernel");
+}
+
+typedef CUresult (*EncodeTiledFn3)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*,
+                                   const cuuint64_t*, const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave,
+                                   CUtensorMapSwizzle, CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+
+static EncodeTiledFn3 get_encode_fn3() {
+  static EncodeTiledFn3 fn = nullptr;
+  if (fn == nullptr) {
+    void* ptr = nullptr;
+    cudaDriverEntryPointQueryResult q;
+    if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &ptr, cudaEnableDefault, &q) == cudaSuccess &&
+        q == cudaDriverEntryPointSuccess)
+      fn = reinterpret_cast<EncodeTiledFn3>(ptr);
+  }
+  return fn;
+}
+
+static int encode_map3(CUtensorMap* m, const void* base, int rank, const cuuint64_t* dims, const cuuint64_t* strides_b,
+                       const cuuint32_t* box, const cuuint32_t* estr) {
+  EncodeTiledFn3 fn = get_encode_fn3();
+  if (fn == nullptr) return fail(SODA_ERR_CUDA, "conv_tc: cuTensorMapEncodeTiled entry point not available");
+  CUresult r = fn(m, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, (cuuint32_t)rank, const_cast<void*>(base), dims, strides_b, box,
+                  estr, CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                  CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  if (r != CUDA_SUCCESS) {
+    set_error("conv_tc: cuTensorMapEncodeTiled failed (%d)", (int)r);
+    return (int)SODA_ERR_CUDA;
+  }
+  return 0;
+}
+
+template <int BN, bool LIF>
+static int launch_tc3(const CUtensorMap& tmA, const CUtensorMap& tmB, const Tc3Params& p, int grid, size_t smem,
+                      cudaStream_t st) {
+  static bool attr_set = false;
+  if (!attr_set) {
+    cudaError_t e = cudaFuncSetAttribute(conv_tc3_kernel<BN, LIF>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                         232448);
+    if (e != cudaSuccess) {
+      set_error("conv_tc: cudaFuncSetAttribute: %s", cudaGetErrorString(e));
+      return (int)SODA_ERR_CUDA;
+    }
+    attr_set = true;
+  }
+  conv_tc3_kernel<BN, LIF><<<grid, T3_THREADS, smem, st>>>(tmA, tmB, p);
+  return after_launch("conv_tc3_kernel");
+}
+
+bool conv_tc3_supported(const soda_conv_desc_t* d, const float* x) {
+  if (d->in_nchw || d->Cin % T3_BK != 0) return false;
+  if (d->in_pix_stride % 4 != 0 || d->in_batch_stride % 4 != 0) return false;
+  if ((reinterpret_cast<uintptr_t>(x) & 15) != 0) return false;
+  if (d->k != 1 && d->k != 3) return false;
+  if (d->stride != 1 && d->stride != 2) return false;
+  return true;
+}
+
+struct Tc3Lif {
+  int T;
+  NP np;
+  const float* v0;
+  const float* i0;
+  float* v_out;
+  float* i_out;
+};
+
+int conv_tc3_dispatch(const soda_conv_desc_t* d, const float* x, const float* packed, const float* shift,
+                      const float* residual, float* y, const Tc3Lif* lif, void* stream) {
+  if (!conv_tc3_supported(d, x))
+    return fail(SODA_ERR_UNSUPPORTED,
+                "conv_tc: needs pixel-major input, Cin % 32 == 0, 16-byte aligned strides, k in {1,3}, stride in {1,2}");
+  Tc3Params p;
+  memset(&p, 0, sizeof(p));
+  {
+    const char* e = getenv("SODA_TC_DBG");
+    p.dbg = e ? atoi(e) : 0;
+  }
+  p.H = d->H, p.W = d->W, p.Cin = d->Cin, p.Cout = d->Cout, p.k = d->k, p.stride = d->stride;
+  p.pad = d->k / 2;
+  p.Ho = (d->H + 2 * p.pad - d->k) / d->stride + 1;
+  p.Wo = (d->W + 2 * p.pad - d->k) / d->stride + 1;
+  if (p.Ho <= 0 || p.Wo <= 0) return fail(SODA_ERR_BAD_ARG, "conv: empty output");
+  p.taps = d->k * d->k;
+  p.cblocks = d->Cin / T3_BK;
+  p.kblocks = p.taps * p.cblocks;
+  p.a_exact = (d->flags & SODA_CONV_FLAG_INPUT_EXACT_TF32) ? 1 : 0;
+  p.total_pix = (int64_t)d->N * p.Ho * p.Wo;
+  p.out_bs = d->out_batch_stride, p.out_ps = d->out_pix_stride;
+  p.res_bs = d->res_batch_stride, p.res_ps = d->res_pix_stride;
+  p.shift = shift, p.residual = residual, p.y = y;
+  const bool is_lif = lif != nullptr;
+  if (is_lif) {
+    if (lif->T <= 0 || d->N % lif->T != 0) return fail(SODA_ERR_BAD_ARG, "conv_lif: N must be T * batch");
+    if (d->Cout % 16 != 0) return fail(SODA_ERR_UNSUPPORTED, "conv_lif: Cout must be a multiple of 16");
+    if (!lif->v_out || !lif->i_out) return fail(SODA_ERR_BAD_ARG, "conv_lif: null state output");
+    if ((lif->v0 == nullptr) != (lif->i0 == nullptr)) return fail(SODA_ERR_BAD_ARG, "conv_lif: v0 / i0 must come together");
+    p.lif = 1, p.np = lif->np, p.v0 = lif->v0, p.i0 = lif->i0, p.v_out = lif->v_out, p.i_out = lif->i_out;
+    p.T_inner = lif->T, p.Bsz = d->N / lif->T, p.n_outer = p.Bsz;
+  } else {
+    p.T_inner = 1, p.Bsz = d->N, p.n_outer = d->N;
+  }
+  const int BN = tc3_bn_for(d->Cout, is_lif);
+  const int Cout_pad = tc3_cout_pad(d->Cout);
+  p.nch = (d->Cout + BN - 1) / BN;
+  const uint32_t b_stage = 2u * BN * 128u;
+
+  CUtensorMap tmA, tmB;
+  const int64_t HW = (int64_t)d->H * d->W;
+  const bool frames_dense = d->N == 1 || d->in_batch_stride == HW * d->in_pix_stride;
+  p.mode = d->stride == 1 ? 0 : 1;
+  p.flat = (d->k == 1 && d->stride == 1 && frames_dense && !is_lif) ? 1 : 0;
+  p.rows = T3_BM, p.WW = T3_BW, p.sbo = 1024;
+  if (p.flat) {
+    p.n_spatial = (int)ceil_div(p.total_pix, T3_BM);
+    p.tiles_x = p.n_spatial, p.tiles_y = 1;
+    p.n_outer = 1;
+    const cuuint64_t dims[4] = {(cuuint64_t)d->Cin, (cuuint64_t)p.total_pix, 1, 1};
+    const cuuint64_t str[3] = {(cuuint64_t)d->in_pix_stride * 4, (cuuint64_t)p.total_pix * d->in_pix_stride * 4,
+                               (cuuint64_t)p.total_pix * d->in_pix_stride * 4};
+    const cuuint32_t box[4] = {T3_BK, T3_BM, 1, 1};
+    const cuuint32_t es[4] = {1, 1, 1, 1};
+    int rc = encode_map3(&tmA, x, 4, dims, str, box, es);
+    if (rc) return rc;
+  } else {
+    p.tiles_y = (int)ceil_div(p.Ho, T3_BH), p.tiles_x = (int)ceil_div(p.Wo, T3_BW);
+    p.n_spatial = p.tiles_x * p.tiles_y;
+    const cuuint64_t dims[4] = {(cuuint64_t)d->Cin, (cuuint64_t)d->W, (cuuint64_t)d->H, (cuuint64_t)d->N};
+    const cuuint64_t str[3] = {(cuuint64_t)d->in_pix_stride * 4, (cuuint64_t)d->W * d->in_pix_stride * 4,
+                               (cuuint64_t)(d->N == 1 ? HW * d->in_pix_stride : d->in_batch_stride) * 4};
+    if (p.mode == 0) {
+      p.WW = T3_BW + 2 * p.pad;
+      const int HH = T3_BH + 2 * p.pad;
+      p.rows = p.WW * HH;
+      p.sbo = (uint32_t)p.WW * 128u;
+      const cuuint32_t box[4] = {T3_BK, (cuuint32_t)p.WW, (cuuint32_t)HH, 1};
+      const cuuint32_t es[4] = {1, 1, 1, 1};
+      int rc = encode_map3(&tmA, x, 4, dims, str, box, es);
+      if (rc) return rc;
+    } else {
+      const cuuint32_t box[4] = {T3_BK, (cuuint32_t)(T3_BW * d->stride), (cuuint32_t)(T3_BH * d->stride), 1};
+      const cuuint32_t es[4] = {1, (cuuint32_t)d->stride, (cuuint32_t)d->stride, 1};
+      int rc = encode_map3(&tmA, x, 4, dims, str, box, es);
+      if (rc) return rc;
+    }
+  }
+  p.a_tx_bytes = (uint32_t)p.rows * 128u;
+  p.plane_bytes = (p.a_tx_bytes + 1023u) & ~1023u;
+  p.a_stage_bytes = 2u * p.plane_bytes;
+  {
+    const cuuint64_t dims[3] = {(cuuint64_t)d->Cin, (cuuint64_t)Cout_pad, (cuuint64_t)(2 * p.taps)};
+    const cuuint64_t str[2] = {(cuuint64_t)d->Cin * 4, (cuuint64_t)Cout_pad * d->Cin * 4};
+    const cuuint32_t box[3] = {T3_BK, (cuuint32_t)BN, 1};
+    const cuuint32_t es[3] = {1, 1, 1};
+    int rc = encode_map3(&tmB, packed, 3, dims, str, box, es);
+    if (rc) return rc;
+  }
+  // shared-memory plan: weights resident if one chunk fits beside a useful A ring, else two rings
+  const int64_t b_total = (int64_t)p.kblocks * b_stage;
+  const bool halo3 = p.mode == 0 && p.k == 3;
+  const int a_min = halo3 ? 2 : 3;
+  const int a_want = halo3 ? 3 : 6;
+  if (b_total + (int64_t)a_min * p.a_stage_bytes <= T3_SMEM_LIMIT && b_total < (1 << 20)) {
+    p.b_stationary = 1, p.b_stages = 1;
+    p.b_region_bytes = (uint32_t)b_total;
+    p.a_stages = (int)std::min<int64_t>(a_want, (T3_SMEM_LIMIT - b_total) / p.a_stage_bytes);
+  } else {
+    p.b_stationary = 0;
+    p.a_stages = halo3 ? 2 : 3;
+    p.b_stages = (int)std::min<int64_t>(T3_MAX_RING, (T3_SMEM_LIMIT - (int64_t)p.a_stages * p.a_stage_bytes) / b_stage);
+    if (p.b_stages < 2) return fail(SODA_ERR_UNSUPPORTED, "conv_tc: shared-memory plan does not fit");
+    p.b_region_bytes = (uint32_t)p.b_stages * b_stage;
+  }
+  p.n_items = p.nch * p.n_spatial * p.n_outer;
+  int grid = p.n_items < kNumSMs ? p.n_items : kNumSMs;
+  grid = grid / p.nch * p.nch;
+  if (grid < p.nch) grid = p.nch;
+  const size_t smem = (size_t)p.b_region_bytes + (size_t)p.a_stages * p.a_stage_bytes + 512 + 1024;
+  cudaStream_t st = (cudaStream_t)stream;
+  if (is_lif) {
+    if (BN == 32) return launch_tc3<32, true>(tmA, tmB, p, grid, smem, st);
+    return launch_tc3<64, true>(tmA, tmB, p, grid, smem, st);
+  }
+  if (BN == 32) return launch_tc3<32, false>(tmA, tmB, p, grid, smem, st);
+  if (BN == 64) return launch_tc3<64, false>(tmA, tmB, p, grid, smem, st);
+  return launch_tc3<128, false>(tmA, tmB, p, grid, smem, st);
+}
+
+int conv_tc3_lif_dispatch(const soda_conv_desc_t* d, const float* x, const float* packed, const float* shift,
+                          const float* residual, int T, const soda_neuron_params_t* np, const float* v0,
+                          const float* i0, float* y, float* v_out, float* i_out, void* stream) {
+  Tc3Lif l;
+  l.T = T, l.np = to_np(np), l.v0 = v0, l.i0 = i0, l.v_out = v_out, l.i_out = i_out;
+  return conv_tc3_dispatch(d, x, packed, shift, residual, y, &l, stream);
+}
+
+}  // namespace soda
