@@ -256,17 +256,23 @@ def run_gpu_arm(args):
         ms_e2e, _ = timed(step_e2e, args.steps, args.warmup)
 
         # ---- per-kernel-family device time of one eager step (CUDA events on the launch stream) --
+        # The GPU is parked on a spin kernel while the host enqueues the whole step, so that each
+        # (start, end) event pair brackets device time only, not host launch latency.
         prof = {}
+        step_device()
+        torch.cuda.synchronize()
+        torch.cuda._sleep(int(1.2e9))
         pkg.ops.PROFILE = prof
         step_device()
         torch.cuda.synchronize()
         pkg.ops.PROFILE = None
-        tags = prof.pop("conv2d_tags", [])
+        tags = {k: prof.pop(k + "_tags", []) for k in ("conv2d", "conv_lif")}
         fam = {k: sum(a.elapsed_time(b) for a, b in v) for k, v in prof.items()}
         if args.per_layer:
-            for tag, (a, b) in zip(tags, prof.get("conv2d", [])):
-                sys.stderr.write(f"conv {a.elapsed_time(b):8.3f} ms  {tag}\n")
-        n_conv = len(prof.get("conv2d", []))
+            for k in ("conv2d", "conv_lif"):
+                for tag, (a, b) in zip(tags[k], prof.get(k, [])):
+                    sys.stderr.write(f"{k:8s} {a.elapsed_time(b):8.3f} ms  {tag}\n")
+        n_conv = len(prof.get("conv2d", [])) + len(prof.get("conv_lif", []))
         rate = float((g_cls.abs() > 0).float().mean())
 
     frames_per_step = T * B
@@ -274,7 +280,7 @@ def run_gpu_arm(args):
     value = world * frames_per_step / (ms_per_step * 1e-3)
     e2e_value = world * frames_per_step / (ms_e2e / args.steps * 1e-3)
     pk, pk_src = peaks()
-    conv_ms = fam.get("conv2d", 0.0)
+    conv_ms = fam.get("conv2d", 0.0) + fam.get("conv_lif", 0.0)
     conv_flops = GFLOP_PER_FRAME * 1e9 * frames_per_step * (1.0 if T == T_STEPS or True else 1.0)
     achieved = conv_flops / (conv_ms * 1e-3) / 1e12 if conv_ms > 0 else None
     peak = pk["bf16_tflops_sustained"]

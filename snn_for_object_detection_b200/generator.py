@@ -16,6 +16,7 @@ of T*B images, neuron cells scan T steps inside one kernel with the membrane sta
 from __future__ import annotations
 
 import inspect
+import os
 from typing import List, Optional, Tuple, Union
 
 import torch
@@ -23,7 +24,7 @@ from torch import nn
 
 from . import ops
 from .modules import *  # noqa: F401,F403
-from .modules.cells import LICell, LIFCell, SNNCell
+from .modules.cells import LICell, LIFCell, LIFFeedForwardState, SNNCell
 from .modules.common import SodaBatchNorm2d, SodaConv2d, StateStorage, Storage
 from .modules.layer_gen import Dense, LayerGen, Residual, Return
 from .utils.anchors import AnchorGenerator
@@ -50,6 +51,26 @@ def _has_state(block: "BlockGen") -> bool:
 def _copy_into(src: torch.Tensor, dst: torch.Tensor) -> None:
     """Strided pixel-major copy on our own kernel (concat-slice store, generator.py:158)."""
     ops.channel_affine(src, None, None, out=dst)
+
+
+def _fused_lif_plan(conv: SodaConv2d, norm: SodaBatchNorm2d, x: torch.Tensor, T: int):
+    """Packed weights for the fused Conv->Norm->LIF kernel, or None when the unfused pair
+    (conv over T*B images + stand-alone scan) is the better launch.  The fused kernel walks the T
+    steps inside one work item, so it needs (channel chunks x spatial tiles x samples) >= about one
+    wave of CTAs; small maps at small batch stay unfused."""
+    if conv.bias is not None or conv.groups != 1 or conv.dilation != (1, 1):
+        return None
+    k, s = conv.kernel_size[0], conv.stride[0]
+    kind = ops.conv_kind_for(x, conv.in_channels, k, s)
+    pc = conv.packed(norm, kind)
+    if not ops.conv_lif_supported(x, pc):
+        return None
+    Ho, Wo = ops.conv_out_hw(x.shape[2], x.shape[3], k, s)
+    B = x.shape[0] // T
+    items = -(-pc.Cout // (32 if pc.Cout <= 32 else 64)) * (-(-Ho // 16)) * (-(-Wo // 8)) * B
+    if T > 1 and items < int(os.environ.get("SODA_FUSE_LIF_MIN_ITEMS", "96")):
+        return None
+    return pc
 
 
 class BlockGen(nn.Module):
@@ -133,8 +154,18 @@ class BlockGen(nn.Module):
                 c0 += self.branch_channels[bi]
             elif self.merge == "forward":
                 dst = out
-            outs.append(self._run_branch(X, T, branch, flags, branch_state, dst))
+            # Residual([[..., Conv, Norm, LIF], [Pass]]): the identity branch is added in the fused
+            # Conv->Norm->LIF epilogue of the other branch instead of a separate add_n pass.
+            fuse_res = None
+            if self.merge == "residual" and len(self.net) == 2 and self._is_identity(self.net[1 - bi]):
+                fuse_res = X
+            Y, consumed = self._run_branch(X, T, branch, flags, branch_state, dst, fuse_res, out)
             out_state.append(branch_state)
+            if consumed:
+                # the other branch is the identity: its state list is all None
+                other = [None] * len(self.net[1 - bi])
+                return Y, ([branch_state, other] if bi == 0 else [other, branch_state])
+            outs.append(Y)
         if self.merge == "dense":
             return dense_buf, out_state
         if self.merge == "residual":
@@ -159,9 +190,15 @@ class BlockGen(nn.Module):
                 H, W = (H - k) // s + 1, (W - k) // s + 1
         return H, W
 
-    def _run_branch(self, X, T, branch, flags, branch_state, dst):
-        """Runs one branch; fuses Conv+Norm(eval) and LI+Tanh; the branch's last layer writes
-        straight into ``dst`` (concat slice / caller's buffer) when it can."""
+    @staticmethod
+    def _is_identity(branch) -> bool:
+        return len(branch) > 0 and all(type(m) is nn.Identity for m in branch)
+
+    def _run_branch(self, X, T, branch, flags, branch_state, dst, residual=None, residual_dst=None):
+        """Runs one branch; fuses Conv+Norm(eval)(+LIF) and LI+Tanh; the branch's last layer writes
+        straight into ``dst`` (concat slice / caller's buffer) when it can.  ``residual``: tensor the
+        caller wants added to the branch result (then written to ``residual_dst`` if given); returns
+        ``(Y, residual_consumed)``."""
         n = len(branch)
         Y = X
         idx = 0
@@ -173,18 +210,35 @@ class BlockGen(nn.Module):
                 if idx + 1 < n and isinstance(branch[idx + 1], SodaBatchNorm2d) and not branch[idx + 1].training:
                     norm = branch[idx + 1]
                     last = idx + 1
+                cell = branch[last + 1] if last + 1 < n else None
+                if norm is not None and type(cell) is LIFCell and not torch.is_grad_enabled():
+                    pc = _fused_lif_plan(layer, norm, Y, T)
+                    if pc is not None:
+                        # Conv -> Norm -> LIF over all T steps in one kernel, membrane state on-chip
+                        last += 1
+                        is_last = last == n - 1
+                        st = branch_state[last]
+                        v0, i0 = (None, None) if st is None else (st.v, st.i)
+                        Y, v, i = ops.conv_lif(Y, pc, T, cell._const, v0, i0,
+                                               residual=residual if is_last else None,
+                                               out=(dst if residual is None else residual_dst) if is_last else None)
+                        branch_state[last] = LIFFeedForwardState(v, i)
+                        idx = last + 1
+                        if is_last:
+                            return Y, residual is not None
+                        continue
                 o = dst if last == n - 1 else None
                 Y = layer(Y, norm=norm, out=o)
                 idx = last + 1
                 if o is not None:
-                    return Y
+                    return Y, False
                 continue
             if isinstance(layer, BlockGen):
                 o = dst if idx == n - 1 else None
                 Y, branch_state[idx] = layer.forward_seq(Y, T, branch_state[idx], out=o)
                 idx += 1
                 if o is not None:
-                    return Y
+                    return Y, False
                 continue
             if isinstance(layer, (SNNCell, StateStorage)):
                 fuse = (
@@ -217,7 +271,7 @@ class BlockGen(nn.Module):
         if dst is not None and dst.data_ptr() != Y.data_ptr():
             _copy_into(Y, dst)
             Y = dst
-        return Y
+        return Y, False
 
 
 class ModelGen(nn.Module):

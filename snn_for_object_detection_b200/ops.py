@@ -43,7 +43,8 @@ __all__ = [
 # When set to a dict, every op records a (start, end) CUDA-event pair on the launching stream under
 # its family name: bench.py uses it for the per-kernel-family device time of one eager step.
 PROFILE = None
-CONV_KERNEL_NAME = "conv_tc2_kernel (tcgen05: tf32 main + bf16 correction pass) + conv_ffma_kernel (Cin % 32 != 0)"
+CONV_KERNEL_NAME = ("conv_tc3_kernel (tcgen05/TMEM/TMA implicit GEMM, tf32 main + bf16 correction pass, fused BN/LIF/residual "
+                    "epilogue) + conv_ffma_kernel (Cin % 32 != 0)")
 
 
 def _prof(name):
@@ -56,9 +57,9 @@ def _prof(name):
             r = fn(*a, **k)
             e1.record()
             PROFILE.setdefault(name, []).append((e0, e1))
-            if name == "conv2d":
+            if name in ("conv2d", "conv_lif"):
                 x, pc = a[0], a[1]
-                PROFILE.setdefault("conv2d_tags", []).append(
+                PROFILE.setdefault(name + "_tags", []).append(
                     f"{tuple(x.shape)}->{pc.Cout} k{pc.k} s{pc.stride} kind{pc.kind} exact{int(is_exact(x))}")
             return r
 

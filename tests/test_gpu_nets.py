@@ -61,7 +61,13 @@ def test_vgg_time_major_equals_layer_major():
     assert torch.equal(torch.cat([y1, y2]), Yseq)
 
 
-def test_tiny_yolo_matches_golden_reference_output():
+def test_tiny_yolo_matches_golden_reference_output(monkeypatch):
+    """End-to-end golden outputs (oracle/make_golden.py, produced by the reference's own model code).
+    Run on the FP32-pipe convolution: the calibrated random-weight net is chaotic (one borderline spike
+    flip in an early layer grows to percent-level differences 15 LIF layers later, DESIGN.md "Parity"),
+    so an end-to-end equality only holds for an accumulation that happens not to flip any neuron on this
+    seed.  The tensor-core path is held to the per-block gate and the first-divergence test below."""
+    monkeypatch.setenv("SODA_CONV_KIND", "fp32")
     model, X, g, digest_ok = tiny_yolo_from_golden()
     assert digest_ok
     cls_ref, bbox_ref = torch.from_numpy(g["cls"]), torch.from_numpy(g["bbox"])
@@ -174,9 +180,51 @@ def test_tiny_yolo_end_to_end_fp32_pipe(monkeypatch):
         assert _rel(a.cpu(), b) < 5e-4
 
 
-def test_tiny_yolo_detections_identical():
+def test_tiny_yolo_end_to_end_tensor_core_first_divergence():
+    """End to end on the tcgen05 path (the default).  Walk the 19 LIF layers in execution order: every
+    layer before the first one with a flipped spike must agree with the oracle exactly (spikes) and
+    within 1e-4 relative (membranes); in the first layer that has flips, every flipped neuron must have
+    been within 1e-4 * max|v| of the threshold on the non-spiking side - i.e. the divergence is a
+    threshold decision inside the membrane tolerance, not an arithmetic error.  Later layers see
+    different inputs and are not comparable (chaotic amplification)."""
+    from snn_for_object_detection_b200.modules.common import StateStorage
+
+    model, X = _storage_model()
+    taps = {}
+    onr.soda_forward(model, X, taps)
+    cells = [(n, m) for n, m in model.named_modules()
+             if isinstance(m, StateStorage) and type(m.module).__name__ == "LIFCell"]
+    assert len(cells) == 19
+    ref = {n: taps[id(m)] for n, m in cells}
+    model = model.to(DEV)
+    with torch.no_grad():
+        model(X.to(DEV))
+    clean_layers = 0
+    for n, m in cells:
+        outs = torch.stack([o for o, _ in ref[n]])
+        v_ref = torch.stack([s.v for _, s in ref[n]])
+        got, v = m.get_spikes().cpu(), m.get_state().v.cpu()
+        flips = got != outs
+        vmax = float(v_ref.abs().max())
+        if not flips.any():
+            assert float((v - v_ref).abs().max()) <= V_RTOL * vmax, n
+            clean_layers += 1
+            continue
+        assert float(flips.float().mean()) <= SPIKE_TOL, n
+        # earliest flipped step of each neuron: its input history was identical up to there
+        first_t = flips.float().argmax(dim=0, keepdim=True)
+        first = torch.zeros_like(flips).scatter_(0, first_t, True) & flips
+        side = torch.where(outs == 0, v_ref, v)[first]   # post-step membrane of the side that did not spike
+        assert float((side - 1.0).abs().max()) <= V_RTOL * vmax, (n, float((side - 1.0).abs().max()))
+        break
+    assert clean_layers >= 1
+    print(f"first divergence after {clean_layers} bit-identical LIF layers")
+
+
+def test_tiny_yolo_detections_identical(monkeypatch):
     from snn_for_object_detection_b200.utils import box
 
+    monkeypatch.setenv("SODA_CONV_KIND", "fp32")  # see test_tiny_yolo_matches_golden_reference_output
     model, X, g, _ = tiny_yolo_from_golden()
     anchors, cls_ref, bbox_ref = (torch.from_numpy(g[k]) for k in ("anchors", "cls", "bbox"))
     model = model.to(DEV)
@@ -224,3 +272,48 @@ def test_full_size_gen1_forward_properties():
     assert torch.isfinite(cls).all() and torch.isfinite(bbox).all()
     assert torch.equal(torch.cat([cls_a, cls_b]), cls) and torch.equal(torch.cat([bbox_a, bbox_b]), bbox)
     assert float(cls.std()) > 0
+
+
+def _flat_states(state, acc=None):
+    acc = [] if acc is None else acc
+    if state is None:
+        return acc
+    if isinstance(state, (list,)):
+        for s in state:
+            _flat_states(s, acc)
+    elif hasattr(state, "v"):
+        acc.append(state.v)
+        acc.append(state.i)
+    return acc
+
+
+def test_fused_conv_norm_lif_planner_equals_unfused(monkeypatch):
+    """The planner's fused route (Conv -> Norm -> LIF (+ Residual identity) in ONE kernel, membrane
+    state on-chip over all T steps) gives bit-identical predictions and final states to the unfused
+    route (conv over T*B images, stand-alone scan, add_n), and launches fewer kernels."""
+    from snn_for_object_detection_b200 import _lib
+
+    model = calibrated_tiny_yolo(seed=3).to(DEV)
+    gen = torch.Generator().manual_seed(7)
+    X = (torch.rand(5, 2, 2, 128, 160, generator=gen) < 0.07).float().to(DEV)
+    with torch.no_grad():
+        monkeypatch.setenv("SODA_FUSE_LIF_MIN_ITEMS", "1")
+        model.forward_seq(X)  # weight packing out of the launch count
+        n0 = _lib.launch_count()
+        preds_f, state_f = model.forward_seq(X)
+        n_fused = _lib.launch_count() - n0
+        # streaming: split the sequence and carry the state through the fused kernel's v0 / i0
+        _, s1 = model.forward_seq(X[:2])
+        preds_s, state_s = model.forward_seq(X[2:], s1)
+        monkeypatch.setenv("SODA_FUSE_LIF", "0")
+        n0 = _lib.launch_count()
+        preds_u, state_u = model.forward_seq(X)
+        n_unfused = _lib.launch_count() - n0
+    assert n_fused < n_unfused - 20, (n_fused, n_unfused)
+    for a, b, c in zip(preds_f, preds_u, preds_s):
+        assert torch.equal(a, b) and torch.equal(a, c)
+    fa, fb, fc = _flat_states(state_f), _flat_states(state_u), _flat_states(state_s)
+    assert len(fa) == len(fb) == len(fc) == 2 * 22
+    for a, b, c in zip(fa, fb, fc):
+        assert torch.equal(a, b) and torch.equal(a, c)
+    assert float(preds_f[1].std()) > 0
