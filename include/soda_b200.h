@@ -133,7 +133,10 @@ SODA_API int soda_conv2d_fwd(const soda_conv_desc_t* d, const float* x, const fl
  *   v_out, i_out : state after step T-1, same layout (never NULL)
  *   The work item of the kernel is (sample, pixel tile, channel chunk) and t runs inside it, so the
  *   membrane state lives in registers for all T steps.  LIF arithmetic is op-for-op soda_lif_fwd's.
- *   Needs d->kind == SODA_CONV_TC and Cout % 16 == 0.
+ *   d->kind == SODA_CONV_TC : tcgen05 kernel, needs Cout % 16 == 0.
+ *   d->kind == SODA_CONV_FP32 with in_nchw = 1 (the event frames, Cin = 2): direct FP32-pipe kernel
+ *       for tiny K = Cin*k*k (Cin*k*k*Cout <= 11000, Cout % 8 == 0, no residual): one thread owns 8
+ *       channels of one pixel for all T steps.
  * ------------------------------------------------------------------------------------------- */
 SODA_API int soda_conv_lif_fwd(const soda_conv_desc_t* d, const float* x, const float* packed,
                       const float* shift, const float* residual, int T,
@@ -167,6 +170,19 @@ typedef struct soda_neuron_params_s {
 SODA_API int soda_lif_fwd(const soda_neuron_params_t* p, const float* x, const float* v0, const float* i0,
                  int T, int64_t n, float* out, float* v_out, float* i_out, float* v_dec_trace,
                  float* v_trace, float* i_trace, void* stream);
+
+/* LIF scan with the Residual sum and the Dense concat-slice store fused (one pass instead of
+ * scan + add_n + slice copy).
+ *   replaces: LIFCell (layer_gen.py:233) as the last layer of a Residual branch whose other branch
+ *             is Pass (models/tiny_yolo.py:60-65; sum at models/generator.py:146), the result
+ *             being one input of a Dense cat (generator.py:158).
+ *   x, v0, i0, v_out, i_out : dense pixel-major, x = [T][n_pix][C], state = [n_pix][C]
+ *   residual : NULL or element (t, q, c) at residual[(t*n_pix + q)*res_pix_stride + c]
+ *   out      : element (t, q, c) at out[(t*n_pix + q)*out_pix_stride + c] = z (+ residual)
+ *   Needs C % 4 == 0, strides % 4 == 0, 16-byte aligned pointers. */
+SODA_API int soda_lif_res_fwd(const soda_neuron_params_t* p, const float* x, const float* v0, const float* i0,
+                     int T, int64_t n_pix, int C, const float* residual, int64_t res_pix_stride,
+                     float* out, int64_t out_pix_stride, float* v_out, float* i_out, void* stream);
 
 SODA_API int soda_li_fwd(const soda_neuron_params_t* p, const float* x, const float* v0, const float* i0,
                 int T, int64_t n, int apply_tanh, float* out, float* v_out, float* i_out,

@@ -102,6 +102,29 @@ def run_lif(spec, T=8, iters=5):
           f"mismatch {mism:.2e} dv {dv:.2e}", flush=True)
 
 
+def run_direct(spec, iters=5):
+    """Event-frame layer: direct Conv->BN->LIF kernel vs conv2d(fp32) + lif_scan.  spec = T,B,H,W,Cout,k,s"""
+    T, B, H, W, Cout, k, s = map(int, spec.split(","))
+    dev = "cuda"
+    g = torch.Generator(device=dev).manual_seed(3)
+    x = (torch.rand(T * B, 2, H, W, device=dev, generator=g) < 0.07).float()
+    w = torch.randn(Cout, 2, k, k, device=dev, generator=g)
+    pc = ops.pack_conv(w, s, None, torch.zeros(Cout, device=dev), _lib.SODA_CONV_FP32)
+    y0 = ops.conv2d(x, pc)
+    z0, v0, i0, _, _, _ = ops.lif_scan(y0, T)
+    z1, v1, i1 = ops.conv_lif(x, pc, T, ops.LIF_DEFAULT)
+    torch.cuda.synchronize()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for _ in range(iters):
+        ops.conv_lif(x, pc, T, ops.LIF_DEFAULT)
+    e1.record()
+    torch.cuda.synchronize()
+    ms = e0.elapsed_time(e1) / iters
+    print(f"DIRECT {spec:30s} {ms:8.4f} ms  {z1.numel() * 4 / ms / 1e6:8.1f} GB/s out  rate {float(z1.mean()):.3f} "
+          f"equal {bool(torch.equal(z0, z1) and torch.equal(v0, v1))}", flush=True)
+
+
 if __name__ == "__main__":
     specs = [a for a in sys.argv[1:] if not a.startswith("--")] or DEFAULT
     iters = 10
@@ -112,6 +135,8 @@ if __name__ == "__main__":
         for sp in specs:
             if sp.startswith("lif:"):
                 run_lif(sp[4:])
+            elif sp.startswith("direct:"):
+                run_direct(sp[7:])
             else:
                 run(sp, iters=iters, check="--nocheck" not in sys.argv)
 

@@ -20,6 +20,9 @@ int conv_tc3_lif_dispatch(const soda_conv_desc_t* d, const float* x, const float
                           const soda_neuron_params_t* np, const float* v0, const float* i0, float* y,
                           float* v_out, float* i_out, void* stream);
 bool conv_tc3_supported(const soda_conv_desc_t* d, const float* x);
+int conv_direct_lif_dispatch(const soda_conv_desc_t* d, const float* x, const float* wp, int cout_pad,
+                             const float* shift, int T, const soda_neuron_params_t* np, const float* v0,
+                             const float* i0, float* y, float* v_out, float* i_out, void* stream);
 static inline int cout_pad_of(int Cout) { return (Cout + 31) / 32 * 32; }
 }  // namespace soda
 
@@ -66,6 +69,10 @@ extern "C" int soda_conv_lif_fwd(const soda_conv_desc_t* d, const float* x, cons
     return fail(SODA_ERR_BAD_ARG, "conv_lif: null pointer");
   if (d->N <= 0 || d->H <= 0 || d->W <= 0 || d->Cin <= 0 || d->Cout <= 0 || d->k <= 0 || d->stride <= 0)
     return fail(SODA_ERR_BAD_ARG, "conv_lif: non-positive size");
-  if (d->kind != SODA_CONV_TC) return fail(SODA_ERR_UNSUPPORTED, "conv_lif: tensor-core kind only");
+  if (d->kind == SODA_CONV_FP32) {
+    if (residual != nullptr) return fail(SODA_ERR_UNSUPPORTED, "conv_lif(fp32): no residual input");
+    return conv_direct_lif_dispatch(d, x, packed, cout_pad_of(d->Cout), shift, T, np, v0, i0, y, v_out, i_out, stream);
+  }
+  if (d->kind != SODA_CONV_TC) return fail(SODA_ERR_UNSUPPORTED, "conv_lif: unknown kind");
   return conv_tc3_lif_dispatch(d, x, packed, shift, residual, T, np, v0, i0, y, v_out, i_out, stream);
 }

@@ -187,6 +187,56 @@ neuron_bwd_kernel(NP p, const float* __restrict__ gout, const float* __restrict_
   if (gi0 != nullptr) vstore<V>(gi0 + e, gi);
 }
 
+// LIF scan whose output goes through a pixel stride (a channel slice of a Dense concat buffer) with
+// an optional residual add: out = z (+ residual).  One pass instead of scan + add_n + slice copy
+// (Residual sum models/generator.py:146, Dense cat :158).  x and the state are dense [T][P][C].
+__global__ void __launch_bounds__(256)
+lif_res_fwd_kernel(NP p, const float* __restrict__ x, const float* __restrict__ v0,
+                   const float* __restrict__ i0, int T, int64_t P, int C,
+                   const float* __restrict__ res, int64_t res_ps, float* __restrict__ out, int64_t out_ps,
+                   float* __restrict__ v_out, float* __restrict__ i_out) {
+  const int64_t n = P * C;
+  const int64_t e = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) * 4;
+  if (e >= n) return;
+  const int64_t q = e / C;
+  const int c = (int)(e - q * C);
+  float v[4], i[4];
+  if (v0 != nullptr) {
+    vload<4>(v, v0 + e);
+    vload<4>(i, i0 + e);
+  } else {
+#pragma unroll
+    for (int k = 0; k < 4; ++k) v[k] = p.v_leak, i[k] = 0.0f;
+  }
+  for (int t0 = 0; t0 < T; t0 += kUnroll) {
+    float xs[kUnroll][4], rs[kUnroll][4];
+#pragma unroll
+    for (int u = 0; u < kUnroll; ++u) {
+      if (t0 + u < T) {
+        vload<4>(xs[u], x + (int64_t)(t0 + u) * n + e);
+        if (res != nullptr) {
+          const float4 r4 = __ldg(reinterpret_cast<const float4*>(res + ((int64_t)(t0 + u) * P + q) * res_ps + c));
+          rs[u][0] = r4.x, rs[u][1] = r4.y, rs[u][2] = r4.z, rs[u][3] = r4.w;
+        }
+      }
+    }
+#pragma unroll
+    for (int u = 0; u < kUnroll; ++u) {
+      if (t0 + u < T) {
+        float o[4], vd;
+#pragma unroll
+        for (int k = 0; k < 4; ++k) {
+          lif_step(p, xs[u][k], v[k], i[k], o[k], vd);
+          if (res != nullptr) o[k] = __fadd_rn(o[k], rs[u][k]);
+        }
+        vstore<4>(out + ((int64_t)(t0 + u) * P + q) * out_ps + c, o);
+      }
+    }
+  }
+  vstore<4>(v_out + e, v);
+  vstore<4>(i_out + e, i);
+}
+
 static bool all_aligned16(std::initializer_list<const void*> ptrs) {
   for (const void* q : ptrs)
     if (q != nullptr && (reinterpret_cast<uintptr_t>(q) & 15) != 0) return false;
@@ -244,6 +294,23 @@ extern "C" int soda_lif_fwd(const soda_neuron_params_t* p, const float* x, const
                             void* stream) {
   return soda::launch_fwd<0>(p, x, v0, i0, T, n, out, v_out, i_out, v_dec_trace, v_trace, i_trace,
                              stream, "lif_fwd");
+}
+
+extern "C" int soda_lif_res_fwd(const soda_neuron_params_t* q, const float* x, const float* v0,
+                                const float* i0, int T, int64_t n_pix, int C, const float* residual,
+                                int64_t res_pix_stride, float* out, int64_t out_pix_stride,
+                                float* v_out, float* i_out, void* stream) {
+  using namespace soda;
+  if (!q || !x || !out || !v_out || !i_out) return fail(SODA_ERR_BAD_ARG, "lif_res_fwd: null pointer");
+  if (T <= 0 || n_pix <= 0 || C <= 0) return fail(SODA_ERR_BAD_ARG, "lif_res_fwd: non-positive size");
+  if ((v0 == nullptr) != (i0 == nullptr)) return fail(SODA_ERR_BAD_ARG, "lif_res_fwd: v0 / i0 must come together");
+  if (C % 4 != 0 || out_pix_stride % 4 != 0 || (residual != nullptr && res_pix_stride % 4 != 0) ||
+      !all_aligned16({x, v0, i0, out, v_out, i_out, residual}))
+    return fail(SODA_ERR_UNSUPPORTED, "lif_res_fwd: needs C % 4 == 0, strides % 4 == 0 and 16-byte aligned buffers");
+  const int64_t blocks = ceil_div(n_pix * C / 4, 256);
+  lif_res_fwd_kernel<<<(unsigned)blocks, 256, 0, (cudaStream_t)stream>>>(
+      to_np(q), x, v0, i0, T, n_pix, C, residual, res_pix_stride, out, out_pix_stride, v_out, i_out);
+  return after_launch("lif_res_fwd");
 }
 
 extern "C" int soda_li_fwd(const soda_neuron_params_t* p, const float* x, const float* v0,

@@ -22,7 +22,7 @@ from typing import List, Optional, Tuple, Union
 import torch
 from torch import nn
 
-from . import ops
+from . import _lib, ops
 from .modules import *  # noqa: F401,F403
 from .modules.cells import LICell, LIFCell, LIFFeedForwardState, SNNCell
 from .modules.common import SodaBatchNorm2d, SodaConv2d, StateStorage, Storage
@@ -65,10 +65,16 @@ def _fused_lif_plan(conv: SodaConv2d, norm: SodaBatchNorm2d, x: torch.Tensor, T:
     pc = conv.packed(norm, kind)
     if not ops.conv_lif_supported(x, pc):
         return None
+    if pc.kind != _lib.SODA_CONV_TC:
+        return pc  # direct small-K kernel (event-frame layer): thread-per-pixel, always enough work
     Ho, Wo = ops.conv_out_hw(x.shape[2], x.shape[3], k, s)
     B = x.shape[0] // T
     items = -(-pc.Cout // (32 if pc.Cout <= 32 else 64)) * (-(-Ho // 16)) * (-(-Wo // 8)) * B
     if T > 1 and items < int(os.environ.get("SODA_FUSE_LIF_MIN_ITEMS", "96")):
+        return None
+    # The fused kernel keeps 2 x 32 state registers per epilogue thread, i.e. 64-channel chunks with
+    # N = 64 MMAs; measured on B200 it beats conv + scan (+ add) only for the 32-channel layers.
+    if pc.Cout > int(os.environ.get("SODA_FUSE_LIF_MAX_COUT", "32")):
         return None
     return pc
 
@@ -240,6 +246,18 @@ class BlockGen(nn.Module):
                 if o is not None:
                     return Y, False
                 continue
+            if (type(layer) is LIFCell and idx == n - 1 and not torch.is_grad_enabled()
+                    and (residual is not None or dst is not None)):
+                # last layer of the branch: the scan adds the Residual identity and stores straight
+                # into the destination (concat slice) in the same pass
+                o = dst if residual is None else residual_dst
+                Yc = Y if Y.is_contiguous(memory_format=torch.channels_last) else None
+                if Yc is not None and ops.lif_scan_out_ok(Yc, residual, o):
+                    st = branch_state[idx]
+                    v0, i0 = (None, None) if st is None else (st.v, st.i)
+                    Y, v, i = ops.lif_scan_out(Yc, T, v0, i0, layer._const, residual=residual, out=o)
+                    branch_state[idx] = LIFFeedForwardState(v, i)
+                    return Y, residual is not None
             if isinstance(layer, (SNNCell, StateStorage)):
                 fuse = (
                     isinstance(layer, LICell)

@@ -29,6 +29,7 @@ __all__ = [
     "conv2d",
     "conv_lif",
     "lif_scan",
+    "lif_scan_out",
     "li_scan",
     "lif_scan_bwd",
     "li_scan_bwd",
@@ -289,9 +290,18 @@ def conv2d(
     return out
 
 
+def _direct_lif_ok(x: torch.Tensor, pc: "PackedConv") -> bool:
+    """Direct FP32-pipe Conv->BN->LIF kernel: plain NCHW frames, tiny K (the event-frame layer)."""
+    return (pc.kind == _lib.SODA_CONV_FP32 and x.is_contiguous() and x.shape[1] > 1 and x.shape[2] * x.shape[3] > 1
+            and pc.Cout % 8 == 0 and pc.Cin * pc.k * pc.k * pc.Cout <= 11000)
+
+
 def conv_lif_supported(x: torch.Tensor, pc: "PackedConv") -> bool:
-    """The fused Conv->BN->LIF kernel takes tensor-core convolutions with Cout % 16 == 0."""
-    return pc.kind == _lib.SODA_CONV_TC and pc.Cout % 16 == 0 and os.environ.get("SODA_FUSE_LIF", "1") != "0"
+    """The fused Conv->BN->LIF kernels: tensor-core convolutions with Cout % 16 == 0, or the direct
+    small-K kernel on NCHW frames."""
+    if os.environ.get("SODA_FUSE_LIF", "1") == "0":
+        return False
+    return (pc.kind == _lib.SODA_CONV_TC and pc.Cout % 16 == 0) or _direct_lif_ok(x, pc)
 
 
 @_prof("conv_lif")
@@ -320,9 +330,14 @@ def conv_lif(
     d = ConvDesc()
     d.N, d.H, d.W, d.Cin, d.Cout, d.k, d.stride, d.kind = N, H, W, Cin, pc.Cout, pc.k, pc.stride, pc.kind
     d.flags = _lib.SODA_CONV_FLAG_INPUT_EXACT_TF32 if is_exact(x) else 0
-    x = to_pixel_major(x)
-    d.in_nchw = 0
-    d.in_batch_stride, d.in_pix_stride = _pm_strides(x)
+    if _direct_lif_ok(x, pc):
+        d.in_nchw = 1
+        if residual is not None:
+            raise ValueError("conv_lif: the direct (NCHW frames) kernel takes no residual")
+    else:
+        x = to_pixel_major(x)
+        d.in_nchw = 0
+        d.in_batch_stride, d.in_pix_stride = _pm_strides(x)
     if out is None:
         out = empty_pixel_major(N, pc.Cout, Ho, Wo, x.device)
     elif out.shape != (N, pc.Cout, Ho, Wo):
@@ -420,6 +435,67 @@ def lif_scan(
         "soda_lif_fwd",
     )
     return z, v, i, vd, vt, it
+
+
+def _pix_dense(t: torch.Tensor) -> Optional[int]:
+    """Pixel stride of a pixel-major tensor whose pixels (over N, H, W) are equally spaced, else None."""
+    st = _pm_strides(t)
+    if st is None:
+        return None
+    bs, ps = st
+    if t.shape[0] > 1 and bs != t.shape[2] * t.shape[3] * ps:
+        return None
+    return ps
+
+
+def lif_scan_out_ok(x: torch.Tensor, residual: Optional[torch.Tensor], out: Optional[torch.Tensor]) -> bool:
+    if x.dim() != 4 or x.shape[1] % 4 or not x.is_contiguous(memory_format=torch.channels_last):
+        return False
+    for t in (residual, out):
+        if t is None:
+            continue
+        ps = _pix_dense(t)
+        if t.shape != x.shape or ps is None or ps % 4 or t.data_ptr() % 16:
+            return False
+    return True
+
+
+@_prof("lif_scan")
+def lif_scan_out(
+    x: torch.Tensor,
+    T: int,
+    v0: Optional[torch.Tensor] = None,
+    i0: Optional[torch.Tensor] = None,
+    p: NeuronConst = None,
+    residual: Optional[torch.Tensor] = None,
+    out: Optional[torch.Tensor] = None,
+):
+    """``LIF_T(x) (+ residual)`` written straight into ``out`` (may be a channel slice of a concat
+    buffer).  ``x [T*B, C, H, W]`` dense pixel-major.  Returns ``(out, v_T, i_T)``."""
+    _need_cuda(x, v0, i0, residual, out)
+    p = LIF_DEFAULT if p is None else p
+    N, Cc, H, W = x.shape
+    if N % T:
+        raise ValueError("lif_scan_out: leading dimension is not a multiple of T")
+    if not lif_scan_out_ok(x, residual, out):
+        raise ValueError("lif_scan_out: unsupported layout (see lif_scan_out_ok)")
+    if out is None:
+        out = torch.empty_like(x)
+    v = torch.empty_like(x[: N // T])
+    i = torch.empty_like(v)
+    if v0 is not None:
+        v0 = _like_block(v0, v)
+        i0 = _like_block(i0, v)
+    pc = p.c()
+    check(
+        lib.soda_lif_res_fwd(C.byref(pc), x.data_ptr(), _ptr(v0), _ptr(i0), T, (N // T) * H * W, Cc, _ptr(residual),
+                             0 if residual is None else _pix_dense(residual), out.data_ptr(), _pix_dense(out),
+                             v.data_ptr(), i.data_ptr(), _stream()),
+        "soda_lif_res_fwd",
+    )
+    if residual is None:
+        mark_exact(out)
+    return out, v, i
 
 
 def _like_block(s: torch.Tensor, ref: torch.Tensor) -> torch.Tensor:

@@ -286,6 +286,104 @@ def test_conv2d_tcgen05_channel_slice_input():
     assert float((y.double() - ref).abs().max() / ref.abs().max()) < 1e-5
 
 
+# ----------------------------------------------------------------------------------------------
+# fused Conv -> BN -> LIF kernels and the residual / slice-store scan
+# ----------------------------------------------------------------------------------------------
+FUSED_CASES = [
+    # T, B, Cin, H, W, Cout, k, s, residual
+    (5, 2, 32, 30, 38, 32, 3, 1, True),
+    (4, 3, 64, 17, 23, 64, 3, 1, True),
+    (6, 1, 64, 32, 40, 128, 3, 2, False),
+    (3, 2, 128, 16, 24, 256, 3, 2, False),
+    (4, 2, 96, 15, 19, 64, 1, 1, False),
+    (7, 1, 128, 8, 10, 128, 3, 1, True),
+]
+
+
+@pytest.mark.parametrize("case", FUSED_CASES)
+def test_conv_lif_tcgen05_equals_conv_then_scan(case):
+    """soda_conv_lif_fwd (state on-chip across T) == soda_conv2d_fwd + soda_lif_fwd (+ residual), bit for
+    bit, including a channel-slice destination and a carried-in state; and against the CPU oracle."""
+    pkg = _pkg()
+    ops = pkg.ops
+    T, B, Cin, H, W, Cout, k, s, with_res = case
+    torch.manual_seed(T * 100 + Cout)
+    x = (torch.randn(T * B, Cin, H, W) * 0.9).to(DEV).contiguous(memory_format=torch.channels_last)
+    w = torch.randn(Cout, Cin, k, k) / (Cin * k * k) ** 0.5 * 2.0
+    scale, shift = torch.rand(Cout) + 0.5, torch.randn(Cout) * 0.2
+    pc = ops.pack_conv(w.to(DEV), s, scale.to(DEV), shift.to(DEV), kind=1)
+    res = x if with_res else None
+    y0 = ops.conv2d(x, pc)
+    z0, v0, i0, _, _, _ = ops.lif_scan(y0, T)
+    ref = z0 + x if with_res else z0
+    Ho, Wo = y0.shape[2:]
+    buf = torch.zeros(T * B, Cout + 8, Ho, Wo, device=DEV).contiguous(memory_format=torch.channels_last)
+    out = buf[:, 4 : 4 + Cout]
+    z1, v1, i1 = ops.conv_lif(x, pc, T, ops.LIF_DEFAULT, residual=res, out=out)
+    assert 0.01 < float(z0.mean()) < 0.9
+    assert torch.equal(z1, ref) and torch.equal(v1, v0) and torch.equal(i1, i0)
+    assert float(buf[:, :4].abs().max()) == 0.0 and float(buf[:, 4 + Cout :].abs().max()) == 0.0
+    # streaming: first 2 steps, then the rest with the carried state
+    za, va, ia = ops.conv_lif(x[: 2 * B], pc, 2, ops.LIF_DEFAULT, residual=None if res is None else x[: 2 * B])
+    zb, vb, ib = ops.conv_lif(x[2 * B :], pc, T - 2, ops.LIF_DEFAULT, va, ia,
+                              residual=None if res is None else x[2 * B :])
+    assert torch.equal(torch.cat([za, zb]), ref) and torch.equal(vb, v0) and torch.equal(ib, i0)
+    # oracle: fp64 conv -> fp32 -> restated LIFCell, time-major
+    yr = (F.conv2d(x.cpu().double(), (w * scale.view(-1, 1, 1, 1)).double(), stride=s, padding=k // 2)
+          + shift.double().view(1, -1, 1, 1)).float()
+    cell, st, zs = nr.LIFCell(), None, []
+    for t in range(T):
+        z, st = cell(yr[t * B : (t + 1) * B], st)
+        zs.append(z)
+    zr = torch.cat(zs)
+    assert float((z0.cpu() != zr).float().mean()) <= 1e-4
+
+
+def test_conv_lif_direct_event_frames():
+    """First layer of the detector: NCHW {0,1} event frames, Cin = 2, 3x3 stride 2 -> BN -> LIF in the direct
+    FP32-pipe kernel == conv2d(fp32 kind) + lif_scan bit for bit; odd sizes, state carry, slice output."""
+    pkg = _pkg()
+    ops = pkg.ops
+    for (T, B, H, W, Cout, k, s) in [(6, 2, 37, 51, 64, 3, 2), (4, 1, 24, 32, 16, 3, 1), (5, 3, 16, 20, 8, 1, 1)]:
+        torch.manual_seed(T + Cout)
+        x = (torch.rand(T * B, 2, H, W) < 0.3).float().to(DEV)
+        w = torch.randn(Cout, 2, k, k) * 2.0
+        scale, shift = torch.rand(Cout) + 1.0, torch.randn(Cout) * 0.1
+        pc = ops.pack_conv(w.to(DEV), s, scale.to(DEV), shift.to(DEV), kind=0)
+        assert ops.conv_lif_supported(x, pc)
+        y0 = ops.conv2d(x, pc)
+        z0, v0, i0, _, _, _ = ops.lif_scan(y0, T)
+        Ho, Wo = y0.shape[2:]
+        buf = torch.zeros(T * B, Cout + 8, Ho, Wo, device=DEV).contiguous(memory_format=torch.channels_last)
+        z1, v1, i1 = ops.conv_lif(x, pc, T, ops.LIF_DEFAULT, out=buf[:, 4 : 4 + Cout])
+        assert float(z0.mean()) > 0.005
+        assert torch.equal(z1, z0) and torch.equal(v1, v0) and torch.equal(i1, i0)
+        assert float(buf[:, :4].abs().max()) == 0.0 and float(buf[:, 4 + Cout :].abs().max()) == 0.0
+        za, va, ia = ops.conv_lif(x[:B], pc, 1, ops.LIF_DEFAULT)
+        zb, vb, ib = ops.conv_lif(x[B:], pc, T - 1, ops.LIF_DEFAULT, va, ia)
+        assert torch.equal(torch.cat([za, zb]), z0) and torch.equal(vb, v0) and torch.equal(ib, i0)
+
+
+@pytest.mark.parametrize("with_res", [False, True])
+def test_lif_scan_out_residual_and_slice_store(with_res):
+    """soda_lif_res_fwd == soda_lif_fwd (+ residual) written into a concat slice."""
+    ops = _pkg().ops
+    T, B, Cc, H, W = 5, 2, 32, 15, 19
+    torch.manual_seed(3)
+    x = (torch.randn(T * B, Cc, H, W) * 3).to(DEV).contiguous(memory_format=torch.channels_last)
+    big = torch.randn(T * B, 96, H, W, device=DEV).contiguous(memory_format=torch.channels_last)
+    res = big[:, 64:96] if with_res else None
+    z0, v0, i0, _, _, _ = ops.lif_scan(x, T)
+    ref = z0 + res if with_res else z0
+    buf = torch.zeros(T * B, 80, H, W, device=DEV).contiguous(memory_format=torch.channels_last)
+    z1, v1, i1 = ops.lif_scan_out(x, T, residual=res, out=buf[:, 16:48])
+    assert torch.equal(z1, ref) and torch.equal(v1, v0) and torch.equal(i1, i0)
+    assert float(buf[:, :16].abs().max()) == 0.0 and float(buf[:, 48:].abs().max()) == 0.0
+    za, va, ia = ops.lif_scan_out(x[: 2 * B], 2, residual=None if res is None else res[: 2 * B])
+    zb, vb, ib = ops.lif_scan_out(x[2 * B :], T - 2, va, ia, residual=None if res is None else res[2 * B :])
+    assert torch.equal(torch.cat([za, zb]), ref) and torch.equal(vb, v0)
+
+
 @pytest.mark.parametrize("mode", ["S", "A", "M"])
 @pytest.mark.parametrize("shape", [(2, 8, 24, 32), (1, 5, 9, 11), (3, 32, 15, 19)])
 def test_pool2d(mode, shape):

@@ -298,6 +298,7 @@ def test_fused_conv_norm_lif_planner_equals_unfused(monkeypatch):
     X = (torch.rand(5, 2, 2, 128, 160, generator=gen) < 0.07).float().to(DEV)
     with torch.no_grad():
         monkeypatch.setenv("SODA_FUSE_LIF_MIN_ITEMS", "1")
+        monkeypatch.setenv("SODA_FUSE_LIF_MAX_COUT", "100000")
         model.forward_seq(X)  # weight packing out of the launch count
         n0 = _lib.launch_count()
         preds_f, state_f = model.forward_seq(X)
@@ -309,7 +310,7 @@ def test_fused_conv_norm_lif_planner_equals_unfused(monkeypatch):
         n0 = _lib.launch_count()
         preds_u, state_u = model.forward_seq(X)
         n_unfused = _lib.launch_count() - n0
-    assert n_fused < n_unfused - 20, (n_fused, n_unfused)
+    assert n_fused < n_unfused - 10, (n_fused, n_unfused)
     for a, b, c in zip(preds_f, preds_u, preds_s):
         assert torch.equal(a, b) and torch.equal(a, c)
     fa, fb, fc = _flat_states(state_f), _flat_states(state_u), _flat_states(state_s)
