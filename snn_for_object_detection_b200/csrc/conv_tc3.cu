@@ -22,8 +22,9 @@
 //            + bf16(hi a)*bf16(lo b)
 //            + bf16(lo a)*bf16(hi b)  kind::f16, K-stacked in one 128-byte row     -> correction accumulator
 //   The correction terms are 2^-11 of the main term, so 8 mantissa bits on them keep ~2^-20 overall.
-//   Each slab is split ONCE in shared memory by 8 split warps (tf32 hi in place + a second plane of
-//   [bf16 hi | bf16 lo] rows with the same row addressing), not once per tap.  Inputs declared exactly
+//   Each slab is split ONCE in shared memory by 8 split warps into a second plane of [bf16 hi | bf16 lo] rows
+//   with the same row addressing, not once per tap; the fp32 plane itself is the tf32 operand as it is
+//   (kind::tf32 truncates), so the main pass starts as soon as the TMA bytes land.  Inputs declared exactly
 //   representable (spikes, pooled spike counts) skip the lo(a) half.
 // * All synchronisation is per slab (9 k-blocks = 72 MMAs for a 3x3 layer), not per k-block: an mbarrier
 //   round trip costs several hundred clocks, a k-block of a 32-channel tile only 128.
@@ -56,7 +57,8 @@ constexpr int T3_BH = 16, T3_BW = 8;     // spatial tile (one 8-row descriptor g
 constexpr int T3_THREADS = 640;
 constexpr int T3_W_PROD_A = 16, T3_W_MMA_MAIN = 17, T3_W_PROD_B = 18, T3_W_MMA_CORR = 19;
 constexpr int T3_MAX_RING = 8;           // max stages of the A / B shared-memory rings
-constexpr int T3_SMEM_LIMIT = 232448 - 1024 /*alignment slack*/ - 512 /*barriers*/;
+constexpr int T3_STAGE_BYTES = 8 * 1536;  // per epilogue warp: 1 KB transpose staging (16 rows x 16 cols) + 512 B row-offset table
+constexpr int T3_SMEM_LIMIT = 232448 - 1024 /*alignment slack*/ - 512 /*barriers*/ - T3_STAGE_BYTES;
 
 struct Tc3Params {
   int H, W, Cin, Cout, k, stride, pad, Ho, Wo;
@@ -80,6 +82,7 @@ struct Tc3Params {
   const float* shift;
   const float* residual;
   float* y;
+  int vec_store;                 // Cout % 4 == 0 and 16-byte aligned output / residual: coalesced staged stores
   int dbg;                       // SODA_TC_DBG timing experiments (results are garbage when set)
   int lif;
   NP np;
@@ -107,7 +110,8 @@ __device__ __forceinline__ Tc3Item tc3_item(const Tc3Params& p, int item) {
 // lane issues, so descriptors live in uniform registers.
 template <int BN, bool CORR>
 __device__ __forceinline__ void tc3_mma_role(const Tc3Params& p, uint32_t tmem_base, uint32_t smem_a_u32,
-                                             uint32_t smem_b_u32, uint64_t* a_ready, uint64_t* a_empty,
+                                             uint32_t smem_b_u32, uint64_t* a_ready /* CORR: split done; main: TMA landed */,
+                                             uint64_t* a_empty,
                                              uint64_t* b_full, uint64_t* b_empty, uint64_t* acc_full,
                                              uint64_t* acc_empty) {
   constexpr uint32_t B_TILE = BN * 128, B_STAGE = 2 * B_TILE;
@@ -299,7 +303,7 @@ conv_tc3_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__
       }
     }
   } else if (warp == T3_W_MMA_MAIN) {
-    tc3_mma_role<BN, false>(p, tmem_base, smem_u32(smem_a), smem_u32(smem_b), a_ready, a_empty, b_full, b_empty,
+    tc3_mma_role<BN, false>(p, tmem_base, smem_u32(smem_a), smem_u32(smem_b), a_full, a_empty, b_full, b_empty,
                             acc_full, acc_empty);
   } else if (warp == T3_W_MMA_CORR) {
     tc3_mma_role<BN, true>(p, tmem_base, smem_u32(smem_a), smem_u32(smem_b), a_ready, a_empty, b_full, b_empty,
@@ -336,9 +340,10 @@ conv_tc3_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__
               sts128(cr + ((q ^ sw) << 4), __uint_as_float(pack_bf16x2(fh[0], fh[1])),
                      __uint_as_float(pack_bf16x2(fh[2], fh[3])), __uint_as_float(pack_bf16x2(fh[4], fh[5])),
                      __uint_as_float(pack_bf16x2(fh[6], fh[7])));
+              // The fp32 plane is left as TMA wrote it: kind::tf32 reads the upper 19 bits of each element and
+              // ignores the rest (measured: bit-identical results with and without rewriting hi in place),
+              // so hi(a) = truncation is exactly what the main pass sees.
               if (!p.a_exact) {
-                sts128(a0, fh[0], fh[1], fh[2], fh[3]);
-                sts128(a1, fh[4], fh[5], fh[6], fh[7]);
                 sts128(cr + (((4u + q) ^ sw) << 4), __uint_as_float(pack_bf16x2(fl[0], fl[1])),
                        __uint_as_float(pack_bf16x2(fl[2], fl[3])), __uint_as_float(pack_bf16x2(fl[4], fl[5])),
                        __uint_as_float(pack_bf16x2(fl[6], fl[7])));
@@ -360,6 +365,8 @@ conv_tc3_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__
     static_assert(!LIF || NCOL <= 32, "fused LIF keeps 2*NCOL state registers per thread");
     const int e = (warp - 8) >> 2;
     const int q = warp & 3;
+    const uint32_t stage_u32 = smem_u32(reinterpret_cast<uint8_t*>(bars) + 512) + (uint32_t)(warp - 8) * 1536u;
+    const uint32_t table_u32 = stage_u32 + 1024u;
     const int row = q * 32 + lane;
     const int64_t hw = (int64_t)p.Ho * p.Wo;
     uint32_t local = 0;
@@ -403,6 +410,14 @@ conv_tc3_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__
         const int64_t frame = frame0 + (int64_t)t * p.Bsz;
         const int64_t out_off = frame * p.out_bs + rr * p.out_ps;
         const int64_t res_off = frame * p.res_bs + rr * p.res_ps;
+        if (p.vec_store) {
+          // row -> (output offset | -1, residual offset) table of this warp's 32 rows for the staged stores
+          __syncwarp();
+          const int64_t my_out = valid ? out_off : -1;
+          asm volatile("st.shared.v2.b64 [%0], {%1, %2};" ::"r"(table_u32 + (uint32_t)lane * 16u), "l"(my_out), "l"(res_off)
+                       : "memory");
+          __syncwarp();
+        }
         mbar_wait(&acc_full[acc], acc_ph);
         tc_fence_after();
         const uint32_t t_row = tmem_base + ((uint32_t)(q * 32) << 16) + acc * (2 * BN) + e * NCOL;
@@ -444,30 +459,54 @@ conv_tc3_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__
               o[jj] = z;
             }
           }
-          if (live && !(p.dbg & 8)) {
+          if (p.vec_store) {
+            // Coalesced store: the warp transposes its 32 rows x 16 columns through 1 KB of shared memory,
+            // 16 rows at a time, so that one store instruction writes 8 rows x 64 contiguous bytes (8 sectors
+            // pairs) instead of 32 scattered 16-byte pieces; the residual is read with the same mapping.
+            if (!(p.dbg & 8)) {
+#pragma unroll
+              for (int half = 0; half < 2; ++half) {
+                __syncwarp();
+                if ((lane >> 4) == half) {
+                  const uint32_t r16 = lane & 15u;
+                  const uint32_t rowa = stage_u32 + r16 * 64u;
+                  const uint32_t f = (r16 >> 1) & 3u;
+#pragma unroll
+                  for (uint32_t j = 0; j < 4; ++j)
+                    sts128(rowa + ((j ^ f) << 4), o[4 * j], o[4 * j + 1], o[4 * j + 2], o[4 * j + 3]);
+                }
+                __syncwarp();
+#pragma unroll
+                for (int it = 0; it < 2; ++it) {
+                  const uint32_t rrow = (uint32_t)it * 8u + ((uint32_t)lane >> 2);
+                  const uint32_t j = lane & 3u;
+                  const float4 val = lds128(stage_u32 + rrow * 64u + ((j ^ ((rrow >> 1) & 3u)) << 4));
+                  int64_t ooff, roff;
+                  asm volatile("ld.shared.v2.b64 {%0, %1}, [%2];"
+                               : "=l"(ooff), "=l"(roff)
+                               : "r"(table_u32 + ((uint32_t)half * 16u + rrow) * 16u));
+                  const int col = co0 + (int)j * 4;
+                  if (ooff >= 0 && col < p.Cout) {
+                    float4 ov = val;
+                    if (p.residual != nullptr) {
+                      const float4 rv = __ldg(reinterpret_cast<const float4*>(p.residual + roff + col));
+                      ov.x += rv.x, ov.y += rv.y, ov.z += rv.z, ov.w += rv.w;
+                    }
+                    *reinterpret_cast<float4*>(p.y + ooff + col) = ov;
+                  }
+                }
+              }
+            }
+          } else if (live && !(p.dbg & 8)) {
             float* dst = p.y + out_off + co0;
             const float* rs = p.residual ? p.residual + res_off + co0 : nullptr;
             const int nvalid = min(16, p.Cout - co0);
-            const bool vec = nvalid == 16 && ((reinterpret_cast<uintptr_t>(dst) & 15) == 0) &&
-                             (rs == nullptr || (reinterpret_cast<uintptr_t>(rs) & 15) == 0);
-            if (vec) {
 #pragma unroll
-              for (int jj = 0; jj < 16; jj += 4) {
-                float4 ov = make_float4(o[jj], o[jj + 1], o[jj + 2], o[jj + 3]);
-                if (rs) {
-                  const float4 rv = __ldg(reinterpret_cast<const float4*>(rs + jj));
-                  ov.x += rv.x, ov.y += rv.y, ov.z += rv.z, ov.w += rv.w;
-                }
-                *reinterpret_cast<float4*>(dst + jj) = ov;
-              }
-            } else {
-#pragma unroll
-              for (int jj = 0; jj < 16; ++jj) {
-                if (jj < nvalid) {
-                  float ov = o[jj];
-                  if (rs) ov += __ldg(rs + jj);
-                  dst[jj] = ov;
-                }
+            for (int jj = 0; jj < 16; ++jj) {
+              if (jj < nvalid) {
+                float ov = o[jj];
+                if (rs) ov += __ldg(rs + jj);
+                dst[jj] = ov;
               }
             }
           }
@@ -641,6 +680,10 @@ int conv_tc3_dispatch(const soda_conv_desc_t* d, const float* x, const float* pa
   p.out_bs = d->out_batch_stride, p.out_ps = d->out_pix_stride;
   p.res_bs = d->res_batch_stride, p.res_ps = d->res_pix_stride;
   p.shift = shift, p.residual = residual, p.y = y;
+  p.vec_store = d->Cout % 4 == 0 && d->out_pix_stride % 4 == 0 && d->out_batch_stride % 4 == 0 &&
+                (reinterpret_cast<uintptr_t>(y) & 15) == 0 &&
+                (residual == nullptr || (d->res_pix_stride % 4 == 0 && d->res_batch_stride % 4 == 0 &&
+                                         (reinterpret_cast<uintptr_t>(residual) & 15) == 0));
   const bool is_lif = lif != nullptr;
   if (is_lif) {
     if (lif->T <= 0 || d->N % lif->T != 0) return fail(SODA_ERR_BAD_ARG, "conv_lif: N must be T * batch");
@@ -727,7 +770,7 @@ int conv_tc3_dispatch(const soda_conv_desc_t* d, const float* x, const float* pa
   int grid = p.n_items < kNumSMs ? p.n_items : kNumSMs;
   grid = grid / p.nch * p.nch;
   if (grid < p.nch) grid = p.nch;
-  const size_t smem = (size_t)p.b_region_bytes + (size_t)p.a_stages * p.a_stage_bytes + 512 + 1024;
+  const size_t smem = (size_t)p.b_region_bytes + (size_t)p.a_stages * p.a_stage_bytes + 512 + T3_STAGE_BYTES + 1024;
   cudaStream_t st = (cudaStream_t)stream;
   if (is_lif) {
     if (BN == 32) return launch_tc3<32, true>(tmA, tmB, p, grid, smem, st);

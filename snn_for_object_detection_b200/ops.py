@@ -62,6 +62,9 @@ def _prof(name):
                 x, pc = a[0], a[1]
                 PROFILE.setdefault(name + "_tags", []).append(
                     f"{tuple(x.shape)}->{pc.Cout} k{pc.k} s{pc.stride} kind{pc.kind} exact{int(is_exact(x))}")
+                PROFILE.setdefault(name + "_meta", []).append(
+                    dict(N=x.shape[0], Cin=x.shape[1], H=x.shape[2], W=x.shape[3], Cout=pc.Cout, k=pc.k,
+                         stride=pc.stride, kind=pc.kind))
             return r
 
         wrapped.__name__, wrapped.__doc__ = fn.__name__, fn.__doc__
