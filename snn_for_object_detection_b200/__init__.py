@@ -5,7 +5,7 @@ fallback — a missing library is an ImportError, a non-CUDA tensor a RuntimeErr
 """
 
 from . import _lib  # noqa: F401  (fails loudly when the CUDA library is not built)
-from . import ops, events  # noqa: F401
+from . import ops, events, sharding  # noqa: F401
 from .generator import BackboneGen, BlockGen, Head, HeadGen, ListGen, ListState, ModelGen, NeckGen  # noqa: F401
 from .modules import *  # noqa: F401,F403
 from .soda import SODa  # noqa: F401
