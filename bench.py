@@ -302,13 +302,15 @@ def run_gpu_arm(args):
     peak = pk["bf16_tflops_sustained"]
     traffic = None
     tpath = os.path.join(ROOT, "profiles", "r1b_traffic.json")
+    traffic_launch = None
     if os.path.exists(tpath):
-        traffic = json.load(open(tpath))
+        tj = json.load(open(tpath))
+        traffic, traffic_launch = tj.get("bytes"), tj.get("launch")
     all_flops = sum(flops(m) for _, m, _ in conv_launches)
     roofline = {
         "bound": "tensor", "achieved": achieved, "peak": peak, "unit": "TFLOP/s",
         "frac": (achieved / peak) if achieved else None,
-        "traffic": traffic,
+        "traffic": traffic, "traffic_launch": traffic_launch,
         "kernel": "soda::conv_tc3_kernel<128, false> (tcgen05/TMEM/TMA implicit GEMM; tf32 main pass + K-stacked bf16 "
                   "correction pass = 2 tensor passes per product for fp32-level accuracy)",
         "peak_source": f"{pk_src} dense bf16 sustained (kernel timed inside a long step); the 2-pass fp32-accurate "
