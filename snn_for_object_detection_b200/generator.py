@@ -200,6 +200,32 @@ class BlockGen(nn.Module):
     def _is_identity(branch) -> bool:
         return len(branch) > 0 and all(type(m) is nn.Identity for m in branch)
 
+    def _identity_slice(self) -> Optional[Tuple[int, int]]:
+        """Channel range of the single ``[Pass]`` branch of a Dense block (its input re-appears there)."""
+        if self.merge != "dense":
+            return None
+        ids = [bi for bi, br in enumerate(self.net) if self._is_identity(br)]
+        if len(ids) != 1:
+            return None
+        lo = sum(self.branch_channels[: ids[0]])
+        return lo, lo + self.branch_channels[ids[0]]
+
+    def _lookahead_dst(self, branch, end_idx, n, N, C, H, W, dst, device, prealloc):
+        """Destination for the output of the layer group ending at ``end_idx`` when the NEXT layer is a Dense
+        block with a ``[Pass]`` branch: the group writes straight into that block's concat buffer (allocated
+        here, or the caller's ``dst`` when the block closes the branch), so the identity branch costs no copy."""
+        if end_idx + 1 >= n or torch.is_grad_enabled():
+            return None
+        nxt = branch[end_idx + 1]
+        if not isinstance(nxt, BlockGen):
+            return None
+        sl = nxt._identity_slice()
+        if sl is None or sl[1] - sl[0] != C or nxt.out_hw(H, W) != (H, W):
+            return None
+        buf = dst if (end_idx + 1 == n - 1 and dst is not None) else ops.empty_pixel_major(N, nxt.out_channels, H, W, device)
+        prealloc[end_idx + 1] = buf
+        return buf[:, sl[0] : sl[1]]
+
     def _run_branch(self, X, T, branch, flags, branch_state, dst, residual=None, residual_dst=None):
         """Runs one branch; fuses Conv+Norm(eval)(+LIF) and LI+Tanh; the branch's last layer writes
         straight into ``dst`` (concat slice / caller's buffer) when it can.  ``residual``: tensor the
@@ -208,6 +234,7 @@ class BlockGen(nn.Module):
         n = len(branch)
         Y = X
         idx = 0
+        prealloc = {}  # index of a Dense block -> its concat buffer, allocated early by _lookahead_dst
         while idx < n:
             layer = branch[idx]
             if isinstance(layer, SodaConv2d):
@@ -225,25 +252,41 @@ class BlockGen(nn.Module):
                         is_last = last == n - 1
                         st = branch_state[last]
                         v0, i0 = (None, None) if st is None else (st.v, st.i)
+                        if is_last:
+                            o = dst if residual is None else residual_dst
+                        else:
+                            Ho, Wo = ops.conv_out_hw(Y.shape[2], Y.shape[3], pc.k, pc.stride)
+                            o = self._lookahead_dst(branch, last, n, Y.shape[0], pc.Cout, Ho, Wo, dst, Y.device, prealloc)
                         Y, v, i = ops.conv_lif(Y, pc, T, cell._const, v0, i0,
-                                               residual=residual if is_last else None,
-                                               out=(dst if residual is None else residual_dst) if is_last else None)
+                                               residual=residual if is_last else None, out=o)
                         branch_state[last] = LIFFeedForwardState(v, i)
                         idx = last + 1
                         if is_last:
                             return Y, residual is not None
                         continue
-                o = dst if last == n - 1 else None
+                if last == n - 1:
+                    o = dst
+                else:
+                    Ho, Wo = ops.conv_out_hw(Y.shape[2], Y.shape[3], layer.kernel_size[0], layer.stride[0])
+                    o = self._lookahead_dst(branch, last, n, Y.shape[0], layer.out_channels, Ho, Wo, dst, Y.device,
+                                            prealloc)
                 Y = layer(Y, norm=norm, out=o)
                 idx = last + 1
-                if o is not None:
+                if last == n - 1 and o is not None:
                     return Y, False
                 continue
             if isinstance(layer, BlockGen):
-                o = dst if idx == n - 1 else None
+                if idx in prealloc:
+                    o = prealloc.pop(idx)
+                elif idx == n - 1:
+                    o = dst
+                else:
+                    Ho, Wo = layer.out_hw(Y.shape[2], Y.shape[3])
+                    o = self._lookahead_dst(branch, idx, n, Y.shape[0], layer.out_channels, Ho, Wo, dst, Y.device,
+                                            prealloc)
                 Y, branch_state[idx] = layer.forward_seq(Y, T, branch_state[idx], out=o)
                 idx += 1
-                if o is not None:
+                if idx == n and o is not None:
                     return Y, False
                 continue
             if (type(layer) is LIFCell and idx == n - 1 and not torch.is_grad_enabled()
