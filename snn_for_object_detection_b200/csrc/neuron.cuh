@@ -27,7 +27,9 @@ __device__ __forceinline__ void lif_step(const NP& p, float x, float& v, float& 
   float i_dec = __fadd_rn(i_src, di);
   if (!p.jump_first) i_dec = __fadd_rn(i_dec, x);
   z = (__fsub_rn(v_dec, p.v_th) > 0.0f) ? 1.0f : 0.0f;
-  v = __fadd_rn(__fmul_rn(__fsub_rn(1.0f, z), v_dec), __fmul_rn(z, p.v_reset));
+  // (1 - z) * v_dec + z * v_reset with z in {0, 1}: one of the two products is an exact zero, so the sum IS
+  // the other operand (up to the sign of zero) - a select gives the same fp32 value as the four-op form.
+  v = (z != 0.0f) ? p.v_reset : v_dec;
   i = i_dec;
 }
 
