@@ -1,1 +1,1 @@
-for d in 0 1 4 8 5 12 13; do echo "== dbg $d"; SODA_TC_DBG=$d timeout 100 python scripts/conv_probe.py --nocheck 160,32,120,152,32,3,1 160,128,30,38,128,3,1 160,128,60,76,256,3,2 160,128,120,152,64,1,1 160,64,120,152,128,3,2 lif:160,32,120,152,32,3,1 lif:160,128,60,76,256,3,2 2>&1 | grep -v Warn; done
+for d in 0 1 4 8 5 12 13; do echo "== dbg $d"; SODA_TC_DBG=$d timeout 100 python scripts/conv_probe.py --nocheck "$@" 2>&1 | grep -v Warn; done

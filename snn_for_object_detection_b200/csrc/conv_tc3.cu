@@ -63,6 +63,8 @@ constexpr int T3_SMEM_LIMIT = 232448 - 1024 /*alignment slack*/ - 512 /*barriers
 struct Tc3Params {
   int H, W, Cin, Cout, k, stride, pad, Ho, Wo;
   int tiles_x, tiles_y, n_spatial;
+  int mt;                        // M-tiles per work item sharing every streamed weight k-block (1 or 2)
+  int n_sp_items;                // ceil(n_spatial / mt)
   int taps, cblocks, kblocks;
   int mode;                      // 0 = HALO (one A stage per 32-channel slab, `taps` k-blocks), 1 = TAP
   int flat;                      // 1x1 stride-1 over the flattened pixel list
@@ -99,8 +101,8 @@ __device__ __forceinline__ Tc3Item tc3_item(const Tc3Params& p, int item) {
   Tc3Item it;
   it.chunk = item % p.nch;
   const int r = item / p.nch;
-  it.sp = r % p.n_spatial;
-  it.outer = r / p.n_spatial;
+  it.sp = r % p.n_sp_items;      // tiles sp * mt .. sp * mt + mt - 1
+  it.outer = r / p.n_sp_items;
   return it;
 }
 
@@ -108,7 +110,7 @@ __device__ __forceinline__ Tc3Item tc3_item(const Tc3Params& p, int item) {
 // One warp per accumulator.  CORR = false: tf32 main pass over the hi planes; CORR = true: bf16 correction
 // pass over the [bf16 hi | bf16 lo] x [bf16 lo | bf16 hi] planes.  Warp-uniform control flow; one elected
 // lane issues, so descriptors live in uniform registers.
-template <int BN, bool CORR>
+template <int BN, bool CORR, int MT>
 __device__ __forceinline__ void tc3_mma_role(const Tc3Params& p, uint32_t tmem_base, uint32_t smem_a_u32,
                                              uint32_t smem_b_u32, uint64_t* a_ready /* CORR: split done; main: TMA landed */,
                                              uint64_t* a_empty,
@@ -125,20 +127,33 @@ __device__ __forceinline__ void tc3_mma_role(const Tc3Params& p, uint32_t tmem_b
   const int stages_per_tile = p.mode == 0 ? p.cblocks : p.kblocks;
   const int kb_per_stage = p.mode == 0 ? p.taps : 1;
   const uint32_t a_stage16 = p.a_stage_bytes >> 4;
+  constexpr uint32_t NACC = BN <= 64 ? 4 : 2;   // accumulator stages of (main | correction) in TMEM
   uint32_t sa = 0, pa = 0;    // A ring stage / parity
   uint32_t sb = 0, pb = 0;    // B ring stage / parity (streamed B)
-  uint32_t acc = 0, acc_ph = 0;
+  uint32_t cnt = 0;           // running accumulator-stage counter
+  constexpr int mt = MT;
   if (stat) mbar_wait(&b_full[0], 0);
   for (int item = blockIdx.x; item < p.n_items; item += gridDim.x) {
     for (int t = 0; t < p.T_inner; ++t) {
-      mbar_wait(&acc_empty[acc], acc_ph ^ 1);
+      uint32_t d_acc[2];
+      _Pragma("unroll") for (int m = 0; m < 2; ++m) if (m < mt) {
+        const uint32_t a = (cnt + m) % NACC, ph = ((cnt + m) / NACC) & 1u;
+        mbar_wait(&acc_empty[a], ph ^ 1);
+        d_acc[m] = tmem_base + a * (2 * BN) + (CORR ? (uint32_t)BN : 0u);
+      }
       tc_fence_after();
-      const uint32_t d_acc = tmem_base + acc * (2 * BN) + (CORR ? (uint32_t)BN : 0u);
       uint32_t accum = 0;
       for (int st = 0; st < stages_per_tile; ++st) {
-        mbar_wait(&a_ready[sa], pa);
+        // the mt tiles of the item own consecutive ring stages for this slab / k-block
+        uint32_t s_m[2];
+        uint64_t a_st[2];
+        _Pragma("unroll") for (int m = 0; m < 2; ++m) if (m < mt) {
+          mbar_wait(&a_ready[sa], pa);
+          s_m[m] = sa;
+          a_st[m] = a_desc0 + (uint64_t)(sa * a_stage16);
+          if (++sa == (uint32_t)p.a_stages) sa = 0, pa ^= 1;
+        }
         tc_fence_after();
-        const uint64_t a_st = a_desc0 + (uint64_t)(sa * a_stage16);
         int ky = 0, kx = 0;
         for (int tp = 0; tp < kb_per_stage; ++tp) {
           // resident weights are stored (tap, cb); HALO stage = channel slab st, k-block = tap tp
@@ -152,22 +167,25 @@ __device__ __forceinline__ void tc3_mma_role(const Tc3Params& p, uint32_t tmem_b
             b_desc = b_desc0 + (uint64_t)(sb * (B_STAGE >> 4));
           }
           // tap (ky, kx) of the halo = the same slab, started (ky * WW + kx) rows further
-          const uint64_t a_desc = a_st + (uint64_t)(halo3 ? (uint32_t)(ky * p.WW + kx) * 8u : 0u);
+          const uint64_t tap_off = (uint64_t)(halo3 ? (uint32_t)(ky * p.WW + kx) * 8u : 0u);
           if (elect_one()) {
             // 32 bytes along the 128-byte row = 8 tf32 / 16 bf16 K elements; descriptor unit is 16 B
             if (!(p.dbg & 4)) {
-              if (CORR) {
-                mma_bf16_ss(d_acc, a_desc, b_desc, idesc, accum);
-                mma_bf16_ss(d_acc, a_desc + 2, b_desc + 2, idesc, 1);
-                if (!half) {
-                  mma_bf16_ss(d_acc, a_desc + 4, b_desc + 4, idesc, 1);
-                  mma_bf16_ss(d_acc, a_desc + 6, b_desc + 6, idesc, 1);
+              _Pragma("unroll") for (int m = 0; m < 2; ++m) if (m < mt) {
+                const uint64_t a_desc = a_st[m] + tap_off;
+                if (CORR) {
+                  mma_bf16_ss(d_acc[m], a_desc, b_desc, idesc, accum);
+                  mma_bf16_ss(d_acc[m], a_desc + 2, b_desc + 2, idesc, 1);
+                  if (!half) {
+                    mma_bf16_ss(d_acc[m], a_desc + 4, b_desc + 4, idesc, 1);
+                    mma_bf16_ss(d_acc[m], a_desc + 6, b_desc + 6, idesc, 1);
+                  }
+                } else {
+                  mma_tf32_ss(d_acc[m], a_desc, b_desc, idesc, accum);
+                  mma_tf32_ss(d_acc[m], a_desc + 2, b_desc + 2, idesc, 1);
+                  mma_tf32_ss(d_acc[m], a_desc + 4, b_desc + 4, idesc, 1);
+                  mma_tf32_ss(d_acc[m], a_desc + 6, b_desc + 6, idesc, 1);
                 }
-              } else {
-                mma_tf32_ss(d_acc, a_desc, b_desc, idesc, accum);
-                mma_tf32_ss(d_acc, a_desc + 2, b_desc + 2, idesc, 1);
-                mma_tf32_ss(d_acc, a_desc + 4, b_desc + 4, idesc, 1);
-                mma_tf32_ss(d_acc, a_desc + 6, b_desc + 6, idesc, 1);
               }
             }
             if (!stat) mma_commit(&b_empty[sb]);
@@ -176,11 +194,14 @@ __device__ __forceinline__ void tc3_mma_role(const Tc3Params& p, uint32_t tmem_b
           if (++kx == 3) kx = 0, ++ky;
           if (!stat && ++sb == (uint32_t)p.b_stages) sb = 0, pb ^= 1;
         }
-        if (elect_one()) mma_commit(&a_empty[sa]);
-        if (++sa == (uint32_t)p.a_stages) sa = 0, pa ^= 1;
+        if (elect_one()) {
+          _Pragma("unroll") for (int m = 0; m < 2; ++m) if (m < mt) mma_commit(&a_empty[s_m[m]]);
+        }
       }
-      if (elect_one()) mma_commit(&acc_full[acc]);
-      if (++acc == 2) acc = 0, acc_ph ^= 1;
+      if (elect_one()) {
+        _Pragma("unroll") for (int m = 0; m < 2; ++m) if (m < mt) mma_commit(&acc_full[(cnt + m) % NACC]);
+      }
+      cnt += mt;
     }
   }
 }
@@ -190,7 +211,8 @@ __global__ void __launch_bounds__(T3_THREADS, 1)
 conv_tc3_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB, Tc3Params p) {
   constexpr uint32_t B_TILE = BN * 128;        // one plane of one k-block: BN rows x 128 B
   constexpr uint32_t B_STAGE = 2 * B_TILE;     // tf32 hi plane + bf16 [lo|hi] plane
-  constexpr uint32_t TMEM_COLS = 4 * BN;       // two accumulator stages of (main | correction)
+  constexpr uint32_t NACC = BN <= 64 ? 4 : 2;  // accumulator stages of (main | correction)
+  constexpr uint32_t TMEM_COLS = NACC * 2 * BN;
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
   uint8_t* smem_b = smem;
@@ -201,9 +223,9 @@ conv_tc3_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__
   uint64_t* a_empty = bars + 16;                  // both MMA streams done with the stage     [8]
   uint64_t* b_full = bars + 24;                   // [8]
   uint64_t* b_empty = bars + 32;                  // [8]
-  uint64_t* acc_full = bars + 40;                 // [2]
-  uint64_t* acc_empty = bars + 42;                // [2]
-  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 44);
+  uint64_t* acc_full = bars + 40;                 // [4]
+  uint64_t* acc_empty = bars + 44;                // [4]
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 48);
 
   const int warp = threadIdx.x >> 5;
   const int lane = threadIdx.x & 31;
@@ -218,7 +240,7 @@ conv_tc3_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__
       mbar_init(&b_full[s], 1);
       mbar_init(&b_empty[s], 2);
     }
-    for (int a = 0; a < 2; ++a) {
+    for (int a = 0; a < 4; ++a) {
       mbar_init(&acc_full[a], 2);
       mbar_init(&acc_empty[a], 8);    // one arrival per epilogue warp
     }
@@ -239,13 +261,17 @@ conv_tc3_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__
     const uint32_t smem_a_u32 = smem_u32(smem_a);
     for (int item = blockIdx.x; item < p.n_items; item += gridDim.x) {
       const Tc3Item it = tc3_item(p, item);
-      int x0 = 0, y0 = 0;
-      if (p.flat) {
-        x0 = it.sp * T3_BM;
-      } else {
-        const int ty = it.sp / p.tiles_x, tx = it.sp - ty * p.tiles_x;
-        y0 = ty * T3_BH * p.stride - p.pad;
-        x0 = tx * T3_BW * p.stride - p.pad;
+      int x0[2] = {0, 0}, y0[2] = {0, 0};
+      _Pragma("unroll") for (int m = 0; m < 2; ++m) if (m < p.mt) {
+        // a tile index past the last one (odd tile count) loads zeros (out of bounds) and is never stored
+        const int spt = it.sp * p.mt + m;
+        if (p.flat) {
+          x0[m] = spt * T3_BM;
+        } else {
+          const int ty = spt / p.tiles_x, tx = spt - ty * p.tiles_x;
+          y0[m] = ty * T3_BH * p.stride - p.pad;
+          x0[m] = tx * T3_BW * p.stride - p.pad;
+        }
       }
       for (int t = 0; t < p.T_inner; ++t) {
         const int img = p.flat ? 0 : t * p.Bsz + it.outer;
@@ -253,13 +279,16 @@ conv_tc3_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__
         int ky = 0, kx = 0;
         for (int tap = 0; tap < n_tap; ++tap) {
           for (int cb = 0; cb < p.cblocks; ++cb) {
-            mbar_wait(&a_empty[s], ph ^ 1);
-            if (elect_one()) {
-              mbar_expect_tx(&a_full[s], p.a_tx_bytes);
-              tma_load_4d_s(smem_a_u32 + s * p.a_stage_bytes, &tmA, &a_full[s], cb * T3_BK, x0 + kx, y0 + ky, img);
+            _Pragma("unroll") for (int m = 0; m < 2; ++m) if (m < p.mt) {
+              mbar_wait(&a_empty[s], ph ^ 1);
+              if (elect_one()) {
+                mbar_expect_tx(&a_full[s], p.a_tx_bytes);
+                tma_load_4d_s(smem_a_u32 + s * p.a_stage_bytes, &tmA, &a_full[s], cb * T3_BK, x0[m] + kx, y0[m] + ky,
+                              img);
+              }
+              __syncwarp();
+              if (++s == (uint32_t)p.a_stages) s = 0, ph ^= 1;
             }
-            __syncwarp();
-            if (++s == (uint32_t)p.a_stages) s = 0, ph ^= 1;
           }
           if (++kx == p.k) kx = 0, ++ky;
         }
@@ -303,11 +332,19 @@ conv_tc3_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__
       }
     }
   } else if (warp == T3_W_MMA_MAIN) {
-    tc3_mma_role<BN, false>(p, tmem_base, smem_u32(smem_a), smem_u32(smem_b), a_full, a_empty, b_full, b_empty,
-                            acc_full, acc_empty);
+    if (p.mt == 2)
+      tc3_mma_role<BN, false, 2>(p, tmem_base, smem_u32(smem_a), smem_u32(smem_b), a_full, a_empty, b_full, b_empty,
+                                 acc_full, acc_empty);
+    else
+      tc3_mma_role<BN, false, 1>(p, tmem_base, smem_u32(smem_a), smem_u32(smem_b), a_full, a_empty, b_full, b_empty,
+                                 acc_full, acc_empty);
   } else if (warp == T3_W_MMA_CORR) {
-    tc3_mma_role<BN, true>(p, tmem_base, smem_u32(smem_a), smem_u32(smem_b), a_ready, a_empty, b_full, b_empty,
-                           acc_full, acc_empty);
+    if (p.mt == 2)
+      tc3_mma_role<BN, true, 2>(p, tmem_base, smem_u32(smem_a), smem_u32(smem_b), a_ready, a_empty, b_full, b_empty,
+                                acc_full, acc_empty);
+    else
+      tc3_mma_role<BN, true, 1>(p, tmem_base, smem_u32(smem_a), smem_u32(smem_b), a_ready, a_empty, b_full, b_empty,
+                                acc_full, acc_empty);
   } else if (warp < 8) {
     // ============ split: fp32 slab -> tf32 hi (in place) + [bf16 hi | bf16 lo] correction plane =========
     // Task = (pixel row P, 8 channels q).  SWIZZLE_128B: logical 16-byte chunk c of row P sits at chunk
@@ -315,7 +352,7 @@ conv_tc3_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__
     // convention so that one descriptor arithmetic serves both).
     const uint32_t smem_a_u32 = smem_u32(smem_a);
     const int n_task = p.rows * 4;
-    const int stages_per_tile = p.mode == 0 ? p.cblocks : p.kblocks;
+    const int stages_per_tile = (p.mode == 0 ? p.cblocks : p.kblocks) * p.mt;
     uint32_t s = 0, ph = 0;
     for (int item = blockIdx.x; item < p.n_items; item += gridDim.x) {
       for (int t = 0; t < p.T_inner; ++t) {
@@ -372,16 +409,18 @@ conv_tc3_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__
     uint32_t local = 0;
     for (int item = blockIdx.x; item < p.n_items; item += gridDim.x) {
       const Tc3Item it = tc3_item(p, item);
+      for (int m = 0; m < p.mt; ++m) {   // (mt == 2 only without LIF: T_inner == 1)
+      const int spt = it.sp * p.mt + m;
       bool valid;
       int64_t rr;      // pixel index inside its frame
       int64_t frame0;  // frame of step t = 0
       if (p.flat) {
-        const int64_t pix = (int64_t)it.sp * T3_BM + row;
+        const int64_t pix = (int64_t)spt * T3_BM + row;
         valid = pix < p.total_pix;
         frame0 = pix / hw;
         rr = pix - frame0 * hw;
       } else {
-        const int ty = it.sp / p.tiles_x, tx = it.sp - ty * p.tiles_x;
+        const int ty = spt / p.tiles_x, tx = spt - ty * p.tiles_x;
         const int oy = ty * T3_BH + (row >> 3);
         const int ox = tx * T3_BW + (row & 7);
         valid = oy < p.Ho && ox < p.Wo;
@@ -405,8 +444,8 @@ conv_tc3_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__
         }
       }
       for (int t = 0; t < p.T_inner; ++t, ++local) {
-        const uint32_t acc = local & 1u;
-        const uint32_t acc_ph = (local >> 1) & 1u;
+        const uint32_t acc = local % NACC;
+        const uint32_t acc_ph = (local / NACC) & 1u;
         const int64_t frame = frame0 + (int64_t)t * p.Bsz;
         const int64_t out_off = frame * p.out_bs + rr * p.out_ps;
         const int64_t res_off = frame * p.res_bs + rr * p.res_ps;
@@ -522,6 +561,7 @@ conv_tc3_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__
           }
         }
       }
+      }  // m
     }
   }
 
@@ -756,17 +796,39 @@ int conv_tc3_dispatch(const soda_conv_desc_t* d, const float* x, const float* pa
   const int a_min = halo3 ? 2 : 3;
   const int a_want = halo3 ? 3 : 6;
   if (b_total + (int64_t)a_min * p.a_stage_bytes <= T3_SMEM_LIMIT && b_total < (1 << 20)) {
-    p.b_stationary = 1, p.b_stages = 1;
+    p.b_stationary = 1, p.b_stages = 1, p.mt = 1;
     p.b_region_bytes = (uint32_t)b_total;
     p.a_stages = (int)std::min<int64_t>(a_want, (T3_SMEM_LIMIT - b_total) / p.a_stage_bytes);
   } else {
+    // Streamed weights: every k-block (2 * BN * 128 B) comes from L2 once per work item, and at one 128-pixel tile
+    // per item that stream alone exceeds what L2 can deliver to 148 SMs (measured floor: the load skeleton of the
+    // stride-2 and 768-channel layers ran at ~12.7 TB/s of weight traffic).  So an item takes TWO M-tiles that
+    // share each weight k-block (two accumulators), halving the stream.  Only where TMEM still double-buffers
+    // (BN <= 64: 4 accumulator stages; at BN = 128 the pair would serialise MMA and epilogue - measured slower) and
+    // not with LIF (state registers).
     p.b_stationary = 0;
-    p.a_stages = halo3 ? 2 : 3;
-    p.b_stages = (int)std::min<int64_t>(T3_MAX_RING, (T3_SMEM_LIMIT - (int64_t)p.a_stages * p.a_stage_bytes) / b_stage);
+    p.mt = 1;
+    const char* e_mt = getenv("SODA_TC_MT");
+    const bool want_pair = !is_lif && p.n_spatial > 1 && (e_mt ? atoi(e_mt) == 2 : BN <= 64);
+    bool planned = false;
+    if (want_pair) {
+      for (int a = 4; a >= 2 && !planned; --a) {
+        const int64_t rem = T3_SMEM_LIMIT - (int64_t)a * p.a_stage_bytes;
+        const int bs = (int)std::min<int64_t>(T3_MAX_RING, rem / (int64_t)b_stage);
+        if (rem > 0 && bs >= (a > 2 ? 3 : 2)) {
+          p.mt = 2, p.a_stages = a, p.b_stages = bs, planned = true;
+        }
+      }
+    }
+    if (!planned) {
+      p.a_stages = halo3 ? 2 : 3;
+      p.b_stages = (int)std::min<int64_t>(T3_MAX_RING, (T3_SMEM_LIMIT - (int64_t)p.a_stages * p.a_stage_bytes) / b_stage);
+    }
     if (p.b_stages < 2) return fail(SODA_ERR_UNSUPPORTED, "conv_tc: shared-memory plan does not fit");
     p.b_region_bytes = (uint32_t)p.b_stages * b_stage;
   }
-  p.n_items = p.nch * p.n_spatial * p.n_outer;
+  p.n_sp_items = (p.n_spatial + p.mt - 1) / p.mt;
+  p.n_items = p.nch * p.n_sp_items * p.n_outer;
   int grid = p.n_items < kNumSMs ? p.n_items : kNumSMs;
   grid = grid / p.nch * p.nch;
   if (grid < p.nch) grid = p.nch;
