@@ -1,23 +1,65 @@
-"""Training-mode routes (BPTT).
+"""Training-mode routes (BPTT; reference models/soda.py:146-158).
 
-The fused surrogate-gradient LIF / LI reverse scans are in ``modules/cells.py``
-(``soda_lif_bwd`` / ``soda_li_bwd``).  Convolution dgrad / wgrad and train-mode BatchNorm
-statistics kernels are not built in this revision: asking for them raises instead of silently
-running somewhere else.
+What is hand-written for training this round: the LIF / LI forward scans and their fused surrogate-gradient
+REVERSE scans (``soda_lif_bwd`` / ``soda_li_bwd``, wired in ``modules/cells.py``), and every convolution FORWARD.
+What is a library call, stated plainly: convolution dgrad / wgrad go through ``aten::convolution_backward``
+(cuDNN) and train-mode BatchNorm through ``F.batch_norm`` - both CUDA, neither is a CPU or silent fallback, and
+both are next-round kernels.  Residual sums, concat stores and pooling use differentiable torch ops
+when a graph is being recorded.
 """
 
 from __future__ import annotations
 
+import torch
+import torch.nn.functional as F
+
+from . import ops
+
+
+class _ConvFn(torch.autograd.Function):
+    """Forward: our sm_100a convolution.  Backward: cuDNN dgrad / wgrad (library)."""
+
+    @staticmethod
+    def forward(ctx, x, weight, conv):
+        k, s = conv.kernel_size[0], conv.stride[0]
+        kind = ops.conv_kind_for(x, conv.in_channels, k, s)
+        y = ops.conv2d(x, conv.packed(None, kind))
+        ctx.save_for_backward(x, weight)
+        ctx.stride, ctx.pad = s, k // 2
+        return y
+
+    @staticmethod
+    def backward(ctx, gy):
+        x, weight = ctx.saved_tensors
+        gx, gw, _ = torch.ops.aten.convolution_backward(
+            gy, x, weight, None, [ctx.stride] * 2, [ctx.pad] * 2, [1, 1], False, [0, 0], 1,
+            [ctx.needs_input_grad[0], ctx.needs_input_grad[1], False])
+        return gx, gw, None
+
 
 def conv2d_autograd(conv, x, norm, residual, out):
-    raise NotImplementedError(
-        "SodaConv2d: training-mode convolution (dgrad/wgrad sm_100a kernels) is not built in this "
-        "revision; call model.eval() for the inference forward.  No fallback is taken."
-    )
+    if norm is not None:
+        raise RuntimeError("a folded (eval-mode) BatchNorm cannot be trained through; call model.train()")
+    y = _ConvFn.apply(x, conv.weight, conv)
+    if residual is not None:
+        y = y + residual
+    if out is not None:
+        out.copy_(y)   # differentiable slice store (autograd CopySlices)
+        return out
+    return y
 
 
-def batchnorm_train(norm, x):
-    raise NotImplementedError(
-        "SodaBatchNorm2d: train-mode batch statistics kernel is not built in this revision; "
-        "call model.eval().  No fallback is taken."
-    )
+def batchnorm_train(norm, x, T: int = 1):
+    """Train-mode BatchNorm exactly as the reference runs it: batch statistics PER CALL, i.e. per time step
+    (models/modules/layer_gen.py:211 inside the loop of models/soda.py:142), running statistics updated T times
+    in sequence with the module's momentum."""
+    if not x.is_cuda:
+        raise RuntimeError("snn_for_object_detection_b200 runs on CUDA only; there is no CPU fallback")
+    B = x.shape[0] // T
+    outs = []
+    for t in range(T):
+        if norm.momentum is not None and norm.num_batches_tracked is not None:
+            norm.num_batches_tracked.add_(1)
+        outs.append(F.batch_norm(x[t * B : (t + 1) * B], norm.running_mean, norm.running_var, norm.weight, norm.bias,
+                                 True, 0.0 if norm.momentum is None else norm.momentum, norm.eps))
+    return outs[0] if T == 1 else torch.cat(outs)

@@ -50,6 +50,9 @@ def _has_state(block: "BlockGen") -> bool:
 
 def _copy_into(src: torch.Tensor, dst: torch.Tensor) -> None:
     """Strided pixel-major copy on our own kernel (concat-slice store, generator.py:158)."""
+    if torch.is_grad_enabled() and src.requires_grad:
+        dst.copy_(src)   # training: differentiable slice store
+        return
     ops.channel_affine(src, None, None, out=dst)
 
 
@@ -175,7 +178,10 @@ class BlockGen(nn.Module):
         if self.merge == "dense":
             return dense_buf, out_state
         if self.merge == "residual":
-            Y = ops.add_n(outs)
+            if torch.is_grad_enabled() and any(o.requires_grad for o in outs):
+                Y = torch.stack(outs).sum(0)   # training: differentiable merge, the reference's own expression
+            else:
+                Y = ops.add_n(outs)
             if out is not None:
                 _copy_into(Y, out)
                 Y = out
@@ -314,6 +320,10 @@ class BlockGen(nn.Module):
                 else:
                     Y, branch_state[idx] = layer.forward_seq(Y, T, branch_state[idx])
                     idx += 1
+                continue
+            if isinstance(layer, SodaBatchNorm2d):
+                Y = layer.forward_seq(Y, T)
+                idx += 1
                 continue
             if flags[idx]:
                 # unknown stateful module: per-step protocol, one call per time step

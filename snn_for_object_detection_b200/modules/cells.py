@@ -83,8 +83,7 @@ class _LIFScanFn(torch.autograd.Function):
         (vd,) = ctx.saved_tensors
         if gz is None:
             gz = torch.zeros_like(vd)
-        gx, gv0, gi0 = ops.lif_scan_bwd(gz.contiguous(memory_format=torch.preserve_format), gv, gi, vd, ctx.T,
-                                        ctx.const)
+        gx, gv0, gi0 = ops.lif_scan_bwd(gz, gv, gi, vd, ctx.T, ctx.const)  # re-laid out like v_dec if needed
         if not ctx.has_state:
             gv0 = gi0 = None
         return gx, gv0, gi0, None, None

@@ -10,6 +10,7 @@ from __future__ import annotations
 from typing import Any, List, Optional
 
 import torch
+import torch.nn.functional as F
 from torch import nn
 
 from .. import _lib, ops
@@ -87,10 +88,14 @@ class SodaBatchNorm2d(nn.BatchNorm2d):
         return scale.float(), shift.float()
 
     def forward(self, x: torch.Tensor, out=None) -> torch.Tensor:
+        return self.forward_seq(x, 1, out=out)
+
+    def forward_seq(self, x: torch.Tensor, T: int, out=None) -> torch.Tensor:
+        """``x [T*B, C, H, W]``: train mode normalises every time step with its own batch statistics."""
         if self.training:
             from ..autograd import batchnorm_train
 
-            return batchnorm_train(self, x)
+            return batchnorm_train(self, x, T)
         scale, shift = self.fold()
         return ops.channel_affine(x, scale, shift, out=out)
 
@@ -105,6 +110,9 @@ class SodaPool2d(nn.Module):
         self.mode = mode
 
     def forward(self, X: torch.Tensor) -> torch.Tensor:
+        if torch.is_grad_enabled() and X.requires_grad:   # training: differentiable torch pooling
+            fn = F.avg_pool2d if self.mode == "A" else F.max_pool2d
+            return fn(X, self.kernel_size, self.stride)
         return ops.pool2d(X, self.kernel_size, self.stride, self.mode)
 
 
@@ -118,6 +126,8 @@ class SumPool2d(nn.Module):
         self.kernel_size, self.stride, self.padding = kernel_size, stride, padding
 
     def forward(self, X: torch.Tensor) -> torch.Tensor:
+        if torch.is_grad_enabled() and X.requires_grad:   # training: differentiable torch pooling
+            return F.avg_pool2d(X, self.kernel_size, self.stride) * (self.kernel_size * self.kernel_size)
         return ops.pool2d(X, self.kernel_size, self.stride, "S")
 
 

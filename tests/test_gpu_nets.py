@@ -318,3 +318,54 @@ def test_fused_conv_norm_lif_planner_equals_unfused(monkeypatch):
     for a, b, c in zip(fa, fb, fc):
         assert torch.equal(a, b) and torch.equal(a, c)
     assert float(preds_f[1].std()) > 0
+
+
+def test_bptt_training_step_gradients_match_oracle(monkeypatch):
+    """BPTT through a generated net in TRAIN mode (batch-statistics BatchNorm per time step, surrogate-gradient
+    LIF, LI readout): our forward kernels + fused reverse scans (+ cuDNN dgrad/wgrad) against autograd through the
+    CPU oracle (reference executor order, restated norse SuperSpike).  Reference: models/soda.py:146-158."""
+    import copy
+
+    from snn_for_object_detection_b200 import BlockGen
+    from snn_for_object_detection_b200.modules import LI, LIF, Conv, Norm, Pass, Residual
+
+    monkeypatch.setenv("SODA_CONV_KIND", "fp32")  # fp32-exact products: no borderline spike flips in this check
+    torch.manual_seed(11)
+    cfg = [Conv(32, 3, stride=2), Norm(), LIF(),
+           Residual([[Conv(kernel_size=3), Norm(), LIF()], [Pass()]]),
+           Conv(8, 1), Norm(), LI()]
+    block = BlockGen(2, cfg)
+    for m in block.modules():
+        if isinstance(m, torch.nn.BatchNorm2d):
+            m.weight.data.fill_(3.0)
+    T, B, H, W = 4, 3, 20, 24
+    X = (torch.rand(T, B, 2, H, W) < 0.15).float()
+    ref = copy.deepcopy(block).train()
+    state, ys = None, []
+    for ts in X:   # the reference's time loop, with autograd recording
+        y, state = onr.block_forward(ref, ts, state)
+        ys.append(y)
+    Yr = torch.stack(ys)
+    Wt = torch.randn_like(Yr)
+    (Yr * Wt).sum().backward()
+
+    dev = copy.deepcopy(block).to(DEV).train()
+    Y, _ = dev.forward_seq(X.to(DEV).reshape(T * B, 2, H, W), T)
+    Y = Y.reshape(T, B, *Y.shape[1:])
+    assert float((Y.detach().cpu() - Yr.detach()).abs().max()) <= 1e-4 * float(Yr.detach().abs().max())
+    (Y * Wt.to(DEV)).sum().backward()
+    n_checked = 0
+    for (n, pr), (_, pd) in zip(ref.named_parameters(), dev.named_parameters()):
+        assert pd.grad is not None, n
+        scale = float(pr.grad.abs().max())
+        assert scale > 0, n
+        err = float((pd.grad.cpu() - pr.grad).abs().max()) / scale
+        assert err < 2e-3, (n, err)
+        n_checked += 1
+    assert n_checked == 6
+    # running statistics were updated T times, per time step
+    for (n, br), (_, bd) in zip(ref.named_buffers(), dev.named_buffers()):
+        if br.dtype.is_floating_point:
+            assert torch.allclose(bd.cpu(), br, rtol=1e-4, atol=1e-6), n
+        else:
+            assert int(bd) == int(br) == T, n
