@@ -335,7 +335,8 @@ def run_gpu_arm(args):
             "warmup": args.warmup, "ms_per_step": ms_per_step, "higher_is_better": True, "scaling": "weak",
             "vs_baseline": None, "dtype": "f32", "data": "synthetic",
             "config": {
-                "workload": f"TinyYolo SODa fwd, GEN1 304x240x2, B={B}/GPU, T={T}, 16 ms step (configs[1]); "
+                "workload": f"TinyYolo SODa fwd, {'1Mpx 1280x720' if args.mpx else 'GEN1 304x240'}x2, B={B}/GPU, T={T}, "
+                            f"16 ms step ({'configs[2] shape' if args.mpx else 'configs[1]'}); "
                             "step = event binning + layer-major forward",
                 "events_per_step_per_sample": EVENTS_PER_STEP, "weights": "synthetic, calibrated (gain 5)",
                 "l2": "per-step working set (>2 GB of fp32 activations) exceeds the 126 MB L2; no explicit flush",
@@ -362,10 +363,16 @@ def main():
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--T", type=int, default=T_STEPS)
     ap.add_argument("--batch", type=int, default=BATCH)
+    ap.add_argument("--mpx", action="store_true",
+                    help="1Mpx 1280x720 frames, 150 k events / step (BASELINE configs[2] shape; use --batch 1 per GPU)")
     ap.add_argument("--no-graph", action="store_true")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--per-layer", action="store_true", help="print per-conv device times to stderr")
     args = ap.parse_args()
+    if args.mpx:
+        global H, W, EVENTS_PER_STEP, GFLOP_PER_FRAME, METRIC
+        H, W, EVENTS_PER_STEP, GFLOP_PER_FRAME = 720, 1280, 150000, 95.974
+        METRIC = "timestep-frames/s, SODa 1Mpx 1280x720 T=32 fwd"
     args.warmup = max(args.warmup, 3) if args.impl == "b200" else args.warmup
     if args.impl == "reference":
         run_reference_arm(args)
