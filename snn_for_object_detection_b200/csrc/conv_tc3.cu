@@ -744,7 +744,7 @@ int conv_tc3_dispatch(const soda_conv_desc_t* d, const float* x, const float* pa
   const int64_t HW = (int64_t)d->H * d->W;
   const bool frames_dense = d->N == 1 || d->in_batch_stride == HW * d->in_pix_stride;
   p.mode = d->stride == 1 ? 0 : 1;
-  p.flat = (d->k == 1 && d->stride == 1 && frames_dense && !is_lif) ? 1 : 0;
+  p.flat = (d->k == 1 && d->stride == 1 && frames_dense && !is_lif && !(p.dbg & 32)) ? 1 : 0;   // dbg 32: tiled 1x1
   p.rows = T3_BM, p.WW = T3_BW, p.sbo = 1024;
   if (p.flat) {
     p.n_spatial = (int)ceil_div(p.total_pix, T3_BM);
