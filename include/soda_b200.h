@@ -222,6 +222,22 @@ SODA_API int soda_channel_affine(const float* x, int64_t n_pix, int C, int64_t i
 /* Sum of k pixel-major tensors of equal shape (Residual merge, generator.py:146). */
 SODA_API int soda_add_n(const float* const* xs, int k, int64_t n, float* y, void* stream);
 
+/* ---------------------------------------------------------------------------------------------
+ * Detection decode + per-class greedy NMS + row assembly (the step right after the forward in predict)
+ *   replaces: utils/box.py:122-153 multibox_detection (with offset_inverse :72-91, box_iou :24-45, nms :94-119),
+ *             called by models/soda.py:226-233 / :299-302.
+ *   cls_probs : [B, A, C] class probabilities AFTER softmax (index 0 = background), dense
+ *   offsets   : [B, A, 4] predicted box offsets;  anchors : [A, 4] corner-format anchors (16-byte aligned)
+ *   out       : [B, A, 6] rows (class, conf, x1, y1, x2, y2): kept boxes first (class by class, best first), then
+ *               the others in anchor order with class -1; conf < pos_threshold -> class -1, conf = 1 - conf
+ *   workspace : soda_multibox_workspace_bytes(B, A) bytes of device memory, 16-byte aligned
+ *   One CTA per sample; A <= 16384 anchors (GEN1: 13 545), C <= 64.
+ * ------------------------------------------------------------------------------------------- */
+SODA_API int64_t soda_multibox_workspace_bytes(int B, int A);
+SODA_API int soda_multibox_detection(const float* cls_probs, const float* offsets, const float* anchors, int B, int A,
+                            int C, float nms_threshold, float pos_threshold, void* workspace, float* out,
+                            void* stream);
+
 #ifdef __cplusplus
 }
 #endif

@@ -36,6 +36,7 @@ __all__ = [
     "pool2d",
     "channel_affine",
     "add_n",
+    "multibox_detection",
     "to_pixel_major",
     "empty_pixel_major",
 ]
@@ -657,4 +658,32 @@ def add_n(xs: Sequence[torch.Tensor]) -> torch.Tensor:
     out = torch.empty_like(ref)
     arr = (C.c_void_p * len(ys))(*[t.data_ptr() for t in ys])
     check(lib.soda_add_n(arr, len(ys), ref.numel(), out.data_ptr(), _stream()), "soda_add_n")
+    return out
+
+
+# --------------------------------------------------------------------------------------------
+# detection decode + NMS
+# --------------------------------------------------------------------------------------------
+MULTIBOX_MAX_ANCHORS = 16384
+
+
+@_prof("multibox")
+def multibox_detection(cls_probs: torch.Tensor, offset_preds: torch.Tensor, anchors: torch.Tensor,
+                       nms_threshold: float = 0.1, pos_threshold: float = 0.009999999) -> torch.Tensor:
+    """``[B, A, 6]`` rows ``(class, conf, x1, y1, x2, y2)`` exactly as the reference's
+    ``utils/box.py:122-153 multibox_detection`` orders and fills them; one CTA per sample, no host sync."""
+    _need_cuda(cls_probs, offset_preds, anchors)
+    B, A, Cn = cls_probs.shape
+    if offset_preds.shape != (B, A, 4) or anchors.shape != (A, 4):
+        raise ValueError("multibox_detection: shape mismatch")
+    cp = cls_probs.detach().contiguous().float()
+    of = offset_preds.detach().contiguous().float()
+    an = anchors.detach().contiguous().float()
+    ws = torch.empty(lib.soda_multibox_workspace_bytes(B, A), dtype=torch.uint8, device=cp.device)
+    out = torch.empty((B, A, 6), dtype=torch.float32, device=cp.device)
+    check(
+        lib.soda_multibox_detection(cp.data_ptr(), of.data_ptr(), an.data_ptr(), B, A, Cn, float(nms_threshold),
+                                    float(pos_threshold), ws.data_ptr(), out.data_ptr(), _stream()),
+        "soda_multibox_detection",
+    )
     return out

@@ -18,6 +18,7 @@ from torch import nn
 from torch.nn import functional as F
 
 from .generator import BackboneGen, Head, ListGen, ListState, NeckGen
+from . import ops
 from .utils import box
 
 
@@ -88,7 +89,11 @@ class SODa(nn.Module):
         """Streaming inference on one frame ``X[2,H,W]``: rows ``(class, conf, xlu, ylu, xrd, yrd)``."""
         preds, state = self._forward_impl(X.unsqueeze(0), state)
         anchors, cls, bbox = preds
-        prep_pred = box.multibox_detection(F.softmax(cls, dim=2), bbox, anchors).squeeze(0)
+        probs = F.softmax(cls, dim=2)
+        if anchors.shape[0] <= ops.MULTIBOX_MAX_ANCHORS:
+            prep_pred = ops.multibox_detection(probs, bbox, anchors).squeeze(0)   # one kernel, no host sync
+        else:  # > 16384 anchors (1Mpx): torch restatement of the same algorithm, still on the GPU
+            prep_pred = box.multibox_detection(probs, bbox, anchors).squeeze(0)
         prep_pred = prep_pred[prep_pred[:, 0] >= 0]
         prep_pred[:, 2:] = torch.clamp(prep_pred[:, 2:], min=0.0, max=1.0)
         return prep_pred, state

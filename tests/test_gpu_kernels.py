@@ -418,3 +418,62 @@ def test_cpu_tensor_is_rejected_not_computed():
     pkg = _pkg()
     with pytest.raises(RuntimeError, match="no CPU fallback"):
         pkg.ops.lif_scan(torch.zeros(4, 8), 4)
+
+
+# ----------------------------------------------------------------------------------------------
+# detection decode + NMS
+# ----------------------------------------------------------------------------------------------
+def _det_close(got, ref):
+    """Same rows in the same order: class and confidence exact, boxes to 1e-5 (GPU expf vs CPU exp)."""
+    assert got.shape == ref.shape
+    assert torch.equal(got[..., 0], ref[..., 0]), int((got[..., 0] != ref[..., 0]).sum())
+    assert torch.equal(got[..., 1], ref[..., 1])
+    assert torch.allclose(got[..., 2:], ref[..., 2:], atol=1e-5, rtol=1e-5)
+
+
+def test_multibox_detection_matches_reference_golden():
+    """soda_multibox_detection against the output of the reference's OWN utils/box.py:multibox_detection
+    (tests/golden/box.npz, produced by oracle/make_golden.py from /root/reference)."""
+    ops = _pkg().ops
+    g = golden("box.npz")
+    det = ops.multibox_detection(torch.from_numpy(g["cls_probs"]).to(DEV), torch.from_numpy(g["offsets"]).to(DEV),
+                                 torch.from_numpy(g["anchors"]).to(DEV))
+    ref = torch.from_numpy(g["det"])
+    assert int((ref[..., 0] >= 0).sum()) > 0
+    _det_close(det.cpu(), ref)
+
+
+@pytest.mark.parametrize("A,C,B", [(13545, 3, 5), (1000, 4, 2), (1, 2, 1), (4097, 3, 3)])
+def test_multibox_detection_random_against_oracle(A, C, B):
+    """GEN1-sized anchor sets with many overlapping candidates per class; odd sizes; a single anchor."""
+    from snn_for_object_detection_b200.utils import box
+
+    ops = _pkg().ops
+    torch.manual_seed(A + C)
+    ctr = torch.rand(A, 2)
+    wh = torch.rand(A, 2) * 0.2 + 0.02
+    anchors = torch.cat([ctr - wh / 2, ctr + wh / 2], dim=1)
+    probs = torch.softmax(torch.randn(B, A, C) * 2.0, dim=2)
+    probs[:, ::7, 0] = 0.999  # background rows
+    probs[0, : min(A, 5)] = torch.tensor([0.995] + [0.005 / (C - 1)] * (C - 1))  # conf below nothing; background wins
+    offsets = torch.randn(B, A, 4) * 0.5
+    ref = box.multibox_detection(probs, offsets, anchors)  # CPU restatement == reference (test_box_utils_match_reference)
+    det = ops.multibox_detection(probs.to(DEV), offsets.to(DEV), anchors.to(DEV)).cpu()
+    n_keep = int((ref[..., 0] >= 0).sum())
+    assert A < 100 or n_keep > 10
+    _det_close(det, ref)
+
+
+def test_multibox_detection_low_confidence_rule_and_limits():
+    ops = _pkg().ops
+    # two identical boxes of class 0: the better one is kept, the other suppressed (class -1, conf kept);
+    # a third, far away, with conf below pos_threshold: class -1 and conf = 1 - conf
+    anchors = torch.tensor([[0.1, 0.1, 0.3, 0.3], [0.1, 0.1, 0.3, 0.3], [0.6, 0.6, 0.9, 0.9]], device=DEV)
+    probs = torch.tensor([[[0.2, 0.8], [0.1, 0.9], [0.995, 0.005]]], device=DEV)
+    det = ops.multibox_detection(probs, torch.zeros(1, 3, 4, device=DEV), anchors).cpu()[0]
+    assert det[0, 0] == 0 and abs(float(det[0, 1]) - 0.9) < 1e-7
+    assert det[1, 0] == -1 and abs(float(det[1, 1]) - 0.8) < 1e-7
+    assert det[2, 0] == -1 and abs(float(det[2, 1]) - 0.995) < 1e-7
+    with pytest.raises(_pkg()._lib.SodaError):
+        ops.multibox_detection(torch.zeros(1, 20000, 3, device=DEV), torch.zeros(1, 20000, 4, device=DEV),
+                               torch.zeros(20000, 4, device=DEV))
