@@ -1,5 +1,5 @@
 // soda_conv_pack_weights / soda_conv2d_fwd: argument checking and dispatch between the FP32-pipe
-// kernel (conv_ffma.cu) and the tcgen05 kernel (conv_tc.cu).
+// kernel (conv_ffma.cu), the tcgen05 kernel (conv_tc3.cu) and the direct event-frame kernel (conv_direct_lif.cu).
 #include "common.cuh"
 
 namespace soda {

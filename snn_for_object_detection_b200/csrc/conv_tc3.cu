@@ -84,6 +84,7 @@ struct Tc3Params {
   const float* shift;
   const float* residual;
   float* y;
+  int prefetch;                  // A producer issues L2 prefetches one item ahead
   int vec_store;                 // Cout % 4 == 0 and 16-byte aligned output / residual: coalesced staged stores
   int dbg;                       // SODA_TC_DBG timing experiments (results are garbage when set)
   int lif;
@@ -276,6 +277,40 @@ conv_tc3_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__
       for (int t = 0; t < p.T_inner; ++t) {
         const int img = p.flat ? 0 : t * p.Bsz + it.outer;
         const int n_tap = p.mode == 0 ? 1 : p.taps;   // HALO: one stage per channel slab
+        if (p.prefetch) {
+          // L2 prefetch of what this CTA loads next (its next item, or the next time step of this one): the
+          // shared-memory ring holds only 2-6 stages, far less than HBM latency x bandwidth per SM
+          int pimg = img, px0[2] = {x0[0], x0[1]}, py0[2] = {y0[0], y0[1]};
+          bool have = true;
+          if (t + 1 < p.T_inner) {
+            pimg = img + p.Bsz;
+          } else if (item + (int)gridDim.x < p.n_items) {
+            const Tc3Item nx = tc3_item(p, item + (int)gridDim.x);
+            pimg = p.flat ? 0 : nx.outer;
+            _Pragma("unroll") for (int m = 0; m < 2; ++m) if (m < p.mt) {
+              const int spt = nx.sp * p.mt + m;
+              if (p.flat) {
+                px0[m] = spt * T3_BM, py0[m] = 0;
+              } else {
+                const int ty = spt / p.tiles_x, tx = spt - ty * p.tiles_x;
+                py0[m] = ty * T3_BH * p.stride - p.pad;
+                px0[m] = tx * T3_BW * p.stride - p.pad;
+              }
+            }
+          } else {
+            have = false;
+          }
+          if (have && elect_one()) {
+            int qy = 0, qx = 0;
+            for (int tap = 0; tap < n_tap; ++tap) {
+              for (int cb = 0; cb < p.cblocks; ++cb)
+                _Pragma("unroll") for (int m = 0; m < 2; ++m) if (m < p.mt)
+                  tma_prefetch_4d(&tmA, cb * T3_BK, px0[m] + qx, py0[m] + qy, pimg);
+              if (++qx == p.k) qx = 0, ++qy;
+            }
+          }
+          __syncwarp();
+        }
         int ky = 0, kx = 0;
         for (int tap = 0; tap < n_tap; ++tap) {
           for (int cb = 0; cb < p.cblocks; ++cb) {
@@ -828,6 +863,11 @@ int conv_tc3_dispatch(const soda_conv_desc_t* d, const float* x, const float* pa
     p.b_region_bytes = (uint32_t)p.b_stages * b_stage;
   }
   p.n_sp_items = (p.n_spatial + p.mt - 1) / p.mt;
+  {
+    // measured on B200: no gain (-1 % .. +8 % time) - the hand-off chain, not HBM latency, paces the ring; off by default
+    const char* e_pf = getenv("SODA_TC_PREFETCH");
+    p.prefetch = e_pf ? atoi(e_pf) : 0;
+  }
   p.n_items = p.nch * p.n_sp_items * p.n_outer;
   int grid = p.n_items < kNumSMs ? p.n_items : kNumSMs;
   grid = grid / p.nch * p.nch;

@@ -1,5 +1,5 @@
 // LIF / LI step arithmetic shared by the stand-alone scans (neuron_scan.cu) and the fused
-// convolution epilogue (conv_tc2.cu).  Op-for-op the fp32 restatement of norse 1.1.0's
+// convolution epilogues (conv_tc3.cu, conv_direct_lif.cu).  Op-for-op the fp32 restatement of norse 1.1.0's
 // lif_feed_forward_step / li_feed_forward_step (oracle/norse_restated.py; reference call sites
 // models/modules/layer_gen.py:233,253): explicit round-to-nearest intrinsics, no FMA contraction.
 #pragma once
