@@ -184,6 +184,18 @@ SODA_API int soda_lif_res_fwd(const soda_neuron_params_t* p, const float* x, con
                      int T, int64_t n_pix, int C, const float* residual, int64_t res_pix_stride,
                      float* out, int64_t out_pix_stride, float* v_out, float* i_out, void* stream);
 
+/* LIF scan with the following 2x2 / stride-2 pooling of the spikes fused into the store (the generator block
+ * Conv, Norm, LIF, Pool - reference README.md:57-64, models/modules/layer_gen.py:139-173, common.py:45-49):
+ * the full-resolution spike map is never written.
+ *   x            : dense pixel-major [T*B, H, W, C] input currents (frame t*B + b)
+ *   out          : pooled spikes, element (t, b, oy, ox, c) at
+ *                  out[(((t*B + b)*Ho + oy)*Wo + ox)*out_pix_stride + c],  Ho = H/2, Wo = W/2 (floor mode)
+ *   v0, i0, v_out, i_out : dense [B, H, W, C] state at FULL resolution (NULL in = initial state)
+ *   mode: 0 = sum, 1 = average, 2 = max.  Needs C % 4 == 0. */
+SODA_API int soda_lif_pool_fwd(const soda_neuron_params_t* p, const float* x, const float* v0, const float* i0, int T,
+                      int B, int H, int W, int C, int mode, float* out, int64_t out_pix_stride, float* v_out,
+                      float* i_out, void* stream);
+
 SODA_API int soda_li_fwd(const soda_neuron_params_t* p, const float* x, const float* v0, const float* i0,
                 int T, int64_t n, int apply_tanh, float* out, float* v_out, float* i_out,
                 float* i_trace, void* stream);

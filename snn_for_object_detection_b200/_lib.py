@@ -74,6 +74,8 @@ SIGNATURES = {
     "soda_lif_fwd": (_i, [C.POINTER(NeuronParams), _vp, _vp, _vp, _i, _i64, _vp, _vp, _vp, _vp, _vp, _vp, _vp]),
     "soda_lif_res_fwd": (_i, [C.POINTER(NeuronParams), _vp, _vp, _vp, _i, _i64, _i, _vp, _i64, _vp, _i64, _vp, _vp,
                               _vp]),
+    "soda_lif_pool_fwd": (_i, [C.POINTER(NeuronParams), _vp, _vp, _vp, _i, _i, _i, _i, _i, _i, _vp, _i64, _vp, _vp,
+                               _vp]),
     "soda_li_fwd": (_i, [C.POINTER(NeuronParams), _vp, _vp, _vp, _i, _i64, _i, _vp, _vp, _vp, _vp, _vp]),
     "soda_lif_bwd": (_i, [C.POINTER(NeuronParams), _vp, _vp, _vp, _vp, _i, _i64, _vp, _vp, _vp, _vp]),
     "soda_li_bwd": (_i, [C.POINTER(NeuronParams), _vp, _vp, _vp, _i, _i64, _vp, _vp, _vp, _vp]),

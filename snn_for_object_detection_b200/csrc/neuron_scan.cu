@@ -237,6 +237,86 @@ lif_res_fwd_kernel(NP p, const float* __restrict__ x, const float* __restrict__ 
   vstore<4>(i_out + e, i);
 }
 
+// LIF scan with a fused non-overlapping 2x2 pooling of the spikes (generator block Conv/Norm/LIF/Pool,
+// reference models/modules/layer_gen.py:139-173 + common.py:45-49): one thread owns the 4 pixels of a pooling
+// window (x 4 channels) for all T steps - membrane state of the 16 neurons in registers - and stores only the
+// pooled value, so the full-resolution spike map never exists in HBM.  Pixels of an odd last row / column belong
+// to no window (floor mode) but still integrate: their state is part of v_out / i_out.
+// mode: 0 = sum (avg * 2 * 2 like the reference), 1 = avg, 2 = max.  Same op order as pool2d_kernel.
+__global__ void __launch_bounds__(256)
+lif_pool2_fwd_kernel(NP p, const float* __restrict__ x, const float* __restrict__ v0, const float* __restrict__ i0,
+                     int T, int B, int H, int W, int C, int mode, float* __restrict__ out, int64_t out_ps,
+                     float* __restrict__ v_out, float* __restrict__ i_out) {
+  const int cv = C / 4;
+  const int Hw = (H + 1) / 2, Ww = (W + 1) / 2, Ho = H / 2, Wo = W / 2;
+  const int64_t idx = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (idx >= (int64_t)B * Hw * Ww * cv) return;
+  const int c = (int)(idx % cv) * 4;
+  int64_t r = idx / cv;
+  const int wx = (int)(r % Ww);
+  r /= Ww;
+  const int wy = (int)(r % Hw);
+  const int b = (int)(r / Hw);
+  const bool full = wy < Ho && wx < Wo;
+  bool have[4];
+  int64_t poff[4];   // element offset of the window's pixels inside one frame
+#pragma unroll
+  for (int q = 0; q < 4; ++q) {
+    const int iy = wy * 2 + (q >> 1), ix = wx * 2 + (q & 1);
+    have[q] = iy < H && ix < W;
+    poff[q] = ((int64_t)iy * W + ix) * C + c;
+  }
+  const int64_t frame = (int64_t)H * W * C;
+  float v[4][4], cur[4][4];
+#pragma unroll
+  for (int q = 0; q < 4; ++q) {
+#pragma unroll
+    for (int k = 0; k < 4; ++k) v[q][k] = p.v_leak, cur[q][k] = 0.0f;
+    if (have[q] && v0 != nullptr) {
+      vload<4>(v[q], v0 + (int64_t)b * frame + poff[q]);
+      vload<4>(cur[q], i0 + (int64_t)b * frame + poff[q]);
+    }
+  }
+  for (int t = 0; t < T; ++t) {
+    const float* xf = x + ((int64_t)t * B + b) * frame;
+    float xs[4][4];
+#pragma unroll
+    for (int q = 0; q < 4; ++q)
+      if (have[q]) vload<4>(xs[q], xf + poff[q]);
+    float acc[4];
+#pragma unroll
+    for (int k = 0; k < 4; ++k) acc[k] = (mode == 2) ? -3.402823466e+38f : 0.0f;
+#pragma unroll
+    for (int q = 0; q < 4; ++q) {
+      if (have[q]) {
+#pragma unroll
+        for (int k = 0; k < 4; ++k) {
+          float z, vd;
+          lif_step(p, xs[q][k], v[q][k], cur[q][k], z, vd);
+          acc[k] = (mode == 2) ? fmaxf(acc[k], z) : __fadd_rn(acc[k], z);
+        }
+      }
+    }
+    if (full) {
+      float o[4];
+#pragma unroll
+      for (int k = 0; k < 4; ++k) {
+        if (mode == 2) o[k] = acc[k];
+        else if (mode == 1) o[k] = __fmul_rn(acc[k], 0.25f);
+        else o[k] = __fmul_rn(__fmul_rn(__fmul_rn(acc[k], 0.25f), 2.0f), 2.0f);
+      }
+      vstore<4>(out + ((((int64_t)t * B + b) * Ho + wy) * Wo + wx) * out_ps + c, o);
+    }
+  }
+#pragma unroll
+  for (int q = 0; q < 4; ++q) {
+    if (have[q]) {
+      vstore<4>(v_out + (int64_t)b * frame + poff[q], v[q]);
+      vstore<4>(i_out + (int64_t)b * frame + poff[q], cur[q]);
+    }
+  }
+}
+
 static bool all_aligned16(std::initializer_list<const void*> ptrs) {
   for (const void* q : ptrs)
     if (q != nullptr && (reinterpret_cast<uintptr_t>(q) & 15) != 0) return false;
@@ -311,6 +391,22 @@ extern "C" int soda_lif_res_fwd(const soda_neuron_params_t* q, const float* x, c
   lif_res_fwd_kernel<<<(unsigned)blocks, 256, 0, (cudaStream_t)stream>>>(
       to_np(q), x, v0, i0, T, n_pix, C, residual, res_pix_stride, out, out_pix_stride, v_out, i_out);
   return after_launch("lif_res_fwd");
+}
+
+extern "C" int soda_lif_pool_fwd(const soda_neuron_params_t* q, const float* x, const float* v0, const float* i0,
+                                 int T, int B, int H, int W, int C, int mode, float* out, int64_t out_pix_stride,
+                                 float* v_out, float* i_out, void* stream) {
+  using namespace soda;
+  if (!q || !x || !out || !v_out || !i_out) return fail(SODA_ERR_BAD_ARG, "lif_pool_fwd: null pointer");
+  if (T <= 0 || B <= 0 || H < 2 || W < 2 || C <= 0 || mode < 0 || mode > 2)
+    return fail(SODA_ERR_BAD_ARG, "lif_pool_fwd: bad size or mode");
+  if ((v0 == nullptr) != (i0 == nullptr)) return fail(SODA_ERR_BAD_ARG, "lif_pool_fwd: v0 / i0 must come together");
+  if (C % 4 != 0 || out_pix_stride % 4 != 0 || !all_aligned16({x, v0, i0, out, v_out, i_out}))
+    return fail(SODA_ERR_UNSUPPORTED, "lif_pool_fwd: needs C % 4 == 0, stride % 4 == 0 and 16-byte aligned buffers");
+  const int64_t threads = (int64_t)B * ((H + 1) / 2) * ((W + 1) / 2) * (C / 4);
+  lif_pool2_fwd_kernel<<<(unsigned)ceil_div(threads, 256), 256, 0, (cudaStream_t)stream>>>(
+      to_np(q), x, v0, i0, T, B, H, W, C, mode, out, out_pix_stride, v_out, i_out);
+  return after_launch("lif_pool_fwd");
 }
 
 extern "C" int soda_li_fwd(const soda_neuron_params_t* p, const float* x, const float* v0,

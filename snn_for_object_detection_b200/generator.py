@@ -25,7 +25,7 @@ from torch import nn
 from . import _lib, ops
 from .modules import *  # noqa: F401,F403
 from .modules.cells import LICell, LIFCell, LIFFeedForwardState, SNNCell
-from .modules.common import SodaBatchNorm2d, SodaConv2d, StateStorage, Storage
+from .modules.common import SodaBatchNorm2d, SodaConv2d, SodaPool2d, StateStorage, Storage, SumPool2d
 from .modules.layer_gen import Dense, LayerGen, Residual, Return
 from .utils.anchors import AnchorGenerator
 
@@ -295,6 +295,26 @@ class BlockGen(nn.Module):
                 if idx == n and o is not None:
                     return Y, False
                 continue
+            if type(layer) is LIFCell and idx + 1 < n and not torch.is_grad_enabled():
+                # Conv, Norm, LIF, Pool block: 2x2 / stride-2 pooling of the spikes fused into the scan's store
+                pool = branch[idx + 1]
+                mode = None
+                if isinstance(pool, SumPool2d) and pool.kernel_size == 2 and pool.stride == 2:
+                    mode = "S"
+                elif isinstance(pool, SodaPool2d) and pool.kernel_size == 2 and pool.stride == 2:
+                    mode = pool.mode
+                if mode is not None and Y.is_contiguous(memory_format=torch.channels_last):
+                    is_last = idx + 1 == n - 1
+                    o = (dst if residual is None else None) if is_last else None
+                    if ops.lif_pool_ok(Y, o):
+                        st = branch_state[idx]
+                        v0, i0 = (None, None) if st is None else (st.v, st.i)
+                        Y, v, i = ops.lif_pool_scan(Y, T, mode, v0, i0, layer._const, out=o)
+                        branch_state[idx] = LIFFeedForwardState(v, i)
+                        idx += 2
+                        if is_last and o is not None:
+                            return Y, False
+                        continue
             if (type(layer) is LIFCell and idx == n - 1 and not torch.is_grad_enabled()
                     and (residual is not None or dst is not None)):
                 # last layer of the branch: the scan adds the Residual identity and stores straight

@@ -30,6 +30,7 @@ __all__ = [
     "conv_lif",
     "lif_scan",
     "lif_scan_out",
+    "lif_pool_scan",
     "li_scan",
     "lif_scan_bwd",
     "li_scan_bwd",
@@ -498,6 +499,51 @@ def lif_scan_out(
         "soda_lif_res_fwd",
     )
     if residual is None:
+        mark_exact(out)
+    return out, v, i
+
+
+def lif_pool_ok(x: torch.Tensor, out: Optional[torch.Tensor]) -> bool:
+    if x.dim() != 4 or x.shape[1] % 4 or x.shape[2] < 2 or x.shape[3] < 2:
+        return False
+    if not x.is_contiguous(memory_format=torch.channels_last):
+        return False
+    if out is not None:
+        ps = _pix_dense(out)
+        if ps is None or ps % 4 or out.data_ptr() % 16:
+            return False
+    return True
+
+
+@_prof("lif_scan")
+def lif_pool_scan(x: torch.Tensor, T: int, mode: str, v0: Optional[torch.Tensor] = None,
+                  i0: Optional[torch.Tensor] = None, p: NeuronConst = None, out: Optional[torch.Tensor] = None):
+    """``Pool2x2(LIF_T(x))`` in one pass (Sum / Avg / Max pooling, stride 2, floor mode); the full-resolution
+    spikes never reach HBM.  Returns ``(pooled, v_T, i_T)`` with the state at full resolution."""
+    _need_cuda(x, v0, i0, out)
+    p = LIF_DEFAULT if p is None else p
+    N, Cc, H, W = x.shape
+    if N % T:
+        raise ValueError("lif_pool_scan: leading dimension is not a multiple of T")
+    if not lif_pool_ok(x, out):
+        raise ValueError("lif_pool_scan: unsupported layout (see lif_pool_ok)")
+    B = N // T
+    if out is None:
+        out = empty_pixel_major(N, Cc, H // 2, W // 2, x.device)
+    elif out.shape != (N, Cc, H // 2, W // 2):
+        raise ValueError("lif_pool_scan: out shape mismatch")
+    v = torch.empty_like(x[:B])
+    i = torch.empty_like(v)
+    if v0 is not None:
+        v0 = _like_block(v0, v)
+        i0 = _like_block(i0, v)
+    pc = p.c()
+    check(
+        lib.soda_lif_pool_fwd(C.byref(pc), x.data_ptr(), _ptr(v0), _ptr(i0), T, B, H, W, Cc, _POOL_MODES[mode],
+                              out.data_ptr(), _pix_dense(out), v.data_ptr(), i.data_ptr(), _stream()),
+        "soda_lif_pool_fwd",
+    )
+    if mode in ("S", "M"):
         mark_exact(out)
     return out, v, i
 

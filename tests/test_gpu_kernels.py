@@ -477,3 +477,34 @@ def test_multibox_detection_low_confidence_rule_and_limits():
     with pytest.raises(_pkg()._lib.SodaError):
         ops.multibox_detection(torch.zeros(1, 20000, 3, device=DEV), torch.zeros(1, 20000, 4, device=DEV),
                                torch.zeros(20000, 4, device=DEV))
+
+
+@pytest.mark.parametrize("mode", ["S", "A", "M"])
+@pytest.mark.parametrize("hw", [(24, 32), (15, 19), (4, 7)])
+def test_lif_pool_scan_equals_scan_then_pool(mode, hw):
+    """soda_lif_pool_fwd == soda_lif_fwd followed by soda_pool2d_fwd (2x2, stride 2, floor mode) bit for bit,
+    full-resolution state included (odd last row / column integrates but is not pooled), slice output, state carry."""
+    ops = _pkg().ops
+    H, W = hw
+    T, B, Cc = 5, 2, 8
+    torch.manual_seed(H * W)
+    x = (torch.randn(T * B, Cc, H, W) * 3).to(DEV).contiguous(memory_format=torch.channels_last)
+    z0, v0, i0, _, _, _ = ops.lif_scan(x, T)
+    ref = ops.pool2d(z0, 2, 2, mode)
+    buf = torch.zeros(T * B, Cc + 8, H // 2, W // 2, device=DEV).contiguous(memory_format=torch.channels_last)
+    y, v1, i1 = ops.lif_pool_scan(x, T, mode, out=buf[:, 4 : 4 + Cc])
+    assert float(z0.mean()) > 0.05
+    assert torch.equal(y, ref) and torch.equal(v1, v0) and torch.equal(i1, i0)
+    assert float(buf[:, :4].abs().max()) == 0.0 and float(buf[:, 4 + Cc :].abs().max()) == 0.0
+    ya, va, ia = ops.lif_pool_scan(x[: 2 * B], 2, mode)
+    yb, vb, ib = ops.lif_pool_scan(x[2 * B :], T - 2, mode, va, ia)
+    assert torch.equal(torch.cat([ya, yb]), ref) and torch.equal(vb, v0) and torch.equal(ib, i0)
+    # and against the CPU oracle: restated LIFCell + torch pooling
+    cell, st, zs = nr.LIFCell(), None, []
+    xc = x.cpu().contiguous()
+    for t in range(T):
+        z, st = cell(xc[t * B : (t + 1) * B], st)
+        zs.append(z)
+    zc = torch.cat(zs)
+    pc = {"S": F.avg_pool2d(zc, 2, 2) * 4, "A": F.avg_pool2d(zc, 2, 2), "M": F.max_pool2d(zc, 2, 2)}[mode]
+    assert torch.equal(y.cpu(), pc)

@@ -369,3 +369,22 @@ def test_bptt_training_step_gradients_match_oracle(monkeypatch):
             assert torch.allclose(bd.cpu(), br, rtol=1e-4, atol=1e-6), n
         else:
             assert int(bd) == int(br) == T, n
+
+
+def test_vgg_planner_fuses_lif_and_pool():
+    """Config 1 net (Conv/Norm/LIF/Pool blocks): the planner's LIF+Pool fused scan gives the golden output and
+    launches fewer kernels than scan + pool."""
+    from snn_for_object_detection_b200 import _lib
+
+    block, g = vgg_block_from_golden()
+    X = torch.from_numpy(g["X"]).float().to(DEV)
+    T, B = X.shape[:2]
+    block = block.to(DEV)
+    with torch.no_grad():
+        block.forward_seq(X.reshape(T * B, *X.shape[2:]), T)
+        n0 = _lib.launch_count()
+        Y, _ = block.forward_seq(X.reshape(T * B, *X.shape[2:]), T)
+        n = _lib.launch_count() - n0
+    Y = Y.reshape(T, B, *Y.shape[1:]).cpu()
+    assert float((Y != torch.from_numpy(g["Y"])).float().mean()) <= SPIKE_TOL
+    assert n <= 6, n   # conv, lif+pool, conv, lif+pool, conv(+lif)
