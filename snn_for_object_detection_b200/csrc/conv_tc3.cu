@@ -65,6 +65,7 @@ struct Tc3Params {
   int tiles_x, tiles_y, n_spatial;
   int mt;                        // M-tiles per work item sharing every streamed weight k-block (1 or 2)
   int n_sp_items;                // ceil(n_spatial / mt)
+  int it_step_sp, it_step_outer; // (gridDim.x / nch) decomposed over (sp, outer): per-CTA item iterator increments
   int taps, cblocks, kblocks;
   int mode;                      // 0 = HALO (one A stage per 32-channel slab, `taps` k-blocks), 1 = TAP
   int flat;                      // 1x1 stride-1 over the flattened pixel list
@@ -87,6 +88,7 @@ struct Tc3Params {
   int prefetch;                  // A producer issues L2 prefetches one item ahead
   int vec_store;                 // Cout % 4 == 0 and 16-byte aligned output / residual: coalesced staged stores
   int dbg;                       // SODA_TC_DBG timing experiments (results are garbage when set)
+  unsigned long long* tl;        // dbg & 64: per-role clock64 timeline of CTA 0's first tiles (TL_TILES x 16 events)
   int lif;
   NP np;
   const float* v0;
@@ -94,6 +96,18 @@ struct Tc3Params {
   float* v_out;
   float* i_out;
 };
+
+constexpr int TL_TILES = 40;
+// events: 0 producer saw a_empty / issues TMA, 1 split saw a_full, 2 split arrived a_ready, 3 main-MMA saw a_full,
+// 4 main-MMA committed the tile, 5 corr-MMA saw a_ready, 6 corr-MMA committed, 7 epilogue saw acc_full,
+// 8 epilogue released the accumulator, 9 main-MMA saw acc_empty (tile start)
+// Compiled in only with -DSODA_TC_TIMELINE (make TIMELINE=1) and then enabled by SODA_TC_DBG=64.
+__device__ __forceinline__ void tl_mark(const Tc3Params& p, int tile, int ev) {
+#ifdef SODA_TC_TIMELINE
+  if ((p.dbg & 64) && blockIdx.x == 0 && tile < TL_TILES && (threadIdx.x & 31) == 0)
+    p.tl[tile * 16 + ev] = (unsigned long long)clock64();
+#endif
+}
 
 struct Tc3Item {
   int chunk, sp, outer;
@@ -106,6 +120,23 @@ __device__ __forceinline__ Tc3Item tc3_item(const Tc3Params& p, int item) {
   it.outer = r / p.n_sp_items;
   return it;
 }
+
+// A CTA's items are blockIdx.x + k * gridDim.x.  gridDim.x is a multiple of nch, so the channel chunk is fixed and
+// (sp, outer) advance by a constant step: no integer divisions in the per-tile paths (they cost the epilogue warps
+// ~1200 clk per tile when done with / and % - measured with the SODA_TC_DBG=64 timeline).
+struct Tc3Iter {
+  int sp, outer;
+  __device__ __forceinline__ void init(const Tc3Params& p) {
+    const int r0 = (int)blockIdx.x / p.nch;
+    sp = r0 % p.n_sp_items;
+    outer = r0 / p.n_sp_items;
+  }
+  __device__ __forceinline__ void next(const Tc3Params& p) {
+    sp += p.it_step_sp;
+    outer += p.it_step_outer;
+    if (sp >= p.n_sp_items) sp -= p.n_sp_items, ++outer;
+  }
+};
 
 // ================================ MMA issuers ===================================================
 // One warp per accumulator.  CORR = false: tf32 main pass over the hi planes; CORR = true: bf16 correction
@@ -142,6 +173,7 @@ __device__ __forceinline__ void tc3_mma_role(const Tc3Params& p, uint32_t tmem_b
         mbar_wait(&acc_empty[a], ph ^ 1);
         d_acc[m] = tmem_base + a * (2 * BN) + (CORR ? (uint32_t)BN : 0u);
       }
+      if (!CORR) tl_mark(p, (int)cnt, 9);
       tc_fence_after();
       uint32_t accum = 0;
       for (int st = 0; st < stages_per_tile; ++st) {
@@ -154,6 +186,7 @@ __device__ __forceinline__ void tc3_mma_role(const Tc3Params& p, uint32_t tmem_b
           a_st[m] = a_desc0 + (uint64_t)(sa * a_stage16);
           if (++sa == (uint32_t)p.a_stages) sa = 0, pa ^= 1;
         }
+        if (st == 0) tl_mark(p, (int)cnt, CORR ? 5 : 3);
         tc_fence_after();
         int ky = 0, kx = 0;
         for (int tp = 0; tp < kb_per_stage; ++tp) {
@@ -202,6 +235,7 @@ __device__ __forceinline__ void tc3_mma_role(const Tc3Params& p, uint32_t tmem_b
       if (elect_one()) {
         _Pragma("unroll") for (int m = 0; m < 2; ++m) if (m < mt) mma_commit(&acc_full[(cnt + m) % NACC]);
       }
+      tl_mark(p, (int)cnt, CORR ? 6 : 4);
       cnt += mt;
     }
   }
@@ -259,9 +293,11 @@ conv_tc3_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__
   if (warp == T3_W_PROD_A) {
     // ================================ A producer (TMA) =========================================
     uint32_t s = 0, ph = 0;  // ring position / parity
+    int tl_tile = 0;
     const uint32_t smem_a_u32 = smem_u32(smem_a);
-    for (int item = blockIdx.x; item < p.n_items; item += gridDim.x) {
-      const Tc3Item it = tc3_item(p, item);
+    Tc3Iter it;
+    it.init(p);
+    for (int item = blockIdx.x; item < p.n_items; item += gridDim.x, it.next(p)) {
       int x0[2] = {0, 0}, y0[2] = {0, 0};
       _Pragma("unroll") for (int m = 0; m < 2; ++m) if (m < p.mt) {
         // a tile index past the last one (odd tile count) loads zeros (out of bounds) and is never stored
@@ -316,6 +352,7 @@ conv_tc3_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__
           for (int cb = 0; cb < p.cblocks; ++cb) {
             _Pragma("unroll") for (int m = 0; m < 2; ++m) if (m < p.mt) {
               mbar_wait(&a_empty[s], ph ^ 1);
+              if (tap == 0 && cb == 0 && m == 0) tl_mark(p, tl_tile, 0);
               if (elect_one()) {
                 mbar_expect_tx(&a_full[s], p.a_tx_bytes);
                 tma_load_4d_s(smem_a_u32 + s * p.a_stage_bytes, &tmA, &a_full[s], cb * T3_BK, x0[m] + kx, y0[m] + ky,
@@ -327,6 +364,7 @@ conv_tc3_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__
           }
           if (++kx == p.k) kx = 0, ++ky;
         }
+        tl_tile += p.mt;
       }
     }
   } else if (warp == T3_W_PROD_B) {
@@ -389,10 +427,12 @@ conv_tc3_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__
     const int n_task = p.rows * 4;
     const int stages_per_tile = (p.mode == 0 ? p.cblocks : p.kblocks) * p.mt;
     uint32_t s = 0, ph = 0;
+    int tl_tile = 0;
     for (int item = blockIdx.x; item < p.n_items; item += gridDim.x) {
-      for (int t = 0; t < p.T_inner; ++t) {
+      for (int t = 0; t < p.T_inner; ++t, tl_tile += p.mt) {
         for (int st = 0; st < stages_per_tile; ++st) {
           mbar_wait(&a_full[s], ph);
+          if (st == 0 && warp == 0) tl_mark(p, tl_tile, 1);
           const uint32_t hi_pl = smem_a_u32 + s * p.a_stage_bytes;
           const uint32_t cr_pl = hi_pl + p.plane_bytes;
           if (!(p.dbg & 1)) {
@@ -426,6 +466,7 @@ conv_tc3_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__
           fence_proxy_async_smem();
           __syncwarp();
           if (lane == 0) mbar_arrive(&a_ready[s]);
+          if (st == 0 && warp == 0) tl_mark(p, tl_tile, 2);
           if (++s == (uint32_t)p.a_stages) s = 0, ph ^= 1;
         }
       }
@@ -442,18 +483,21 @@ conv_tc3_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__
     const int row = q * 32 + lane;
     const int64_t hw = (int64_t)p.Ho * p.Wo;
     uint32_t local = 0;
-    for (int item = blockIdx.x; item < p.n_items; item += gridDim.x) {
-      const Tc3Item it = tc3_item(p, item);
+    Tc3Iter it;
+    it.init(p);
+    for (int item = blockIdx.x; item < p.n_items; item += gridDim.x, it.next(p)) {
       for (int m = 0; m < p.mt; ++m) {   // (mt == 2 only without LIF: T_inner == 1)
       const int spt = it.sp * p.mt + m;
       bool valid;
       int64_t rr;      // pixel index inside its frame
       int64_t frame0;  // frame of step t = 0
       if (p.flat) {
+        // flat mode is only planned when output (and residual) frames are dense in pixels, so the flattened
+        // pixel index addresses them directly: frame 0, "row" = global pixel
         const int64_t pix = (int64_t)spt * T3_BM + row;
         valid = pix < p.total_pix;
-        frame0 = pix / hw;
-        rr = pix - frame0 * hw;
+        frame0 = 0;
+        rr = pix;
       } else {
         const int ty = spt / p.tiles_x, tx = spt - ty * p.tiles_x;
         const int oy = ty * T3_BH + (row >> 3);
@@ -462,7 +506,7 @@ conv_tc3_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__
         rr = (int64_t)oy * p.Wo + ox;
         frame0 = it.outer;
       }
-      const int co_base = it.chunk * BN + e * NCOL;
+      const int co_base = my_chunk * BN + e * NCOL;
       float sv[LIF ? NCOL : 1], si[LIF ? NCOL : 1];
       if constexpr (LIF) {
         const int64_t soff = ((int64_t)it.outer * hw + rr) * p.Cout + co_base;
@@ -484,6 +528,7 @@ conv_tc3_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__
         const int64_t frame = frame0 + (int64_t)t * p.Bsz;
         const int64_t out_off = frame * p.out_bs + rr * p.out_ps;
         const int64_t res_off = frame * p.res_bs + rr * p.res_ps;
+        if (warp == 8) tl_mark(p, (int)local, 10);
         if (p.vec_store) {
           // row -> (output offset | -1, residual offset) table of this warp's 32 rows for the staged stores
           __syncwarp();
@@ -493,6 +538,7 @@ conv_tc3_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__
           __syncwarp();
         }
         mbar_wait(&acc_full[acc], acc_ph);
+        if (warp == 8) tl_mark(p, (int)local, 7);
         tc_fence_after();
         const uint32_t t_row = tmem_base + ((uint32_t)(q * 32) << 16) + acc * (2 * BN) + e * NCOL;
 #pragma unroll
@@ -501,11 +547,13 @@ conv_tc3_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__
           tmem_ld_32x16(t_row + c0, r);
           tmem_ld_32x16(t_row + BN + c0, rc);
           tmem_ld_wait();
+          if (c0 == 0 && warp == 8) tl_mark(p, (int)local, 11);
           if (c0 + 16 >= NCOL) {
             // last TMEM read of this tile: hand the accumulator back before the global traffic
             tc_fence_before();
             __syncwarp();
             if (lane == 0) mbar_arrive(&acc_empty[acc]);
+            if (warp == 8) tl_mark(p, (int)local, 8);
           }
           const int co0 = co_base + c0;
           const bool live = valid && co0 < p.Cout;
@@ -585,6 +633,7 @@ conv_tc3_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__
             }
           }
         }
+        if (warp == 8) tl_mark(p, (int)local, 12);
       }
       if constexpr (LIF) {
         if (valid && co_base < p.Cout) {
@@ -779,7 +828,10 @@ int conv_tc3_dispatch(const soda_conv_desc_t* d, const float* x, const float* pa
   const int64_t HW = (int64_t)d->H * d->W;
   const bool frames_dense = d->N == 1 || d->in_batch_stride == HW * d->in_pix_stride;
   p.mode = d->stride == 1 ? 0 : 1;
-  p.flat = (d->k == 1 && d->stride == 1 && frames_dense && !is_lif && !(p.dbg & 32)) ? 1 : 0;   // dbg 32: tiled 1x1
+  const int64_t HWo = (int64_t)p.Ho * p.Wo;
+  const bool out_dense = (d->N == 1 || d->out_batch_stride == HWo * d->out_pix_stride) &&
+                         (residual == nullptr || d->N == 1 || d->res_batch_stride == HWo * d->res_pix_stride);
+  p.flat = (d->k == 1 && d->stride == 1 && frames_dense && out_dense && !is_lif && !(p.dbg & 32)) ? 1 : 0;   // dbg 32: tiled 1x1
   p.rows = T3_BM, p.WW = T3_BW, p.sbo = 1024;
   if (p.flat) {
     p.n_spatial = (int)ceil_div(p.total_pix, T3_BM);
@@ -872,8 +924,42 @@ int conv_tc3_dispatch(const soda_conv_desc_t* d, const float* x, const float* pa
   int grid = p.n_items < kNumSMs ? p.n_items : kNumSMs;
   grid = grid / p.nch * p.nch;
   if (grid < p.nch) grid = p.nch;
+  p.it_step_sp = (grid / p.nch) % p.n_sp_items;
+  p.it_step_outer = (grid / p.nch) / p.n_sp_items;
   const size_t smem = (size_t)p.b_region_bytes + (size_t)p.a_stages * p.a_stage_bytes + 512 + T3_STAGE_BYTES + 1024;
   cudaStream_t st = (cudaStream_t)stream;
+#ifdef SODA_TC_TIMELINE
+  if (p.dbg & 64) {
+    // debug only: synchronous timeline dump of CTA 0's first tiles (clock64 per role, relative to the first event)
+    static unsigned long long* d_tl = nullptr;
+    const size_t nb = (size_t)TL_TILES * 16 * sizeof(unsigned long long);
+    if (d_tl == nullptr) cudaMalloc(&d_tl, nb);
+    cudaMemsetAsync(d_tl, 0, nb, st);
+    p.tl = d_tl;
+    int rc;
+    if (is_lif) rc = BN == 32 ? launch_tc3<32, true>(tmA, tmB, p, grid, smem, st) : launch_tc3<64, true>(tmA, tmB, p, grid, smem, st);
+    else if (BN == 32) rc = launch_tc3<32, false>(tmA, tmB, p, grid, smem, st);
+    else if (BN == 64) rc = launch_tc3<64, false>(tmA, tmB, p, grid, smem, st);
+    else rc = launch_tc3<128, false>(tmA, tmB, p, grid, smem, st);
+    static int dumps = 0;
+    if (rc == 0 && dumps++ < 1) {
+      unsigned long long h[TL_TILES * 16];
+      cudaStreamSynchronize(st);
+      cudaMemcpy(h, d_tl, nb, cudaMemcpyDeviceToHost);
+      unsigned long long t0 = ~0ull;
+      for (int i = 0; i < TL_TILES * 16; ++i) if (h[i] && h[i] < t0) t0 = h[i];
+      fprintf(stderr, "conv_tc3 timeline (clk since first event) BN=%d mt=%d a_stages=%d b_stat=%d mode=%d items=%d grid=%d\n"
+              "tile  prodTMA splitFul splitRdy mainFull mainCmt  corrRdy  corrCmt  epiFull  epiFree mainAccE epiStart  epiTmem   epiEnd\n",
+              BN, p.mt, p.a_stages, p.b_stationary, p.mode, p.n_items, grid);
+      for (int t = 0; t < TL_TILES; ++t) {
+        fprintf(stderr, "%4d", t);
+        for (int e = 0; e < 13; ++e) fprintf(stderr, " %8lld", h[t * 16 + e] ? (long long)(h[t * 16 + e] - t0) : -1LL);
+        fprintf(stderr, "\n");
+      }
+    }
+    return rc;
+  }
+#endif
   if (is_lif) {
     if (BN == 32) return launch_tc3<32, true>(tmA, tmB, p, grid, smem, st);
     return launch_tc3<64, true>(tmA, tmB, p, grid, smem, st);
