@@ -78,7 +78,8 @@ struct Tc3Params {
   int n_outer, T_inner, Bsz;     // work items = nch * n_spatial * n_outer, each walks T_inner frames
   int n_items;
   int b_stationary, b_stages;
-  int a_stages;
+  int a_stages;                  // fp32 planes in the TMA ring
+  int c_stages;                  // correction planes (written by the split warps, read by the correction MMAs)
   uint32_t a_stage_bytes, a_tx_bytes, b_region_bytes;
   int64_t total_pix;
   int64_t out_bs, out_ps, res_bs, res_ps;
@@ -144,21 +145,26 @@ struct Tc3Iter {
 // lane issues, so descriptors live in uniform registers.
 template <int BN, bool CORR, int MT>
 __device__ __forceinline__ void tc3_mma_role(const Tc3Params& p, uint32_t tmem_base, uint32_t smem_a_u32,
-                                             uint32_t smem_b_u32, uint64_t* a_ready /* CORR: split done; main: TMA landed */,
-                                             uint64_t* a_empty,
+                                             uint32_t smem_b_u32,
+                                             uint64_t* a_ready /* CORR: correction plane written (c_full); main: TMA landed */,
+                                             uint64_t* a_empty, uint64_t* c_empty,
                                              uint64_t* b_full, uint64_t* b_empty, uint64_t* acc_full,
                                              uint64_t* acc_empty) {
   constexpr uint32_t B_TILE = BN * 128, B_STAGE = 2 * B_TILE;
   constexpr uint32_t idesc = CORR ? idesc_bf16(T3_BM, BN) : idesc_tf32(T3_BM, BN);
   // + (bytes >> 4) on a descriptor moves its start address
-  const uint64_t a_desc0 = smem_desc_sw128_sbo(smem_a_u32 + (CORR ? p.plane_bytes : 0u), p.sbo);
+  // fp32 planes [a_stages] then correction planes [c_stages]: two rings, so that the TMA ring can be deeper than
+  // the short-lived correction planes (measured: with 32 KB coupled stages the ring of a 1x1 layer held ONE tile and
+  // the tile period was TMA latency + one stage of MMAs)
+  const uint64_t a_desc0 = smem_desc_sw128_sbo(smem_a_u32 + (CORR ? (uint32_t)p.a_stages * p.plane_bytes : 0u), p.sbo);
   const uint64_t b_desc0 = smem_desc_sw128(smem_b_u32 + (CORR ? B_TILE : 0u));
   const bool half = CORR && p.a_exact;   // exact inputs have no lo(a) half
   const bool stat = p.b_stationary != 0;
   const bool halo3 = p.mode == 0 && p.k == 3;
   const int stages_per_tile = p.mode == 0 ? p.cblocks : p.kblocks;
   const int kb_per_stage = p.mode == 0 ? p.taps : 1;
-  const uint32_t a_stage16 = p.a_stage_bytes >> 4;
+  const uint32_t a_stage16 = p.plane_bytes >> 4;
+  uint32_t sc = 0, pc = 0;    // correction ring slot / parity (CORR only)
   constexpr uint32_t NACC = BN <= 64 ? 4 : 2;   // accumulator stages of (main | correction) in TMEM
   uint32_t sa = 0, pa = 0;    // A ring stage / parity
   uint32_t sb = 0, pb = 0;    // B ring stage / parity (streamed B)
@@ -178,12 +184,19 @@ __device__ __forceinline__ void tc3_mma_role(const Tc3Params& p, uint32_t tmem_b
       uint32_t accum = 0;
       for (int st = 0; st < stages_per_tile; ++st) {
         // the mt tiles of the item own consecutive ring stages for this slab / k-block
-        uint32_t s_m[2];
+        uint32_t s_m[2], c_m[2];
         uint64_t a_st[2];
         _Pragma("unroll") for (int m = 0; m < 2; ++m) if (m < mt) {
-          mbar_wait(&a_ready[sa], pa);
+          if (CORR) {
+            mbar_wait(&a_ready[sc], pc);
+            c_m[m] = sc;
+            a_st[m] = a_desc0 + (uint64_t)(sc * a_stage16);
+            if (++sc == (uint32_t)p.c_stages) sc = 0, pc ^= 1;
+          } else {
+            mbar_wait(&a_ready[sa], pa);
+            a_st[m] = a_desc0 + (uint64_t)(sa * a_stage16);
+          }
           s_m[m] = sa;
-          a_st[m] = a_desc0 + (uint64_t)(sa * a_stage16);
           if (++sa == (uint32_t)p.a_stages) sa = 0, pa ^= 1;
         }
         if (st == 0) tl_mark(p, (int)cnt, CORR ? 5 : 3);
@@ -229,7 +242,10 @@ __device__ __forceinline__ void tc3_mma_role(const Tc3Params& p, uint32_t tmem_b
           if (!stat && ++sb == (uint32_t)p.b_stages) sb = 0, pb ^= 1;
         }
         if (elect_one()) {
-          _Pragma("unroll") for (int m = 0; m < 2; ++m) if (m < mt) mma_commit(&a_empty[s_m[m]]);
+          _Pragma("unroll") for (int m = 0; m < 2; ++m) if (m < mt) {
+            mma_commit(&a_empty[s_m[m]]);
+            if (CORR) mma_commit(&c_empty[c_m[m]]);
+          }
         }
       }
       if (elect_one()) {
@@ -252,7 +268,7 @@ conv_tc3_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
   uint8_t* smem_b = smem;
   uint8_t* smem_a = smem + p.b_region_bytes;
-  uint64_t* bars = reinterpret_cast<uint64_t*>(smem_a + (size_t)p.a_stages * p.a_stage_bytes);
+  uint64_t* bars = reinterpret_cast<uint64_t*>(smem_a + (size_t)(p.a_stages + p.c_stages) * p.plane_bytes);
   uint64_t* a_full = bars;                        // TMA bytes of an A stage landed            [8]
   uint64_t* a_ready = bars + 8;                   // stage split (hi in place + correction plane) [8]
   uint64_t* a_empty = bars + 16;                  // both MMA streams done with the stage     [8]
@@ -260,7 +276,8 @@ conv_tc3_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__
   uint64_t* b_empty = bars + 32;                  // [8]
   uint64_t* acc_full = bars + 40;                 // [4]
   uint64_t* acc_empty = bars + 44;                // [4]
-  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 48);
+  uint64_t* c_empty = bars + 48;                  // correction MMAs done with a correction plane  [8]
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 56);
 
   const int warp = threadIdx.x >> 5;
   const int lane = threadIdx.x & 31;
@@ -274,6 +291,7 @@ conv_tc3_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__
       mbar_init(&a_empty[s], 2);      // one commit per MMA stream
       mbar_init(&b_full[s], 1);
       mbar_init(&b_empty[s], 2);
+      mbar_init(&c_empty[s], 1);      // the correction MMA stream's commit
     }
     for (int a = 0; a < 4; ++a) {
       mbar_init(&acc_full[a], 2);
@@ -355,7 +373,7 @@ conv_tc3_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__
               if (tap == 0 && cb == 0 && m == 0) tl_mark(p, tl_tile, 0);
               if (elect_one()) {
                 mbar_expect_tx(&a_full[s], p.a_tx_bytes);
-                tma_load_4d_s(smem_a_u32 + s * p.a_stage_bytes, &tmA, &a_full[s], cb * T3_BK, x0[m] + kx, y0[m] + ky,
+                tma_load_4d_s(smem_a_u32 + s * p.plane_bytes, &tmA, &a_full[s], cb * T3_BK, x0[m] + kx, y0[m] + ky,
                               img);
               }
               __syncwarp();
@@ -406,17 +424,17 @@ conv_tc3_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__
     }
   } else if (warp == T3_W_MMA_MAIN) {
     if (p.mt == 2)
-      tc3_mma_role<BN, false, 2>(p, tmem_base, smem_u32(smem_a), smem_u32(smem_b), a_full, a_empty, b_full, b_empty,
+      tc3_mma_role<BN, false, 2>(p, tmem_base, smem_u32(smem_a), smem_u32(smem_b), a_full, a_empty, c_empty, b_full, b_empty,
                                  acc_full, acc_empty);
     else
-      tc3_mma_role<BN, false, 1>(p, tmem_base, smem_u32(smem_a), smem_u32(smem_b), a_full, a_empty, b_full, b_empty,
+      tc3_mma_role<BN, false, 1>(p, tmem_base, smem_u32(smem_a), smem_u32(smem_b), a_full, a_empty, c_empty, b_full, b_empty,
                                  acc_full, acc_empty);
   } else if (warp == T3_W_MMA_CORR) {
     if (p.mt == 2)
-      tc3_mma_role<BN, true, 2>(p, tmem_base, smem_u32(smem_a), smem_u32(smem_b), a_ready, a_empty, b_full, b_empty,
+      tc3_mma_role<BN, true, 2>(p, tmem_base, smem_u32(smem_a), smem_u32(smem_b), a_ready, a_empty, c_empty, b_full, b_empty,
                                 acc_full, acc_empty);
     else
-      tc3_mma_role<BN, true, 1>(p, tmem_base, smem_u32(smem_a), smem_u32(smem_b), a_ready, a_empty, b_full, b_empty,
+      tc3_mma_role<BN, true, 1>(p, tmem_base, smem_u32(smem_a), smem_u32(smem_b), a_ready, a_empty, c_empty, b_full, b_empty,
                                 acc_full, acc_empty);
   } else if (warp < 8) {
     // ============ split: fp32 slab -> tf32 hi (in place) + [bf16 hi | bf16 lo] correction plane =========
@@ -427,14 +445,16 @@ conv_tc3_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__
     const int n_task = p.rows * 4;
     const int stages_per_tile = (p.mode == 0 ? p.cblocks : p.kblocks) * p.mt;
     uint32_t s = 0, ph = 0;
+    uint32_t c = 0, cph = 0;   // correction ring slot / parity
     int tl_tile = 0;
     for (int item = blockIdx.x; item < p.n_items; item += gridDim.x) {
       for (int t = 0; t < p.T_inner; ++t, tl_tile += p.mt) {
         for (int st = 0; st < stages_per_tile; ++st) {
           mbar_wait(&a_full[s], ph);
           if (st == 0 && warp == 0) tl_mark(p, tl_tile, 1);
-          const uint32_t hi_pl = smem_a_u32 + s * p.a_stage_bytes;
-          const uint32_t cr_pl = hi_pl + p.plane_bytes;
+          mbar_wait(&c_empty[c], cph ^ 1);
+          const uint32_t hi_pl = smem_a_u32 + s * p.plane_bytes;
+          const uint32_t cr_pl = smem_a_u32 + ((uint32_t)p.a_stages + c) * p.plane_bytes;
           if (!(p.dbg & 1)) {
             for (int task = (int)threadIdx.x; task < n_task; task += 256) {
               const uint32_t P = (uint32_t)task >> 2, q = (uint32_t)task & 3u, sw = P & 7u;
@@ -465,7 +485,8 @@ conv_tc3_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__
           // generic-proxy writes must be visible to the tensor core's (async proxy) operand reads
           fence_proxy_async_smem();
           __syncwarp();
-          if (lane == 0) mbar_arrive(&a_ready[s]);
+          if (lane == 0) mbar_arrive(&a_ready[c]);
+          if (++c == (uint32_t)p.c_stages) c = 0, cph ^= 1;
           if (st == 0 && warp == 0) tl_mark(p, tl_tile, 2);
           if (++s == (uint32_t)p.a_stages) s = 0, ph ^= 1;
         }
@@ -877,15 +898,22 @@ int conv_tc3_dispatch(const soda_conv_desc_t* d, const float* x, const float* pa
     int rc = encode_map3(&tmB, packed, 3, dims, str, box, es);
     if (rc) return rc;
   }
-  // shared-memory plan: weights resident if one chunk fits beside a useful A ring, else two rings
+  // shared-memory plan (in planes of plane_bytes): fp32 TMA ring of a_stages planes + c_stages correction planes,
+  // weights resident if one chunk fits beside a useful ring, else a weight ring as well
   const int64_t b_total = (int64_t)p.kblocks * b_stage;
   const bool halo3 = p.mode == 0 && p.k == 3;
-  const int a_min = halo3 ? 2 : 3;
-  const int a_want = halo3 ? 3 : 6;
-  if (b_total + (int64_t)a_min * p.a_stage_bytes <= T3_SMEM_LIMIT && b_total < (1 << 20)) {
+  const int64_t plane = p.plane_bytes;
+  const char* e_as = getenv("SODA_TC_ASTAGES");   // experiments: cap on the fp32 ring depth
+  const int a_cap = e_as ? std::max(2, std::min(T3_MAX_RING, atoi(e_as))) : T3_MAX_RING;
+  const char* e_cs = getenv("SODA_TC_CSTAGES");
+  const int c_env = e_cs ? std::max(2, std::min(T3_MAX_RING, atoi(e_cs))) : 0;
+  if (b_total + 5 * plane <= T3_SMEM_LIMIT && b_total < (1 << 20)) {
     p.b_stationary = 1, p.b_stages = 1, p.mt = 1;
     p.b_region_bytes = (uint32_t)b_total;
-    p.a_stages = (int)std::min<int64_t>(a_want, (T3_SMEM_LIMIT - b_total) / p.a_stage_bytes);
+    // two correction planes are enough (SODA_TC_CSTAGES sweep: 3-4 planes gain nothing in isolation and cost 15 % of
+    // the whole step by shortening the fp32 ring)
+    p.c_stages = c_env > 0 ? c_env : 2;
+    p.a_stages = (int)std::min<int64_t>(a_cap, (T3_SMEM_LIMIT - b_total) / plane - p.c_stages);
   } else {
     // Streamed weights: every k-block (2 * BN * 128 B) comes from L2 once per work item, and at one 128-pixel tile
     // per item that stream alone exceeds what L2 can deliver to 148 SMs (measured floor: the load skeleton of the
@@ -894,23 +922,19 @@ int conv_tc3_dispatch(const soda_conv_desc_t* d, const float* x, const float* pa
     // (BN <= 64: 4 accumulator stages; at BN = 128 the pair would serialise MMA and epilogue - measured slower) and
     // not with LIF (state registers).
     p.b_stationary = 0;
-    p.mt = 1;
     const char* e_mt = getenv("SODA_TC_MT");
     const bool want_pair = !is_lif && p.n_spatial > 1 && (e_mt ? atoi(e_mt) == 2 : BN <= 64);
-    bool planned = false;
-    if (want_pair) {
-      for (int a = 4; a >= 2 && !planned; --a) {
-        const int64_t rem = T3_SMEM_LIMIT - (int64_t)a * p.a_stage_bytes;
-        const int bs = (int)std::min<int64_t>(T3_MAX_RING, rem / (int64_t)b_stage);
-        if (rem > 0 && bs >= (a > 2 ? 3 : 2)) {
-          p.mt = 2, p.a_stages = a, p.b_stages = bs, planned = true;
-        }
-      }
-    }
-    if (!planned) {
-      p.a_stages = halo3 ? 2 : 3;
-      p.b_stages = (int)std::min<int64_t>(T3_MAX_RING, (T3_SMEM_LIMIT - (int64_t)p.a_stages * p.a_stage_bytes) / b_stage);
-    }
+    p.mt = want_pair ? 2 : 1;
+    p.c_stages = c_env > 0 ? c_env : 2;
+    // weight ring first (>= 4 stages if possible), the rest goes to the fp32 ring
+    const int a_floor = p.mt == 2 ? 2 : 2;
+    int bs = 4;
+    while (bs > 2 && (int64_t)bs * b_stage + (a_floor + p.c_stages) * plane > T3_SMEM_LIMIT) --bs;
+    int64_t a = (T3_SMEM_LIMIT - (int64_t)bs * b_stage) / plane - p.c_stages;
+    if (a < a_floor) return fail(SODA_ERR_UNSUPPORTED, "conv_tc: shared-memory plan does not fit");
+    const int a_pref = halo3 ? 3 : 6;   // beyond this, extra room serves the weight ring better
+    p.a_stages = (int)std::min<int64_t>(std::min<int64_t>(a, a_cap), p.mt == 2 ? std::max(a_pref, 4) : a_pref);
+    p.b_stages = (int)std::min<int64_t>(T3_MAX_RING, (T3_SMEM_LIMIT - (int64_t)(p.a_stages + p.c_stages) * plane) / b_stage);
     if (p.b_stages < 2) return fail(SODA_ERR_UNSUPPORTED, "conv_tc: shared-memory plan does not fit");
     p.b_region_bytes = (uint32_t)p.b_stages * b_stage;
   }
@@ -926,7 +950,7 @@ int conv_tc3_dispatch(const soda_conv_desc_t* d, const float* x, const float* pa
   if (grid < p.nch) grid = p.nch;
   p.it_step_sp = (grid / p.nch) % p.n_sp_items;
   p.it_step_outer = (grid / p.nch) / p.n_sp_items;
-  const size_t smem = (size_t)p.b_region_bytes + (size_t)p.a_stages * p.a_stage_bytes + 512 + T3_STAGE_BYTES + 1024;
+  const size_t smem = (size_t)p.b_region_bytes + (size_t)(p.a_stages + p.c_stages) * p.plane_bytes + 512 + T3_STAGE_BYTES + 1024;
   cudaStream_t st = (cudaStream_t)stream;
 #ifdef SODA_TC_TIMELINE
   if (p.dbg & 64) {
@@ -949,7 +973,7 @@ int conv_tc3_dispatch(const soda_conv_desc_t* d, const float* x, const float* pa
       unsigned long long t0 = ~0ull;
       for (int i = 0; i < TL_TILES * 16; ++i) if (h[i] && h[i] < t0) t0 = h[i];
       fprintf(stderr, "conv_tc3 timeline (clk since first event) BN=%d mt=%d a_stages=%d b_stat=%d mode=%d items=%d grid=%d\n"
-              "tile  prodTMA splitFul splitRdy mainFull mainCmt  corrRdy  corrCmt  epiFull  epiFree mainAccE epiStart  epiTmem   epiEnd\n",
+              "a_stages/c_stages/b_stages see header\n" "tile  prodTMA splitFul splitRdy mainFull mainCmt  corrRdy  corrCmt  epiFull  epiFree mainAccE epiStart  epiTmem   epiEnd\n",
               BN, p.mt, p.a_stages, p.b_stationary, p.mode, p.n_items, grid);
       for (int t = 0; t < TL_TILES; ++t) {
         fprintf(stderr, "%4d", t);
