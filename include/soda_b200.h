@@ -103,6 +103,12 @@ SODA_API int soda_bin_events(const void* events, const int64_t* sample_offsets, 
 /* flags: the input tensor holds only values exactly representable in TF32 (spikes {0,1}, pooled
  * spike counts, event frames): the tensor-core kernel then skips the A-operand split pass. */
 #define SODA_CONV_FLAG_INPUT_EXACT_TF32 1
+/* flags: every input value has at most 8 significant bits (spikes {0,1}, sums / 2x2 sum pools of a few spike
+ * maps: integers <= 256), i.e. is exact in bf16.  The tensor-core kernel then drops the tf32 pass altogether:
+ * x (bf16, exact) times [bf16 rn(w) | bf16 rn(w - rn(w))] in two kind::f16 products with fp32 accumulation -
+ * 16+ significant weight bits, half the tensor-core work and half the weight bytes of the tf32 + correction
+ * scheme.  Implies SODA_CONV_FLAG_INPUT_EXACT_TF32. */
+#define SODA_CONV_FLAG_INPUT_EXACT_BF16 2
 
 typedef struct {
   int N, H, W, Cin, Cout, k, stride;

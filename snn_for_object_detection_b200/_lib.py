@@ -17,6 +17,7 @@ LIB_PATH = os.path.join(_HERE, "libsoda_b200.so")
 SODA_CONV_FP32 = 0
 SODA_CONV_TC = 1
 SODA_CONV_FLAG_INPUT_EXACT_TF32 = 1
+SODA_CONV_FLAG_INPUT_EXACT_BF16 = 2
 
 
 class SodaError(RuntimeError):

@@ -70,6 +70,9 @@ struct Tc3Params {
   int mode;                      // 0 = HALO (one A stage per 32-channel slab, `taps` k-blocks), 1 = TAP
   int flat;                      // 1x1 stride-1 over the flattened pixel list
   int a_exact;
+  int spk;                       // input exact in bf16 (spikes, pooled spike counts): bf16-only products against the
+                                 // [bf16 hi | bf16 mid] weight plane - no tf32 pass, no main weight plane
+  uint32_t b_stage_bytes;        // one k-block of weights in shared memory: BN*128 (spk) or 2*BN*128
   int rows;                      // 128-byte rows in one A plane (180 halo pixels, or 128)
   int WW;                        // halo row pitch in pixels
   uint32_t sbo;                  // bytes between the 8-row groups of the A operand
@@ -143,21 +146,22 @@ struct Tc3Iter {
 // One warp per accumulator.  CORR = false: tf32 main pass over the hi planes; CORR = true: bf16 correction
 // pass over the [bf16 hi | bf16 lo] x [bf16 lo | bf16 hi] planes.  Warp-uniform control flow; one elected
 // lane issues, so descriptors live in uniform registers.
-template <int BN, bool CORR, int MT>
+template <int BN, bool CORR, int MT, bool SPK>
 __device__ __forceinline__ void tc3_mma_role(const Tc3Params& p, uint32_t tmem_base, uint32_t smem_a_u32,
                                              uint32_t smem_b_u32,
                                              uint64_t* a_ready /* CORR: correction plane written (c_full); main: TMA landed */,
                                              uint64_t* a_empty, uint64_t* c_empty,
                                              uint64_t* b_full, uint64_t* b_empty, uint64_t* acc_full,
                                              uint64_t* acc_empty) {
-  constexpr uint32_t B_TILE = BN * 128, B_STAGE = 2 * B_TILE;
+  static_assert(CORR || !SPK, "the bf16-only scheme has no tf32 stream");
+  constexpr uint32_t B_TILE = BN * 128, B_STAGE = SPK ? B_TILE : 2 * B_TILE;
   constexpr uint32_t idesc = CORR ? idesc_bf16(T3_BM, BN) : idesc_tf32(T3_BM, BN);
   // + (bytes >> 4) on a descriptor moves its start address
   // fp32 planes [a_stages] then correction planes [c_stages]: two rings, so that the TMA ring can be deeper than
   // the short-lived correction planes (measured: with 32 KB coupled stages the ring of a 1x1 layer held ONE tile and
   // the tile period was TMA latency + one stage of MMAs)
   const uint64_t a_desc0 = smem_desc_sw128_sbo(smem_a_u32 + (CORR ? (uint32_t)p.a_stages * p.plane_bytes : 0u), p.sbo);
-  const uint64_t b_desc0 = smem_desc_sw128(smem_b_u32 + (CORR ? B_TILE : 0u));
+  const uint64_t b_desc0 = smem_desc_sw128(smem_b_u32 + ((CORR && !SPK) ? B_TILE : 0u));
   const bool half = CORR && p.a_exact;   // exact inputs have no lo(a) half
   const bool stat = p.b_stationary != 0;
   const bool halo3 = p.mode == 0 && p.k == 3;
@@ -177,7 +181,7 @@ __device__ __forceinline__ void tc3_mma_role(const Tc3Params& p, uint32_t tmem_b
       _Pragma("unroll") for (int m = 0; m < 2; ++m) if (m < mt) {
         const uint32_t a = (cnt + m) % NACC, ph = ((cnt + m) / NACC) & 1u;
         mbar_wait(&acc_empty[a], ph ^ 1);
-        d_acc[m] = tmem_base + a * (2 * BN) + (CORR ? (uint32_t)BN : 0u);
+        d_acc[m] = tmem_base + a * (2 * BN) + ((CORR && !SPK) ? (uint32_t)BN : 0u);
       }
       if (!CORR) tl_mark(p, (int)cnt, 9);
       tc_fence_after();
@@ -220,7 +224,13 @@ __device__ __forceinline__ void tc3_mma_role(const Tc3Params& p, uint32_t tmem_b
             if (!(p.dbg & 4)) {
               _Pragma("unroll") for (int m = 0; m < 2; ++m) if (m < mt) {
                 const uint64_t a_desc = a_st[m] + tap_off;
-                if (CORR) {
+                if (SPK) {
+                  // a(32 ch, bf16, first half of the row) x [W_hi | W_mid]: the A descriptor revisits the same 64 bytes
+                  mma_bf16_ss(d_acc[m], a_desc, b_desc, idesc, accum);
+                  mma_bf16_ss(d_acc[m], a_desc + 2, b_desc + 2, idesc, 1);
+                  mma_bf16_ss(d_acc[m], a_desc, b_desc + 4, idesc, 1);
+                  mma_bf16_ss(d_acc[m], a_desc + 2, b_desc + 6, idesc, 1);
+                } else if (CORR) {
                   mma_bf16_ss(d_acc[m], a_desc, b_desc, idesc, accum);
                   mma_bf16_ss(d_acc[m], a_desc + 2, b_desc + 2, idesc, 1);
                   if (!half) {
@@ -243,7 +253,7 @@ __device__ __forceinline__ void tc3_mma_role(const Tc3Params& p, uint32_t tmem_b
         }
         if (elect_one()) {
           _Pragma("unroll") for (int m = 0; m < 2; ++m) if (m < mt) {
-            mma_commit(&a_empty[s_m[m]]);
+            if (!SPK) mma_commit(&a_empty[s_m[m]]);   // SPK: the split warps release the fp32 plane themselves
             if (CORR) mma_commit(&c_empty[c_m[m]]);
           }
         }
@@ -257,11 +267,11 @@ __device__ __forceinline__ void tc3_mma_role(const Tc3Params& p, uint32_t tmem_b
   }
 }
 
-template <int BN, bool LIF>
+template <int BN, bool LIF, bool SPK>
 __global__ void __launch_bounds__(T3_THREADS, 1)
 conv_tc3_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB, Tc3Params p) {
   constexpr uint32_t B_TILE = BN * 128;        // one plane of one k-block: BN rows x 128 B
-  constexpr uint32_t B_STAGE = 2 * B_TILE;     // tf32 hi plane + bf16 [lo|hi] plane
+  constexpr uint32_t B_STAGE = SPK ? B_TILE : 2 * B_TILE;   // tf32 hi plane + bf16 [lo|hi] plane, or the [hi|mid] plane alone
   constexpr uint32_t NACC = BN <= 64 ? 4 : 2;  // accumulator stages of (main | correction)
   constexpr uint32_t TMEM_COLS = NACC * 2 * BN;
   extern __shared__ uint8_t smem_raw[];
@@ -288,13 +298,13 @@ conv_tc3_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__
     for (int s = 0; s < T3_MAX_RING; ++s) {
       mbar_init(&a_full[s], 1);
       mbar_init(&a_ready[s], 8);      // one arrival per split warp
-      mbar_init(&a_empty[s], 2);      // one commit per MMA stream
+      mbar_init(&a_empty[s], SPK ? 8 : 2);   // one commit per MMA stream; spk: one arrival per split warp
       mbar_init(&b_full[s], 1);
-      mbar_init(&b_empty[s], 2);
+      mbar_init(&b_empty[s], SPK ? 1 : 2);
       mbar_init(&c_empty[s], 1);      // the correction MMA stream's commit
     }
     for (int a = 0; a < 4; ++a) {
-      mbar_init(&acc_full[a], 2);
+      mbar_init(&acc_full[a], SPK ? 1 : 2);
       mbar_init(&acc_empty[a], 8);    // one arrival per epilogue warp
     }
     fence_barrier_init();
@@ -395,8 +405,12 @@ conv_tc3_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__
         for (int cb = 0; cb < p.cblocks; ++cb) {
           const uint32_t dst = smem_b_u32 + (uint32_t)(tap * p.cblocks + cb) * B_STAGE;
           if (elect_one()) {
-            tma_load_3d_s(dst, &tmB, &b_full[0], cb * T3_BK, my_chunk * BN, tap);
-            tma_load_3d_s(dst + B_TILE, &tmB, &b_full[0], cb * T3_BK, my_chunk * BN, p.taps + tap);
+            if (SPK) {
+              tma_load_3d_s(dst, &tmB, &b_full[0], cb * T3_BK, my_chunk * BN, 2 * p.taps + tap);
+            } else {
+              tma_load_3d_s(dst, &tmB, &b_full[0], cb * T3_BK, my_chunk * BN, tap);
+              tma_load_3d_s(dst + B_TILE, &tmB, &b_full[0], cb * T3_BK, my_chunk * BN, p.taps + tap);
+            }
           }
           __syncwarp();
         }
@@ -413,8 +427,12 @@ conv_tc3_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__
               if (elect_one()) {
                 mbar_expect_tx(&b_full[s], B_STAGE);
                 const uint32_t dst = smem_b_u32 + s * B_STAGE;
-                tma_load_3d_s(dst, &tmB, &b_full[s], cb * T3_BK, my_chunk * BN, tap);
-                tma_load_3d_s(dst + B_TILE, &tmB, &b_full[s], cb * T3_BK, my_chunk * BN, p.taps + tap);
+                if (SPK) {
+                  tma_load_3d_s(dst, &tmB, &b_full[s], cb * T3_BK, my_chunk * BN, 2 * p.taps + tap);
+                } else {
+                  tma_load_3d_s(dst, &tmB, &b_full[s], cb * T3_BK, my_chunk * BN, tap);
+                  tma_load_3d_s(dst + B_TILE, &tmB, &b_full[s], cb * T3_BK, my_chunk * BN, p.taps + tap);
+                }
               }
               __syncwarp();
               if (++s == (uint32_t)p.b_stages) s = 0, ph ^= 1;
@@ -423,19 +441,22 @@ conv_tc3_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__
       }
     }
   } else if (warp == T3_W_MMA_MAIN) {
-    if (p.mt == 2)
-      tc3_mma_role<BN, false, 2>(p, tmem_base, smem_u32(smem_a), smem_u32(smem_b), a_full, a_empty, c_empty, b_full, b_empty,
-                                 acc_full, acc_empty);
-    else
-      tc3_mma_role<BN, false, 1>(p, tmem_base, smem_u32(smem_a), smem_u32(smem_b), a_full, a_empty, c_empty, b_full, b_empty,
-                                 acc_full, acc_empty);
+    // bf16-only scheme (SPK): no tf32 stream, this warp only owns the TMEM allocation
+    if constexpr (!SPK) {
+      if (p.mt == 2)
+        tc3_mma_role<BN, false, 2, false>(p, tmem_base, smem_u32(smem_a), smem_u32(smem_b), a_full, a_empty, c_empty, b_full,
+                                          b_empty, acc_full, acc_empty);
+      else
+        tc3_mma_role<BN, false, 1, false>(p, tmem_base, smem_u32(smem_a), smem_u32(smem_b), a_full, a_empty, c_empty, b_full,
+                                          b_empty, acc_full, acc_empty);
+    }
   } else if (warp == T3_W_MMA_CORR) {
     if (p.mt == 2)
-      tc3_mma_role<BN, true, 2>(p, tmem_base, smem_u32(smem_a), smem_u32(smem_b), a_ready, a_empty, c_empty, b_full, b_empty,
-                                acc_full, acc_empty);
+      tc3_mma_role<BN, true, 2, SPK>(p, tmem_base, smem_u32(smem_a), smem_u32(smem_b), a_ready, a_empty, c_empty, b_full,
+                                     b_empty, acc_full, acc_empty);
     else
-      tc3_mma_role<BN, true, 1>(p, tmem_base, smem_u32(smem_a), smem_u32(smem_b), a_ready, a_empty, c_empty, b_full, b_empty,
-                                acc_full, acc_empty);
+      tc3_mma_role<BN, true, 1, SPK>(p, tmem_base, smem_u32(smem_a), smem_u32(smem_b), a_ready, a_empty, c_empty, b_full,
+                                     b_empty, acc_full, acc_empty);
   } else if (warp < 8) {
     // ============ split: fp32 slab -> tf32 hi (in place) + [bf16 hi | bf16 lo] correction plane =========
     // Task = (pixel row P, 8 channels q).  SWIZZLE_128B: logical 16-byte chunk c of row P sits at chunk
@@ -462,6 +483,13 @@ conv_tc3_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__
               const uint32_t a1 = hi_pl + P * 128u + (((2u * q + 1u) ^ sw) << 4);
               const float4 v0 = lds128(a0), v1 = lds128(a1);
               const float f[8] = {v0.x, v0.y, v0.z, v0.w, v1.x, v1.y, v1.z, v1.w};
+              if constexpr (SPK) {
+                // values are exact in bf16: one conversion, first half of the row only
+                sts128(cr_pl + P * 128u + ((q ^ sw) << 4), __uint_as_float(pack_bf16x2(f[0], f[1])),
+                       __uint_as_float(pack_bf16x2(f[2], f[3])), __uint_as_float(pack_bf16x2(f[4], f[5])),
+                       __uint_as_float(pack_bf16x2(f[6], f[7])));
+                continue;
+              }
               float fh[8], fl[8];
 #pragma unroll
               for (int e = 0; e < 8; ++e) {
@@ -485,7 +513,10 @@ conv_tc3_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__
           // generic-proxy writes must be visible to the tensor core's (async proxy) operand reads
           fence_proxy_async_smem();
           __syncwarp();
-          if (lane == 0) mbar_arrive(&a_ready[c]);
+          if (lane == 0) {
+            mbar_arrive(&a_ready[c]);
+            if (SPK) mbar_arrive(&a_empty[s]);   // the fp32 plane has been read; nobody else needs it
+          }
           if (++c == (uint32_t)p.c_stages) c = 0, cph ^= 1;
           if (st == 0 && warp == 0) tl_mark(p, tl_tile, 2);
           if (++s == (uint32_t)p.a_stages) s = 0, ph ^= 1;
@@ -566,7 +597,7 @@ conv_tc3_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__
         for (int c0 = 0; c0 < NCOL; c0 += 16) {
           uint32_t r[16], rc[16];
           tmem_ld_32x16(t_row + c0, r);
-          tmem_ld_32x16(t_row + BN + c0, rc);
+          if constexpr (!SPK) tmem_ld_32x16(t_row + BN + c0, rc);
           tmem_ld_wait();
           if (c0 == 0 && warp == 8) tl_mark(p, (int)local, 11);
           if (c0 + 16 >= NCOL) {
@@ -580,7 +611,8 @@ conv_tc3_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__
           const bool live = valid && co0 < p.Cout;
           float o[16];
 #pragma unroll
-          for (int jj = 0; jj < 16; ++jj) o[jj] = __uint_as_float(r[jj]) + __uint_as_float(rc[jj]);
+          for (int jj = 0; jj < 16; ++jj)
+            o[jj] = SPK ? __uint_as_float(r[jj]) : __uint_as_float(r[jj]) + __uint_as_float(rc[jj]);
           if (p.shift != nullptr && co0 < p.Cout) {
             if (co0 + 16 <= p.Cout) {
 #pragma unroll
@@ -696,7 +728,7 @@ static inline int tc3_cout_pad(int Cout) {
 
 int64_t conv_tc3_packed_elems(int Cout, int Cin, int k) {
   if (Cin % T3_BK != 0) return 0;
-  return 2LL * k * k * tc3_cout_pad(Cout) * Cin;
+  return 3LL * k * k * tc3_cout_pad(Cout) * Cin;
 }
 
 __device__ __forceinline__ uint16_t tc3_bf16_bits(float f) {
@@ -705,10 +737,13 @@ __device__ __forceinline__ uint16_t tc3_bf16_bits(float f) {
 
 // [Cout, Cin, k, k] -> plane 0: [tap][Cout_pad][Cin] tf32 hi of (w * scale)
 //                      plane 1: [tap][Cout_pad][Cin/32] rows of 128 B = bf16 lo[32] | bf16 hi[32]
+//                      plane 2: same rows = bf16 rn(w)[32] | bf16 rn(w - rn(w))[32]   (bf16-only scheme for
+//                               inputs exact in bf16: 16+ significant weight bits, no tf32 pass)
 __global__ void pack_weights_tc3_kernel(const float* __restrict__ w, const float* __restrict__ scale, int Cout,
                                         int Cin, int taps, int Cout_pad, float* __restrict__ wp) {
   const int64_t plane = (int64_t)taps * Cout_pad * Cin;
   uint16_t* corr = reinterpret_cast<uint16_t*>(wp + plane);
+  uint16_t* spk = reinterpret_cast<uint16_t*>(wp + 2 * plane);
   for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < plane;
        i += (int64_t)gridDim.x * blockDim.x) {
     const int ci = (int)(i % Cin);
@@ -725,6 +760,9 @@ __global__ void pack_weights_tc3_kernel(const float* __restrict__ w, const float
     const int64_t row16 = (r * Cin + (ci & ~31)) * 2;  // start of this 128-byte row, in uint16
     corr[row16 + (ci & 31)] = tc3_bf16_bits(v - hi);
     corr[row16 + 32 + (ci & 31)] = tc3_bf16_bits(hi);
+    const uint16_t wh = tc3_bf16_bits(v);
+    spk[row16 + (ci & 31)] = wh;
+    spk[row16 + 32 + (ci & 31)] = tc3_bf16_bits(v - __uint_as_float((uint32_t)wh << 16));
   }
 }
 
@@ -766,12 +804,12 @@ static int encode_map3(CUtensorMap* m, const void* base, int rank, const cuuint6
   return 0;
 }
 
-template <int BN, bool LIF>
-static int launch_tc3(const CUtensorMap& tmA, const CUtensorMap& tmB, const Tc3Params& p, int grid, size_t smem,
+template <int BN, bool LIF, bool SPK>
+static int launch_tc3_(const CUtensorMap& tmA, const CUtensorMap& tmB, const Tc3Params& p, int grid, size_t smem,
                       cudaStream_t st) {
   static bool attr_set = false;
   if (!attr_set) {
-    cudaError_t e = cudaFuncSetAttribute(conv_tc3_kernel<BN, LIF>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+    cudaError_t e = cudaFuncSetAttribute(conv_tc3_kernel<BN, LIF, SPK>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                          232448);
     if (e != cudaSuccess) {
       set_error("conv_tc: cudaFuncSetAttribute: %s", cudaGetErrorString(e));
@@ -779,8 +817,15 @@ static int launch_tc3(const CUtensorMap& tmA, const CUtensorMap& tmB, const Tc3P
     }
     attr_set = true;
   }
-  conv_tc3_kernel<BN, LIF><<<grid, T3_THREADS, smem, st>>>(tmA, tmB, p);
+  conv_tc3_kernel<BN, LIF, SPK><<<grid, T3_THREADS, smem, st>>>(tmA, tmB, p);
   return after_launch("conv_tc3_kernel");
+}
+
+template <int BN, bool LIF>
+static int launch_tc3(const CUtensorMap& tmA, const CUtensorMap& tmB, const Tc3Params& p, int grid, size_t smem,
+                      cudaStream_t st) {
+  return p.spk ? launch_tc3_<BN, LIF, true>(tmA, tmB, p, grid, smem, st)
+               : launch_tc3_<BN, LIF, false>(tmA, tmB, p, grid, smem, st);
 }
 
 bool conv_tc3_supported(const soda_conv_desc_t* d, const float* x) {
@@ -820,7 +865,11 @@ int conv_tc3_dispatch(const soda_conv_desc_t* d, const float* x, const float* pa
   p.taps = d->k * d->k;
   p.cblocks = d->Cin / T3_BK;
   p.kblocks = p.taps * p.cblocks;
-  p.a_exact = (d->flags & SODA_CONV_FLAG_INPUT_EXACT_TF32) ? 1 : 0;
+  p.a_exact = (d->flags & (SODA_CONV_FLAG_INPUT_EXACT_TF32 | SODA_CONV_FLAG_INPUT_EXACT_BF16)) ? 1 : 0;
+  {
+    const char* e = getenv("SODA_TC_SPK");   // 0: keep the tf32 + correction scheme for bf16-exact inputs (A/B runs)
+    p.spk = (d->flags & SODA_CONV_FLAG_INPUT_EXACT_BF16) && !(e && atoi(e) == 0) ? 1 : 0;
+  }
   p.total_pix = (int64_t)d->N * p.Ho * p.Wo;
   p.out_bs = d->out_batch_stride, p.out_ps = d->out_pix_stride;
   p.res_bs = d->res_batch_stride, p.res_ps = d->res_pix_stride;
@@ -843,7 +892,8 @@ int conv_tc3_dispatch(const soda_conv_desc_t* d, const float* x, const float* pa
   const int BN = tc3_bn_for(d->Cout, is_lif);
   const int Cout_pad = tc3_cout_pad(d->Cout);
   p.nch = (d->Cout + BN - 1) / BN;
-  const uint32_t b_stage = 2u * BN * 128u;
+  const uint32_t b_stage = (p.spk ? 1u : 2u) * BN * 128u;
+  p.b_stage_bytes = b_stage;
 
   CUtensorMap tmA, tmB;
   const int64_t HW = (int64_t)d->H * d->W;
@@ -891,7 +941,7 @@ int conv_tc3_dispatch(const soda_conv_desc_t* d, const float* x, const float* pa
   p.plane_bytes = (p.a_tx_bytes + 1023u) & ~1023u;
   p.a_stage_bytes = 2u * p.plane_bytes;
   {
-    const cuuint64_t dims[3] = {(cuuint64_t)d->Cin, (cuuint64_t)Cout_pad, (cuuint64_t)(2 * p.taps)};
+    const cuuint64_t dims[3] = {(cuuint64_t)d->Cin, (cuuint64_t)Cout_pad, (cuuint64_t)(3 * p.taps)};
     const cuuint64_t str[2] = {(cuuint64_t)d->Cin * 4, (cuuint64_t)Cout_pad * d->Cin * 4};
     const cuuint32_t box[3] = {T3_BK, (cuuint32_t)BN, 1};
     const cuuint32_t es[3] = {1, 1, 1};

@@ -54,6 +54,7 @@ def _copy_into(src: torch.Tensor, dst: torch.Tensor) -> None:
         dst.copy_(src)   # training: differentiable slice store
         return
     ops.channel_affine(src, None, None, out=dst)
+    ops.mark_exact(dst, ops.exact_bound(src))
 
 
 def _fused_lif_plan(conv: SodaConv2d, norm: SodaBatchNorm2d, x: torch.Tensor, T: int):
@@ -176,6 +177,11 @@ class BlockGen(nn.Module):
                 return Y, ([branch_state, other] if bi == 0 else [other, branch_state])
             outs.append(Y)
         if self.merge == "dense":
+            # a concat of spike maps / spike counts is itself one (largest bound): the next Conv may use the
+            # bf16-only operand scheme
+            bounds = [ops.exact_bound(o) for o in outs]
+            if bounds and all(b is not None for b in bounds):
+                ops.mark_exact(dense_buf, max(bounds))
             return dense_buf, out_state
         if self.merge == "residual":
             if torch.is_grad_enabled() and any(o.requires_grad for o in outs):
@@ -357,7 +363,10 @@ class BlockGen(nn.Module):
                         ys.append(y)
                     Y, branch_state[idx] = torch.cat(ys), s
             else:
+                b = ops.exact_bound(Y) if isinstance(layer, (nn.Identity, nn.Upsample)) else None
                 Y = layer(Y)
+                if b is not None and not (isinstance(layer, nn.Upsample) and layer.mode != "nearest"):
+                    ops.mark_exact(Y, b)
             idx += 1
         if dst is not None and dst.data_ptr() != Y.data_ptr():
             _copy_into(Y, dst)

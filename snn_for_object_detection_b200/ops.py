@@ -63,7 +63,7 @@ def _prof(name):
             if name in ("conv2d", "conv_lif"):
                 x, pc = a[0], a[1]
                 PROFILE.setdefault(name + "_tags", []).append(
-                    f"{tuple(x.shape)}->{pc.Cout} k{pc.k} s{pc.stride} kind{pc.kind} exact{int(is_exact(x))}")
+                    f"{tuple(x.shape)}->{pc.Cout} k{pc.k} s{pc.stride} kind{pc.kind} exact{exact_bound(x)}")
                 PROFILE.setdefault(name + "_meta", []).append(
                     dict(N=x.shape[0], Cin=x.shape[1], H=x.shape[2], W=x.shape[3], Cout=pc.Cout, k=pc.k,
                          stride=pc.stride, kind=pc.kind))
@@ -231,14 +231,44 @@ def conv_kind_for(x: torch.Tensor, Cin: int, k: int, stride: int) -> int:
     return _lib.SODA_CONV_TC
 
 
-def mark_exact(t: torch.Tensor) -> torch.Tensor:
-    """Tags a tensor whose values are exactly representable in TF32 (spikes, pooled spike counts)."""
-    t._soda_exact = True
+def mark_exact(t: torch.Tensor, bound: Optional[int] = 1) -> torch.Tensor:
+    """Tags a tensor that holds only non-negative integers ``<= bound`` (spikes: 1; sums and sum pools of spike
+    maps: the sum of their bounds).  ``bound <= 256`` means exact in bf16, ``<= 2048`` exact in TF32 - the
+    tensor-core convolution picks its cheaper operand schemes from that (SODA_CONV_FLAG_INPUT_EXACT_*).
+    ``bound=None`` leaves the tensor untagged."""
+    if bound is not None:
+        t._soda_exact = int(bound)
     return t
 
 
+def exact_bound(t: Optional[torch.Tensor]) -> Optional[int]:
+    b = None if t is None else getattr(t, "_soda_exact", None)
+    return None if b is None else int(b)
+
+
+def sum_bound(*ts) -> Optional[int]:
+    """Bound of an elementwise sum (None if any term is untagged)."""
+    bs = [exact_bound(t) for t in ts]
+    return None if any(b is None for b in bs) else sum(bs)
+
+
+def _plus(b: Optional[int], k: int) -> Optional[int]:
+    return None if b is None else b + k
+
+
 def is_exact(t: torch.Tensor) -> bool:
-    return bool(getattr(t, "_soda_exact", False))
+    b = exact_bound(t)
+    return b is not None and b <= 2048
+
+
+def _exact_flags(t: torch.Tensor) -> int:
+    b = exact_bound(t)
+    if b is None or b > 2048:
+        return 0
+    f = _lib.SODA_CONV_FLAG_INPUT_EXACT_TF32
+    if b <= 256:
+        f |= _lib.SODA_CONV_FLAG_INPUT_EXACT_BF16
+    return f
 
 
 def conv_out_hw(H: int, W: int, k: int, stride: int) -> Tuple[int, int]:
@@ -267,7 +297,7 @@ def conv2d(
     Ho, Wo = conv_out_hw(H, W, pc.k, pc.stride)
     d = ConvDesc()
     d.N, d.H, d.W, d.Cin, d.Cout, d.k, d.stride, d.kind = N, H, W, Cin, pc.Cout, pc.k, pc.stride, pc.kind
-    d.flags = _lib.SODA_CONV_FLAG_INPUT_EXACT_TF32 if is_exact(x) else 0
+    d.flags = _exact_flags(x)
     if pc.kind == _lib.SODA_CONV_FP32 and x.is_contiguous() and not (Cin == 1 or (H == 1 and W == 1)):
         d.in_nchw = 1  # plain NCHW frames (the binned events)
     else:
@@ -334,7 +364,7 @@ def conv_lif(
     Ho, Wo = conv_out_hw(H, W, pc.k, pc.stride)
     d = ConvDesc()
     d.N, d.H, d.W, d.Cin, d.Cout, d.k, d.stride, d.kind = N, H, W, Cin, pc.Cout, pc.k, pc.stride, pc.kind
-    d.flags = _lib.SODA_CONV_FLAG_INPUT_EXACT_TF32 if is_exact(x) else 0
+    d.flags = _exact_flags(x)
     if _direct_lif_ok(x, pc):
         d.in_nchw = 1
         if residual is not None:
@@ -368,8 +398,7 @@ def conv_lif(
                               _stream()),
         "soda_conv_lif_fwd",
     )
-    if residual is None:
-        mark_exact(out)
+    mark_exact(out, 1 if residual is None else _plus(exact_bound(residual), 1))
     return out, v, i
 
 
@@ -498,8 +527,7 @@ def lif_scan_out(
                              v.data_ptr(), i.data_ptr(), _stream()),
         "soda_lif_res_fwd",
     )
-    if residual is None:
-        mark_exact(out)
+    mark_exact(out, 1 if residual is None else _plus(exact_bound(residual), 1))
     return out, v, i
 
 
@@ -544,7 +572,7 @@ def lif_pool_scan(x: torch.Tensor, T: int, mode: str, v0: Optional[torch.Tensor]
         "soda_lif_pool_fwd",
     )
     if mode in ("S", "M"):
-        mark_exact(out)
+        mark_exact(out, 4 if mode == "S" else 1)
     return out, v, i
 
 
@@ -659,8 +687,8 @@ def pool2d(x: torch.Tensor, k: int, stride: int, mode: str, out: Optional[torch.
                             ops_, _stream()),
         "soda_pool2d_fwd",
     )
-    if mode in ("S", "M") and is_exact(x):
-        mark_exact(out)
+    if mode in ("S", "M") and exact_bound(x) is not None:
+        mark_exact(out, exact_bound(x) * (k * k if mode == "S" else 1))
     return out
 
 
@@ -704,7 +732,7 @@ def add_n(xs: Sequence[torch.Tensor]) -> torch.Tensor:
     out = torch.empty_like(ref)
     arr = (C.c_void_p * len(ys))(*[t.data_ptr() for t in ys])
     check(lib.soda_add_n(arr, len(ys), ref.numel(), out.data_ptr(), _stream()), "soda_add_n")
-    return out
+    return mark_exact(out, sum_bound(*xs))
 
 
 # --------------------------------------------------------------------------------------------

@@ -109,3 +109,20 @@ def test_sharding_two_ranks_gloo():
     for p in procs:
         p.join(timeout=60)
     assert res == [(0, True), (1, True)]
+
+
+def test_spike_count_bounds_pick_the_conv_operand_scheme():
+    """Host logic of the exact-input tags (ops.mark_exact): bounds add over Residual sums and 2x2 sum pools, and the
+    conv flags follow them - <= 256 (8 significant bits): bf16-only scheme; <= 2048: tf32 without the lo(a) half."""
+    from snn_for_object_detection_b200 import _lib, ops
+
+    a, b, c = torch.zeros(1), torch.zeros(1), torch.zeros(1)
+    assert ops.exact_bound(a) is None and ops._exact_flags(a) == 0
+    ops.mark_exact(a)
+    ops.mark_exact(b, 4)
+    assert ops.exact_bound(a) == 1 and ops.sum_bound(a, b) == 5 and ops.sum_bound(a, c) is None
+    both = _lib.SODA_CONV_FLAG_INPUT_EXACT_TF32 | _lib.SODA_CONV_FLAG_INPUT_EXACT_BF16
+    assert ops._exact_flags(a) == both and ops._exact_flags(ops.mark_exact(c, 256)) == both
+    assert ops._exact_flags(ops.mark_exact(c, 257)) == _lib.SODA_CONV_FLAG_INPUT_EXACT_TF32
+    assert ops._exact_flags(ops.mark_exact(c, 4096)) == 0 and not ops.is_exact(c)
+    assert ops.exact_bound(ops.mark_exact(torch.zeros(1), None)) is None

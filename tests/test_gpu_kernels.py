@@ -508,3 +508,53 @@ def test_lif_pool_scan_equals_scan_then_pool(mode, hw):
     zc = torch.cat(zs)
     pc = {"S": F.avg_pool2d(zc, 2, 2) * 4, "A": F.avg_pool2d(zc, 2, 2), "M": F.max_pool2d(zc, 2, 2)}[mode]
     assert torch.equal(y.cpu(), pc)
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("case", [(2, 64, 30, 38, 64, 3, 1), (2, 64, 60, 76, 128, 3, 2), (3, 96, 17, 23, 40, 1, 1),
+                                  (2, 384, 8, 10, 256, 1, 1)])
+@pytest.mark.parametrize("bound", [1, 256, 257])
+def test_conv2d_spike_count_inputs_bf16_only_scheme(case, bound, monkeypatch):
+    """Inputs tagged as spike counts <= 256 take the bf16-only operand scheme (x exact in bf16 times
+    [bf16 rn(w) | bf16 rn(w - rn(w))]); 257 falls back to tf32 + correction.  Both within the conv bar against fp64,
+    and equal to each other to 1e-5."""
+    pkg = _pkg()
+    N, Cin, H, W, Cout, k, s = case
+    torch.manual_seed(bound)
+    x = torch.randint(0, bound + 1, (N, Cin, H, W)).float()
+    x[0, 0, 0, 0] = bound
+    w = torch.randn(Cout, Cin, k, k) / (Cin * k * k) ** 0.5
+    scale, shift = torch.rand(Cout) + 0.5, torch.randn(Cout)
+    ref = F.conv2d(x.double(), (w * scale.view(-1, 1, 1, 1)).double(), stride=s, padding=k // 2) + shift.double().view(1, -1, 1, 1)
+    xd = pkg.ops.mark_exact(x.to(DEV).contiguous(memory_format=torch.channels_last), bound)
+    pc = pkg.ops.pack_conv(w.to(DEV), s, scale.to(DEV), shift.to(DEV), kind=1)
+    y = pkg.ops.conv2d(xd, pc).cpu().double()
+    monkeypatch.setenv("SODA_TC_SPK", "0")
+    y0 = pkg.ops.conv2d(xd, pc).cpu().double()
+    sc = float(ref.abs().max())
+    assert float((y - ref).abs().max()) / sc < 1e-5
+    assert float((y0 - ref).abs().max()) / sc < 1e-5
+    assert float((y - y0).abs().max()) / sc < 1e-5
+    if bound == 257:
+        assert torch.equal(y, y0)   # not bf16-exact: the flag is not set, same kernel both times
+
+
+@pytest.mark.gpu
+def test_fused_conv_lif_spike_inputs_bf16_only_scheme(monkeypatch):
+    """Fused Conv -> BN -> LIF over T with spike inputs: the bf16-only scheme gives the same spikes as the
+    tf32 + correction scheme up to the spike-mismatch bar and the same final membranes to 1e-4."""
+    pkg = _pkg()
+    torch.manual_seed(5)
+    T, B, C, H, W = 6, 2, 32, 40, 24
+    x = (torch.rand(T * B, C, H, W) < 0.3).float().to(DEV).contiguous(memory_format=torch.channels_last)
+    pkg.ops.mark_exact(x)
+    w = torch.randn(C, C, 3, 3) * 0.25
+    pc = pkg.ops.pack_conv(w.to(DEV), 1, (torch.rand(C) + 0.5).to(DEV), (torch.randn(C) * 0.1).to(DEV), kind=1)
+    z1, v1, i1 = pkg.ops.conv_lif(x, pc, T, pkg.ops.LIF_DEFAULT)
+    monkeypatch.setenv("SODA_TC_SPK", "0")
+    z0, v0, i0 = pkg.ops.conv_lif(x, pc, T, pkg.ops.LIF_DEFAULT)
+    assert 0.01 < float(z0.mean()) < 0.9
+    assert float((z1 != z0).float().mean()) <= 1e-4
+    same = (z1 == z0).reshape(T, B, C, H, W).all(0)   # neurons with identical spike trains: membranes to 1e-4
+    assert float(((v1 - v0).abs() / (v0.abs() + 1.0))[same].max()) < 1e-4
+    assert pkg.ops.exact_bound(z1) == 1

@@ -388,3 +388,42 @@ def test_vgg_planner_fuses_lif_and_pool():
     Y = Y.reshape(T, B, *Y.shape[1:]).cpu()
     assert float((Y != torch.from_numpy(g["Y"])).float().mean()) <= SPIKE_TOL
     assert n <= 6, n   # conv, lif+pool, conv, lif+pool, conv(+lif)
+
+
+@pytest.mark.gpu
+def test_planner_tags_spike_inputs_through_pools_residuals_and_concats():
+    """Every Conv of a Conv/Norm/LIF/Pool chain, a Residual with [Pass] and a Dense concat sees an input tagged with
+    its spike-count bound (1, 4 after a 2x2 sum pool, 2 after spike + spike), and the tagged run equals an
+    untagged run to the block bars."""
+    from snn_for_object_detection_b200 import BlockGen, ops
+    from snn_for_object_detection_b200.modules.layer_gen import LIF, Conv, Dense, Norm, Pass, Pool, Residual
+
+    torch.manual_seed(11)
+    cb = lambda c, k=3: (Conv(c, kernel_size=k), Norm(), LIF())
+    cfg = [*cb(32), Pool("S"), *cb(32), Residual([[*cb(32)], [Pass()]]), Dense([[*cb(32)], [Pass()]]), *cb(64, 1)]
+    block = BlockGen(2, [cfg]).to(DEV).eval()
+    for m in block.modules():
+        if isinstance(m, torch.nn.Conv2d):
+            torch.nn.init.normal_(m.weight, std=6.0 / (m.in_channels * m.kernel_size[0] ** 2) ** 0.5)
+    T, B = 8, 2
+    X = (torch.rand(T * B, 2, 32, 48, device=DEV) < 0.3).float()
+    prof = {}
+    ops.PROFILE = prof
+    try:
+        with torch.no_grad():
+            Y, _ = block.forward_seq(X, T)
+    finally:
+        ops.PROFILE = None
+    tags = prof.get("conv2d_tags", []) + prof.get("conv_lif_tags", [])
+    bounds = sorted(t.split("exact")[1] for t in tags)
+    # first conv: event frame (untagged); then pooled spikes (4), spikes (1), spike + spike (2), concat (2)
+    assert bounds == ["1", "2", "2", "4", "None"], tags
+    assert ops.exact_bound(Y) == 1 and 0.0 < float(Y.mean()) < 1.0
+    real_mark = ops.mark_exact
+    ops.mark_exact = lambda t, bound=1: t
+    try:
+        with torch.no_grad():
+            Y0, _ = block.forward_seq(X, T)
+    finally:
+        ops.mark_exact = real_mark
+    assert float((Y != Y0).float().mean()) <= 2e-3   # end to end through 6 spiking layers (flips propagate)
