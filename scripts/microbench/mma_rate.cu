@@ -8,12 +8,9 @@
 #include "../../snn_for_object_detection_b200/csrc/tc_common.cuh"
 using namespace soda::tc;
 
-__device__ __forceinline__ void mma_bf16_ss(uint32_t d, uint64_t a, uint64_t b, uint32_t idesc, uint32_t acc) {
-  asm volatile("{\n\t.reg .pred p;\n\tsetp.ne.b32 p, %4, 0;\n\t"
-               "tcgen05.mma.cta_group::1.kind::f16 [%0], %1, %2, %3, p;\n\t}" ::"r"(d), "l"(a), "l"(b), "r"(idesc), "r"(acc) : "memory");
-}
-
-// MODE: 0 tf32 TS, 1 tf32 SS, 2 bf16 TS, 3 bf16 SS ; NACC = accumulators cycled through
+// MODE: 0 tf32 TS, 1 tf32 SS, 2 bf16 TS, 3 bf16 SS, 4 alternating groups of 4 tf32 SS / 4 bf16 SS (the conv kernel's
+// two products of a k-block issued by ONE thread) ; NACC = accumulators cycled through (MODE 4: NACC = 1 both kinds on
+// one accumulator, NACC = 2 one accumulator per kind)
 template <int N, int MODE, int NACC>
 __global__ void __launch_bounds__(128, 1) k(int reps, long long* out) {
   extern __shared__ uint8_t raw[];
@@ -27,7 +24,8 @@ __global__ void __launch_bounds__(128, 1) k(int reps, long long* out) {
   tc_fence_before(); __syncthreads(); tc_fence_after();
   const uint32_t tb = slot;
   if (threadIdx.x < 32) {
-    constexpr uint32_t idesc = (MODE >= 2) ? idesc_bf16(128, N) : idesc_tf32(128, N);
+    constexpr uint32_t idesc = (MODE == 2 || MODE == 3) ? idesc_bf16(128, N) : idesc_tf32(128, N);
+    constexpr uint32_t idesc_b = idesc_bf16(128, N);
     const uint64_t bdesc = smem_desc_sw128(smem_u32(smem));
     const uint64_t adesc = smem_desc_sw128(smem_u32(smem + 48 * 1024));
     long long t0 = 0, t1 = 0;
@@ -40,7 +38,11 @@ __global__ void __launch_bounds__(128, 1) k(int reps, long long* out) {
             const uint32_t d = tb + (uint32_t)(u % NACC) * N;
             const uint32_t a_t = tb + 256 + (u & 3) * 64 + (u & 1) * 8;
             const uint64_t b = bdesc + 2 * (u & 3);
-            if (MODE == 0) mma_tf32_ts(d, a_t, b, idesc, 1);
+            if (MODE == 4) {
+              const uint32_t dk = tb + (uint32_t)((u >> 2) % NACC) * N;
+              if (u < 4) mma_tf32_ss(dk, adesc + 2 * (u & 3), b, idesc, 1);
+              else mma_bf16_ss(dk, adesc + 2 * (u & 3), b, idesc_b, 1);
+            } else if (MODE == 0) mma_tf32_ts(d, a_t, b, idesc, 1);
             else if (MODE == 1) mma_tf32_ss(d, adesc + 2 * (u & 3), b, idesc, 1);
             else if (MODE == 2) mma_bf16_ts(d, a_t, b, idesc, 1);
             else mma_bf16_ss(d, adesc + 2 * (u & 3), b, idesc, 1);
@@ -60,7 +62,7 @@ __global__ void __launch_bounds__(128, 1) k(int reps, long long* out) {
 
 template <int N, int MODE, int NACC>
 void run(long long* d) {
-  const char* names[4] = {"tf32 TS", "tf32 SS", "bf16 TS", "bf16 SS"};
+  const char* names[5] = {"tf32 TS", "tf32 SS", "bf16 TS", "bf16 SS", "tf32+bf16 SS"};
   const int reps = 1024;
   cudaFuncSetAttribute(k<N, MODE, NACC>, cudaFuncAttributeMaxDynamicSharedMemorySize, 100 * 1024);
   k<N, MODE, NACC><<<148, 128, 100 * 1024>>>(reps, d);
@@ -80,5 +82,6 @@ void run_mode(long long* d) {
 int main() {
   long long* d; cudaMalloc(&d, 8);
   run_mode<0>(d); run_mode<1>(d); run_mode<2>(d); run_mode<3>(d);
+  run<32, 4, 1>(d); run<32, 4, 2>(d); run<64, 4, 1>(d); run<64, 4, 2>(d); run<128, 4, 1>(d); run<128, 4, 2>(d);
   return 0;
 }

@@ -34,6 +34,12 @@ inline int after_launch(const char* name) {
 
 constexpr int kNumSMs = 148;  // B200
 
+// Programmatic dependent launch (PDL).  pdl_trigger(): once every CTA of this grid has executed it (or exited), a
+// dependent grid launched with cudaLaunchAttributeProgrammaticStreamSerialization may start.  pdl_wait(): in such a
+// dependent grid, blocks until the preceding grid has completed and its memory is visible; no-op otherwise.
+__device__ __forceinline__ void pdl_trigger() { asm volatile("griddepcontrol.launch_dependents;" ::: "memory"); }
+__device__ __forceinline__ void pdl_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
+
 static inline int64_t ceil_div(int64_t a, int64_t b) { return (a + b - 1) / b; }
 
 __device__ __forceinline__ bool aligned16(const void* p) {

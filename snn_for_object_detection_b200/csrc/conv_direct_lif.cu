@@ -46,6 +46,7 @@ conv_direct_lif_kernel(DirectP p, const float* __restrict__ x, const float* __re
                        const float* __restrict__ shift, const float* __restrict__ v0,
                        const float* __restrict__ i0, float* __restrict__ y, float* __restrict__ v_out,
                        float* __restrict__ i_out) {
+  pdl_trigger();   // lets a dependent tensor-core conv start its prologue in this grid's tail
   extern __shared__ float smem_w[];  // [Ktot][Cout] weights, then [Cout] shift
   float* smem_shift = smem_w + p.Ktot * p.Cout;
   for (int e = threadIdx.x; e < p.Ktot * p.Cout; e += blockDim.x) {

@@ -310,10 +310,14 @@ conv_tc3_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__
     fence_barrier_init();
   }
   if (warp == T3_W_MMA_MAIN) tmem_alloc(tmem_slot, TMEM_COLS);
+  pdl_trigger();
   tc_fence_before();
   __syncthreads();
   tc_fence_after();
   const uint32_t tmem_base = *tmem_slot;
+  // Launched as a programmatic dependent: everything above (barrier init, TMEM allocation, descriptor prefetch)
+  // overlapped the tail of the previous kernel of the stream; its results are visible from here on.
+  pdl_wait();
   const int my_chunk = blockIdx.x % p.nch;   // gridDim.x is a multiple of nch: fixed per CTA
 
   // Roles 16-19 run warp-uniform control flow and elect one lane only around the asynchronous instructions
@@ -817,7 +821,20 @@ static int launch_tc3_(const CUtensorMap& tmA, const CUtensorMap& tmB, const Tc3
     }
     attr_set = true;
   }
-  conv_tc3_kernel<BN, LIF, SPK><<<grid, T3_THREADS, smem, st>>>(tmA, tmB, p);
+  static const bool pdl = []() { const char* e = getenv("SODA_PDL"); return !(e && atoi(e) == 0); }();
+  if (pdl) {
+    cudaLaunchConfig_t cfg;
+    memset(&cfg, 0, sizeof(cfg));
+    cfg.gridDim = dim3((unsigned)grid), cfg.blockDim = dim3(T3_THREADS);
+    cfg.dynamicSmemBytes = smem, cfg.stream = st;
+    cudaLaunchAttribute at[1];
+    at[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    at[0].val.programmaticStreamSerializationAllowed = 1;
+    cfg.attrs = at, cfg.numAttrs = 1;
+    cudaLaunchKernelEx(&cfg, conv_tc3_kernel<BN, LIF, SPK>, tmA, tmB, p);
+  } else {
+    conv_tc3_kernel<BN, LIF, SPK><<<grid, T3_THREADS, smem, st>>>(tmA, tmB, p);
+  }
   return after_launch("conv_tc3_kernel");
 }
 

@@ -15,6 +15,7 @@ __global__ void __launch_bounds__(256)
 pool2d_kernel(const float* __restrict__ x, int N, int H, int W, int C, int k, int stride, int mode,
               int Ho, int Wo, int64_t in_bs, int64_t in_ps, float* __restrict__ y, int64_t out_bs,
               int64_t out_ps) {
+  pdl_trigger();   // lets a dependent tensor-core conv start its prologue in this grid's tail
   const int cv = C / V;
   const int64_t total = (int64_t)N * Ho * Wo * cv;
   const float inv = 1.0f / (float)(k * k);
@@ -60,6 +61,7 @@ __global__ void __launch_bounds__(256)
 channel_affine_kernel(const float* __restrict__ x, int64_t n_pix, int C, int64_t in_ps,
                       const float* __restrict__ scale, const float* __restrict__ shift,
                       float* __restrict__ y, int64_t out_ps) {
+  pdl_trigger();   // lets a dependent tensor-core conv start its prologue in this grid's tail
   const int cv = C / V;
   const int64_t total = n_pix * cv;
   for (int64_t idx = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; idx < total;
@@ -91,6 +93,7 @@ struct AddPtrs {
 
 template <int V>
 __global__ void __launch_bounds__(256) add_n_kernel(AddPtrs xs, int k, int64_t n, float* __restrict__ y) {
+  pdl_trigger();   // lets a dependent tensor-core conv start its prologue in this grid's tail
   for (int64_t e = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) * V; e < n;
        e += (int64_t)gridDim.x * blockDim.x * V) {
     float acc[V];

@@ -52,6 +52,7 @@ neuron_fwd_kernel(NP p, const float* __restrict__ x, const float* __restrict__ v
                   float* __restrict__ v_out, float* __restrict__ i_out,
                   float* __restrict__ v_dec_trace, float* __restrict__ v_trace,
                   float* __restrict__ i_trace) {
+  pdl_trigger();   // lets a dependent tensor-core conv start its prologue in this grid's tail
   const int64_t e = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) * V;
   if (e >= n) return;
   float v[V], i[V];
@@ -125,6 +126,7 @@ neuron_bwd_kernel(NP p, const float* __restrict__ gout, const float* __restrict_
                   const float* __restrict__ giT, const float* __restrict__ v_dec_trace, int T,
                   int64_t n, float* __restrict__ gx, float* __restrict__ gv0,
                   float* __restrict__ gi0) {
+  pdl_trigger();   // lets a dependent tensor-core conv start its prologue in this grid's tail
   const int64_t e = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) * V;
   if (e >= n) return;
   float gv[V], gi[V];
@@ -195,6 +197,7 @@ lif_res_fwd_kernel(NP p, const float* __restrict__ x, const float* __restrict__ 
                    const float* __restrict__ i0, int T, int64_t P, int C,
                    const float* __restrict__ res, int64_t res_ps, float* __restrict__ out, int64_t out_ps,
                    float* __restrict__ v_out, float* __restrict__ i_out) {
+  pdl_trigger();   // lets a dependent tensor-core conv start its prologue in this grid's tail
   const int64_t n = P * C;
   const int64_t e = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) * 4;
   if (e >= n) return;
@@ -247,6 +250,7 @@ __global__ void __launch_bounds__(256)
 lif_pool2_fwd_kernel(NP p, const float* __restrict__ x, const float* __restrict__ v0, const float* __restrict__ i0,
                      int T, int B, int H, int W, int C, int mode, float* __restrict__ out, int64_t out_ps,
                      float* __restrict__ v_out, float* __restrict__ i_out) {
+  pdl_trigger();   // lets a dependent tensor-core conv start its prologue in this grid's tail
   const int cv = C / 4;
   const int Hw = (H + 1) / 2, Ww = (W + 1) / 2, Ho = H / 2, Wo = W / 2;
   const int64_t idx = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
