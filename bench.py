@@ -301,7 +301,7 @@ def run_gpu_arm(args):
     achieved = dom_flops / (dom_ms * 1e-3) / 1e12 if dom_ms > 0 else None
     peak = pk["bf16_tflops_sustained"]
     traffic = None
-    tpath = os.path.join(ROOT, "profiles", "r1b_traffic.json")
+    tpath = os.path.join(ROOT, "profiles", "r1d_traffic.json")
     traffic_launch = None
     if os.path.exists(tpath):
         tj = json.load(open(tpath))
@@ -311,7 +311,7 @@ def run_gpu_arm(args):
         "bound": "tensor", "achieved": achieved, "peak": peak, "unit": "TFLOP/s",
         "frac": (achieved / peak) if achieved else None,
         "traffic": traffic, "traffic_launch": traffic_launch,
-        "kernel": "soda::conv_tc3_kernel<128, false> (tcgen05/TMEM/TMA implicit GEMM; tf32 main pass + K-stacked bf16 "
+        "kernel": "soda::conv_tc3_kernel<128, false, *> (tcgen05/TMEM/TMA implicit GEMM; tf32 main pass + K-stacked bf16 "
                   "correction pass = 2 tensor passes per product for fp32-level accuracy)",
         "peak_source": f"{pk_src} dense bf16 sustained (kernel timed inside a long step); the 2-pass fp32-accurate "
                        "scheme itself tops out near peak/4 (tf32 rate = bf16/2, two passes)",
