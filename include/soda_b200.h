@@ -256,6 +256,21 @@ SODA_API int soda_multibox_detection(const float* cls_probs, const float* offset
                             int C, float nms_threshold, float pos_threshold, void* workspace, float* out,
                             void* stream);
 
+/* ---------------------------------------------------------------------------------------------
+ * Anchor labelling for the detection loss (the step right after the forward in training)
+ *   replaces: utils/roi.py:18-63 RoI.__call__ with _assign_anchor_to_box :65-109, utils/box.py:24-57 box_iou and
+ *             :60-67 offset_boxes, called by models/soda.py:265 (_loss).
+ *   anchors      : [A, 4] corner-format anchors (16-byte aligned)
+ *   labels       : [B, G, 5] rows (class, x1, y1, x2, y2); padded rows are all -1 and take part as in the reference
+ *   bbox_offset  : [B, A, 4] regression targets, already multiplied by the mask
+ *   bbox_mask    : [B, A, 4] 1 for anchors with a box, else 0
+ *   class_labels : [B, A] int64, 0 = background, else label class + 1
+ *   Each anchor takes its best box if IoU >= iou_threshold; then every box claims the best anchor still free
+ *   (ties: smallest anchor * G + box index).  One CTA per sample; G <= 256, A * G < 2^32.
+ * ------------------------------------------------------------------------------------------- */
+SODA_API int soda_roi_assign(const float* anchors, const float* labels, int B, int A, int G, float iou_threshold,
+                             float* bbox_offset, float* bbox_mask, long long* class_labels, void* stream);
+
 #ifdef __cplusplus
 }
 #endif

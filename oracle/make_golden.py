@@ -206,11 +206,41 @@ def golden_box(ref):
     print("box: kept per image", [(det[b, :, 0] >= 0).sum().item() for b in range(2)])
 
 
+def golden_roi(ref):
+    """Anchor labelling by the reference's own utils/roi.py: GEN1-like 3-level anchor set (coarse), 3 samples with
+    5 / 2 / 0 real boxes padded to 6 rows with -1 (datasets.py:127-135), boxes placed on anchors so that the
+    threshold rule, the per-box claim and the all-zero ties of the padded rows are all exercised."""
+    torch.manual_seed(7)
+    sizes = torch.tensor([0.2, 0.35, 0.5])
+    ratios = torch.tensor([0.5, 1.0, 2.0])
+    gen = ref.anchors.AnchorGenerator(sizes=sizes, ratios=ratios)
+    anchors = torch.cat([gen(torch.zeros(1, 4, h, w)) for h, w in ((12, 15), (6, 8), (3, 4))])
+    A = anchors.shape[0]
+    labels = torch.full((3, 6, 5), -1.0)
+    pick = torch.randperm(A)[:7]
+    for k in range(5):
+        jit = (torch.rand(4) - 0.5) * 0.06
+        labels[0, k, 0] = float(k % 2)
+        labels[0, k, 1:] = anchors[pick[k]] + jit
+    labels[0, 4, 1:] = torch.tensor([0.91, 0.93, 0.99, 0.995])   # tiny box: below the threshold everywhere, claimed anyway
+    for k in range(2):
+        labels[1, k, 0] = 1.0
+        labels[1, k, 1:] = anchors[pick[5 + k]]                      # exact anchors: IoU 1 ties with their duplicates
+    out = ref.roi.RoI(0.5)(anchors, labels.clone())
+    np.savez_compressed(
+        os.path.join(OUT, "roi.npz"), anchors=anchors.numpy(), labels=labels.numpy(), iou_threshold=0.5,
+        bbox_offset=out[0].numpy(), bbox_mask=out[1].numpy(), class_labels=out[2].numpy(),
+    )
+    print("roi: anchors", A, "assigned per sample", [(out[2][b] > 0).sum().item() for b in range(3)],
+          "masked", [int(out[1][b, :, 0].sum()) for b in range(3)])
+
+
 def main():
     os.makedirs(OUT, exist_ok=True)
     ref = load_reference()
     golden_binning(ref)
     golden_box(ref)
+    golden_roi(ref)
     golden_vgg(ref)
     golden_tiny_yolo(ref)
 

@@ -161,6 +161,7 @@ def load_reference() -> argparse.Namespace:
         psee = importlib.import_module("prophesee_toolbox.src.io.psee_loader")
         datasets = importlib.import_module("utils.datasets")
         box = importlib.import_module("utils.box")
+        roi = importlib.import_module("utils.roi")
         anchors = importlib.import_module("utils.anchors")
         models = importlib.import_module("models")
         generator = importlib.import_module("models.generator")
@@ -174,6 +175,7 @@ def load_reference() -> argparse.Namespace:
         modules=modules,
         datasets=datasets,
         box=box,
+        roi=roi,
         anchors=anchors,
         psee=psee,
         dat=dat,

@@ -85,6 +85,7 @@ SIGNATURES = {
     "soda_add_n": (_i, [C.POINTER(_vp), _i, _i64, _vp, _vp]),
     "soda_multibox_workspace_bytes": (_i64, [_i, _i]),
     "soda_multibox_detection": (_i, [_vp, _vp, _vp, _i, _i, _i, _f, _f, _vp, _vp, _vp]),
+    "soda_roi_assign": (_i, [_vp, _vp, _i, _i, _i, _f, _vp, _vp, _vp, _vp]),
 }
 
 if not os.path.exists(LIB_PATH):

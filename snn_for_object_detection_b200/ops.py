@@ -38,6 +38,7 @@ __all__ = [
     "channel_affine",
     "add_n",
     "multibox_detection",
+    "roi_assign",
     "to_pixel_major",
     "empty_pixel_major",
 ]
@@ -761,3 +762,28 @@ def multibox_detection(cls_probs: torch.Tensor, offset_preds: torch.Tensor, anch
         "soda_multibox_detection",
     )
     return out
+
+
+# --------------------------------------------------------------------------------------------
+# anchor labelling for the detection loss
+# --------------------------------------------------------------------------------------------
+@_prof("roi_assign")
+def roi_assign(anchors: torch.Tensor, labels: torch.Tensor, iou_threshold: float = 0.5
+               ) -> Tuple[torch.Tensor, torch.Tensor, torch.Tensor]:
+    """``(bbox_offset [B,A,4], bbox_mask [B,A,4], class_labels [B,A] int64)`` exactly as the reference's
+    ``utils/roi.py:18-63 RoI.__call__`` (padded ``-1`` label rows included); one CTA per sample, no host sync."""
+    _need_cuda(anchors, labels)
+    if anchors.dim() != 2 or anchors.shape[1] != 4 or labels.dim() != 3 or labels.shape[2] != 5:
+        raise ValueError("roi_assign: anchors [A,4] and labels [B,G,5] expected")
+    A, (B, G) = anchors.shape[0], labels.shape[:2]
+    an = anchors.detach().contiguous().float()
+    lb = labels.detach().contiguous().float()
+    off = torch.empty((B, A, 4), dtype=torch.float32, device=an.device)
+    msk = torch.empty((B, A, 4), dtype=torch.float32, device=an.device)
+    cls = torch.empty((B, A), dtype=torch.int64, device=an.device)
+    check(
+        lib.soda_roi_assign(an.data_ptr(), lb.data_ptr(), B, A, G, float(iou_threshold), off.data_ptr(),
+                            msk.data_ptr(), cls.data_ptr(), _stream()),
+        "soda_roi_assign",
+    )
+    return off, msk, cls

@@ -20,6 +20,7 @@ from torch.nn import functional as F
 from .generator import BackboneGen, Head, ListGen, ListState, NeckGen
 from . import ops
 from .utils import box
+from .utils.roi import RoI
 
 
 class SODa(nn.Module):
@@ -46,6 +47,9 @@ class SODa(nn.Module):
         self.base_net = BackboneGen(self.backbone_cfgs, in_channels=2, init_weights=init_weights)
         self.neck_net = NeckGen(self.neck_cfgs, self.base_net.out_channels, init_weights=init_weights)
         self.head_net = Head(self.head_cfgs, num_classes, self.neck_net.out_shape, init_weights=init_weights)
+        self.roi_blk = RoI(iou_threshold)
+        self.cls_loss = nn.CrossEntropyLoss(reduction="none")
+        self.box_loss = nn.L1Loss(reduction="none")
 
     # ---- configuration hooks -------------------------------------------------------------
     def backbone_cfgs(self) -> ListGen:
@@ -97,6 +101,26 @@ class SODa(nn.Module):
         prep_pred = prep_pred[prep_pred[:, 0] >= 0]
         prep_pred[:, 2:] = torch.clamp(prep_pred[:, 2:], min=0.0, max=1.0)
         return prep_pred, state
+
+    def _loss(self, preds: Tuple[torch.Tensor, torch.Tensor, torch.Tensor], labels: torch.Tensor) -> torch.Tensor:
+        """Detection loss of the reference (``models/soda.py:259-281``): anchors labelled by ``roi_blk`` (one CUDA
+        kernel, no host sync), per-anchor cross entropy split into object / background means weighted by
+        ``loss_ratio``, plus the masked L1 box loss."""
+        anchors, cls_preds, bbox_preds = preds
+        bbox_offset, bbox_mask, class_labels = self.roi_blk(anchors, labels)
+        num_classes = cls_preds.shape[2]
+        cls = self.cls_loss(cls_preds.reshape(-1, num_classes), class_labels.reshape(-1))
+        bbox = self.box_loss(bbox_preds * bbox_mask, bbox_offset * bbox_mask)
+        mask = class_labels.reshape(-1) > 0
+        gt_loss = cls[mask].mean()
+        background_loss = cls[~mask].mean()
+        return gt_loss * self.hparams.loss_ratio + background_loss * (1 - self.hparams.loss_ratio) + bbox.mean()
+
+    def training_step(self, batch: Tuple[torch.Tensor, torch.Tensor], batch_idx: int = 0) -> torch.Tensor:
+        """``models/soda.py:146-158``: forward over a random-length window, loss against the labels."""
+        data, labels = batch
+        preds = self.forward(data[self._rand_start_time():])
+        return self._loss(preds, labels)
 
     def _rand_start_time(self) -> int:
         if not self.hparams.time_window:

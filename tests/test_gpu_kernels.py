@@ -558,3 +558,76 @@ def test_fused_conv_lif_spike_inputs_bf16_only_scheme(monkeypatch):
     same = (z1 == z0).reshape(T, B, C, H, W).all(0)   # neurons with identical spike trains: membranes to 1e-4
     assert float(((v1 - v0).abs() / (v0.abs() + 1.0))[same].max()) < 1e-4
     assert pkg.ops.exact_bound(z1) == 1
+
+
+def _roi_check(anchors, labels, thr):
+    from oracle import roi_restated as rr
+
+    ops = _pkg().ops
+    off, msk, cls = ops.roi_assign(torch.from_numpy(anchors).to(DEV), torch.from_numpy(labels).to(DEV), thr)
+    o_off, o_msk, o_cls = rr.roi(anchors, labels, thr)
+    assert cls.dtype == torch.int64
+    assert np.array_equal(cls.cpu().numpy(), o_cls)            # index work: identical
+    assert np.array_equal(msk.cpu().numpy(), o_msk)
+    np.testing.assert_allclose(off.cpu().numpy(), o_off, rtol=2e-6, atol=2e-6)   # logf vs np.log
+    return o_cls, o_msk
+
+
+@pytest.mark.gpu
+def test_roi_assign_matches_reference_golden():
+    """soda_roi_assign against the output of the reference's OWN utils/roi.py (tests/golden/roi.npz)."""
+    ops = _pkg().ops
+    g = golden("roi.npz")
+    off, msk, cls = ops.roi_assign(torch.from_numpy(g["anchors"]).to(DEV), torch.from_numpy(g["labels"]).to(DEV),
+                                   float(g["iou_threshold"]))
+    assert np.array_equal(cls.cpu().numpy(), g["class_labels"])
+    assert np.array_equal(msk.cpu().numpy(), g["bbox_mask"])
+    np.testing.assert_allclose(off.cpu().numpy(), g["bbox_offset"], rtol=2e-6, atol=2e-6)
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("A,G,B,thr", [(13545, 12, 5, 0.4), (700, 9, 4, 0.5), (33, 40, 2, 0.3), (4097, 1, 3, 0.5),
+                                       (1000, 0, 2, 0.5)])
+def test_roi_assign_random_against_oracle(A, G, B, thr):
+    """GEN1-sized anchor set; ragged label counts padded with -1; more boxes than free anchors; a single box; no boxes."""
+    rng = np.random.default_rng(A + G)
+    ctr = rng.random((A, 2), dtype=np.float32)
+    wh = rng.random((A, 2), dtype=np.float32) * 0.3 + 0.03
+    anchors = np.concatenate([ctr - wh / 2, ctr + wh / 2], axis=1).astype(np.float32)
+    anchors[A // 2] = anchors[0]                       # duplicate anchors: exact IoU ties -> smallest index wins
+    labels = np.full((B, G, 5), -1.0, np.float32)
+    for b in range(B):
+        for k in range(min(G, (3 * b + 1) if G < 33 else G)):
+            labels[b, k, 0] = k % 3
+            src = anchors[0] if k == 0 else anchors[rng.integers(A)]
+            labels[b, k, 1:] = src + (0 if k < 2 else (rng.random(4, dtype=np.float32) - 0.5) * 0.08)
+    if G > A:
+        pytest.skip("more label rows than anchors: the reference starts re-picking discarded entries")
+    o_cls, o_msk = _roi_check(anchors, labels, thr)
+    if G > 0:
+        assert int(o_msk[:, :, 0].sum()) >= B * min(G, A)   # every label row, padded ones included, claims an anchor
+
+
+@pytest.mark.gpu
+def test_detection_loss_matches_reference_expression():
+    """SODa._loss (roi kernel + cross entropy / L1 as models/soda.py:259-281) against the same expression evaluated
+    on the oracle's labelling; gradients flow to the predictions."""
+    from oracle import roi_restated as rr
+    from snn_for_object_detection_b200 import TinyYolo
+
+    torch.manual_seed(2)
+    g = golden("roi.npz")
+    anchors = torch.from_numpy(g["anchors"]).to(DEV)
+    labels = torch.from_numpy(g["labels"]).to(DEV)
+    A = anchors.shape[0]
+    model = TinyYolo(num_classes=2, iou_threshold=float(g["iou_threshold"]))
+    cls_preds = torch.randn(3, A, 3, device=DEV, requires_grad=True)
+    bbox_preds = torch.randn(3, A, 4, device=DEV, requires_grad=True)
+    loss = model._loss((anchors, cls_preds, bbox_preds), labels)
+    loss.backward()
+    o_off, o_msk, o_cls = (torch.from_numpy(x) for x in rr.roi(g["anchors"], g["labels"], float(g["iou_threshold"])))
+    ce = F.cross_entropy(cls_preds.detach().cpu().reshape(-1, 3), o_cls.reshape(-1), reduction="none")
+    m = o_cls.reshape(-1) > 0
+    want = ce[m].mean() * 0.04 + ce[~m].mean() * 0.96 + (bbox_preds.detach().cpu() * o_msk - o_off * o_msk).abs().mean()
+    assert abs(float(loss.detach()) - float(want)) < 1e-5 * max(1.0, abs(float(want)))
+    assert cls_preds.grad is not None and float(cls_preds.grad.abs().sum()) > 0 and float(bbox_preds.grad.abs().sum()) > 0

@@ -1,6 +1,7 @@
 """CPU: the oracle restatements against the golden vectors produced by the reference's own Python
 (oracle/make_golden.py).  Bit-exact unless stated."""
 import numpy as np
+import pytest
 import torch
 
 from helpers import golden, tiny_yolo_from_golden, vgg_block_from_golden
@@ -105,3 +106,40 @@ def test_norse_restatement_known_answers():
     xg = torch.tensor([0.5], requires_grad=True)
     nr.threshold(xg, "super", 100.0).backward()
     assert abs(float(xg.grad) - 1.0 / (100 * 0.5 + 1) ** 2) < 1e-9
+
+
+def test_roi_restatement_matches_reference_golden():
+    """oracle/roi_restated.py against the output of the reference's OWN utils/roi.py (tests/golden/roi.npz):
+    anchor -> box map (mask, classes) identical, incl. the padded -1 rows that claim anchors; offsets to 1 ulp of
+    np.log vs torch.log."""
+    from oracle import roi_restated as rr
+
+    g = golden("roi.npz")
+    off, msk, cls = rr.roi(g["anchors"], g["labels"], float(g["iou_threshold"]))
+    assert np.array_equal(cls, g["class_labels"])
+    assert np.array_equal(msk, g["bbox_mask"])
+    assert int((g["class_labels"] > 0).sum()) > 100 and int(g["bbox_mask"][2, :, 0].sum()) == 6
+    np.testing.assert_allclose(off, g["bbox_offset"], rtol=1e-6, atol=1e-6)
+
+
+def test_roi_restatement_live_reference():
+    """Same check against the live reference on fresh random boxes, when /root/reference is present (build container)."""
+    from oracle import ref_shim
+    from oracle import roi_restated as rr
+
+    if not ref_shim.reference_available():
+        pytest.skip("reference tree not present")
+    ref = ref_shim.load_reference()
+    rng = np.random.default_rng(5)
+    ctr = rng.random((700, 2), dtype=np.float32)
+    wh = rng.random((700, 2), dtype=np.float32) * 0.3 + 0.05
+    anchors = np.concatenate([ctr - wh / 2, ctr + wh / 2], axis=1)
+    labels = np.full((4, 9, 5), -1.0, np.float32)
+    for b in range(4):
+        for k in range(2 * b + 1):
+            labels[b, k, 0] = k % 3
+            labels[b, k, 1:] = anchors[rng.integers(700)] + (rng.random(4, dtype=np.float32) - 0.5) * 0.1
+    want = ref.roi.RoI(0.4)(torch.from_numpy(anchors), torch.from_numpy(labels.copy()))
+    off, msk, cls = rr.roi(anchors, labels, 0.4)
+    assert np.array_equal(cls, want[2].numpy()) and np.array_equal(msk, want[1].numpy())
+    np.testing.assert_allclose(off, want[0].numpy(), rtol=1e-6, atol=1e-6)
