@@ -1,8 +1,8 @@
 """BPTT training step of TinyYolo (BASELINE config 4 shape per GPU: GEN1 304x240, B=5, T=32): forward in train mode
 (our conv / LIF / LI kernels, batch-statistics BatchNorm per time step), backward (our fused LIF / LI reverse scans,
 cuDNN dgrad / wgrad), flat gradient all-reduce over NCCL when launched under torchrun, Adamax step
-(models/soda.py:135-136).  The loss is a synthetic weighted sum of the predictions: the reference's ROI target
-assignment + focal/L1 loss (utils/roi.py, models/soda.py:259-281) is outside the hot path.
+(models/soda.py:135-136).  The loss is the reference's detection loss (models/soda.py:259-281) on synthetic labels
+(6 random boxes per sample padded to 10 rows with -1): anchor labelling by soda_roi_assign, cross entropy + masked L1.
 
   python scripts/train_step_probe.py [--steps 3] [--T 32] [--batch 5] [--hw 240 304]
   python -m torch.distributed.run --nproc-per-node 2 --master-addr 127.0.0.1 scripts/train_step_probe.py
@@ -41,17 +41,18 @@ params = [p for p in model.parameters() if p.requires_grad]
 T, B, (H, W) = args.T, args.batch, args.hw
 gen = torch.Generator(device=dev).manual_seed(100 + rank)
 X = (torch.rand(T, B, 2, H, W, device=dev, generator=gen) < 0.07).float()
-wc = wb = None
+labels = torch.full((B, 10, 5), -1.0, device=dev)
+ctr = torch.rand(B, 6, 2, device=dev, generator=gen) * 0.6 + 0.2
+wh = torch.rand(B, 6, 2, device=dev, generator=gen) * 0.25 + 0.05
+labels[:, :6, 0] = torch.randint(0, 2, (B, 6), device=dev, generator=gen).float()
+labels[:, :6, 1:3], labels[:, :6, 3:5] = ctr - wh / 2, ctr + wh / 2
 times = []
 for it in range(args.steps + 1):
     torch.cuda.synchronize()
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     e0.record()
     opt.zero_grad(set_to_none=True)
-    anchors, cls, bbox = model(X)
-    if wc is None:
-        wc, wb = torch.randn_like(cls), torch.randn_like(bbox)
-    loss = (cls * wc).mean() + (bbox * wb).mean()
+    loss = model._loss(model(X), labels)
     loss.backward()
     sharding.allreduce_flat_gradients(params)
     opt.step()
@@ -66,7 +67,7 @@ if world > 1:
     ms = float(t)
 gn = float(torch.sqrt(sum((p.grad.double() ** 2).sum() for p in params if p.grad is not None)))
 if rank == 0:
-    print(json.dumps({"what": "TinyYolo BPTT training step (synthetic loss)", "n_gpus": world, "batch_per_gpu": B, "T": T,
+    print(json.dumps({"what": "TinyYolo BPTT training step (detection loss on synthetic labels)", "n_gpus": world, "batch_per_gpu": B, "T": T,
                       "hw": [H, W], "ms_per_step": ms, "frames_per_s": world * T * B / (ms * 1e-3),
                       "loss": float(loss), "grad_norm": gn,
                       "peak_mem_gb": torch.cuda.max_memory_allocated() / 2**30}))
