@@ -13,8 +13,9 @@
 //   utils/box.py:60-67    offset_boxes : 10 * (c_gt - c_anc) / wh_anc, 5 * log(1e-6 + wh_gt / wh_anc), times the mask
 // The reference runs (2) as a Python loop of argmax over the [A, G] matrix plus two fills per box, and (1)-(3) once
 // per sample; here one CTA per sample keeps the boxes in shared memory, recomputes IoUs on the fly (25 flops each,
-// cheaper than an [A, G] matrix in HBM), does (2) as G block-wide 64-bit max reductions with the discarded rows in a
-// shared-memory bitmap, and writes offsets / mask / classes in one final pass.  Integer/compare-bound.
+// cheaper than an [A, G] matrix in HBM), does (2) from per-box cached maxima (one block-wide 64-bit max reduction per
+// box, lazily redone when the cached anchor was claimed by another box) with the discarded rows in a shared-memory
+// bitmap, and writes offsets / mask / classes in one final pass.  Integer/compare-bound: ~2 A G IoU evaluations.
 #include "common.cuh"
 
 namespace soda {
@@ -50,6 +51,9 @@ roi_assign_kernel(const float4* __restrict__ anchors, const float* __restrict__ 
   __shared__ unsigned char s_col_dead[ROI_MAX_G];
   __shared__ unsigned long long s_red[32];
   __shared__ unsigned long long s_best;
+  __shared__ unsigned long long s_colkey[ROI_MAX_G];
+  __shared__ unsigned char s_colzero[ROI_MAX_G];
+  __shared__ int s_first_free;
   uint32_t* row_dead = roi_smem;                 // bitmap over anchors
   const int b = blockIdx.x;
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
@@ -81,48 +85,97 @@ roi_assign_kernel(const float4* __restrict__ anchors, const float* __restrict__ 
   }
   __syncthreads();
 
-  // (2) every box claims the best anchor still free
-  for (int it = 0; it < G; ++it) {
-    unsigned long long key = 0;   // (order bits of the IoU) << 32 | ~flat index : max = largest IoU, smallest index
+  // (2) every box claims the best anchor still free.  Per box (column) the best free anchor is cached as a 64-bit key
+  // (order bits of the IoU << 32 | ~(anchor * G + box): max = largest IoU, then smallest flattened index, torch.argmax's
+  // rule).  Removing anchors can only lower a column's maximum, so a cached key is an upper bound: an iteration takes
+  // the largest cached key among the free columns; if its anchor has been claimed meanwhile the column is rescanned
+  // and the pick repeated.  A column whose maximum over the free anchors has dropped to 0 (padded -1 rows from the
+  // start) stays at 0 for good and its best is simply the first free anchor - no rescan.
+  auto scan_column = [&](int j) -> unsigned long long {   // block-wide; result valid in every thread
+    unsigned long long key = 0;
+    const float4 g = s_box[j];
+    const float area_g = s_area[j];
     for (int a = tid; a < A; a += ROI_THREADS) {
       if (row_dead[a >> 5] & (1u << (a & 31))) continue;
       const float4 an = anchors[a];
       const float area_a = __fmul_rn(__fsub_rn(an.z, an.x), __fsub_rn(an.w, an.y));
-      for (int j = 0; j < G; ++j) {
-        if (s_col_dead[j]) continue;
-        const float v = roi_iou(an, area_a, s_box[j], s_area[j]);
-        const uint32_t flat = (uint32_t)a * (uint32_t)G + (uint32_t)j;
-        const unsigned long long k = ((unsigned long long)roi_order_bits(v) << 32) | (unsigned long long)(~flat);
-        key = k > key ? k : key;
-      }
+      const float v = roi_iou(an, area_a, g, area_g);
+      const uint32_t flat = (uint32_t)a * (uint32_t)G + (uint32_t)j;
+      const unsigned long long k = ((unsigned long long)roi_order_bits(v) << 32) | (unsigned long long)(~flat);
+      key = k > key ? k : key;
     }
 #pragma unroll
     for (int o = 16; o > 0; o >>= 1) {
       const unsigned long long other = __shfl_xor_sync(0xffffffffu, key, o);
       key = other > key ? other : key;
     }
+    __syncthreads();   // s_red free again
     if (lane == 0) s_red[warp] = key;
     __syncthreads();
-    if (warp == 0) {
-      key = s_red[lane];
+    key = s_red[lane];
 #pragma unroll
-      for (int o = 16; o > 0; o >>= 1) {
-        const unsigned long long other = __shfl_xor_sync(0xffffffffu, key, o);
-        key = other > key ? other : key;
+    for (int o = 16; o > 0; o >>= 1) {
+      const unsigned long long other = __shfl_xor_sync(0xffffffffu, key, o);
+      key = other > key ? other : key;
+    }
+    return key;
+  };
+  constexpr uint32_t ZERO_BITS = 0x80000000u;   // roi_order_bits(+0.0f)
+  for (int j = 0; j < G; ++j) {
+    const unsigned long long k = scan_column(j);
+    if (tid == 0) s_colkey[j] = k, s_colzero[j] = (uint32_t)(k >> 32) == ZERO_BITS;
+  }
+  if (tid == 0) s_first_free = 0;
+  __syncthreads();
+  for (int it = 0; it < G; ++it) {
+    bool exhausted = false;
+    while (true) {
+      if (warp == 0) {
+        // largest key among the free columns; zero-class columns are keyed on the first free anchor
+        const int a0 = s_first_free;
+        unsigned long long key = 0;
+        for (int j = lane; j < G; j += 32) {
+          if (s_col_dead[j]) continue;
+          unsigned long long k = s_colkey[j];
+          if (s_colzero[j])
+            k = a0 < A ? (((unsigned long long)ZERO_BITS << 32) | (unsigned long long)(~((uint32_t)a0 * (uint32_t)G + (uint32_t)j)))
+                       : 0ull;
+          key = k > key ? k : key;
+        }
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) {
+          const unsigned long long other = __shfl_xor_sync(0xffffffffu, key, o);
+          key = other > key ? other : key;
+        }
+        if (lane == 0) s_best = key;
       }
-      if (lane == 0) {
-        s_best = key;
-        if (key != 0) {
-          const uint32_t flat = ~(uint32_t)(key & 0xFFFFFFFFull);
-          const int a = (int)(flat / (uint32_t)G), j = (int)(flat % (uint32_t)G);
+      __syncthreads();
+      const unsigned long long key = s_best;
+      if (key == 0) {                           // no free anchor left (A < G)
+        exhausted = true;
+        break;
+      }
+      const uint32_t flat = ~(uint32_t)(key & 0xFFFFFFFFull);
+      const int a = (int)(flat / (uint32_t)G), j = (int)(flat % (uint32_t)G);
+      if (!(row_dead[a >> 5] & (1u << (a & 31)))) {
+        __syncthreads();                        // everyone has read s_best / row_dead
+        if (tid == 0) {
           amap[a] = j;
           row_dead[a >> 5] |= 1u << (a & 31);
           s_col_dead[j] = 1;
+          int f = s_first_free;
+          while (f < A && (row_dead[f >> 5] & (1u << (f & 31)))) ++f;
+          s_first_free = f;
         }
+        __syncthreads();
+        break;
       }
+      // stale: the cached anchor of column j was claimed by another box - rescan this column only
+      const unsigned long long k = scan_column(j);
+      if (tid == 0) s_colkey[j] = k, s_colzero[j] = (uint32_t)(k >> 32) == ZERO_BITS;
+      __syncthreads();
     }
-    __syncthreads();
-    if (s_best == 0) break;   // nothing left (A < G): the reference would start re-picking discarded entries
+    if (exhausted) break;
   }
   __threadfence_block();
   __syncthreads();
