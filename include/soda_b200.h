@@ -271,6 +271,28 @@ SODA_API int soda_multibox_detection(const float* cls_probs, const float* offset
 SODA_API int soda_roi_assign(const float* anchors, const float* labels, int B, int A, int G, float iou_threshold,
                              float* bbox_offset, float* bbox_mask, long long* class_labels, void* stream);
 
+/* ---------------------------------------------------------------------------------------------
+ * Train-mode BatchNorm over T time steps (BPTT route)
+ *   replaces: nn.BatchNorm2d in train mode, models/modules/layer_gen.py:197-214, called once per time step by the
+ *             loop of models/soda.py:142 - batch statistics per step over (B, H, W), running statistics updated T
+ *             times in sequence - and its autograd backward.
+ *   x, y, grad_y, grad_x : [T * B, H, W, C] dense pixel-major (frame t * B + b), 16-byte aligned; n_pix = B * H * W
+ *   C                    : 4 * a power of two, <= 1024
+ *   gamma, beta          : [C] or NULL (1 / 0);  running_mean / running_var : [C] updated in place, or both NULL
+ *   save_mean, save_invstd : [T, C], written by fwd, read by bwd
+ *   grad_gamma, grad_beta  : [C] (summed over the T steps) or NULL
+ *   workspace            : soda_bn_train_workspace_bytes(T, C) bytes, 16-byte aligned
+ *   y = (x - mean_t) * rsqrt(var_t + eps) * gamma + beta, var_t biased; running_var takes var_t * n / (n - 1).
+ *   Deterministic (fixed-order reductions, partials combined in fp64).
+ * ------------------------------------------------------------------------------------------- */
+SODA_API int64_t soda_bn_train_workspace_bytes(int T, int C);
+SODA_API int soda_bn_train_fwd(const float* x, int T, int64_t n_pix, int C, const float* gamma, const float* beta,
+                               float eps, float momentum, float* running_mean, float* running_var, float* y,
+                               float* save_mean, float* save_invstd, void* workspace, void* stream);
+SODA_API int soda_bn_train_bwd(const float* grad_y, const float* x, int T, int64_t n_pix, int C, const float* gamma,
+                               const float* save_mean, const float* save_invstd, float* grad_x, float* grad_gamma,
+                               float* grad_beta, void* workspace, void* stream);
+
 #ifdef __cplusplus
 }
 #endif

@@ -1,14 +1,16 @@
 """Training-mode routes (BPTT; reference models/soda.py:146-158).
 
-What is hand-written for training this round: the LIF / LI forward scans and their fused surrogate-gradient
-REVERSE scans (``soda_lif_bwd`` / ``soda_li_bwd``, wired in ``modules/cells.py``), and every convolution FORWARD.
+What is hand-written for training this round: every convolution FORWARD, the LIF / LI forward scans and their fused
+surrogate-gradient REVERSE scans (``soda_lif_bwd`` / ``soda_li_bwd``, wired in ``modules/cells.py``), and train-mode
+BatchNorm forward and backward over all T steps (``soda_bn_train_fwd`` / ``soda_bn_train_bwd``).
 What is a library call, stated plainly: convolution dgrad / wgrad go through ``aten::convolution_backward``
-(cuDNN) and train-mode BatchNorm through ``F.batch_norm`` - both CUDA, neither is a CPU or silent fallback, and
-both are next-round kernels.  Residual sums, concat stores and pooling use differentiable torch ops
-when a graph is being recorded.
+(cuDNN) - CUDA, not a CPU or silent fallback, and a next-round kernel.  Residual sums, concat stores
+and pooling use differentiable torch ops when a graph is being recorded.
 """
 
 from __future__ import annotations
+
+import os
 
 import torch
 import torch.nn.functional as F
@@ -49,12 +51,37 @@ def conv2d_autograd(conv, x, norm, residual, out):
     return y
 
 
+class _BNTrainFn(torch.autograd.Function):
+    """Per-time-step train-mode BatchNorm on our kernels (soda_bn_train_fwd / soda_bn_train_bwd)."""
+
+    @staticmethod
+    def forward(ctx, x, gamma, beta, norm, T):
+        y, mean, invstd, xk = ops.bn_train_fwd(x, T, gamma, beta, norm.eps, norm.momentum, norm.running_mean,
+                                               norm.running_var)
+        ctx.save_for_backward(xk, gamma, mean, invstd)
+        ctx.T = T
+        ctx.affine = gamma is not None
+        return y
+
+    @staticmethod
+    def backward(ctx, gy):
+        xk, gamma, mean, invstd = ctx.saved_tensors
+        gx, gg, gb = ops.bn_train_bwd(gy, xk, ctx.T, gamma, mean, invstd, want_affine=ctx.affine)
+        return gx, (gg if ctx.needs_input_grad[1] else None), (gb if ctx.needs_input_grad[2] else None), None, None
+
+
 def batchnorm_train(norm, x, T: int = 1):
     """Train-mode BatchNorm exactly as the reference runs it: batch statistics PER CALL, i.e. per time step
     (models/modules/layer_gen.py:211 inside the loop of models/soda.py:142), running statistics updated T times
     in sequence with the module's momentum."""
     if not x.is_cuda:
         raise RuntimeError("snn_for_object_detection_b200 runs on CUDA only; there is no CPU fallback")
+    if (ops.bn_train_supported(x) and norm.momentum is not None and os.environ.get("SODA_BN_TRAIN", "1") != "0"
+            and (norm.running_mean is None) == (norm.running_var is None)):
+        if norm.running_mean is not None and norm.num_batches_tracked is not None:
+            norm.num_batches_tracked.add_(T)
+        return _BNTrainFn.apply(x, norm.weight, norm.bias, norm, T)
+    # channel counts the kernel does not take (C not 4 * 2^k) and cumulative-average momentum: ATen, per time step
     B = x.shape[0] // T
     outs = []
     for t in range(T):

@@ -787,3 +787,54 @@ def roi_assign(anchors: torch.Tensor, labels: torch.Tensor, iou_threshold: float
         "soda_roi_assign",
     )
     return off, msk, cls
+
+
+# --------------------------------------------------------------------------------------------
+# train-mode BatchNorm over T time steps (BPTT route)
+# --------------------------------------------------------------------------------------------
+def bn_train_supported(x: torch.Tensor) -> bool:
+    C = x.shape[1] if x.dim() == 4 else 0
+    return (x.dim() == 4 and x.is_cuda and x.dtype == torch.float32 and C >= 4 and C <= 1024 and C & (C - 1) == 0)
+
+
+@_prof("bn_train")
+def bn_train_fwd(x: torch.Tensor, T: int, gamma, beta, eps: float, momentum: float, running_mean, running_var):
+    """Per-time-step batch statistics + normalise for ``x [T*B, C, H, W]``; updates the running statistics T times
+    in order.  Returns ``(y, save_mean [T,C], save_invstd [T,C])``; ``y`` is channels_last like the kernel's ``x``."""
+    _need_cuda(x, gamma, beta, running_mean, running_var)
+    if not _is_dense(x) or not x.is_contiguous(memory_format=torch.channels_last):
+        x = x.contiguous(memory_format=torch.channels_last)
+    N, Cc, H, W = x.shape
+    if N % T:
+        raise ValueError("bn_train: leading dimension is not a multiple of T")
+    y = torch.empty_like(x)
+    mean = torch.empty((T, Cc), dtype=torch.float32, device=x.device)
+    invstd = torch.empty_like(mean)
+    ws = torch.empty(lib.soda_bn_train_workspace_bytes(T, Cc), dtype=torch.uint8, device=x.device)
+    check(
+        lib.soda_bn_train_fwd(x.data_ptr(), T, (N // T) * H * W, Cc, _ptr(gamma), _ptr(beta), float(eps), float(momentum),
+                              _ptr(running_mean), _ptr(running_var), y.data_ptr(), mean.data_ptr(), invstd.data_ptr(),
+                              ws.data_ptr(), _stream()),
+        "soda_bn_train_fwd",
+    )
+    return y, mean, invstd, x
+
+
+@_prof("bn_train")
+def bn_train_bwd(gy: torch.Tensor, x: torch.Tensor, T: int, gamma, mean: torch.Tensor, invstd: torch.Tensor,
+                 want_affine: bool = True):
+    """``(grad_x, grad_gamma, grad_beta)`` of :func:`bn_train_fwd`; ``x`` is the channels_last tensor it returned."""
+    _need_cuda(gy, x, gamma, mean, invstd)
+    if gy.stride() != x.stride():
+        gy = gy.contiguous(memory_format=torch.channels_last)
+    N, Cc, H, W = x.shape
+    gx = torch.empty_like(x)
+    gg = torch.empty(Cc, dtype=torch.float32, device=x.device) if want_affine else None
+    gb = torch.empty(Cc, dtype=torch.float32, device=x.device) if want_affine else None
+    ws = torch.empty(lib.soda_bn_train_workspace_bytes(T, Cc), dtype=torch.uint8, device=x.device)
+    check(
+        lib.soda_bn_train_bwd(gy.data_ptr(), x.data_ptr(), T, (N // T) * H * W, Cc, _ptr(gamma), mean.data_ptr(),
+                              invstd.data_ptr(), gx.data_ptr(), _ptr(gg), _ptr(gb), ws.data_ptr(), _stream()),
+        "soda_bn_train_bwd",
+    )
+    return gx, gg, gb

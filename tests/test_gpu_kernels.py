@@ -631,3 +631,65 @@ def test_detection_loss_matches_reference_expression():
     want = ce[m].mean() * 0.04 + ce[~m].mean() * 0.96 + (bbox_preds.detach().cpu() * o_msk - o_off * o_msk).abs().mean()
     assert abs(float(loss.detach()) - float(want)) < 1e-5 * max(1.0, abs(float(want)))
     assert cls_preds.grad is not None and float(cls_preds.grad.abs().sum()) > 0 and float(bbox_preds.grad.abs().sum()) > 0
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("T,B,C,H,W,affine", [(4, 3, 32, 17, 23, True), (8, 5, 64, 30, 38, True), (1, 2, 8, 24, 30, True),
+                                              (3, 2, 256, 8, 10, False), (2, 1, 128, 5, 7, True)])
+def test_bn_train_per_time_step_matches_torch(T, B, C, H, W, affine):
+    """soda_bn_train_fwd / _bwd against T calls of F.batch_norm(training=True) (what the reference's loop does,
+    soda.py:142 + layer_gen.py:211): outputs, running statistics after T sequential updates, and all gradients.
+    Floating-point kernel: torch fp32 on the same GPU is the reference, tolerance 2e-5 of the tensor scale."""
+    ops = _pkg().ops
+    torch.manual_seed(T * 100 + C)
+    x = (torch.randn(T * B, C, H, W, device=DEV) * 1.7 + 0.3).contiguous(memory_format=torch.channels_last)
+    gamma = (torch.rand(C, device=DEV) + 0.5) if affine else None
+    beta = torch.randn(C, device=DEV) if affine else None
+    gy = torch.randn(T * B, C, H, W, device=DEV).contiguous(memory_format=torch.channels_last)
+    rm0, rv0 = torch.randn(C, device=DEV) * 0.1, torch.rand(C, device=DEV) + 0.5
+    # reference: per-time-step torch
+    xr = x.clone().requires_grad_(True)
+    gr = gamma.clone().requires_grad_(True) if affine else None
+    br = beta.clone().requires_grad_(True) if affine else None
+    rm, rv = rm0.clone(), rv0.clone()
+    yr = torch.cat([F.batch_norm(xr[t * B:(t + 1) * B], rm, rv, gr, br, True, 0.1, 1e-5) for t in range(T)])
+    yr.backward(gy)
+    # ours
+    rm2, rv2 = rm0.clone(), rv0.clone()
+    y, mean, invstd, xk = ops.bn_train_fwd(x, T, gamma, beta, 1e-5, 0.1, rm2, rv2)
+    gx, gg, gb = ops.bn_train_bwd(gy, xk, T, gamma, mean, invstd, want_affine=affine)
+
+    def close(a, b, tol=2e-5):
+        assert float((a - b).abs().max()) <= tol * max(1.0, float(b.abs().max())), float((a - b).abs().max())
+
+    close(y, yr.detach())
+    close(rm2, rm)
+    close(rv2, rv)
+    close(gx, xr.grad, 5e-5)
+    if affine:
+        close(gg, gr.grad, 5e-5)
+        close(gb, br.grad, 5e-5)
+    # deterministic
+    y2, *_ = ops.bn_train_fwd(x, T, gamma, beta, 1e-5, 0.1, rm0.clone(), rv0.clone())
+    assert torch.equal(y, y2)
+
+
+@pytest.mark.gpu
+def test_bn_train_module_route_and_fallback(monkeypatch):
+    """SodaBatchNorm2d.forward_seq in train mode takes the kernel for C = 4 * 2^k and ATen otherwise; both give the
+    per-time-step result, update num_batches_tracked by T and let gradients reach the input."""
+    from snn_for_object_detection_b200.modules.common import SodaBatchNorm2d
+
+    for C in (32, 24):
+        torch.manual_seed(C)
+        bn = SodaBatchNorm2d(C).to(DEV).train()
+        ref = torch.nn.BatchNorm2d(C).to(DEV).train()
+        T, B = 3, 2
+        x = torch.randn(T * B, C, 9, 11, device=DEV, requires_grad=True)
+        y = bn.forward_seq(x, T)
+        yr = torch.cat([ref(x.detach()[t * B:(t + 1) * B]) for t in range(T)])
+        assert float((y.detach() - yr).abs().max()) < 2e-5
+        assert int(bn.num_batches_tracked) == T
+        assert float((bn.running_var - ref.running_var).abs().max()) < 1e-5
+        y.square().mean().backward()
+        assert x.grad is not None and float(x.grad.abs().sum()) > 0
