@@ -12,8 +12,8 @@
 // of a step are one contiguous run of n * C floats.  Three HBM-bound kernels per direction instead of T library calls:
 //   bn_partial_kernel   grid (S, T): per-channel partial sums of (x, x*x) or (gy, gy*xhat) of one slice of one step,
 //                       4 channels per thread as one 16-byte load, fixed-order block tree -> deterministic
-//   bn_finalize_*       one thread per channel: partials combined in fp64 in slice order, per-(t, c) coefficients,
-//                       the running-statistics chain / the parameter gradients
+//   bn_finalize_*       one thread per (t, c): partials combined in fp64 in slice order, per-(t, c) coefficients; the
+//                       running-statistics chain / the sum over t of the parameter gradients by one row per channel
 //   bn_apply_*          elementwise  y = x*a + b   /   dx = gy*c1 + x*c2 + c3   with per-(t, c) coefficients
 // Algorithmic bytes: forward 12 B per element (x twice, y once), backward 20 B (gy, x twice each, dx once).
 #include "common.cuh"
@@ -74,66 +74,94 @@ bn_partial_kernel(const float* __restrict__ x, const float* __restrict__ g, cons
   }
 }
 
+// Finalize kernels: block = 32 channels x BN_FT time rows; thread (ty, c) combines the S partials of its (t, c) in
+// fp64 in slice order; the sequential part (running-statistics chain / sum over t) is done by row 0 from shared memory.
+constexpr int BN_FT = 32;
+
 // forward: mean / invstd per (t, c), affine coefficients, running statistics chained over t
-__global__ void bn_finalize_fwd_kernel(const float* __restrict__ partial, int T, int S, int C, int64_t n_pix, float eps,
-                                       float momentum, const float* __restrict__ gamma, const float* __restrict__ beta,
-                                       float* __restrict__ mean, float* __restrict__ invstd, float* __restrict__ scale,
-                                       float* __restrict__ shift, float* __restrict__ running_mean,
-                                       float* __restrict__ running_var) {
-  const int c = blockIdx.x * blockDim.x + threadIdx.x;
-  if (c >= C) return;
+__global__ void __launch_bounds__(32 * BN_FT)
+bn_finalize_fwd_kernel(const float* __restrict__ partial, int T, int S, int C, int64_t n_pix, float eps,
+                       float momentum, const float* __restrict__ gamma, const float* __restrict__ beta,
+                       float* __restrict__ mean, float* __restrict__ invstd, float* __restrict__ scale,
+                       float* __restrict__ shift, float* __restrict__ running_mean, float* __restrict__ running_var) {
+  __shared__ float s_m[BN_FT][32], s_v[BN_FT][32];
+  const int cl = threadIdx.x & 31, ty = threadIdx.x >> 5;
+  const int c = blockIdx.x * 32 + cl;
+  const bool live = c < C;
   const double n = (double)n_pix;
-  const float gm = gamma ? gamma[c] : 1.0f, bt = beta ? beta[c] : 0.0f;
-  float rm = running_mean ? running_mean[c] : 0.f, rv = running_var ? running_var[c] : 0.f;
-  for (int t = 0; t < T; ++t) {
-    double s0 = 0.0, s1 = 0.0;
-    for (int s = 0; s < S; ++s) {
-      const float* p = partial + (((int64_t)t * S + s) * 2) * C;
-      s0 += (double)p[c], s1 += (double)p[C + c];
+  const float gm = (live && gamma) ? gamma[c] : 1.0f, bt = (live && beta) ? beta[c] : 0.0f;
+  float rm = (live && running_mean) ? running_mean[c] : 0.f, rv = (live && running_var) ? running_var[c] : 0.f;
+  for (int t0 = 0; t0 < T; t0 += BN_FT) {
+    const int t = t0 + ty;
+    if (live && t < T) {
+      double s0 = 0.0, s1 = 0.0;
+      for (int s = 0; s < S; ++s) {
+        const float* p = partial + (((int64_t)t * S + s) * 2) * C;
+        s0 += (double)p[c], s1 += (double)p[C + c];
+      }
+      const double m = s0 / n;
+      double var = s1 / n - m * m;
+      var = var < 0.0 ? 0.0 : var;
+      const float is = (float)(1.0 / sqrt(var + (double)eps));
+      mean[(int64_t)t * C + c] = (float)m;
+      invstd[(int64_t)t * C + c] = is;
+      const float a = gm * is;
+      scale[(int64_t)t * C + c] = a;
+      shift[(int64_t)t * C + c] = bt - (float)m * a;
+      s_m[ty][cl] = (float)m;
+      s_v[ty][cl] = (float)(n > 1.0 ? var * n / (n - 1.0) : var);
     }
-    const double m = s0 / n;
-    double var = s1 / n - m * m;
-    var = var < 0.0 ? 0.0 : var;
-    const float is = (float)(1.0 / sqrt(var + (double)eps));
-    mean[(int64_t)t * C + c] = (float)m;
-    invstd[(int64_t)t * C + c] = is;
-    const float a = gm * is;
-    scale[(int64_t)t * C + c] = a;
-    shift[(int64_t)t * C + c] = bt - (float)m * a;
-    if (running_mean) {
-      rm = (1.0f - momentum) * rm + momentum * (float)m;
-      rv = (1.0f - momentum) * rv + momentum * (float)(n > 1.0 ? var * n / (n - 1.0) : var);
+    __syncthreads();
+    if (ty == 0 && live && running_mean) {
+      for (int k = 0; k < BN_FT && t0 + k < T; ++k) {
+        rm = (1.0f - momentum) * rm + momentum * s_m[k][cl];
+        rv = (1.0f - momentum) * rv + momentum * s_v[k][cl];
+      }
     }
+    __syncthreads();
   }
-  if (running_mean) running_mean[c] = rm, running_var[c] = rv;
+  if (ty == 0 && live && running_mean) running_mean[c] = rm, running_var[c] = rv;
 }
 
 // backward: dgamma / dbeta and the three per-(t, c) coefficients of dx = gy*c1 + x*c2 + c3
-__global__ void bn_finalize_bwd_kernel(const float* __restrict__ partial, int T, int S, int C, int64_t n_pix,
-                                       const float* __restrict__ gamma, const float* __restrict__ mean,
-                                       const float* __restrict__ invstd, float* __restrict__ coef /*[T][3][C]*/,
-                                       float* __restrict__ dgamma, float* __restrict__ dbeta) {
-  const int c = blockIdx.x * blockDim.x + threadIdx.x;
-  if (c >= C) return;
+__global__ void __launch_bounds__(32 * BN_FT)
+bn_finalize_bwd_kernel(const float* __restrict__ partial, int T, int S, int C, int64_t n_pix,
+                       const float* __restrict__ gamma, const float* __restrict__ mean,
+                       const float* __restrict__ invstd, float* __restrict__ coef /*[T][3][C]*/,
+                       float* __restrict__ dgamma, float* __restrict__ dbeta) {
+  __shared__ double s_g[BN_FT][32], s_b[BN_FT][32];
+  const int cl = threadIdx.x & 31, ty = threadIdx.x >> 5;
+  const int c = blockIdx.x * 32 + cl;
+  const bool live = c < C;
   const double n = (double)n_pix;
-  const double gm = gamma ? (double)gamma[c] : 1.0;
+  const double gm = (live && gamma) ? (double)gamma[c] : 1.0;
   double dg = 0.0, db = 0.0;
-  for (int t = 0; t < T; ++t) {
+  for (int t0 = 0; t0 < T; t0 += BN_FT) {
+    const int t = t0 + ty;
     double s0 = 0.0, s1 = 0.0;
-    for (int s = 0; s < S; ++s) {
-      const float* p = partial + (((int64_t)t * S + s) * 2) * C;
-      s0 += (double)p[c], s1 += (double)p[C + c];
+    if (live && t < T) {
+      for (int s = 0; s < S; ++s) {
+        const float* p = partial + (((int64_t)t * S + s) * 2) * C;
+        s0 += (double)p[c], s1 += (double)p[C + c];
+      }
+      const double is = (double)invstd[(int64_t)t * C + c], mu = (double)mean[(int64_t)t * C + c];
+      const double a = gm * is, m1 = s0 / n, m2 = s1 / n;
+      float* k = coef + (int64_t)t * 3 * C;
+      k[c] = (float)a;                              // * gy
+      k[C + c] = (float)(-a * m2 * is);             // * x
+      k[2 * C + c] = (float)(-a * m1 + a * m2 * is * mu);
     }
-    db += s0, dg += s1;
-    const double is = (double)invstd[(int64_t)t * C + c], mu = (double)mean[(int64_t)t * C + c];
-    const double a = gm * is, m1 = s0 / n, m2 = s1 / n;
-    float* k = coef + (int64_t)t * 3 * C;
-    k[c] = (float)a;                              // * gy
-    k[C + c] = (float)(-a * m2 * is);             // * x
-    k[2 * C + c] = (float)(-a * m1 + a * m2 * is * mu);
+    s_b[ty][cl] = s0, s_g[ty][cl] = s1;
+    __syncthreads();
+    if (ty == 0) {
+      for (int k = 0; k < BN_FT; ++k) db += s_b[k][cl], dg += s_g[k][cl];   // fixed order over t
+    }
+    __syncthreads();
   }
-  if (dgamma) dgamma[c] = (float)dg;
-  if (dbeta) dbeta[c] = (float)db;
+  if (ty == 0 && live) {
+    if (dgamma) dgamma[c] = (float)dg;
+    if (dbeta) dbeta[c] = (float)db;
+  }
 }
 
 // y = x * a[t, c] + b[t, c]  (HAS_G = false)   /   dx = g * k1 + x * k2 + k3  (HAS_G = true, coef [T][3][C])
@@ -206,7 +234,7 @@ extern "C" int soda_bn_train_fwd(const float* x, int T, int64_t n_pix, int C, co
   bn_partial_kernel<0><<<dim3(S, T), BN_THREADS, 0, st>>>(x, nullptr, nullptr, nullptr, n_pix, C, partial);
   rc = after_launch("bn_partial_kernel");
   if (rc) return rc;
-  bn_finalize_fwd_kernel<<<(C + 127) / 128, 128, 0, st>>>(partial, T, S, C, n_pix, eps, momentum, gamma, beta, save_mean,
+  bn_finalize_fwd_kernel<<<(C + 31) / 32, 32 * BN_FT, 0, st>>>(partial, T, S, C, n_pix, eps, momentum, gamma, beta, save_mean,
                                                           save_invstd, scale, shift, running_mean, running_var);
   rc = after_launch("bn_finalize_fwd_kernel");
   if (rc) return rc;
@@ -232,7 +260,7 @@ extern "C" int soda_bn_train_bwd(const float* grad_y, const float* x, int T, int
   bn_partial_kernel<1><<<dim3(S, T), BN_THREADS, 0, st>>>(x, grad_y, save_mean, save_invstd, n_pix, C, partial);
   rc = after_launch("bn_partial_kernel");
   if (rc) return rc;
-  bn_finalize_bwd_kernel<<<(C + 127) / 128, 128, 0, st>>>(partial, T, S, C, n_pix, gamma, save_mean, save_invstd, coef,
+  bn_finalize_bwd_kernel<<<(C + 31) / 32, 32 * BN_FT, 0, st>>>(partial, T, S, C, n_pix, gamma, save_mean, save_invstd, coef,
                                                           grad_gamma, grad_beta);
   rc = after_launch("bn_finalize_bwd_kernel");
   if (rc) return rc;

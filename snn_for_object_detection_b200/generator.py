@@ -150,7 +150,12 @@ class BlockGen(nn.Module):
         out_state = []
         state = [None] * len(self.net) if state is None else state
         dense_buf = None
-        if self.merge == "dense":
+        # Training route (a graph is being recorded): no in-place slice stores - autograd's CopySlices backward clones
+        # the whole concat gradient once per slice - but the reference's own merges, torch.cat / a sum of the branches.
+        recording = torch.is_grad_enabled() and (X.requires_grad or any(p.requires_grad for p in self.parameters()))
+        if recording:
+            out = None
+        if self.merge == "dense" and not recording:
             Ho, Wo = self.out_hw(X.shape[2], X.shape[3])
             dense_buf = out if out is not None else ops.empty_pixel_major(
                 X.shape[0], self.out_channels, Ho, Wo, X.device
@@ -159,7 +164,7 @@ class BlockGen(nn.Module):
         for bi, (branch, flags, branch_state) in enumerate(zip(self.net, self.branch_state, state)):
             branch_state = [None] * len(branch) if branch_state is None else list(branch_state)
             dst = None
-            if self.merge == "dense":
+            if self.merge == "dense" and not recording:
                 dst = dense_buf[:, c0 : c0 + self.branch_channels[bi]]
                 c0 += self.branch_channels[bi]
             elif self.merge == "forward":
@@ -176,6 +181,8 @@ class BlockGen(nn.Module):
                 other = [None] * len(self.net[1 - bi])
                 return Y, ([branch_state, other] if bi == 0 else [other, branch_state])
             outs.append(Y)
+        if self.merge == "dense" and recording:
+            return torch.cat(outs, dim=1), out_state   # models/generator.py:158
         if self.merge == "dense":
             # a concat of spike maps / spike counts is itself one (largest bound): the next Conv may use the
             # bf16-only operand scheme
@@ -185,7 +192,9 @@ class BlockGen(nn.Module):
             return dense_buf, out_state
         if self.merge == "residual":
             if torch.is_grad_enabled() and any(o.requires_grad for o in outs):
-                Y = torch.stack(outs).sum(0)   # training: differentiable merge, the reference's own expression
+                Y = outs[0]
+                for o in outs[1:]:
+                    Y = Y + o                  # training: differentiable merge (= torch.stack(out).sum(0) for two branches)
             else:
                 Y = ops.add_n(outs)
             if out is not None:
