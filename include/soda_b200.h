@@ -206,6 +206,13 @@ SODA_API int soda_li_fwd(const soda_neuron_params_t* p, const float* x, const fl
                 int T, int64_t n, int apply_tanh, float* out, float* v_out, float* i_out,
                 float* i_trace, void* stream);
 
+/* Saturable leaky integrator scan (LayerGen SLI): T steps of the reference's own sli_feed_forward_step,
+ * models/modules/sli.py:110-126 (cell :80-107, LayerGen models/modules/layer_gen.py:331-347):
+ *   i_jump = i + x * sigmoid(v_st - |v|);  v' = v + dt_tau_mem * ((v_leak - v) + i_jump);  i' = i_jump - dt_tau_syn * i_jump
+ *   out = v' per step.  p->v_th carries v_st; layouts as soda_li_fwd; NULL v0 / i0 = initial state (v_leak, 0). */
+SODA_API int soda_sli_fwd(const soda_neuron_params_t* p, const float* x, const float* v0, const float* i0, int T,
+                 int64_t n, float* out, float* v_out, float* i_out, float* i_trace, void* stream);
+
 /* Surrogate-gradient LIF backward (K8): fused reverse scan over T.
  *   replaces: autograd through T calls of LIFCell incl. norse SuperSpike.backward
  *             (g / (alpha*|v_dec - v_th| + 1)^2), models/soda.py:146-158.

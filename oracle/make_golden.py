@@ -235,12 +235,34 @@ def golden_roi(ref):
           "masked", [int(out[1][b, :, 0].sum()) for b in range(3)])
 
 
+def golden_sli(ref):
+    """T = 12 steps of the reference's own sli_feed_forward_step (models/modules/sli.py:110-126) from the cell's
+    initial state, inputs large enough to drive |v| past the saturation potential."""
+    import sys
+
+    sli = sys.modules["models.modules.sli"]
+    torch.manual_seed(11)
+    x = torch.randn(12, 3, 8, 5, 6) * 4.0 + 1.0
+    cell = sli.SLICell()
+    state, outs = None, []
+    for t in range(x.shape[0]):
+        if state is None:
+            state = sli.SLIState(v=cell.p.v_leak.detach().clone(), i=torch.zeros_like(x[t]))
+        out, state = sli.sli_feed_forward_step(x[t], state, cell.p, 0.001)
+        outs.append(out)
+    out = torch.stack(outs)
+    np.savez_compressed(os.path.join(OUT, "sli.npz"), x=x.numpy(), out=out.detach().numpy(),
+                        v=state.v.detach().numpy(), i=state.i.detach().numpy())
+    print("sli: max |v|", float(out.abs().max()), "saturated fraction", float((out.abs() > 1).float().mean()))
+
+
 def main():
     os.makedirs(OUT, exist_ok=True)
     ref = load_reference()
     golden_binning(ref)
     golden_box(ref)
     golden_roi(ref)
+    golden_sli(ref)
     golden_vgg(ref)
     golden_tiny_yolo(ref)
 

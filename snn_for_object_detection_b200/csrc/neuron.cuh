@@ -43,6 +43,18 @@ __device__ __forceinline__ void li_step(const NP& p, float x, float& v, float& i
   i = i_dec;
 }
 
+// Saturable leaky integrator of the reference's own models/modules/sli.py:110-126 (sli_feed_forward_step):
+//   i_jump = i + x * sigmoid(v_st - |v|);  v' = v + dt*tau_mem*((v_leak - v) + i_jump);  i' = i_jump - dt*tau_syn*i_jump
+// v_st travels in the v_th field.  sigmoid(z) = 1 / (1 + exp(-z)) as ATen evaluates it.
+__device__ __forceinline__ void sli_step(const NP& p, float x, float& v, float& i) {
+  const float z = __fsub_rn(p.v_th, fabsf(v));
+  const float gate = __fdiv_rn(1.0f, __fadd_rn(1.0f, expf(-z)));
+  const float i_jump = __fadd_rn(i, __fmul_rn(x, gate));
+  const float dv = __fmul_rn(p.a, __fadd_rn(__fsub_rn(p.v_leak, v), i_jump));
+  v = __fadd_rn(v, dv);
+  i = __fadd_rn(i_jump, __fmul_rn(-p.s, i_jump));
+}
+
 inline NP to_np(const soda_neuron_params_t* q) {
   NP p;
   p.a = q->dt_tau_mem, p.s = q->dt_tau_syn, p.v_leak = q->v_leak, p.v_th = q->v_th;

@@ -44,7 +44,7 @@ __device__ __forceinline__ void vstore(float* p, const float (&r)[V]) {
   }
 }
 
-// kMode: 0 = LIF, 1 = LI, 2 = LI + tanh
+// kMode: 0 = LIF, 1 = LI, 2 = LI + tanh, 3 = SLI (saturable leaky integrator)
 template <int V, int kMode>
 __global__ void __launch_bounds__(256)
 neuron_fwd_kernel(NP p, const float* __restrict__ x, const float* __restrict__ v0,
@@ -81,6 +81,9 @@ neuron_fwd_kernel(NP p, const float* __restrict__ x, const float* __restrict__ v
       for (int k = 0; k < V; ++k) {
         if constexpr (kMode == 0) {
           lif_step(p, xs[u][k], v[k], i[k], o[k], vd[k]);
+        } else if constexpr (kMode == 3) {
+          sli_step(p, xs[u][k], v[k], i[k]);
+          o[k] = v[k];
         } else {
           li_step(p, xs[u][k], v[k], i[k]);
           o[k] = (kMode == 2) ? tanhf(v[k]) : v[k];
@@ -102,6 +105,9 @@ neuron_fwd_kernel(NP p, const float* __restrict__ x, const float* __restrict__ v
     for (int k = 0; k < V; ++k) {
       if constexpr (kMode == 0) {
         lif_step(p, xs[k], v[k], i[k], o[k], vd[k]);
+      } else if constexpr (kMode == 3) {
+        sli_step(p, xs[k], v[k], i[k]);
+        o[k] = v[k];
       } else {
         li_step(p, xs[k], v[k], i[k]);
         o[k] = (kMode == 2) ? tanhf(v[k]) : v[k];
@@ -421,6 +427,11 @@ extern "C" int soda_li_fwd(const soda_neuron_params_t* p, const float* x, const 
                                stream, "li_tanh_fwd");
   return soda::launch_fwd<1>(p, x, v0, i0, T, n, out, v_out, i_out, nullptr, nullptr, i_trace,
                              stream, "li_fwd");
+}
+
+extern "C" int soda_sli_fwd(const soda_neuron_params_t* p, const float* x, const float* v0, const float* i0, int T,
+                            int64_t n, float* out, float* v_out, float* i_out, float* i_trace, void* stream) {
+  return soda::launch_fwd<3>(p, x, v0, i0, T, n, out, v_out, i_out, nullptr, nullptr, i_trace, stream, "sli_fwd");
 }
 
 extern "C" int soda_lif_bwd(const soda_neuron_params_t* p, const float* grad_out,

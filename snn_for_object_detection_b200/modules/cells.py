@@ -18,7 +18,8 @@ from torch import nn
 from .. import ops
 from ..ops import NeuronConst
 
-__all__ = ["LIFParameters", "LIParameters", "LIFFeedForwardState", "LIState", "SNNCell", "LIFCell", "LICell"]
+__all__ = ["LIFParameters", "LIParameters", "LIFFeedForwardState", "LIState", "SNNCell", "LIFCell", "LICell",
+           "SLIParameters", "SLIState", "SLICell"]
 
 
 class LIFParameters(NamedTuple):
@@ -35,6 +36,20 @@ class LIParameters(NamedTuple):
     tau_syn_inv: float = 1.0 / 5e-3
     tau_mem_inv: float = 1.0 / 1e-2
     v_leak: float = 0.0
+
+
+class SLIParameters(NamedTuple):
+    """Parameters of the saturable leaky integrator (reference ``models/modules/sli.py:25-38``)."""
+
+    tau_syn_inv: float = 1.0 / 5e-3
+    tau_mem_inv: float = 1.0 / 1e-2
+    v_leak: float = 0.0
+    v_st: float = 1.0
+
+
+class SLIState(NamedTuple):
+    v: torch.Tensor
+    i: torch.Tensor
 
 
 class LIFFeedForwardState(NamedTuple):
@@ -160,3 +175,35 @@ class LICell(SNNCell):
             # per-step v is the (pre-tanh) output itself
             return out, LIState(v, i), LIState(out if not fuse_tanh else None, it)
         return out, LIState(v, i)
+
+
+class SLICell(SNNCell):
+    """Saturable leaky integrator cell of the reference (``models/modules/sli.py:80-126``); returns
+    ``(v, SLIState(v, i))``.  Inference: one CUDA scan over all T steps (``soda_sli_fwd``); when a graph is being
+    recorded: the reference's own expression step by step in torch ops (differentiable)."""
+
+    def __init__(self, p: SLIParameters = SLIParameters(), **kwargs):
+        super().__init__(p, **kwargs)
+        self._const = self._const._replace(v_th=_f32(p.v_st))
+
+    def forward_seq(self, x, T, state=None, want_trace=False):
+        v0, i0 = (None, None) if state is None else (state.v, state.i)
+        if torch.is_grad_enabled() and (x.requires_grad or (i0 is not None and i0.requires_grad)):
+            return self._forward_torch(x, T, v0, i0)
+        out, v, i, it = ops.sli_scan(x, T, v0, i0, self._const, want_trace=want_trace)
+        if want_trace:
+            return out, SLIState(v, i), SLIState(out, it)
+        return out, SLIState(v, i)
+
+    def _forward_torch(self, x, T, v0, i0):
+        B = x.shape[0] // T
+        c = self._const
+        v = torch.full_like(x[:B], c.v_leak) if v0 is None or v0.dim() == 0 else v0
+        i = torch.zeros_like(x[:B]) if i0 is None else i0
+        outs = []
+        for t in range(T):
+            i_jump = i + x[t * B : (t + 1) * B] * torch.sigmoid(c.v_th - torch.abs(v))
+            v = v + c.dt_tau_mem * ((c.v_leak - v) + i_jump)
+            i = i_jump + (-c.dt_tau_syn) * i_jump
+            outs.append(v)
+        return (outs[0] if T == 1 else torch.cat(outs)), SLIState(v, i)

@@ -14,7 +14,7 @@ import torch.nn.functional as F
 from torch import nn
 
 from .. import _lib, ops
-from .cells import LICell, LIFCell, SNNCell
+from .cells import LICell, LIFCell, SLICell, SNNCell
 
 common_list = ("SumPool2d", "Storage", "StateStorage")
 
@@ -175,7 +175,7 @@ class StateStorage(nn.Module):
         if state is None:
             self.state_list.clear()
             self.spike_list.clear()
-        if self.training or not isinstance(self.module, (LIFCell, LICell)):
+        if self.training or not isinstance(self.module, (LIFCell, LICell, SLICell)):
             return self.module.forward_seq(x, T, state, **kw)
         out, new_state, trace = self.module.forward_seq(x, T, state, want_trace=True, **kw)
         B = x.shape[0] // T

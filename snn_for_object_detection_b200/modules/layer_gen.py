@@ -11,7 +11,7 @@ from typing import Optional, Tuple
 
 from torch import nn
 
-from .cells import LICell, LIFCell, SNNCell
+from .cells import LICell, LIFCell, SLICell, SNNCell
 from .common import SodaBatchNorm2d, SodaConv2d, SodaPool2d, StateStorage, Storage, SumPool2d
 
 layers_list = (
@@ -140,7 +140,7 @@ class Return(LayerGen):
 
 
 class _OutOfScope(LayerGen):
-    """LSTM / Synapse / SLI: experimental reference layers that no shipped net uses.
+    """LSTM / Synapse: experimental reference layers that no shipped net uses.
 
     They are outside this package's hot path; constructing one raises so that the gap is loud."""
 
@@ -163,5 +163,12 @@ class Synapse(_OutOfScope):
     _name = "Synapse"
 
 
-class SLI(_OutOfScope):
-    _name = "SLI"
+class SLI(LayerGen):
+    """Saturable leaky integrator layer (reference ``models/modules/layer_gen.py:331-347``) on ``soda_sli_fwd``."""
+
+    def __init__(self, state_storage: bool = False):
+        self.state_storage = state_storage
+
+    def get(self, in_channels: int) -> Tuple[SNNCell, int]:
+        module = SLICell() if not self.state_storage else StateStorage(SLICell())
+        return module, in_channels

@@ -619,6 +619,29 @@ def li_scan(
     return out, v, i, it
 
 
+@_prof("li_scan")
+def sli_scan(x: torch.Tensor, T: int, v0: Optional[torch.Tensor] = None, i0: Optional[torch.Tensor] = None,
+             p: NeuronConst = None, want_trace: bool = False):
+    """T steps of the reference's saturable leaky integrator (``models/modules/sli.py:110-126``); ``p.v_th`` carries
+    the saturation potential.  Returns ``(v per step, v_T, i_T, i_trace|None)``."""
+    _need_cuda(x, v0, i0)
+    x, n = _flat_T(x, T)
+    out = torch.empty_like(x)
+    v = torch.empty_like(x[: x.shape[0] // T])
+    i = torch.empty_like(v)
+    if i0 is not None:
+        i0 = _like_block(i0, v)
+        v0 = _like_block(v0, v) if v0 is not None and v0.dim() > 0 else None   # a scalar v is the initial v_leak
+    it = torch.empty_like(x) if want_trace else None
+    pc = p.c()
+    check(
+        lib.soda_sli_fwd(C.byref(pc), x.data_ptr(), _ptr(v0), _ptr(i0), T, n, out.data_ptr(), v.data_ptr(),
+                         i.data_ptr(), _ptr(it), _stream()),
+        "soda_sli_fwd",
+    )
+    return out, v, i, it
+
+
 def lif_scan_bwd(grad_out, grad_vT, grad_iT, v_dec, T: int, p: NeuronConst = LIF_DEFAULT):
     """Fused reverse scan: returns ``(grad_x, grad_v0, grad_i0)``."""
     _need_cuda(grad_out, grad_vT, grad_iT, v_dec)

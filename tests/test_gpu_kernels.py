@@ -688,8 +688,39 @@ def test_bn_train_module_route_and_fallback(monkeypatch):
         x = torch.randn(T * B, C, 9, 11, device=DEV, requires_grad=True)
         y = bn.forward_seq(x, T)
         yr = torch.cat([ref(x.detach()[t * B:(t + 1) * B]) for t in range(T)])
-        assert float((y.detach() - yr).abs().max()) < 2e-5
+        assert float((y.detach() - yr).abs().max().item()) < 2e-5
         assert int(bn.num_batches_tracked) == T
         assert float((bn.running_var - ref.running_var).abs().max()) < 1e-5
         y.square().mean().backward()
         assert x.grad is not None and float(x.grad.abs().sum()) > 0
+
+
+@pytest.mark.gpu
+def test_sli_scan_matches_reference_golden_and_carries_state():
+    """soda_sli_fwd against the reference's own sli_feed_forward_step (tests/golden/sli.npz): floating-point kernel
+    (expf vs ATen's exp), 2e-6 of the membrane scale; a scan split in two with carried state equals one scan."""
+    ops = _pkg().ops
+    from snn_for_object_detection_b200.modules.cells import SLICell
+
+    g = golden("sli.npz")
+    x = torch.from_numpy(g["x"])
+    T, B = x.shape[:2]
+    xd = x.reshape(T * B, *x.shape[2:]).to(DEV)
+    cell = SLICell()
+    with torch.no_grad():
+        out, st = cell.forward_seq(xd, T)
+    want = torch.from_numpy(g["out"]).reshape(T * B, *x.shape[2:])
+    scale = float(want.abs().max())
+    assert float((out.cpu() - want).abs().max()) < 2e-6 * scale
+    assert float((st.v.cpu() - torch.from_numpy(g["v"])).abs().max()) < 2e-6 * scale
+    assert float((st.i.cpu() - torch.from_numpy(g["i"])).abs().max()) < 2e-6 * float(np.abs(g["i"]).max())
+    with torch.no_grad():
+        o1, s1 = cell.forward_seq(xd[: 5 * B], 5)
+        o2, s2 = cell.forward_seq(xd[5 * B:], T - 5, s1)
+    assert torch.equal(torch.cat([o1, o2]), out) and torch.equal(s2.v, st.v) and torch.equal(s2.i, st.i)
+    # training route: the reference's expression in torch ops, same values, gradients flow
+    xg = xd.clone().requires_grad_(True)
+    og, _ = cell.forward_seq(xg, T)
+    assert float((og.detach() - out).abs().max()) < 2e-6 * scale
+    og.sum().backward()
+    assert float(xg.grad.abs().sum()) > 0

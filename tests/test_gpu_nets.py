@@ -427,3 +427,34 @@ def test_planner_tags_spike_inputs_through_pools_residuals_and_concats():
     finally:
         ops.mark_exact = real_mark
     assert float((Y != Y0).float().mean()) <= 2e-3   # end to end through 6 spiking layers (flips propagate)
+
+
+@pytest.mark.gpu
+def test_generated_net_with_sli_layers_matches_time_major_oracle():
+    """A ListGen with the reference's SLI LayerGen (Conv, Norm, SLI, Conv, Norm, SLI with state_storage) is a drop-in:
+    layer-major forward == the per-step protocol == the oracle's SLI restatement on the same conv outputs."""
+    from oracle import sli_restated as sr
+    from snn_for_object_detection_b200 import BlockGen
+    from snn_for_object_detection_b200.modules.layer_gen import SLI, Conv, Norm
+
+    torch.manual_seed(4)
+    block = BlockGen(2, [Conv(32, kernel_size=3), Norm(), SLI(), Conv(32, kernel_size=3), Norm(), SLI(state_storage=True)])
+    block = block.to(DEV).eval()
+    T, B = 6, 2
+    X = (torch.rand(T * B, 2, 20, 24, device=DEV) < 0.3).float()
+    with torch.no_grad():
+        Y, state = block.forward_seq(X, T)
+        ys, st = [], None
+        for t in range(T):                       # the reference's per-step protocol
+            y, st = block(X[t * B:(t + 1) * B], st)
+            ys.append(y)
+    assert torch.equal(torch.cat(ys), Y)
+    storage = block.net[0][5]
+    assert storage.get_spikes().shape[0] == T and storage.get_state().v.shape[0] == T
+    # oracle: SLI restatement applied to this net's own second-conv currents
+    with torch.no_grad():
+        c1 = block.net[0][0](X, norm=block.net[0][1])
+        v1, _ = block.net[0][2].forward_seq(c1, T)
+        c2 = block.net[0][3](v1, norm=block.net[0][4])
+    want, _, _ = sr.sli_scan(c2.cpu().reshape(T, B, *c2.shape[1:]))
+    assert float((Y.cpu().reshape(want.shape) - want).abs().max()) < 5e-6 * max(1.0, float(want.abs().max()))

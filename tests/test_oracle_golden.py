@@ -143,3 +143,15 @@ def test_roi_restatement_live_reference():
     off, msk, cls = rr.roi(anchors, labels, 0.4)
     assert np.array_equal(cls, want[2].numpy()) and np.array_equal(msk, want[1].numpy())
     np.testing.assert_allclose(off, want[0].numpy(), rtol=1e-6, atol=1e-6)
+
+
+def test_sli_restatement_matches_reference_golden():
+    """oracle/sli_restated.py against outputs of the reference's OWN sli_feed_forward_step (models/modules/sli.py),
+    bit for bit - this neuron's arithmetic is in the reference tree, so unlike LIF / LI it is pinned."""
+    from oracle import sli_restated as sr
+
+    g = golden("sli.npz")
+    out, v, i = sr.sli_scan(torch.from_numpy(g["x"]))
+    assert torch.equal(out, torch.from_numpy(g["out"]))
+    assert torch.equal(v, torch.from_numpy(g["v"])) and torch.equal(i, torch.from_numpy(g["i"]))
+    assert float((out.abs() > 1).float().mean()) > 0.2   # the saturation branch is exercised
