@@ -213,6 +213,14 @@ SODA_API int soda_li_fwd(const soda_neuron_params_t* p, const float* x, const fl
 SODA_API int soda_sli_fwd(const soda_neuron_params_t* p, const float* x, const float* v0, const float* i0, int T,
                  int64_t n, float* out, float* v_out, float* i_out, float* i_trace, void* stream);
 
+/* Synaptic transmission scan (LayerGen Synapse): T steps of the reference's own synapse_feed_forward_step,
+ * models/modules/synapse.py:73-103 (cell :36-70, LayerGen models/modules/layer_gen.py:321-328):
+ *   tau = x > 0 ? tau_secretion : tau_dissociation;  p' = p + ((x - p) * tau) * dt
+ *   g = sigma_inhibition != 0 ? 4 * sigma * (p' - sigma * p'^2) : p';  out = max(g, 0) per step
+ *   x, out : [T, n];  p0 (NULL = zeros), p_out : [n]. */
+SODA_API int soda_synapse_fwd(float tau_secretion, float tau_dissociation, float sigma_inhibition, float dt,
+                     const float* x, const float* p0, int T, int64_t n, float* out, float* p_out, void* stream);
+
 /* Surrogate-gradient LIF backward (K8): fused reverse scan over T.
  *   replaces: autograd through T calls of LIFCell incl. norse SuperSpike.backward
  *             (g / (alpha*|v_dec - v_th| + 1)^2), models/soda.py:146-158.

@@ -256,6 +256,27 @@ def golden_sli(ref):
     print("sli: max |v|", float(out.abs().max()), "saturated fraction", float((out.abs() > 1).float().mean()))
 
 
+def golden_synapse(ref):
+    """T = 10 steps of the reference's own synapse_feed_forward_step (models/modules/synapse.py:73-103) from p = 0,
+    without and with synaptic inhibition (sigma 0 / 0.7); inputs of both signs and exact zeros."""
+    import sys
+
+    syn = sys.modules["models.modules.synapse"]
+    torch.manual_seed(13)
+    x = torch.randn(10, 2, 6, 5, 4) * 1.5
+    x[x.abs() < 0.3] = 0.0
+    res = {"x": x.numpy()}
+    for tag, sigma in (("s0", 0.0), ("s07", 0.7)):
+        prm = syn.SynapseParameters(sigma_inhibition=torch.as_tensor(sigma))
+        state, outs = syn.SynapseState(p=torch.zeros_like(x[0])), []
+        for t in range(x.shape[0]):
+            out, state = syn.synapse_feed_forward_step(x[t], state, prm, 0.001)
+            outs.append(out)
+        res["out_" + tag], res["p_" + tag] = torch.stack(outs).numpy(), state.p.numpy()
+    np.savez_compressed(os.path.join(OUT, "synapse.npz"), **res)
+    print("synapse: mean out", float(res["out_s0"].mean()), float(res["out_s07"].mean()))
+
+
 def main():
     os.makedirs(OUT, exist_ok=True)
     ref = load_reference()
@@ -263,6 +284,7 @@ def main():
     golden_box(ref)
     golden_roi(ref)
     golden_sli(ref)
+    golden_synapse(ref)
     golden_vgg(ref)
     golden_tiny_yolo(ref)
 

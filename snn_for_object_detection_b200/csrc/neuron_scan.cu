@@ -429,6 +429,60 @@ extern "C" int soda_li_fwd(const soda_neuron_params_t* p, const float* x, const 
                              stream, "li_fwd");
 }
 
+namespace soda {
+
+// Synaptic transmission model of the reference's own models/modules/synapse.py:73-103 (synapse_feed_forward_step):
+//   tau = x > 0 ? tau_secretion : tau_dissociation;  p' = p + ((x - p) * tau) * dt
+//   g = sigma != 0 ? (4 * sigma) * (p' - sigma * p'^2) : p';  out = max(g, 0)          one state (p) per synapse
+template <int V>
+__global__ void __launch_bounds__(256)
+synapse_fwd_kernel(float tau_sec, float tau_dis, float sigma, float dt, const float* __restrict__ x,
+                   const float* __restrict__ p0, int T, int64_t n, float* __restrict__ out, float* __restrict__ p_out) {
+  pdl_trigger();
+  const int64_t e = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) * V;
+  if (e >= n) return;
+  float p[V];
+  if (p0 != nullptr) {
+    vload<V>(p, p0 + e);
+  } else {
+#pragma unroll
+    for (int k = 0; k < V; ++k) p[k] = 0.0f;
+  }
+  const float s4 = __fmul_rn(4.0f, sigma);
+  for (int t = 0; t < T; ++t) {
+    float xs[V], o[V];
+    vload<V>(xs, x + (int64_t)t * n + e);
+#pragma unroll
+    for (int k = 0; k < V; ++k) {
+      const float tau = xs[k] > 0.0f ? tau_sec : tau_dis;
+      p[k] = __fadd_rn(p[k], __fmul_rn(__fmul_rn(__fsub_rn(xs[k], p[k]), tau), dt));
+      const float g = sigma != 0.0f ? __fmul_rn(s4, __fsub_rn(p[k], __fmul_rn(sigma, __fmul_rn(p[k], p[k])))) : p[k];
+      o[k] = fmaxf(g, 0.0f);
+    }
+    vstore<V>(out + (int64_t)t * n + e, o);
+  }
+  vstore<V>(p_out + e, p);
+}
+
+}  // namespace soda
+
+extern "C" int soda_synapse_fwd(float tau_secretion, float tau_dissociation, float sigma_inhibition, float dt,
+                                const float* x, const float* p0, int T, int64_t n, float* out, float* p_out,
+                                void* stream) {
+  using namespace soda;
+  if (!x || !out || !p_out) return fail(SODA_ERR_BAD_ARG, "synapse_fwd: null pointer");
+  if (T <= 0 || n <= 0) return fail(SODA_ERR_BAD_ARG, "synapse_fwd: non-positive size");
+  cudaStream_t st = (cudaStream_t)stream;
+  if (n % 4 == 0 && all_aligned16({x, p0, out, p_out})) {
+    synapse_fwd_kernel<4><<<(unsigned)ceil_div(n / 4, 256), 256, 0, st>>>(tau_secretion, tau_dissociation,
+                                                                         sigma_inhibition, dt, x, p0, T, n, out, p_out);
+  } else {
+    synapse_fwd_kernel<1><<<(unsigned)ceil_div(n, 256), 256, 0, st>>>(tau_secretion, tau_dissociation, sigma_inhibition,
+                                                                     dt, x, p0, T, n, out, p_out);
+  }
+  return after_launch("synapse_fwd");
+}
+
 extern "C" int soda_sli_fwd(const soda_neuron_params_t* p, const float* x, const float* v0, const float* i0, int T,
                             int64_t n, float* out, float* v_out, float* i_out, float* i_trace, void* stream) {
   return soda::launch_fwd<3>(p, x, v0, i0, T, n, out, v_out, i_out, nullptr, nullptr, i_trace, stream, "sli_fwd");

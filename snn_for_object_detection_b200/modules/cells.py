@@ -19,7 +19,7 @@ from .. import ops
 from ..ops import NeuronConst
 
 __all__ = ["LIFParameters", "LIParameters", "LIFFeedForwardState", "LIState", "SNNCell", "LIFCell", "LICell",
-           "SLIParameters", "SLIState", "SLICell"]
+           "SLIParameters", "SLIState", "SLICell", "SynapseParameters", "SynapseState", "SynapseCell"]
 
 
 class LIFParameters(NamedTuple):
@@ -50,6 +50,18 @@ class SLIParameters(NamedTuple):
 class SLIState(NamedTuple):
     v: torch.Tensor
     i: torch.Tensor
+
+
+class SynapseParameters(NamedTuple):
+    """Parameters of the synapse model (reference ``models/modules/synapse.py:22-33``)."""
+
+    tau_med_secretion: float = 1.0 / 1e-3
+    tau_med_dissociation: float = 1.0 / 5e-3
+    sigma_inhibition: float = 0.0
+
+
+class SynapseState(NamedTuple):
+    p: torch.Tensor
 
 
 class LIFFeedForwardState(NamedTuple):
@@ -207,3 +219,36 @@ class SLICell(SNNCell):
             i = i_jump + (-c.dt_tau_syn) * i_jump
             outs.append(v)
         return (outs[0] if T == 1 else torch.cat(outs)), SLIState(v, i)
+
+
+class SynapseCell(SNNCell):
+    """Synaptic transmission cell of the reference (``models/modules/synapse.py:36-103``); returns
+    ``(g, SynapseState(p))``.  Inference: one CUDA scan over all T steps (``soda_synapse_fwd``); when a graph is being
+    recorded: the reference's own expression step by step in torch ops (differentiable)."""
+
+    def __init__(self, p: SynapseParameters = SynapseParameters(), dt: float = 0.001, **kwargs):
+        nn.Module.__init__(self)
+        if p.sigma_inhibition != 0 and p.sigma_inhibition < 0.5:
+            raise ValueError("Valid values for sigma_inhibition are 0 or >= 0.5, but received ", p.sigma_inhibition)
+        self.p, self.dt = p, dt
+        self._c = tuple(_f32(v) for v in (p.tau_med_secretion, p.tau_med_dissociation, p.sigma_inhibition, dt))
+
+    def forward_seq(self, x, T, state=None, want_trace=False):
+        p0 = None if state is None else state.p
+        if torch.is_grad_enabled() and (x.requires_grad or (p0 is not None and p0.requires_grad)):
+            return self._forward_torch(x, T, p0)
+        out, p = ops.synapse_scan(x, T, p0, *self._c)
+        return out, SynapseState(p)
+
+    def _forward_torch(self, x, T, p0):
+        B = x.shape[0] // T
+        ts, td, sg, dt = self._c
+        p = torch.zeros_like(x[:B]) if p0 is None else p0
+        outs = []
+        for t in range(T):
+            xt = x[t * B : (t + 1) * B]
+            tau = torch.where(xt > 0, torch.full_like(xt, ts), torch.full_like(xt, td))
+            p = p + (xt - p) * tau * dt
+            g = 4 * sg * (p - sg * p.square()) if sg != 0 else p
+            outs.append(g.clamp(0.0))
+        return (outs[0] if T == 1 else torch.cat(outs)), SynapseState(p)

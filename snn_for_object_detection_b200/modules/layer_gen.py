@@ -11,7 +11,7 @@ from typing import Optional, Tuple
 
 from torch import nn
 
-from .cells import LICell, LIFCell, SLICell, SNNCell
+from .cells import LICell, LIFCell, SLICell, SNNCell, SynapseCell
 from .common import SodaBatchNorm2d, SodaConv2d, SodaPool2d, StateStorage, Storage, SumPool2d
 
 layers_list = (
@@ -140,7 +140,7 @@ class Return(LayerGen):
 
 
 class _OutOfScope(LayerGen):
-    """LSTM / Synapse: experimental reference layers that no shipped net uses.
+    """LSTM: experimental reference layer that no shipped net uses.
 
     They are outside this package's hot path; constructing one raises so that the gap is loud."""
 
@@ -159,8 +159,11 @@ class LSTM(_OutOfScope):
     _name = "LSTM"
 
 
-class Synapse(_OutOfScope):
-    _name = "Synapse"
+class Synapse(LayerGen):
+    """Synaptic transmission layer (reference ``models/modules/layer_gen.py:321-328``) on ``soda_synapse_fwd``."""
+
+    def get(self, in_channels: int) -> Tuple[SNNCell, int]:
+        return SynapseCell(), in_channels
 
 
 class SLI(LayerGen):

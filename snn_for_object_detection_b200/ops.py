@@ -642,6 +642,25 @@ def sli_scan(x: torch.Tensor, T: int, v0: Optional[torch.Tensor] = None, i0: Opt
     return out, v, i, it
 
 
+@_prof("li_scan")
+def synapse_scan(x: torch.Tensor, T: int, p0: Optional[torch.Tensor], tau_secretion: float, tau_dissociation: float,
+                 sigma_inhibition: float, dt: float):
+    """T steps of the reference's synaptic transmission model (``models/modules/synapse.py:73-103``).
+    Returns ``(g per step, p_T)``."""
+    _need_cuda(x, p0)
+    x, n = _flat_T(x, T)
+    out = torch.empty_like(x)
+    p = torch.empty_like(x[: x.shape[0] // T])
+    if p0 is not None:
+        p0 = _like_block(p0, p)
+    check(
+        lib.soda_synapse_fwd(float(tau_secretion), float(tau_dissociation), float(sigma_inhibition), float(dt),
+                             x.data_ptr(), _ptr(p0), T, n, out.data_ptr(), p.data_ptr(), _stream()),
+        "soda_synapse_fwd",
+    )
+    return out, p
+
+
 def lif_scan_bwd(grad_out, grad_vT, grad_iT, v_dec, T: int, p: NeuronConst = LIF_DEFAULT):
     """Fused reverse scan: returns ``(grad_x, grad_v0, grad_i0)``."""
     _need_cuda(grad_out, grad_vT, grad_iT, v_dec)

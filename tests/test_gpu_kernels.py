@@ -724,3 +724,31 @@ def test_sli_scan_matches_reference_golden_and_carries_state():
     assert float((og.detach() - out).abs().max()) < 2e-6 * scale
     og.sum().backward()
     assert float(xg.grad.abs().sum()) > 0
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("tag,sigma", [("s0", 0.0), ("s07", 0.7)])
+def test_synapse_scan_matches_reference_golden_bit_exact(tag, sigma):
+    """soda_synapse_fwd against the reference's own synapse_feed_forward_step (tests/golden/synapse.npz): only
+    round-to-nearest adds / multiplies and a compare, so bit-exact; carried state; the differentiable torch route."""
+    from snn_for_object_detection_b200.modules.cells import SynapseCell, SynapseParameters
+
+    g = golden("synapse.npz")
+    x = torch.from_numpy(g["x"])
+    T, B = x.shape[:2]
+    xd = x.reshape(T * B, *x.shape[2:]).to(DEV)
+    cell = SynapseCell(SynapseParameters(sigma_inhibition=sigma))
+    with torch.no_grad():
+        out, st = cell.forward_seq(xd, T)
+        o1, s1 = cell.forward_seq(xd[: 4 * B], 4)
+        o2, s2 = cell.forward_seq(xd[4 * B:], T - 4, s1)
+    assert torch.equal(out.cpu().reshape(x.shape), torch.from_numpy(g["out_" + tag]))
+    assert torch.equal(st.p.cpu(), torch.from_numpy(g["p_" + tag]))
+    assert torch.equal(torch.cat([o1, o2]), out) and torch.equal(s2.p, st.p)
+    xg = xd.clone().requires_grad_(True)
+    og, _ = cell.forward_seq(xg, T)
+    assert float((og.detach() - out).abs().max()) < 1e-6
+    og.sum().backward()
+    assert float(xg.grad.abs().sum()) > 0
+    with pytest.raises(ValueError):
+        SynapseCell(SynapseParameters(sigma_inhibition=0.3))

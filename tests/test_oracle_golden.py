@@ -155,3 +155,15 @@ def test_sli_restatement_matches_reference_golden():
     assert torch.equal(out, torch.from_numpy(g["out"]))
     assert torch.equal(v, torch.from_numpy(g["v"])) and torch.equal(i, torch.from_numpy(g["i"]))
     assert float((out.abs() > 1).float().mean()) > 0.2   # the saturation branch is exercised
+
+
+def test_synapse_restatement_matches_reference_golden():
+    """oracle/synapse_restated.py against outputs of the reference's OWN synapse_feed_forward_step
+    (models/modules/synapse.py), bit for bit, with and without synaptic inhibition."""
+    from oracle import synapse_restated as sr
+
+    g = golden("synapse.npz")
+    for tag, sigma in (("s0", 0.0), ("s07", 0.7)):
+        out, p = sr.synapse_scan(torch.from_numpy(g["x"]), sigma_inhibition=sigma)
+        assert torch.equal(out, torch.from_numpy(g["out_" + tag])) and torch.equal(p, torch.from_numpy(g["p_" + tag]))
+        assert float(out.mean()) > 0.01
