@@ -221,6 +221,14 @@ SODA_API int soda_sli_fwd(const soda_neuron_params_t* p, const float* x, const f
 SODA_API int soda_synapse_fwd(float tau_secretion, float tau_dissociation, float sigma_inhibition, float dt,
                      const float* x, const float* p0, int T, int64_t n, float* out, float* p_out, void* stream);
 
+/* ConvLSTM gates (LayerGen LSTM): the elementwise part of the reference's models/modules/conv_lstm.py:62-75 after the
+ * gate convolution (which runs on soda_conv2d_fwd: the input part W_x * X for all T steps at once, the recurrent part
+ * W_h * h per step with the input part as the fused residual):
+ *   pre    : [n_pix, 4 * hidden] pixel-major conv output, channel blocks (input | forget | out gate | in node)
+ *   c_prev : [n_pix, hidden] or NULL (zeros);  c' = sigmoid(f) * c + sigmoid(i) * tanh(g);  h' = sigmoid(o) * tanh(c') */
+SODA_API int soda_lstm_gates(const float* pre, const float* c_prev, int64_t n_pix, int hidden, float* h_out, float* c_out,
+                    void* stream);
+
 /* Surrogate-gradient LIF backward (K8): fused reverse scan over T.
  *   replaces: autograd through T calls of LIFCell incl. norse SuperSpike.backward
  *             (g / (alpha*|v_dec - v_th| + 1)^2), models/soda.py:146-158.

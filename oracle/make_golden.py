@@ -277,6 +277,26 @@ def golden_synapse(ref):
     print("synapse: mean out", float(res["out_s0"].mean()), float(res["out_s07"].mean()))
 
 
+def golden_conv_lstm(ref):
+    """T = 5 steps of the reference's own ConvLSTM (models/modules/conv_lstm.py) with seeded weights, from the zero
+    state; weights stored so the GPU module can load them."""
+    import sys
+
+    cl = sys.modules["models.modules.conv_lstm"]
+    torch.manual_seed(17)
+    m = cl.ConvLSTM(8, 16)
+    torch.nn.init.normal_(m.conv.weight, std=0.6)
+    x = torch.randn(5, 2, 8, 6, 7)
+    state, outs = None, []
+    with torch.no_grad():
+        for t in range(x.shape[0]):
+            y, state = m(x[t], state)
+            outs.append(y)
+    np.savez_compressed(os.path.join(OUT, "conv_lstm.npz"), x=x.numpy(), weight=m.conv.weight.detach().numpy(),
+                        out=torch.stack(outs).numpy(), h=state[0].numpy(), c=state[1].numpy())
+    print("conv_lstm: out std", float(torch.stack(outs).std()))
+
+
 def main():
     os.makedirs(OUT, exist_ok=True)
     ref = load_reference()
@@ -285,6 +305,7 @@ def main():
     golden_roi(ref)
     golden_sli(ref)
     golden_synapse(ref)
+    golden_conv_lstm(ref)
     golden_vgg(ref)
     golden_tiny_yolo(ref)
 

@@ -179,3 +179,49 @@ extern "C" int soda_add_n(const float* const* xs, int k, int64_t n, float* y, vo
   else add_n_kernel<1><<<grid_for(n), 256, 0, st>>>(ap, k, n, y);
   return after_launch("add_n_kernel");
 }
+
+// ConvLSTM gates (reference models/modules/conv_lstm.py:62-75): pre [N, H, W, 4*hid] pixel-major holds the conv output
+// (input | forget | out gate | in node, each hid channels);  c' = sigmoid(f) * c + sigmoid(i) * tanh(g),
+// h' = sigmoid(o) * tanh(c').  One thread = 4 channels of one pixel.
+namespace soda {
+__device__ __forceinline__ float sigmoidf_(float z) { return __fdiv_rn(1.0f, __fadd_rn(1.0f, expf(-z))); }
+
+__global__ void __launch_bounds__(256)
+lstm_gate_kernel(const float* __restrict__ pre, const float* __restrict__ c_prev, int64_t n_pix, int hid,
+                 float* __restrict__ h_out, float* __restrict__ c_out) {
+  pdl_trigger();
+  const int h4 = hid >> 2;
+  const int64_t total = n_pix * h4;
+  for (int64_t idx = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; idx < total; idx += (int64_t)gridDim.x * blockDim.x) {
+    const int64_t pix = idx / h4;
+    const int cg = (int)(idx % h4);
+    const float4* row = reinterpret_cast<const float4*>(pre + pix * 4 * hid);
+    const float4 gi = __ldg(row + cg), gf = __ldg(row + h4 + cg), go = __ldg(row + 2 * h4 + cg), gg = __ldg(row + 3 * h4 + cg);
+    float4 c = make_float4(0.f, 0.f, 0.f, 0.f);
+    if (c_prev != nullptr) c = __ldg(reinterpret_cast<const float4*>(c_prev + pix * hid) + cg);
+    float4 cn, hn;
+    cn.x = __fadd_rn(__fmul_rn(sigmoidf_(gf.x), c.x), __fmul_rn(sigmoidf_(gi.x), tanhf(gg.x)));
+    cn.y = __fadd_rn(__fmul_rn(sigmoidf_(gf.y), c.y), __fmul_rn(sigmoidf_(gi.y), tanhf(gg.y)));
+    cn.z = __fadd_rn(__fmul_rn(sigmoidf_(gf.z), c.z), __fmul_rn(sigmoidf_(gi.z), tanhf(gg.z)));
+    cn.w = __fadd_rn(__fmul_rn(sigmoidf_(gf.w), c.w), __fmul_rn(sigmoidf_(gi.w), tanhf(gg.w)));
+    hn.x = __fmul_rn(sigmoidf_(go.x), tanhf(cn.x)), hn.y = __fmul_rn(sigmoidf_(go.y), tanhf(cn.y));
+    hn.z = __fmul_rn(sigmoidf_(go.z), tanhf(cn.z)), hn.w = __fmul_rn(sigmoidf_(go.w), tanhf(cn.w));
+    reinterpret_cast<float4*>(c_out + pix * hid)[cg] = cn;
+    reinterpret_cast<float4*>(h_out + pix * hid)[cg] = hn;
+  }
+}
+}  // namespace soda
+
+extern "C" int soda_lstm_gates(const float* pre, const float* c_prev, int64_t n_pix, int hidden, float* h_out,
+                               float* c_out, void* stream) {
+  using namespace soda;
+  if (!pre || !h_out || !c_out) return fail(SODA_ERR_BAD_ARG, "lstm_gates: null pointer");
+  if (n_pix <= 0 || hidden <= 0) return fail(SODA_ERR_BAD_ARG, "lstm_gates: non-positive size");
+  if (hidden % 4 != 0 || (reinterpret_cast<uintptr_t>(pre) & 15) || (reinterpret_cast<uintptr_t>(h_out) & 15) ||
+      (reinterpret_cast<uintptr_t>(c_out) & 15) || (reinterpret_cast<uintptr_t>(c_prev) & 15))
+    return fail(SODA_ERR_UNSUPPORTED, "lstm_gates: hidden % 4 == 0 and 16-byte aligned buffers");
+  const int64_t total = n_pix * (hidden / 4);
+  const int grid = (int)std::min<int64_t>((total + 255) / 256, (int64_t)kNumSMs * 16);
+  lstm_gate_kernel<<<grid, 256, 0, (cudaStream_t)stream>>>(pre, c_prev, n_pix, hidden, h_out, c_out);
+  return after_launch("lstm_gate_kernel");
+}

@@ -26,6 +26,7 @@ from . import _lib, ops
 from .modules import *  # noqa: F401,F403
 from .modules.cells import LICell, LIFCell, LIFFeedForwardState, SNNCell
 from .modules.common import SodaBatchNorm2d, SodaConv2d, SodaPool2d, StateStorage, Storage, SumPool2d
+from .modules.conv_lstm import ConvLSTM
 from .modules.layer_gen import Dense, LayerGen, Residual, Return
 from .utils.anchors import AnchorGenerator
 
@@ -358,6 +359,10 @@ class BlockGen(nn.Module):
                 continue
             if isinstance(layer, SodaBatchNorm2d):
                 Y = layer.forward_seq(Y, T)
+                idx += 1
+                continue
+            if isinstance(layer, ConvLSTM):
+                Y, branch_state[idx] = layer.forward_seq(Y, T, branch_state[idx])
                 idx += 1
                 continue
             if flags[idx]:

@@ -12,6 +12,7 @@ from typing import Optional, Tuple
 from torch import nn
 
 from .cells import LICell, LIFCell, SLICell, SNNCell, SynapseCell
+from .conv_lstm import ConvLSTM
 from .common import SodaBatchNorm2d, SodaConv2d, SodaPool2d, StateStorage, Storage, SumPool2d
 
 layers_list = (
@@ -139,24 +140,15 @@ class Return(LayerGen):
         return Storage(), in_channels
 
 
-class _OutOfScope(LayerGen):
-    """LSTM: experimental reference layer that no shipped net uses.
+class LSTM(LayerGen):
+    """ConvLSTM layer (reference ``models/modules/layer_gen.py:287-302``)."""
 
-    They are outside this package's hot path; constructing one raises so that the gap is loud."""
+    def __init__(self, hidden_size: Optional[int] = None):
+        self.hidden_size = hidden_size
 
-    _name = "?"
-
-    def __init__(self, *a, **k):
-        pass
-
-    def get(self, in_channels: int):
-        raise NotImplementedError(
-            f"{self._name}: not part of the SODa spiking forward hot path; no sm_100a kernel in this build"
-        )
-
-
-class LSTM(_OutOfScope):
-    _name = "LSTM"
+    def get(self, in_channels: int) -> Tuple[nn.Module, int]:
+        h_size = in_channels if self.hidden_size is None else self.hidden_size
+        return ConvLSTM(in_channels, h_size), h_size
 
 
 class Synapse(LayerGen):

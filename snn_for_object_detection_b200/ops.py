@@ -661,6 +661,24 @@ def synapse_scan(x: torch.Tensor, T: int, p0: Optional[torch.Tensor], tau_secret
     return out, p
 
 
+@_prof("lstm_gates")
+def lstm_gates(pre: torch.Tensor, c_prev: Optional[torch.Tensor]) -> Tuple[torch.Tensor, torch.Tensor]:
+    """``(h', c')`` from the gate pre-activations ``pre [B, 4*hid, H, W]`` (pixel-major) and ``c_prev [B, hid, H, W]``
+    (reference ``models/modules/conv_lstm.py:62-75``)."""
+    _need_cuda(pre, c_prev)
+    if not pre.is_contiguous(memory_format=torch.channels_last):
+        pre = pre.contiguous(memory_format=torch.channels_last)
+    B, C4, H, W = pre.shape
+    hid = C4 // 4
+    h = empty_pixel_major(B, hid, H, W, pre.device)
+    c = empty_pixel_major(B, hid, H, W, pre.device)
+    if c_prev is not None and not c_prev.is_contiguous(memory_format=torch.channels_last):
+        c_prev = c_prev.contiguous(memory_format=torch.channels_last)
+    check(lib.soda_lstm_gates(pre.data_ptr(), _ptr(c_prev), B * H * W, hid, h.data_ptr(), c.data_ptr(), _stream()),
+          "soda_lstm_gates")
+    return h, c
+
+
 def lif_scan_bwd(grad_out, grad_vT, grad_iT, v_dec, T: int, p: NeuronConst = LIF_DEFAULT):
     """Fused reverse scan: returns ``(grad_x, grad_v0, grad_i0)``."""
     _need_cuda(grad_out, grad_vT, grad_iT, v_dec)

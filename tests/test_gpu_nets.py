@@ -8,7 +8,7 @@ import pytest
 import torch
 import torch.nn.functional as F
 
-from helpers import calibrated_tiny_yolo, tiny_yolo_from_golden, vgg_block_from_golden
+from helpers import golden, calibrated_tiny_yolo, tiny_yolo_from_golden, vgg_block_from_golden
 from oracle import net_restated as onr
 
 pytestmark = pytest.mark.gpu
@@ -458,3 +458,43 @@ def test_generated_net_with_sli_layers_matches_time_major_oracle():
         c2 = block.net[0][3](v1, norm=block.net[0][4])
     want, _, _ = sr.sli_scan(c2.cpu().reshape(T, B, *c2.shape[1:]))
     assert float((Y.cpu().reshape(want.shape) - want).abs().max()) < 5e-6 * max(1.0, float(want.abs().max()))
+
+
+@pytest.mark.gpu
+def test_conv_lstm_matches_reference_golden_and_protocols():
+    """LayerGen LSTM: our ConvLSTM (input part of the gate conv for all T at once, recurrent part per step with the
+    input part as fused residual, gate kernel) against the reference's OWN ConvLSTM (tests/golden/conv_lstm.npz),
+    same state_dict key; layer-major == per-step protocol; inside a generated block; training route in torch ops."""
+    from snn_for_object_detection_b200 import BlockGen
+    from snn_for_object_detection_b200.modules.conv_lstm import ConvLSTM
+    from snn_for_object_detection_b200.modules.layer_gen import LSTM, Conv, Norm
+
+    g = golden("conv_lstm.npz")
+    x = torch.from_numpy(g["x"])
+    T, B = x.shape[:2]
+    m = ConvLSTM(8, 16)
+    m.load_state_dict({"conv.weight": torch.from_numpy(g["weight"])}, strict=True)
+    m = m.to(DEV).eval()
+    xd = x.reshape(T * B, *x.shape[2:]).to(DEV)
+    with torch.no_grad():
+        out, (h, c) = m.forward_seq(xd, T)
+        ys, st = [], None
+        for t in range(T):
+            y, st = m(xd[t * B:(t + 1) * B], st)
+            ys.append(y)
+    want = torch.from_numpy(g["out"]).reshape(T * B, 16, *x.shape[3:])
+    assert float((out.cpu() - want).abs().max()) < 5e-6          # fp32 conv order + expf / tanhf vs ATen
+    assert float((h.cpu() - torch.from_numpy(g["h"])).abs().max()) < 5e-6
+    assert float((c.cpu() - torch.from_numpy(g["c"])).abs().max()) < 5e-6
+    assert torch.equal(torch.cat(ys), out)
+    og, _ = m.forward_seq(xd.clone().requires_grad_(True), T)      # training route
+    assert float((og.detach() - out).abs().max()) < 5e-3           # torch's conv runs cuDNN TF32 here
+    block = BlockGen(2, [Conv(32, kernel_size=3), Norm(), LSTM(32), Conv(16, kernel_size=1)]).to(DEV).eval()
+    X = (torch.rand(4 * 2, 2, 12, 16, device=DEV) < 0.3).float()
+    with torch.no_grad():
+        Y, state = block.forward_seq(X, 4)
+        ys, st = [], None
+        for t in range(4):
+            y, st = block(X[t * 2:(t + 1) * 2], st)
+            ys.append(y)
+    assert Y.shape == (8, 16, 12, 16) and torch.equal(torch.cat(ys), Y)
