@@ -129,3 +129,92 @@ def events_to_frames(
     offs = sample_offsets.to(dev, non_blocking=True)
     t0 = t0_us.to(dev, non_blocking=True)
     return ops.bin_events(ev, offs, t0, step_us, T, H, W, clip_x=clip_x, sorted_by_time=sorted_by_time, out=out)
+
+
+class STSampleStream:
+    """Feature half of the reference's single-target dataset (``utils/datasets.py:346-435``) over several recordings,
+    ending on the device: per recording the next labelled window is located exactly as ``STPropheseeDataset.parse_data``
+    does (``:378-420``), the raw 8-byte records of that window are sliced out of the memory-mapped file (no decode on the
+    host), staged in one of two pinned buffers and binned on the GPU (``soda_bin_events``) into ``X[T, B, 2, H, W]``.
+
+    Label parsing stays with the caller (out of scope): ``label_steps[k]`` is the sorted list of time-step indices of
+    recording ``k`` that carry at least one box passing the reference's size filter (``:392-399``).
+
+    ``next_window(k)`` mirrors ``parse_data``'s control flow and returns ``(window | None, alive)``:
+    ``(None, False)`` recording exhausted / no label left, ``(None, True)`` window skipped because it holds fewer than
+    ``events_threshold`` events per step (``:417-418``), else ``((records, first_event_time_us, label_step), True)``."""
+
+    def __init__(self, sources: Sequence[Union[str, bytes, np.ndarray]], label_steps: Sequence[Sequence[int]],
+                 num_steps: int, time_shift: int, time_step_ms: int, height: int, width: int,
+                 events_threshold: int = 4000, device: Union[str, torch.device] = "cuda"):
+        if len(sources) != len(label_steps):
+            raise ValueError("one label-step list per recording")
+        self.readers = [DatReader(s) for s in sources]
+        self.label_steps = [np.asarray(sorted(int(v) for v in ls), dtype=np.int64) for ls in label_steps]
+        self.num_steps, self.time_shift = int(num_steps), int(time_shift)
+        self.step_us = int(time_step_ms) * 1000
+        self.height, self.width = int(height), int(width)
+        self.events_threshold = int(events_threshold)
+        self.device = torch.device(device)
+        self.alive = [True] * len(self.readers)
+        self._stage = [None, None]   # two pinned staging buffers, used alternately
+        self._flip = 0
+
+    def next_window(self, k: int):
+        rd, steps = self.readers[k], self.label_steps[k]
+        if rd.done:
+            return None, False
+        start_time_us = rd.current_time
+        start_step = start_time_us // self.step_us
+        j = int(np.searchsorted(steps, start_step + self.num_steps, side="left"))
+        if j >= steps.shape[0]:
+            return None, False
+        label_step = int(steps[j])
+        first_label_time_us = label_step * self.step_us
+        first_event_time_us = first_label_time_us - self.step_us * (self.num_steps - self.time_shift)
+        rec = rd.load_delta_t(first_label_time_us + self.step_us * self.time_shift - start_time_us)
+        lo = int(np.searchsorted(rec[:, 0], first_event_time_us, side="left")) if first_event_time_us > 0 else 0
+        rec = rec[lo:]
+        if (rec.shape[0] // self.num_steps) < self.events_threshold:
+            return None, True
+        return (rec, first_event_time_us, label_step), True
+
+    def _pinned(self, n_rec: int) -> torch.Tensor:
+        buf = self._stage[self._flip]
+        if buf is None or buf.shape[0] < n_rec:
+            buf = torch.empty((max(n_rec, 1) * 5 // 4 + 1, 2), dtype=torch.int32)
+            if torch.cuda.is_available():
+                buf = buf.pin_memory()
+            self._stage[self._flip] = buf
+        self._flip ^= 1
+        return buf
+
+    def next_batch(self, batch_size: int):
+        """Up to ``batch_size`` accepted windows, visiting the live recordings round-robin (the reference's
+        ``samples_generator`` without its shuffle).  Returns ``(X[T, B, 2, H, W] on the device, label_steps, recording
+        indices)`` or ``None`` when every recording is exhausted."""
+        picked = []
+        while len(picked) < batch_size and any(self.alive):
+            progressed = False
+            for k in range(len(self.readers)):
+                if not self.alive[k] or len(picked) >= batch_size:
+                    continue
+                win, self.alive[k] = self.next_window(k)
+                progressed = True
+                if win is not None:
+                    picked.append((k,) + win)
+            if not progressed:
+                break
+        if not picked:
+            return None
+        counts = [int(p[1].shape[0]) for p in picked]
+        offs = np.zeros(len(picked) + 1, dtype=np.int64)
+        np.cumsum(counts, out=offs[1:])
+        buf = self._pinned(int(offs[-1]))
+        view = buf.numpy().view(np.uint32)
+        for p, a, b in zip(picked, offs[:-1], offs[1:]):
+            view[a:b] = p[1]
+        frames = events_to_frames(buf[: max(int(offs[-1]), 1)], torch.from_numpy(offs), [p[2] for p in picked],
+                                  self.step_us, self.num_steps, self.height, self.width, clip_x=True,
+                                  device=self.device)
+        return frames, [p[3] for p in picked], [p[0] for p in picked]

@@ -752,3 +752,27 @@ def test_synapse_scan_matches_reference_golden_bit_exact(tag, sigma):
     assert float(xg.grad.abs().sum()) > 0
     with pytest.raises(ValueError):
         SynapseCell(SynapseParameters(sigma_inhibition=0.3))
+
+
+@pytest.mark.gpu
+def test_st_sample_stream_batches_to_device_frames():
+    """events.STSampleStream.next_batch: two recordings, windows located as the reference's parse_data does, raw records
+    staged through pinned memory and binned on the GPU: the golden recording's frames equal the reference's own
+    features bit for bit, the second sample equals the oracle; exhausted recordings end the stream."""
+    from snn_for_object_detection_b200.events import STSampleStream
+
+    g = golden("binning_st.npz")
+    T, H, W, step_us = int(g["T"]), int(g["H"]), int(g["W"]), int(g["step_us"])
+    rng = np.random.default_rng(9)
+    rec2 = ob.make_records(rng, 60000, 0, 12 * step_us, H, W)
+    st = STSampleStream([ob.dat_bytes(g["records"], H, W), ob.dat_bytes(rec2, H, W)], [[6], [5, 10]], num_steps=T,
+                        time_shift=1, time_step_ms=step_us // 1000, height=H, width=W, events_threshold=1000)
+    X, steps, files = st.next_batch(4)
+    assert X.shape == (T, 3, 2, H, W) and X.is_cuda and steps == [6, 5, 10] and files == [0, 1, 1]
+    want = np.unpackbits(g["features_bits"])[: T * 2 * H * W].reshape(T, 2, H, W)
+    assert np.array_equal(X[:, 0].cpu().numpy(), want)
+    for b, s in ((1, 5), (2, 10)):
+        t0 = s * step_us - step_us * (T - 1)
+        keep = (rec2[:, 0] >= t0) & (rec2[:, 0] < s * step_us + step_us)
+        assert np.array_equal(X[:, b].cpu().numpy(), ob.bin_st(rec2[keep], t0, step_us, T, H, W))
+    assert st.next_batch(4) is None and not any(st.alive)

@@ -1,5 +1,7 @@
 """CPU: the oracle restatements against the golden vectors produced by the reference's own Python
 (oracle/make_golden.py).  Bit-exact unless stated."""
+import os
+
 import numpy as np
 import pytest
 import torch
@@ -167,3 +169,69 @@ def test_synapse_restatement_matches_reference_golden():
         out, p = sr.synapse_scan(torch.from_numpy(g["x"]), sigma_inhibition=sigma)
         assert torch.equal(out, torch.from_numpy(g["out_" + tag])) and torch.equal(p, torch.from_numpy(g["p_" + tag]))
         assert float(out.mean()) > 0.01
+
+
+def test_st_sample_stream_window_selection_matches_reference_golden():
+    """events.STSampleStream.next_window against the reference's own STPropheseeDataset.parse_data golden
+    (binning_st.npz): same window start, same records, oracle binning of that window == the reference's features."""
+    from snn_for_object_detection_b200.events import STSampleStream
+
+    g = golden("binning_st.npz")
+    T, H, W, step_us = int(g["T"]), int(g["H"]), int(g["W"]), int(g["step_us"])
+    dat = ob.dat_bytes(g["records"], H, W)
+    st = STSampleStream([dat], [[6]], num_steps=T, time_shift=1, time_step_ms=step_us // 1000, height=H, width=W,
+                        device="cpu")
+    win, alive = st.next_window(0)
+    assert alive and win is not None
+    rec, t0, label_step = win
+    assert t0 == int(g["first_event_time_us"]) and label_step == 6
+    assert st.readers[0].current_time == int(g["load_until_us"])
+    want = np.unpackbits(g["features_bits"])[: T * 2 * H * W].reshape(T, 2, H, W).astype(np.float32)
+    assert np.array_equal(ob.bin_st(np.ascontiguousarray(rec), t0, step_us, T, H, W), want)
+    assert int(rec[0, 0]) >= t0 and int(rec[-1, 0]) < int(g["load_until_us"])
+    # no label far enough ahead any more -> recording dropped; a sparse window -> skipped but alive
+    assert st.next_window(0) == (None, False)
+    st2 = STSampleStream([dat], [[6]], num_steps=T, time_shift=1, time_step_ms=step_us // 1000, height=H, width=W,
+                         events_threshold=10 ** 6, device="cpu")
+    assert st2.next_window(0) == (None, True)
+
+
+def test_st_sample_stream_matches_live_reference_parse_data():
+    """Several recordings, several labels each: the sequence of (accepted / skipped / dropped) decisions and every
+    accepted window's features equal the live reference's parse_data (build container only)."""
+    import tempfile
+
+    from oracle import ref_shim
+    from snn_for_object_detection_b200.events import STSampleStream
+
+    if not ref_shim.reference_available():
+        pytest.skip("reference tree not present")
+    ref = ref_shim.load_reference()
+    H, W, T, step_ms, shift = 60, 80, 4, 16, 1
+    step_us = step_ms * 1000
+    rng = np.random.default_rng(77)
+    recs = [ob.make_records(rng, n, 0, 40 * step_us, H, W) for n in (90000, 30000)]
+    labels = [[6, 7, 15, 16, 30], [5, 22]]
+    with tempfile.TemporaryDirectory() as d:
+        paths = []
+        for k, r in enumerate(recs):
+            paths.append(os.path.join(d, f"r{k}_td.dat"))
+            with open(paths[-1], "wb") as f:
+                f.write(ob.dat_bytes(r, H, W))
+        ds = ref.datasets.STPropheseeDataset(num_steps=T, time_shift=shift, gt_files=[], data_files=[], time_step=step_ms,
+                                             num_load_file=1, name="gen1")
+        ds._height, ds._width = H, W
+        ds.events_threshold = 1500
+        st = STSampleStream(paths, labels, T, shift, step_ms, H, W, events_threshold=1500, device="cpu")
+        for k in range(2):
+            gt = torch.tensor([[float(s), 0.0, 0.1, 0.1, 0.6, 0.7] for s in labels[k]])
+            loader = ref.psee.PSEELoader(paths[k])
+            for _ in range(8):
+                data, ok = ds.parse_data(gt, loader)
+                win, alive = st.next_window(k)
+                assert alive == ok and (data is None) == (win is None)
+                if win is not None:
+                    rec, t0, _ = win
+                    assert np.array_equal(ob.bin_st(np.ascontiguousarray(rec), t0, step_us, T, H, W), data[0].numpy())
+                if not ok:
+                    break
