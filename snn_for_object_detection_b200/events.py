@@ -218,3 +218,42 @@ class STSampleStream:
                                   self.step_us, self.num_steps, self.height, self.width, clip_x=True,
                                   device=self.device)
         return frames, [p[3] for p in picked], [p[0] for p in picked]
+
+
+class MTSampleStream(STSampleStream):
+    """Feature half of the reference's multi-target dataset (``utils/datasets.py:311-336``): consecutive windows of
+    ``num_steps`` time steps per recording (a finished recording restarts, ``:321-322``), binned against
+    ``start_step * step_us`` without clipping x.  ``next_window(k)`` returns ``((records, t0_us, start_step), True)``."""
+
+    def __init__(self, sources, num_steps: int, time_step_ms: int, height: int, width: int,
+                 device: Union[str, torch.device] = "cuda"):
+        super().__init__(sources, [[] for _ in sources], num_steps, 0, time_step_ms, height, width, 0, device)
+
+    def next_window(self, k: int):
+        rd = self.readers[k]
+        if rd.done:
+            rd.reset()
+        start_step = rd.current_time // self.step_us
+        rec = rd.load_delta_t(self.num_steps * self.step_us)
+        return (rec, start_step * self.step_us, int(start_step)), True
+
+    def next_batch(self, batch_size: int):
+        """One window from each recording in turn until ``batch_size`` samples: ``(X[T, B, 2, H, W], start_steps,
+        recording indices)``."""
+        picked = []
+        k = 0
+        while len(picked) < batch_size and self.readers:
+            win, _ = self.next_window(k % len(self.readers))
+            picked.append((k % len(self.readers),) + win)
+            k += 1
+        counts = [int(p[1].shape[0]) for p in picked]
+        offs = np.zeros(len(picked) + 1, dtype=np.int64)
+        np.cumsum(counts, out=offs[1:])
+        buf = self._pinned(int(offs[-1]))
+        view = buf.numpy().view(np.uint32)
+        for p, a, b in zip(picked, offs[:-1], offs[1:]):
+            view[a:b] = p[1]
+        frames = events_to_frames(buf[: max(int(offs[-1]), 1)], torch.from_numpy(offs), [p[2] for p in picked],
+                                  self.step_us, self.num_steps, self.height, self.width, clip_x=False,
+                                  device=self.device)
+        return frames, [p[3] for p in picked], [p[0] for p in picked]

@@ -776,3 +776,21 @@ def test_st_sample_stream_batches_to_device_frames():
         keep = (rec2[:, 0] >= t0) & (rec2[:, 0] < s * step_us + step_us)
         assert np.array_equal(X[:, b].cpu().numpy(), ob.bin_st(rec2[keep], t0, step_us, T, H, W))
     assert st.next_batch(4) is None and not any(st.alive)
+
+
+@pytest.mark.gpu
+def test_mt_sample_stream_consecutive_windows_match_reference_golden():
+    """events.MTSampleStream: two consecutive windows of one recording == the reference's own
+    MTPropheseeDataset.parse_data called twice (binning_mt.npz), bit for bit; then the recording restarts."""
+    from snn_for_object_detection_b200.events import MTSampleStream
+
+    g = golden("binning_mt.npz")
+    T, H, W, step_us = int(g["T"]), int(g["H"]), int(g["W"]), int(g["step_us"])
+    ref = _unpack(g["features_bits"], (2, T, 2, H, W))
+    st = MTSampleStream([ob.dat_bytes(g["records"], H, W)], num_steps=T, time_step_ms=step_us // 1000, height=H, width=W)
+    X, starts, files = st.next_batch(2)
+    assert X.shape == (T, 2, 2, H, W) and starts == [0, T] and files == [0, 0]
+    assert np.array_equal(X[:, 0].cpu().numpy(), ref[0]) and np.array_equal(X[:, 1].cpu().numpy(), ref[1])
+    X2, starts2, _ = st.next_batch(1)
+    if st.readers[0].current_time == T * step_us:          # the recording ended after two windows: restarted
+        assert starts2 == [0] and np.array_equal(X2[:, 0].cpu().numpy(), ref[0])
