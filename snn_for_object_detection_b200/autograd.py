@@ -3,7 +3,8 @@
 What is hand-written for training this round: every convolution FORWARD, the LIF / LI forward scans and their fused
 surrogate-gradient REVERSE scans (``soda_lif_bwd`` / ``soda_li_bwd``, wired in ``modules/cells.py``), and train-mode
 BatchNorm forward and backward over all T steps (``soda_bn_train_fwd`` / ``soda_bn_train_bwd``).
-What is a library call, stated plainly: convolution dgrad / wgrad go through ``aten::convolution_backward``
+The data gradient of stride-1 convolutions runs on our forward kernel (flipped, transposed filter).
+What is a library call, stated plainly: stride-2 dgrad and every wgrad go through ``aten::convolution_backward``
 (cuDNN) - CUDA, not a CPU or silent fallback, and a next-round kernel.  Residual sums, concat stores
 and pooling use differentiable torch ops when a graph is being recorded.
 """
@@ -18,8 +19,13 @@ import torch.nn.functional as F
 from . import ops
 
 
+# SODA_DGRAD=0 sends every dgrad to cuDNN (A/B runs)
+_DGRAD_NATIVE = os.environ.get("SODA_DGRAD", "1") != "0"
+
+
 class _ConvFn(torch.autograd.Function):
-    """Forward: our sm_100a convolution.  Backward: cuDNN dgrad / wgrad (library)."""
+    """Forward: our sm_100a convolution.  Backward: dgrad of stride-1 layers on the same kernel (flipped, transposed
+    filter); stride-2 dgrad and every wgrad: cuDNN (library)."""
 
     @staticmethod
     def forward(ctx, x, weight, conv):
@@ -28,14 +34,27 @@ class _ConvFn(torch.autograd.Function):
         y = ops.conv2d(x, conv.packed(None, kind))
         ctx.save_for_backward(x, weight)
         ctx.stride, ctx.pad = s, k // 2
+        ctx.conv = conv
         return y
 
     @staticmethod
     def backward(ctx, gy):
         x, weight = ctx.saved_tensors
-        gx, gw, _ = torch.ops.aten.convolution_backward(
-            gy, x, weight, None, [ctx.stride] * 2, [ctx.pad] * 2, [1, 1], False, [0, 0], 1,
-            [ctx.needs_input_grad[0], ctx.needs_input_grad[1], False])
+        need_x, need_w = ctx.needs_input_grad[0], ctx.needs_input_grad[1]
+        gx = None
+        if need_x and ctx.stride == 1 and _DGRAD_NATIVE and weight.shape[0] % 32 == 0:
+            # dgrad of a stride-1 'same' convolution IS a convolution of gy with the spatially flipped, (Cout, Cin)-
+            # transposed filter: it runs on our own forward kernel (tcgen05, fp32-accurate operand scheme)
+            gx = ops.conv2d(gy if gy.is_contiguous(memory_format=torch.channels_last)
+                            else gy.contiguous(memory_format=torch.channels_last), ctx.conv.packed_dgrad())
+            need_x = False
+        if need_x or need_w:
+            gx2, gw, _ = torch.ops.aten.convolution_backward(
+                gy, x, weight, None, [ctx.stride] * 2, [ctx.pad] * 2, [1, 1], False, [0, 0], 1,
+                [need_x, need_w, False])
+            gx = gx if gx is not None else gx2
+        else:
+            gw = None
         return gx, gw, None
 
 

@@ -56,6 +56,17 @@ class SodaConv2d(nn.Conv2d):
             self._pack_cache[kind] = hit
         return hit[1]
 
+    def packed_dgrad(self) -> ops.PackedConv:
+        """Packed filter of the data-gradient convolution of a stride-1 layer: ``W'[ci, co, ky, kx] =
+        W[co, ci, k-1-ky, k-1-kx]`` (tensor-core kind), cached on the weight version."""
+        key = (self.weight.data_ptr(), self.weight._version, self.weight.device)
+        hit = self._pack_cache.get("dgrad")
+        if hit is None or hit[0] != key:
+            wt = self.weight.detach().flip(2, 3).transpose(0, 1).contiguous()
+            hit = (key, ops.pack_conv(wt, 1, None, None, _lib.SODA_CONV_TC))
+            self._pack_cache["dgrad"] = hit
+        return hit[1]
+
     def forward(self, x: torch.Tensor, norm: Optional["SodaBatchNorm2d"] = None, residual=None, out=None):
         if self.bias is not None or self.groups != 1 or self.dilation != (1, 1):
             raise NotImplementedError("SodaConv2d: bias / groups / dilation are not part of the reference path")
