@@ -316,6 +316,25 @@ SODA_API int soda_bn_train_bwd(const float* grad_y, const float* x, int T, int64
                                const float* save_mean, const float* save_invstd, float* grad_x, float* grad_gamma,
                                float* grad_beta, void* workspace, void* stream);
 
+/* Cross-rank (SyncBatchNorm, reference config.yaml:76) variant of the train-mode BatchNorm: statistics, then the
+ * caller all-reduces the sums over the ranks (the only exchange; [T][2][C] fp64), then normalise with the global sums.
+ *   soda_bn_train_stats        : sums[t][0][c] = sum x, sums[t][1][c] = sum x^2 of this rank (grad_y == NULL), or
+ *                                sum gy and sum gy * xhat (grad_y != NULL; needs save_mean / save_invstd)
+ *   soda_bn_train_fwd_from_sums: as soda_bn_train_fwd with the statistics taken from the (global) sums over n_total
+ *                                pixels per time step; running_var uses n_total / (n_total - 1)
+ *   soda_bn_train_bwd_from_sums: dx from the GLOBAL sums / n_total; grad_gamma / grad_beta from sums_local (this rank's
+ *                                sums before the all-reduce; NULL = the global ones) */
+SODA_API int soda_bn_train_stats(const float* x, const float* grad_y, const float* save_mean, const float* save_invstd,
+                        int T, int64_t n_pix, int C, double* sums, void* workspace, void* stream);
+SODA_API int soda_bn_train_fwd_from_sums(const float* x, const double* sums, int64_t n_total, int T, int64_t n_pix, int C,
+                                const float* gamma, const float* beta, float eps, float momentum, float* running_mean,
+                                float* running_var, float* y, float* save_mean, float* save_invstd, void* workspace,
+                                void* stream);
+SODA_API int soda_bn_train_bwd_from_sums(const float* grad_y, const float* x, const double* sums_global, int64_t n_total,
+                                const double* sums_local, int T, int64_t n_pix, int C, const float* gamma,
+                                const float* save_mean, const float* save_invstd, float* grad_x, float* grad_gamma,
+                                float* grad_beta, void* workspace, void* stream);
+
 #ifdef __cplusplus
 }
 #endif

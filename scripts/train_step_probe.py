@@ -24,6 +24,7 @@ ap.add_argument("--steps", type=int, default=3)
 ap.add_argument("--T", type=int, default=32)
 ap.add_argument("--batch", type=int, default=5)
 ap.add_argument("--hw", type=int, nargs=2, default=[240, 304])
+ap.add_argument("--sync-bn", action="store_true", help="SyncBatchNorm: per-step statistics over the global batch")
 args = ap.parse_args()
 
 rank, local, world = (int(os.environ.get(k, d)) for k, d in (("RANK", 0), ("LOCAL_RANK", 0), ("WORLD_SIZE", 1)))
@@ -36,6 +37,8 @@ model = pkg.TinyYolo(num_classes=2).to(dev).train()
 for m in model.modules():
     if isinstance(m, torch.nn.BatchNorm2d):
         m.weight.data.fill_(3.0)  # train-mode BN normalises per step, so gamma alone sets the firing rate
+if args.sync_bn:
+    sharding.convert_sync_batchnorm(model)
 opt = model.configure_optimizers()
 params = [p for p in model.parameters() if p.requires_grad]
 T, B, (H, W) = args.T, args.batch, args.hw
@@ -67,7 +70,7 @@ if world > 1:
     ms = float(t)
 gn = float(torch.sqrt(sum((p.grad.double() ** 2).sum() for p in params if p.grad is not None)))
 if rank == 0:
-    print(json.dumps({"what": "TinyYolo BPTT training step (detection loss on synthetic labels)", "n_gpus": world, "batch_per_gpu": B, "T": T,
+    print(json.dumps({"what": "TinyYolo BPTT training step (detection loss on synthetic labels)", "n_gpus": world, "sync_bn": bool(args.sync_bn), "batch_per_gpu": B, "T": T,
                       "hw": [H, W], "ms_per_step": ms, "frames_per_s": world * T * B / (ms * 1e-3),
                       "loss": float(loss), "grad_norm": gn,
                       "peak_mem_gb": torch.cuda.max_memory_allocated() / 2**30}))

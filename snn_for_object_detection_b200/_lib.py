@@ -92,6 +92,9 @@ SIGNATURES = {
     "soda_bn_train_workspace_bytes": (_i64, [_i, _i]),
     "soda_bn_train_fwd": (_i, [_vp, _i, _i64, _i, _vp, _vp, _f, _f, _vp, _vp, _vp, _vp, _vp, _vp, _vp]),
     "soda_bn_train_bwd": (_i, [_vp, _vp, _i, _i64, _i, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp]),
+    "soda_bn_train_stats": (_i, [_vp, _vp, _vp, _vp, _i, _i64, _i, _vp, _vp, _vp]),
+    "soda_bn_train_fwd_from_sums": (_i, [_vp, _vp, _i64, _i, _i64, _i, _vp, _vp, _f, _f, _vp, _vp, _vp, _vp, _vp, _vp, _vp]),
+    "soda_bn_train_bwd_from_sums": (_i, [_vp, _vp, _vp, _i64, _vp, _i, _i64, _i, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp]),
 }
 
 if not os.path.exists(LIB_PATH):

@@ -14,6 +14,7 @@ from __future__ import annotations
 import os
 
 import torch
+import torch.distributed as dist
 import torch.nn.functional as F
 
 from . import ops
@@ -70,13 +71,25 @@ def conv2d_autograd(conv, x, norm, residual, out):
     return y
 
 
+def _all_reduce_sums(sums: torch.Tensor) -> int:
+    """The SyncBatchNorm exchange: one all-reduce of the [T, 2, C] fp64 sums; returns the world size."""
+    dist.all_reduce(sums, op=dist.ReduceOp.SUM)
+    return dist.get_world_size()
+
+
 class _BNTrainFn(torch.autograd.Function):
     """Per-time-step train-mode BatchNorm on our kernels (soda_bn_train_fwd / soda_bn_train_bwd)."""
 
     @staticmethod
     def forward(ctx, x, gamma, beta, norm, T):
-        y, mean, invstd, xk = ops.bn_train_fwd(x, T, gamma, beta, norm.eps, norm.momentum, norm.running_mean,
-                                               norm.running_var)
+        ctx.sync = bool(getattr(norm, "sync", False)) and dist.is_available() and dist.is_initialized() \
+            and dist.get_world_size() > 1
+        if ctx.sync:
+            y, mean, invstd, xk, _ = ops.bn_train_fwd_sync(x, T, gamma, beta, norm.eps, norm.momentum,
+                                                           norm.running_mean, norm.running_var, _all_reduce_sums)
+        else:
+            y, mean, invstd, xk = ops.bn_train_fwd(x, T, gamma, beta, norm.eps, norm.momentum, norm.running_mean,
+                                                   norm.running_var)
         ctx.save_for_backward(xk, gamma, mean, invstd)
         ctx.T = T
         ctx.affine = gamma is not None
@@ -85,7 +98,11 @@ class _BNTrainFn(torch.autograd.Function):
     @staticmethod
     def backward(ctx, gy):
         xk, gamma, mean, invstd = ctx.saved_tensors
-        gx, gg, gb = ops.bn_train_bwd(gy, xk, ctx.T, gamma, mean, invstd, want_affine=ctx.affine)
+        if ctx.sync:
+            gx, gg, gb = ops.bn_train_bwd_sync(gy, xk, ctx.T, gamma, mean, invstd, _all_reduce_sums,
+                                               want_affine=ctx.affine)
+        else:
+            gx, gg, gb = ops.bn_train_bwd(gy, xk, ctx.T, gamma, mean, invstd, want_affine=ctx.affine)
         return gx, (gg if ctx.needs_input_grad[1] else None), (gb if ctx.needs_input_grad[2] else None), None, None
 
 

@@ -80,7 +80,8 @@ constexpr int BN_FT = 32;
 
 // forward: mean / invstd per (t, c), affine coefficients, running statistics chained over t
 __global__ void __launch_bounds__(32 * BN_FT)
-bn_finalize_fwd_kernel(const float* __restrict__ partial, int T, int S, int C, int64_t n_pix, float eps,
+bn_finalize_fwd_kernel(const float* __restrict__ partial, const double* __restrict__ sums /* [T][2][C] or NULL */,
+                       int T, int S, int C, int64_t n_pix, float eps,
                        float momentum, const float* __restrict__ gamma, const float* __restrict__ beta,
                        float* __restrict__ mean, float* __restrict__ invstd, float* __restrict__ scale,
                        float* __restrict__ shift, float* __restrict__ running_mean, float* __restrict__ running_var) {
@@ -95,9 +96,13 @@ bn_finalize_fwd_kernel(const float* __restrict__ partial, int T, int S, int C, i
     const int t = t0 + ty;
     if (live && t < T) {
       double s0 = 0.0, s1 = 0.0;
-      for (int s = 0; s < S; ++s) {
-        const float* p = partial + (((int64_t)t * S + s) * 2) * C;
-        s0 += (double)p[c], s1 += (double)p[C + c];
+      if (sums != nullptr) {
+        s0 = sums[((int64_t)t * 2) * C + c], s1 = sums[((int64_t)t * 2 + 1) * C + c];
+      } else {
+        for (int s = 0; s < S; ++s) {
+          const float* p = partial + (((int64_t)t * S + s) * 2) * C;
+          s0 += (double)p[c], s1 += (double)p[C + c];
+        }
       }
       const double m = s0 / n;
       double var = s1 / n - m * m;
@@ -125,7 +130,9 @@ bn_finalize_fwd_kernel(const float* __restrict__ partial, int T, int S, int C, i
 
 // backward: dgamma / dbeta and the three per-(t, c) coefficients of dx = gy*c1 + x*c2 + c3
 __global__ void __launch_bounds__(32 * BN_FT)
-bn_finalize_bwd_kernel(const float* __restrict__ partial, int T, int S, int C, int64_t n_pix,
+bn_finalize_bwd_kernel(const float* __restrict__ partial, const double* __restrict__ sums /* global, or NULL */,
+                       const double* __restrict__ sums_local /* for dgamma / dbeta, or NULL = same */,
+                       int T, int S, int C, int64_t n_pix,
                        const float* __restrict__ gamma, const float* __restrict__ mean,
                        const float* __restrict__ invstd, float* __restrict__ coef /*[T][3][C]*/,
                        float* __restrict__ dgamma, float* __restrict__ dbeta) {
@@ -138,12 +145,18 @@ bn_finalize_bwd_kernel(const float* __restrict__ partial, int T, int S, int C, i
   double dg = 0.0, db = 0.0;
   for (int t0 = 0; t0 < T; t0 += BN_FT) {
     const int t = t0 + ty;
-    double s0 = 0.0, s1 = 0.0;
+    double s0 = 0.0, s1 = 0.0, l0 = 0.0, l1 = 0.0;
     if (live && t < T) {
-      for (int s = 0; s < S; ++s) {
-        const float* p = partial + (((int64_t)t * S + s) * 2) * C;
-        s0 += (double)p[c], s1 += (double)p[C + c];
+      if (sums != nullptr) {
+        s0 = sums[((int64_t)t * 2) * C + c], s1 = sums[((int64_t)t * 2 + 1) * C + c];
+      } else {
+        for (int s = 0; s < S; ++s) {
+          const float* p = partial + (((int64_t)t * S + s) * 2) * C;
+          s0 += (double)p[c], s1 += (double)p[C + c];
+        }
       }
+      l0 = s0, l1 = s1;
+      if (sums_local != nullptr) l0 = sums_local[((int64_t)t * 2) * C + c], l1 = sums_local[((int64_t)t * 2 + 1) * C + c];
       const double is = (double)invstd[(int64_t)t * C + c], mu = (double)mean[(int64_t)t * C + c];
       const double a = gm * is, m1 = s0 / n, m2 = s1 / n;
       float* k = coef + (int64_t)t * 3 * C;
@@ -151,7 +164,7 @@ bn_finalize_bwd_kernel(const float* __restrict__ partial, int T, int S, int C, i
       k[C + c] = (float)(-a * m2 * is);             // * x
       k[2 * C + c] = (float)(-a * m1 + a * m2 * is * mu);
     }
-    s_b[ty][cl] = s0, s_g[ty][cl] = s1;
+    s_b[ty][cl] = l0, s_g[ty][cl] = l1;
     __syncthreads();
     if (ty == 0) {
       for (int k = 0; k < BN_FT; ++k) db += s_b[k][cl], dg += s_g[k][cl];   // fixed order over t
@@ -191,6 +204,17 @@ bn_apply_kernel(const float* __restrict__ x, const float* __restrict__ g, const 
     }
     reinterpret_cast<float4*>(y)[i] = o;
   }
+}
+
+// partial sums [T][S][2][C] -> double sums [T][2][C], slices added in order (deterministic)
+__global__ void bn_reduce_kernel(const float* __restrict__ partial, int T, int S, int C, double* __restrict__ sums) {
+  const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;   // over T * 2 * C
+  if (i >= (int64_t)T * 2 * C) return;
+  const int t = (int)(i / (2 * C));
+  const int r = (int)(i % (2 * C));
+  double a = 0.0;
+  for (int s = 0; s < S; ++s) a += (double)partial[((int64_t)t * S + s) * 2 * C + r];
+  sums[i] = a;
 }
 
 static int bn_slices(int64_t n_pix, int T) {
@@ -234,7 +258,7 @@ extern "C" int soda_bn_train_fwd(const float* x, int T, int64_t n_pix, int C, co
   bn_partial_kernel<0><<<dim3(S, T), BN_THREADS, 0, st>>>(x, nullptr, nullptr, nullptr, n_pix, C, partial);
   rc = after_launch("bn_partial_kernel");
   if (rc) return rc;
-  bn_finalize_fwd_kernel<<<(C + 31) / 32, 32 * BN_FT, 0, st>>>(partial, T, S, C, n_pix, eps, momentum, gamma, beta, save_mean,
+  bn_finalize_fwd_kernel<<<(C + 31) / 32, 32 * BN_FT, 0, st>>>(partial, nullptr, T, S, C, n_pix, eps, momentum, gamma, beta, save_mean,
                                                           save_invstd, scale, shift, running_mean, running_var);
   rc = after_launch("bn_finalize_fwd_kernel");
   if (rc) return rc;
@@ -260,8 +284,79 @@ extern "C" int soda_bn_train_bwd(const float* grad_y, const float* x, int T, int
   bn_partial_kernel<1><<<dim3(S, T), BN_THREADS, 0, st>>>(x, grad_y, save_mean, save_invstd, n_pix, C, partial);
   rc = after_launch("bn_partial_kernel");
   if (rc) return rc;
-  bn_finalize_bwd_kernel<<<(C + 31) / 32, 32 * BN_FT, 0, st>>>(partial, T, S, C, n_pix, gamma, save_mean, save_invstd, coef,
+  bn_finalize_bwd_kernel<<<(C + 31) / 32, 32 * BN_FT, 0, st>>>(partial, nullptr, nullptr, T, S, C, n_pix, gamma, save_mean, save_invstd, coef,
                                                           grad_gamma, grad_beta);
+  rc = after_launch("bn_finalize_bwd_kernel");
+  if (rc) return rc;
+  const int64_t n_vec = n_pix * C / 4, total = n_vec * T;
+  const int grid = (int)std::min<int64_t>((total + 255) / 256, (int64_t)kNumSMs * 16);
+  bn_apply_kernel<true><<<grid, 256, 0, st>>>(x, grad_y, coef, nullptr, n_vec, C, total, grad_x);
+  return after_launch("bn_apply_kernel");
+}
+
+// ---- cross-rank (SyncBatchNorm) variant: statistics -> [caller all-reduces the sums] -> normalise ------------------
+// The reference trains with sync_batchnorm (config.yaml:76): every time step's statistics are taken over the GLOBAL
+// batch.  soda_bn_train_stats leaves the per-(t, c) sums of this rank in a small fp64 buffer [T][2][C]; the caller
+// all-reduces it (one NCCL call per layer and direction, <= 128 KB) and passes the global sums and the global pixel
+// count to the *_from_sums entry points.  dgamma / dbeta come from the LOCAL sums (the flat gradient all-reduce
+// averages them over ranks like every other parameter gradient).
+extern "C" int soda_bn_train_stats(const float* x, const float* grad_y, const float* save_mean, const float* save_invstd,
+                                   int T, int64_t n_pix, int C, double* sums, void* workspace, void* stream) {
+  using namespace soda;
+  if (!x || !sums || !workspace) return fail(SODA_ERR_BAD_ARG, "bn_train_stats: null pointer");
+  if (grad_y && (!save_mean || !save_invstd)) return fail(SODA_ERR_BAD_ARG, "bn_train_stats: backward sums need mean / invstd");
+  int rc = bn_check(T, n_pix, C, x, grad_y, workspace);
+  if (rc) return rc;
+  cudaStream_t st = (cudaStream_t)stream;
+  float* partial = reinterpret_cast<float*>(workspace);
+  const int S = bn_slices(n_pix, T);
+  if (grad_y) bn_partial_kernel<1><<<dim3(S, T), BN_THREADS, 0, st>>>(x, grad_y, save_mean, save_invstd, n_pix, C, partial);
+  else bn_partial_kernel<0><<<dim3(S, T), BN_THREADS, 0, st>>>(x, nullptr, nullptr, nullptr, n_pix, C, partial);
+  rc = after_launch("bn_partial_kernel");
+  if (rc) return rc;
+  const int64_t n = (int64_t)T * 2 * C;
+  bn_reduce_kernel<<<(unsigned)((n + 255) / 256), 256, 0, st>>>(partial, T, S, C, sums);
+  return after_launch("bn_reduce_kernel");
+}
+
+extern "C" int soda_bn_train_fwd_from_sums(const float* x, const double* sums, int64_t n_total, int T, int64_t n_pix, int C,
+                                           const float* gamma, const float* beta, float eps, float momentum,
+                                           float* running_mean, float* running_var, float* y, float* save_mean,
+                                           float* save_invstd, void* workspace, void* stream) {
+  using namespace soda;
+  if (!x || !sums || !y || !save_mean || !save_invstd || !workspace)
+    return fail(SODA_ERR_BAD_ARG, "bn_train_fwd_from_sums: null pointer");
+  if ((running_mean == nullptr) != (running_var == nullptr) || n_total < n_pix)
+    return fail(SODA_ERR_BAD_ARG, "bn_train_fwd_from_sums: bad running statistics or global count");
+  int rc = bn_check(T, n_pix, C, x, y, workspace);
+  if (rc) return rc;
+  cudaStream_t st = (cudaStream_t)stream;
+  float* scale = reinterpret_cast<float*>(workspace) + (int64_t)T * BN_MAX_SLICES * 2 * C;
+  float* shift = scale + (int64_t)T * C;
+  bn_finalize_fwd_kernel<<<(C + 31) / 32, 32 * BN_FT, 0, st>>>(nullptr, sums, T, 0, C, n_total, eps, momentum, gamma, beta,
+                                                              save_mean, save_invstd, scale, shift, running_mean, running_var);
+  rc = after_launch("bn_finalize_fwd_kernel");
+  if (rc) return rc;
+  const int64_t n_vec = n_pix * C / 4, total = n_vec * T;
+  const int grid = (int)std::min<int64_t>((total + 255) / 256, (int64_t)kNumSMs * 16);
+  bn_apply_kernel<false><<<grid, 256, 0, st>>>(x, nullptr, scale, shift, n_vec, C, total, y);
+  return after_launch("bn_apply_kernel");
+}
+
+extern "C" int soda_bn_train_bwd_from_sums(const float* grad_y, const float* x, const double* sums_global, int64_t n_total,
+                                           const double* sums_local, int T, int64_t n_pix, int C, const float* gamma,
+                                           const float* save_mean, const float* save_invstd, float* grad_x,
+                                           float* grad_gamma, float* grad_beta, void* workspace, void* stream) {
+  using namespace soda;
+  if (!grad_y || !x || !sums_global || !save_mean || !save_invstd || !grad_x || !workspace)
+    return fail(SODA_ERR_BAD_ARG, "bn_train_bwd_from_sums: null pointer");
+  if (n_total < n_pix) return fail(SODA_ERR_BAD_ARG, "bn_train_bwd_from_sums: global count below the local one");
+  int rc = bn_check(T, n_pix, C, x, grad_y, grad_x);
+  if (rc) return rc;
+  cudaStream_t st = (cudaStream_t)stream;
+  float* coef = reinterpret_cast<float*>(workspace) + (int64_t)T * BN_MAX_SLICES * 2 * C;
+  bn_finalize_bwd_kernel<<<(C + 31) / 32, 32 * BN_FT, 0, st>>>(nullptr, sums_global, sums_local, T, 0, C, n_total, gamma,
+                                                              save_mean, save_invstd, coef, grad_gamma, grad_beta);
   rc = after_launch("bn_finalize_bwd_kernel");
   if (rc) return rc;
   const int64_t n_vec = n_pix * C / 4, total = n_vec * T;

@@ -898,3 +898,65 @@ def bn_train_bwd(gy: torch.Tensor, x: torch.Tensor, T: int, gamma, mean: torch.T
         "soda_bn_train_bwd",
     )
     return gx, gg, gb
+
+
+def bn_train_stats(x: torch.Tensor, T: int, gy: Optional[torch.Tensor] = None, mean=None, invstd=None) -> torch.Tensor:
+    """This rank's per-(t, c) sums ``[T, 2, C]`` fp64: ``(sum x, sum x^2)``, or ``(sum gy, sum gy * xhat)`` with ``gy``."""
+    _need_cuda(x, gy, mean, invstd)
+    N, Cc, H, W = x.shape
+    sums = torch.empty((T, 2, Cc), dtype=torch.float64, device=x.device)
+    ws = torch.empty(lib.soda_bn_train_workspace_bytes(T, Cc), dtype=torch.uint8, device=x.device)
+    check(lib.soda_bn_train_stats(x.data_ptr(), _ptr(gy), _ptr(mean), _ptr(invstd), T, (N // T) * H * W, Cc,
+                                  sums.data_ptr(), ws.data_ptr(), _stream()), "soda_bn_train_stats")
+    return sums
+
+
+@_prof("bn_train")
+def bn_train_fwd_sync(x: torch.Tensor, T: int, gamma, beta, eps: float, momentum: float, running_mean, running_var,
+                      all_reduce) -> Tuple[torch.Tensor, torch.Tensor, torch.Tensor, torch.Tensor, int]:
+    """SyncBatchNorm forward: local sums -> ``all_reduce(sums) -> world size`` (in place) -> normalise with the
+    global statistics.  Returns ``(y, save_mean, save_invstd, x as used, world)``."""
+    _need_cuda(x, gamma, beta, running_mean, running_var)
+    if not x.is_contiguous(memory_format=torch.channels_last):
+        x = x.contiguous(memory_format=torch.channels_last)
+    N, Cc, H, W = x.shape
+    if N % T:
+        raise ValueError("bn_train: leading dimension is not a multiple of T")
+    n_pix = (N // T) * H * W
+    sums = bn_train_stats(x, T)
+    world = int(all_reduce(sums))
+    y = torch.empty_like(x)
+    mean = torch.empty((T, Cc), dtype=torch.float32, device=x.device)
+    invstd = torch.empty_like(mean)
+    ws = torch.empty(lib.soda_bn_train_workspace_bytes(T, Cc), dtype=torch.uint8, device=x.device)
+    check(
+        lib.soda_bn_train_fwd_from_sums(x.data_ptr(), sums.data_ptr(), n_pix * world, T, n_pix, Cc, _ptr(gamma), _ptr(beta),
+                                        float(eps), float(momentum), _ptr(running_mean), _ptr(running_var), y.data_ptr(),
+                                        mean.data_ptr(), invstd.data_ptr(), ws.data_ptr(), _stream()),
+        "soda_bn_train_fwd_from_sums",
+    )
+    return y, mean, invstd, x, world
+
+
+@_prof("bn_train")
+def bn_train_bwd_sync(gy: torch.Tensor, x: torch.Tensor, T: int, gamma, mean, invstd, all_reduce, want_affine=True):
+    """SyncBatchNorm backward: dx from the all-reduced ``(sum gy, sum gy * xhat)``, dgamma / dbeta from the local sums."""
+    _need_cuda(gy, x, gamma, mean, invstd)
+    if gy.stride() != x.stride():
+        gy = gy.contiguous(memory_format=torch.channels_last)
+    N, Cc, H, W = x.shape
+    n_pix = (N // T) * H * W
+    local = bn_train_stats(x, T, gy, mean, invstd)
+    glob = local.clone()
+    world = int(all_reduce(glob))
+    gx = torch.empty_like(x)
+    gg = torch.empty(Cc, dtype=torch.float32, device=x.device) if want_affine else None
+    gb = torch.empty(Cc, dtype=torch.float32, device=x.device) if want_affine else None
+    ws = torch.empty(lib.soda_bn_train_workspace_bytes(T, Cc), dtype=torch.uint8, device=x.device)
+    check(
+        lib.soda_bn_train_bwd_from_sums(gy.data_ptr(), x.data_ptr(), glob.data_ptr(), n_pix * world, local.data_ptr(), T,
+                                        n_pix, Cc, _ptr(gamma), mean.data_ptr(), invstd.data_ptr(), gx.data_ptr(),
+                                        _ptr(gg), _ptr(gb), ws.data_ptr(), _stream()),
+        "soda_bn_train_bwd_from_sums",
+    )
+    return gx, gg, gb

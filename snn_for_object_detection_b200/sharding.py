@@ -15,7 +15,7 @@ from typing import List, Optional, Sequence, Tuple
 import torch
 import torch.distributed as dist
 
-__all__ = ["shard_range", "shard_samples", "gather_predictions", "allreduce_flat_gradients"]
+__all__ = ["shard_range", "shard_samples", "gather_predictions", "allreduce_flat_gradients", "convert_sync_batchnorm"]
 
 
 def shard_range(n: int, rank: int, world: int) -> Tuple[int, int]:
@@ -70,3 +70,15 @@ def allreduce_flat_gradients(params: Sequence[torch.nn.Parameter]) -> None:
         n = g.numel()
         g.copy_(flat[off : off + n].view_as(g))
         off += n
+
+
+def convert_sync_batchnorm(model: torch.nn.Module) -> torch.nn.Module:
+    """Role of ``nn.SyncBatchNorm.convert_sync_batchnorm`` / Lightning's ``sync_batchnorm: true`` (reference
+    ``config.yaml:76``): every train-mode BatchNorm takes its per-time-step statistics over the GLOBAL batch - one
+    all-reduce of the ``[T, 2, C]`` sums per layer and direction (``soda_bn_train_stats`` / ``*_from_sums``)."""
+    from .modules.common import SodaBatchNorm2d
+
+    for m in model.modules():
+        if isinstance(m, SodaBatchNorm2d):
+            m.sync = True
+    return model

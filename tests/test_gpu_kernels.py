@@ -794,3 +794,53 @@ def test_mt_sample_stream_consecutive_windows_match_reference_golden():
     X2, starts2, _ = st.next_batch(1)
     if st.readers[0].current_time == T * step_us:          # the recording ended after two windows: restarted
         assert starts2 == [0] and np.array_equal(X2[:, 0].cpu().numpy(), ref[0])
+
+
+@pytest.mark.gpu
+def test_sync_batchnorm_sums_exchange_equals_full_batch():
+    """SyncBatchNorm route (config.yaml:76) on one GPU: the batch is split between two emulated ranks, their
+    [T, 2, C] sums are added (what the all-reduce does) and each rank normalises its own frames with the global sums:
+    outputs, running statistics and input gradients equal the unsplit per-time-step BatchNorm; the ranks' dgamma /
+    dbeta add up to the full ones."""
+    ops = _pkg().ops
+    torch.manual_seed(21)
+    T, B, C, H, W = 4, 6, 32, 9, 13
+    x = (torch.randn(T * B, C, H, W, device=DEV) * 1.3 + 0.2).contiguous(memory_format=torch.channels_last)
+    gy = torch.randn_like(x)
+    gamma, beta = torch.rand(C, device=DEV) + 0.5, torch.randn(C, device=DEV)
+    rm0, rv0 = torch.zeros(C, device=DEV), torch.ones(C, device=DEV)
+    rmF, rvF = rm0.clone(), rv0.clone()
+    yF, meanF, invF, xF = ops.bn_train_fwd(x, T, gamma, beta, 1e-5, 0.1, rmF, rvF)
+    gxF, ggF, gbF = ops.bn_train_bwd(gy, xF, T, gamma, meanF, invF)
+    idx = [torch.cat([torch.arange(t * B + r * 3, t * B + r * 3 + 3) for t in range(T)]).to(DEV) for r in range(2)]
+    xs = [x[i].contiguous(memory_format=torch.channels_last) for i in idx]
+    gs = [gy[i].contiguous(memory_format=torch.channels_last) for i in idx]
+    total = ops.bn_train_stats(xs[0], T) + ops.bn_train_stats(xs[1], T)
+
+    def fake_all_reduce_fwd(s):
+        s.copy_(total)
+        return 2
+
+    outs = [ops.bn_train_fwd_sync(xs[r], T, gamma, beta, 1e-5, 0.1, rm0.clone(), rv0.clone(), fake_all_reduce_fwd)
+            for r in range(2)]
+    local_b = [ops.bn_train_stats(xs[r], T, gs[r], outs[r][1], outs[r][2]) for r in range(2)]
+    total_b = local_b[0] + local_b[1]
+
+    def fake_all_reduce_bwd(s):
+        s.copy_(total_b)
+        return 2
+
+    gg_sum, gb_sum = 0, 0
+    for r in range(2):
+        y, mean, invstd, xk, world = outs[r]
+        assert world == 2
+        assert float((y - yF[idx[r]]).abs().max()) < 2e-5 * float(yF.abs().max())
+        assert float((mean - meanF).abs().max()) < 1e-6 and float((invstd - invF).abs().max()) < 1e-5
+        gx, gg, gb = ops.bn_train_bwd_sync(gs[r], xk, T, gamma, mean, invstd, fake_all_reduce_bwd)
+        assert float((gx - gxF[idx[r]]).abs().max()) < 5e-5 * max(1.0, float(gxF.abs().max()))
+        gg_sum, gb_sum = gg_sum + gg, gb_sum + gb
+    assert float((gg_sum - ggF).abs().max()) < 5e-5 * float(ggF.abs().max())
+    assert float((gb_sum - gbF).abs().max()) < 5e-5 * float(gbF.abs().max())
+    rm1, rv1 = rm0.clone(), rv0.clone()
+    ops.bn_train_fwd_sync(xs[0], T, gamma, beta, 1e-5, 0.1, rm1, rv1, fake_all_reduce_fwd)
+    assert float((rm1 - rmF).abs().max()) < 1e-6 and float((rv1 - rvF).abs().max()) < 1e-5
