@@ -126,3 +126,16 @@ def test_spike_count_bounds_pick_the_conv_operand_scheme():
     assert ops._exact_flags(ops.mark_exact(c, 257)) == _lib.SODA_CONV_FLAG_INPUT_EXACT_TF32
     assert ops._exact_flags(ops.mark_exact(c, 4096)) == 0 and not ops.is_exact(c)
     assert ops.exact_bound(ops.mark_exact(torch.zeros(1), None)) is None
+
+
+def test_convert_sync_batchnorm_marks_every_batchnorm():
+    """Host side of the SyncBatchNorm exchange (reference config.yaml:76): every generated BatchNorm is switched."""
+    from snn_for_object_detection_b200 import BlockGen, sharding
+    from snn_for_object_detection_b200.modules.common import SodaBatchNorm2d
+    from snn_for_object_detection_b200.modules.layer_gen import LIF, Conv, Norm
+
+    block = BlockGen(2, [Conv(8), Norm(), LIF(), Conv(8), Norm(), LIF()])
+    norms = [m for m in block.modules() if isinstance(m, SodaBatchNorm2d)]
+    assert len(norms) == 2 and not any(getattr(m, "sync", False) for m in norms)
+    assert sharding.convert_sync_batchnorm(block) is block
+    assert all(m.sync for m in norms)
