@@ -272,7 +272,8 @@ SODA_API int soda_add_n(const float* const* xs, int k, int64_t n, float* y, void
  *   out       : [B, A, 6] rows (class, conf, x1, y1, x2, y2): kept boxes first (class by class, best first), then
  *               the others in anchor order with class -1; conf < pos_threshold -> class -1, conf = 1 - conf
  *   workspace : soda_multibox_workspace_bytes(B, A) bytes of device memory, 16-byte aligned
- *   One CTA per sample; A <= 16384 anchors (GEN1: 13 545), C <= 64.
+ *   One CTA per sample; A <= 262143 anchors (GEN1: 13 545 - keys sorted in shared memory; 1Mpx: 170 280 - keys in the
+ *   L2-resident workspace), C <= 64.
  * ------------------------------------------------------------------------------------------- */
 SODA_API int64_t soda_multibox_workspace_bytes(int B, int A);
 SODA_API int soda_multibox_detection(const float* cls_probs, const float* offsets, const float* anchors, int B, int A,

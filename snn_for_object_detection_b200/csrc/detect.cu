@@ -13,13 +13,15 @@
 // The reference runs this as a Python while-loop with one device sync per kept box; here one CTA per sample does the
 // whole thing on-chip: decode -> 64-bit key (class | descending confidence | anchor) -> bitonic sort in shared memory ->
 // greedy suppression with the whole CTA computing IoUs against each kept box -> two block scans for the row order.
-// Integer/compare-bound, a few hundred microseconds per sample; anchors <= 16384 (GEN1: 13 545).
+// Integer/compare-bound, a few hundred microseconds per sample at GEN1 size (13 545 anchors: keys in shared memory);
+// larger sets (1Mpx: 170 280) keep the keys in the L2-resident workspace; anchors <= 262 143.
 #include "common.cuh"
 
 namespace soda {
 
 constexpr int DET_THREADS = 1024;
-constexpr int DET_MAX_A = 16384;
+constexpr int DET_MAX_A = 262143;        // anchor index field of the sort key: 18 bits (1Mpx: 170 280 anchors)
+constexpr int DET_SMEM_N = 16384;        // up to this padded size the sort keys / flags live in shared memory
 constexpr int DET_MAX_CLASSES = 64;
 
 struct DetP {
@@ -67,16 +69,25 @@ __device__ __forceinline__ int det_block_scan(int v, int* warp_sums, int* total)
 // per-sample global workspace: conf[A] f32 | cls[A] i32 | box[A] float4 (by anchor) | sbox[n_pad] float4 (sorted)
 __host__ __device__ inline int64_t det_ws_per_sample(int A, int n_pad) {
   const int64_t Aa = (A + 3) & ~3;   // keeps the float4 arrays 16-byte aligned
-  return Aa * 8 + Aa * 16 + (int64_t)n_pad * 16;
+  // + keys[n_pad] u64 | alive[n_pad] u8 | kept[Aa] u8 for anchor sets whose keys do not fit in shared memory
+  const int64_t big = n_pad > DET_SMEM_N ? (int64_t)n_pad * 9 + ((Aa + 15) & ~(int64_t)15) : 0;
+  return Aa * 8 + Aa * 16 + (int64_t)n_pad * 16 + big;
 }
 
 __global__ void __launch_bounds__(DET_THREADS, 1)
 multibox_kernel(DetP p, const float* __restrict__ cls_probs, const float* __restrict__ offsets,
                 const float* __restrict__ anchors, uint8_t* __restrict__ ws, float* __restrict__ out) {
   extern __shared__ __align__(16) uint8_t det_smem[];
-  uint64_t* keys = reinterpret_cast<uint64_t*>(det_smem);        // [n_pad] (class | ~conf | anchor), sorted ascending
-  uint8_t* alive = det_smem + (size_t)p.n_pad * 8;               // [n_pad] by sorted position: 1 candidate, 2 kept, 0 out
-  uint8_t* kept_a = alive + p.n_pad;                             // [A] by anchor
+  // keys [n_pad] (class | ~conf | anchor) sorted ascending; alive [n_pad] by sorted position: 1 candidate, 2 kept, 0 out;
+  // kept_a [A] by anchor.  In shared memory up to 16384 (padded) anchors, else in the (L2-resident) workspace.
+  uint8_t* kbase = det_smem;
+  if (p.n_pad > DET_SMEM_N) {
+    const int64_t Aa0 = (p.A + 3) & ~3;
+    kbase = ws + (int64_t)blockIdx.x * det_ws_per_sample(p.A, p.n_pad) + Aa0 * 8 + Aa0 * 16 + (int64_t)p.n_pad * 16;
+  }
+  uint64_t* keys = reinterpret_cast<uint64_t*>(kbase);
+  uint8_t* alive = kbase + (size_t)p.n_pad * 8;
+  uint8_t* kept_a = alive + p.n_pad;
   __shared__ int warp_sums[32];
   __shared__ int s_next;
   __shared__ int seg_start[DET_MAX_CLASSES + 1];
@@ -234,7 +245,7 @@ extern "C" int soda_multibox_detection(const float* cls_probs, const float* offs
   if (!cls_probs || !offsets || !anchors || !workspace || !out) return fail(SODA_ERR_BAD_ARG, "multibox: null pointer");
   if (B <= 0 || A <= 0 || C < 2) return fail(SODA_ERR_BAD_ARG, "multibox: non-positive size");
   if (A > DET_MAX_A || C > DET_MAX_CLASSES)
-    return fail(SODA_ERR_UNSUPPORTED, "multibox: at most 16384 anchors and 64 classes in this build");
+    return fail(SODA_ERR_UNSUPPORTED, "multibox: at most 262143 anchors and 64 classes in this build");
   if ((reinterpret_cast<uintptr_t>(offsets) & 15) || (reinterpret_cast<uintptr_t>(anchors) & 15) ||
       (reinterpret_cast<uintptr_t>(workspace) & 15))
     return fail(SODA_ERR_BAD_ARG, "multibox: offsets, anchors and workspace must be 16-byte aligned");
@@ -242,7 +253,7 @@ extern "C" int soda_multibox_detection(const float* cls_probs, const float* offs
   p.B = B, p.A = A, p.C = C, p.nms_thr = nms_threshold, p.pos_thr = pos_threshold;
   p.n_pad = 1024;
   while (p.n_pad < A) p.n_pad <<= 1;
-  const size_t smem = (size_t)p.n_pad * 9 + (size_t)((A + 15) / 16 * 16);
+  const size_t smem = p.n_pad > DET_SMEM_N ? 16 : (size_t)p.n_pad * 9 + (size_t)((A + 15) / 16 * 16);
   static bool attr_set = false;
   if (!attr_set) {
     cudaError_t e = cudaFuncSetAttribute(multibox_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024);

@@ -799,7 +799,7 @@ def add_n(xs: Sequence[torch.Tensor]) -> torch.Tensor:
 # --------------------------------------------------------------------------------------------
 # detection decode + NMS
 # --------------------------------------------------------------------------------------------
-MULTIBOX_MAX_ANCHORS = 16384
+MULTIBOX_MAX_ANCHORS = 262143
 
 
 @_prof("multibox")

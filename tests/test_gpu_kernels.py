@@ -475,8 +475,29 @@ def test_multibox_detection_low_confidence_rule_and_limits():
     assert det[1, 0] == -1 and abs(float(det[1, 1]) - 0.8) < 1e-7
     assert det[2, 0] == -1 and abs(float(det[2, 1]) - 0.995) < 1e-7
     with pytest.raises(_pkg()._lib.SodaError):
-        ops.multibox_detection(torch.zeros(1, 20000, 3, device=DEV), torch.zeros(1, 20000, 4, device=DEV),
-                               torch.zeros(20000, 4, device=DEV))
+        ops.multibox_detection(torch.zeros(1, 262144, 3, device=DEV), torch.zeros(1, 262144, 4, device=DEV),
+                               torch.zeros(262144, 4, device=DEV))
+
+
+def test_multibox_detection_1mpx_anchor_count_against_oracle():
+    """170 280 anchors (1Mpx): the sort keys live in the workspace instead of shared memory; rows equal the CPU
+    restatement of the reference (mostly-background scores keep the oracle's Python NMS loop short)."""
+    from snn_for_object_detection_b200.utils import box
+
+    ops = _pkg().ops
+    A, C, B = 170280, 3, 2
+    torch.manual_seed(170)
+    ctr = torch.rand(A, 2)
+    wh = torch.rand(A, 2) * 0.05 + 0.01
+    anchors = torch.cat([ctr - wh / 2, ctr + wh / 2], dim=1)
+    logits = torch.randn(B, A, C)
+    logits[:, :, 0] += 4.0                               # ~98 % background
+    probs = torch.softmax(logits, dim=2)
+    offsets = torch.randn(B, A, 4) * 0.3
+    ref = box.multibox_detection(probs, offsets, anchors)
+    det = ops.multibox_detection(probs.to(DEV), offsets.to(DEV), anchors.to(DEV)).cpu()
+    assert int((ref[..., 0] >= 0).sum()) > 500
+    _det_close(det, ref)
 
 
 @pytest.mark.parametrize("mode", ["S", "A", "M"])
