@@ -96,7 +96,7 @@ class SODa(nn.Module):
         probs = F.softmax(cls, dim=2)
         if anchors.shape[0] <= ops.MULTIBOX_MAX_ANCHORS:
             prep_pred = ops.multibox_detection(probs, bbox, anchors).squeeze(0)   # one kernel, no host sync
-        else:  # > 16384 anchors (1Mpx): torch restatement of the same algorithm, still on the GPU
+        else:  # > 262143 anchors: torch restatement of the same algorithm, still on the GPU
             prep_pred = box.multibox_detection(probs, bbox, anchors).squeeze(0)
         prep_pred = prep_pred[prep_pred[:, 0] >= 0]
         prep_pred[:, 2:] = torch.clamp(prep_pred[:, 2:], min=0.0, max=1.0)
