@@ -229,6 +229,12 @@ SODA_API int soda_synapse_fwd(float tau_secretion, float tau_dissociation, float
 SODA_API int soda_lstm_gates(const float* pre, const float* c_prev, int64_t n_pix, int hidden, float* h_out, float* c_out,
                     void* stream);
 
+/* Stateless LayerGens: ReLU / SiLU / Tanh (models/modules/layer_gen.py:255-284; mode 0 / 1 / 2) over a dense tensor of
+ * n floats, and Up with mode "nearest" and an integer scale (:176-194) over pixel-major frames
+ * x [N, H, W, C] -> y [N, H*scale, W*scale, C]. */
+SODA_API int soda_unary_fwd(const float* x, int64_t n, int mode, float* y, void* stream);
+SODA_API int soda_upsample_nearest(const float* x, int64_t N, int H, int W, int C, int scale, float* y, void* stream);
+
 /* Surrogate-gradient LIF backward (K8): fused reverse scan over T.
  *   replaces: autograd through T calls of LIFCell incl. norse SuperSpike.backward
  *             (g / (alpha*|v_dec - v_th| + 1)^2), models/soda.py:146-158.

@@ -88,6 +88,8 @@ SIGNATURES = {
     "soda_sli_fwd": (_i, [C.POINTER(NeuronParams), _vp, _vp, _vp, _i, _i64, _vp, _vp, _vp, _vp, _vp]),
     "soda_synapse_fwd": (_i, [_f, _f, _f, _f, _vp, _vp, _i, _i64, _vp, _vp, _vp]),
     "soda_lstm_gates": (_i, [_vp, _vp, _i64, _i, _vp, _vp, _vp]),
+    "soda_unary_fwd": (_i, [_vp, _i64, _i, _vp, _vp]),
+    "soda_upsample_nearest": (_i, [_vp, _i64, _i, _i, _i, _i, _vp, _vp]),
     "soda_roi_assign": (_i, [_vp, _vp, _i, _i, _i, _f, _vp, _vp, _vp, _vp]),
     "soda_bn_train_workspace_bytes": (_i64, [_i, _i]),
     "soda_bn_train_fwd": (_i, [_vp, _i, _i64, _i, _vp, _vp, _f, _f, _vp, _vp, _vp, _vp, _vp, _vp, _vp]),

@@ -225,3 +225,60 @@ extern "C" int soda_lstm_gates(const float* pre, const float* c_prev, int64_t n_
   lstm_gate_kernel<<<grid, 256, 0, (cudaStream_t)stream>>>(pre, c_prev, n_pix, hidden, h_out, c_out);
   return after_launch("lstm_gate_kernel");
 }
+
+// Stateless LayerGens of the reference (models/modules/layer_gen.py:176-194 Up, :255-284 ReLU / SiLU / Tanh) as
+// elementwise kernels: activation over a dense tensor, nearest-neighbour upsampling of pixel-major frames.
+namespace soda {
+template <int MODE>   // 0 relu, 1 silu (x * sigmoid(x)), 2 tanh
+__global__ void __launch_bounds__(256) unary_kernel(const float* __restrict__ x, int64_t n, float* __restrict__ y) {
+  pdl_trigger();
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x) {
+    const float v = x[i];
+    float o;
+    if (MODE == 0) o = v > 0.0f ? v : 0.0f;
+    else if (MODE == 1) o = __fmul_rn(v, __fdiv_rn(1.0f, __fadd_rn(1.0f, expf(-v))));
+    else o = tanhf(v);
+    y[i] = o;
+  }
+}
+
+// x [N, H, W, C] pixel-major -> y [N, H*s, W*s, C]: y(n, oy, ox, :) = x(n, oy / s, ox / s, :)
+__global__ void __launch_bounds__(256)
+upsample_nearest_kernel(const float* __restrict__ x, int64_t N, int H, int W, int C, int s, float* __restrict__ y) {
+  pdl_trigger();
+  const int Ho = H * s, Wo = W * s;
+  const int64_t total = N * Ho * Wo * C;
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (int64_t)gridDim.x * blockDim.x) {
+    const int c = (int)(i % C);
+    int64_t r = i / C;
+    const int ox = (int)(r % Wo);
+    r /= Wo;
+    const int oy = (int)(r % Ho);
+    const int64_t n = r / Ho;
+    y[i] = __ldg(x + ((n * H + oy / s) * W + ox / s) * C + c);
+  }
+}
+}  // namespace soda
+
+extern "C" int soda_unary_fwd(const float* x, int64_t n, int mode, float* y, void* stream) {
+  using namespace soda;
+  if (!x || !y) return fail(SODA_ERR_BAD_ARG, "unary_fwd: null pointer");
+  if (n <= 0 || mode < 0 || mode > 2) return fail(SODA_ERR_BAD_ARG, "unary_fwd: bad size or mode");
+  const int grid = (int)std::min<int64_t>((n + 255) / 256, (int64_t)kNumSMs * 32);
+  cudaStream_t st = (cudaStream_t)stream;
+  if (mode == 0) unary_kernel<0><<<grid, 256, 0, st>>>(x, n, y);
+  else if (mode == 1) unary_kernel<1><<<grid, 256, 0, st>>>(x, n, y);
+  else unary_kernel<2><<<grid, 256, 0, st>>>(x, n, y);
+  return after_launch("unary_kernel");
+}
+
+extern "C" int soda_upsample_nearest(const float* x, int64_t N, int H, int W, int C, int scale, float* y, void* stream) {
+  using namespace soda;
+  if (!x || !y) return fail(SODA_ERR_BAD_ARG, "upsample_nearest: null pointer");
+  if (N <= 0 || H <= 0 || W <= 0 || C <= 0 || scale < 1) return fail(SODA_ERR_BAD_ARG, "upsample_nearest: bad size");
+  const int64_t total = N * H * scale * W * scale * C;
+  const int grid = (int)std::min<int64_t>((total + 255) / 256, (int64_t)kNumSMs * 32);
+  upsample_nearest_kernel<<<grid, 256, 0, (cudaStream_t)stream>>>(x, N, H, W, C, scale, y);
+  return after_launch("upsample_nearest_kernel");
+}
+

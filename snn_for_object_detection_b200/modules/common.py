@@ -197,3 +197,37 @@ class StateStorage(nn.Module):
             self.state_list.append(cls(v_steps[sl], trace.i[sl]))
             self.spike_list.append(out[sl])
         return out, new_state
+
+
+class _CudaUnary:
+    """Inference on the elementwise kernel; when a graph is being recorded, the torch module's own forward."""
+
+    _mode = "relu"
+
+    def forward(self, x: torch.Tensor) -> torch.Tensor:
+        if (torch.is_grad_enabled() and x.requires_grad) or not x.is_cuda or x.dtype != torch.float32:
+            return super().forward(x)
+        return ops.unary(x, self._mode)
+
+
+class SodaReLU(_CudaUnary, nn.ReLU):
+    _mode = "relu"
+
+
+class SodaSiLU(_CudaUnary, nn.SiLU):
+    _mode = "silu"
+
+
+class SodaTanh(_CudaUnary, nn.Tanh):
+    _mode = "tanh"
+
+
+class SodaUpsample(nn.Upsample):
+    """``nn.Upsample``; mode "nearest" with an integer scale runs on the CUDA kernel (inference)."""
+
+    def forward(self, x: torch.Tensor) -> torch.Tensor:
+        s = self.scale_factor
+        if (self.mode == "nearest" and s is not None and float(s) == int(s) and x.dim() == 4 and x.is_cuda
+                and x.dtype == torch.float32 and not (torch.is_grad_enabled() and x.requires_grad)):
+            return ops.upsample_nearest(x, int(s))
+        return super().forward(x)

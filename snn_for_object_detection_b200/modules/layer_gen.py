@@ -13,7 +13,8 @@ from torch import nn
 
 from .cells import LICell, LIFCell, SLICell, SNNCell, SynapseCell
 from .conv_lstm import ConvLSTM
-from .common import SodaBatchNorm2d, SodaConv2d, SodaPool2d, StateStorage, Storage, SumPool2d
+from .common import (SodaBatchNorm2d, SodaConv2d, SodaPool2d, SodaReLU, SodaSiLU, SodaTanh, SodaUpsample, StateStorage,
+                     Storage, SumPool2d)
 
 layers_list = (
     "Residual", "Dense", "LayerGen", "Pass", "Conv", "Norm", "LIF", "LI", "ReLU", "SiLU", "Tanh",
@@ -81,7 +82,7 @@ class Up(LayerGen):
         self.mode = mode
 
     def get(self, in_channels: int) -> Tuple[nn.Module, int]:
-        return nn.Upsample(scale_factor=self.scale, mode=self.mode), in_channels
+        return SodaUpsample(scale_factor=self.scale, mode=self.mode), in_channels
 
 
 class Norm(LayerGen):
@@ -117,17 +118,17 @@ class LI(LayerGen):
 
 class ReLU(LayerGen):
     def get(self, in_channels: int) -> Tuple[nn.Module, int]:
-        return nn.ReLU(), in_channels
+        return SodaReLU(), in_channels
 
 
 class SiLU(LayerGen):
     def get(self, in_channels: int) -> Tuple[nn.Module, int]:
-        return nn.SiLU(), in_channels
+        return SodaSiLU(), in_channels
 
 
 class Tanh(LayerGen):
     def get(self, in_channels: int) -> Tuple[nn.Module, int]:
-        return nn.Tanh(), in_channels
+        return SodaTanh(), in_channels
 
 
 class Return(LayerGen):

@@ -960,3 +960,33 @@ def bn_train_bwd_sync(gy: torch.Tensor, x: torch.Tensor, T: int, gamma, mean, in
         "soda_bn_train_bwd_from_sums",
     )
     return gx, gg, gb
+
+
+_UNARY_MODES = {"relu": 0, "silu": 1, "tanh": 2}
+
+
+@_prof("elementwise")
+def unary(x: torch.Tensor, mode: str) -> torch.Tensor:
+    """ReLU / SiLU / Tanh (reference LayerGens, ``models/modules/layer_gen.py:255-284``); keeps x's memory layout."""
+    _need_cuda(x)
+    if not _is_dense(x):
+        x = x.contiguous(memory_format=torch.channels_last) if x.dim() == 4 else x.contiguous()
+    y = torch.empty_like(x)
+    check(lib.soda_unary_fwd(x.data_ptr(), x.numel(), _UNARY_MODES[mode], y.data_ptr(), _stream()), "soda_unary_fwd")
+    if mode == "relu":
+        mark_exact(y, exact_bound(x))
+    return y
+
+
+@_prof("elementwise")
+def upsample_nearest(x: torch.Tensor, scale: int) -> torch.Tensor:
+    """``nn.Upsample(scale_factor=scale, mode="nearest")`` (reference LayerGen ``Up``, ``layer_gen.py:176-194``) on
+    pixel-major frames."""
+    _need_cuda(x)
+    if not x.is_contiguous(memory_format=torch.channels_last):
+        x = x.contiguous(memory_format=torch.channels_last)
+    N, Cc, H, W = x.shape
+    y = empty_pixel_major(N, Cc, H * scale, W * scale, x.device)
+    check(lib.soda_upsample_nearest(x.data_ptr(), N, H, W, Cc, int(scale), y.data_ptr(), _stream()),
+          "soda_upsample_nearest")
+    return mark_exact(y, exact_bound(x))

@@ -865,3 +865,28 @@ def test_sync_batchnorm_sums_exchange_equals_full_batch():
     rm1, rv1 = rm0.clone(), rv0.clone()
     ops.bn_train_fwd_sync(xs[0], T, gamma, beta, 1e-5, 0.1, rm1, rv1, fake_all_reduce_fwd)
     assert float((rm1 - rmF).abs().max()) < 1e-6 and float((rv1 - rvF).abs().max()) < 1e-5
+
+
+@pytest.mark.gpu
+def test_stateless_layergens_on_cuda_kernels():
+    """LayerGens ReLU / SiLU / Tanh / Up (reference layer_gen.py:176-194, :255-284) on the elementwise kernels against
+    torch on the same GPU: ReLU and nearest upsampling bit-exact, SiLU / Tanh to 2e-6 (expf / tanhf vs ATen);
+    channels_last and plain layouts; gradients take the torch route."""
+    from snn_for_object_detection_b200.modules.layer_gen import ReLU, SiLU, Tanh, Up
+
+    torch.manual_seed(8)
+    for x in (torch.randn(3, 20, 9, 11, device=DEV) * 3, (torch.randn(2, 8, 6, 5, device=DEV) * 3).contiguous(memory_format=torch.channels_last)):
+        with torch.no_grad():
+            assert torch.equal(ReLU().get(20)[0](x), torch.relu(x))
+            assert float((SiLU().get(20)[0](x) - F.silu(x)).abs().max()) < 2e-6 * 9
+            assert float((Tanh().get(20)[0](x) - torch.tanh(x)).abs().max()) < 2e-6
+            for s in (2, 3):
+                up = Up(scale=s).get(20)[0]
+                y = up(x)
+                assert y.shape == (x.shape[0], x.shape[1], x.shape[2] * s, x.shape[3] * s)
+                assert torch.equal(y, F.interpolate(x, scale_factor=s, mode="nearest"))
+            yb = Up(scale=2, mode="bilinear").get(20)[0](x)      # other modes: torch
+            assert torch.equal(yb, F.interpolate(x, scale_factor=2.0, mode="bilinear"))
+    xg = torch.randn(2, 4, 5, 5, device=DEV, requires_grad=True)
+    SiLU().get(4)[0](xg).sum().backward()
+    assert float(xg.grad.abs().sum()) > 0

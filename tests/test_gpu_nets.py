@@ -498,3 +498,36 @@ def test_conv_lstm_matches_reference_golden_and_protocols():
             y, st = block(X[t * 2:(t + 1) * 2], st)
             ys.append(y)
     assert Y.shape == (8, 16, 12, 16) and torch.equal(torch.cat(ys), Y)
+
+
+@pytest.mark.gpu
+def test_generated_net_with_up_and_activations_is_a_drop_in():
+    """ListGen mixing Conv/Norm/LIF with Up, ReLU and SiLU: layer-major == per-step protocol; the upsampled spike map
+    keeps its spike-count tag, so the following Conv takes the bf16-only operand scheme."""
+    from snn_for_object_detection_b200 import BlockGen, ops
+    from snn_for_object_detection_b200.modules.layer_gen import LIF, Conv, Norm, ReLU, SiLU, Up
+
+    torch.manual_seed(12)
+    block = BlockGen(2, [Conv(32, kernel_size=3, stride=2), Norm(), LIF(), Up(2), Conv(32, kernel_size=3), ReLU(),
+                         Conv(16, kernel_size=1), SiLU()]).to(DEV).eval()
+    for m in block.modules():
+        if isinstance(m, torch.nn.Conv2d):
+            torch.nn.init.normal_(m.weight, std=6.0 / (m.in_channels * m.kernel_size[0] ** 2) ** 0.5)
+    T, B = 6, 2
+    X = (torch.rand(T * B, 2, 24, 32, device=DEV) < 0.3).float()
+    prof = {}
+    ops.PROFILE = prof
+    try:
+        with torch.no_grad():
+            Y, _ = block.forward_seq(X, T)
+    finally:
+        ops.PROFILE = None
+    assert Y.shape == (T * B, 16, 24, 32) and float(Y.abs().sum()) > 0
+    tags = prof.get("conv2d_tags", []) + prof.get("conv_lif_tags", [])
+    assert any("(12, 32, 24, 32)->32" in t and t.endswith("exact1") for t in tags), tags
+    with torch.no_grad():
+        ys, st = [], None
+        for t in range(T):
+            y, st = block(X[t * B:(t + 1) * B], st)
+            ys.append(y)
+    assert torch.equal(torch.cat(ys), Y)
