@@ -24,6 +24,7 @@ ap.add_argument("--steps", type=int, default=3)
 ap.add_argument("--T", type=int, default=32)
 ap.add_argument("--batch", type=int, default=5)
 ap.add_argument("--hw", type=int, nargs=2, default=[240, 304])
+ap.add_argument("--profile-last", action="store_true", help="cudaProfilerStart/Stop around the last step (ncu --profile-from-start off)")
 ap.add_argument("--sync-bn", action="store_true", help="SyncBatchNorm: per-step statistics over the global batch")
 args = ap.parse_args()
 
@@ -53,6 +54,8 @@ times = []
 for it in range(args.steps + 1):
     torch.cuda.synchronize()
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    if args.profile_last and it == args.steps:
+        torch.cuda.cudart().cudaProfilerStart()
     e0.record()
     opt.zero_grad(set_to_none=True)
     loss = model._loss(model(X), labels)
@@ -61,6 +64,8 @@ for it in range(args.steps + 1):
     opt.step()
     e1.record()
     torch.cuda.synchronize()
+    if args.profile_last and it == args.steps:
+        torch.cuda.cudart().cudaProfilerStop()
     if it > 0:
         times.append(e0.elapsed_time(e1))
 ms = sum(times) / len(times)
