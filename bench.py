@@ -279,6 +279,8 @@ def run_gpu_arm(args):
                     sys.stderr.write(f"{k:8s} {a.elapsed_time(b):8.3f} ms  {tag}\n")
         n_conv = len(prof.get("conv2d", [])) + len(prof.get("conv_lif", []))
         rate = float((g_cls.abs() > 0).float().mean())
+        if not rate > 0.5:
+            raise SystemExit(f"bench.py: the network is silent (class outputs {rate:.3f} non-zero) - calibration failed")
 
     pk, pk_src = peaks()
     frames_per_step = T * B

@@ -13,7 +13,7 @@ from __future__ import annotations
 
 import torch
 
-from .. import ops
+from .. import generator, ops
 from ..modules.common import SodaConv2d
 
 
@@ -34,8 +34,13 @@ def calibrate(model: torch.nn.Module, X: torch.Tensor, gain: float = 5.0) -> Non
     was_training = model.training
     model.eval()
     SodaConv2d.forward = measuring_forward
+    # the planner's fused Conv -> Norm -> LIF kernels never call SodaConv2d.forward: plan them out while measuring,
+    # or the layers they cover keep identity statistics and stay silent (and with them everything downstream)
+    fused_plan = generator._fused_lif_plan
+    generator._fused_lif_plan = lambda *a, **k: None
     try:
         model(X)
     finally:
         SodaConv2d.forward = orig
+        generator._fused_lif_plan = fused_plan
         model.train(was_training)
