@@ -531,3 +531,25 @@ def test_generated_net_with_up_and_activations_is_a_drop_in():
             y, st = block(X[t * B:(t + 1) * B], st)
             ys.append(y)
     assert torch.equal(torch.cat(ys), Y)
+
+
+@pytest.mark.gpu
+def test_package_calibration_reaches_the_fused_layers_and_the_network_is_alive():
+    """bench.py's synthetic-weight calibration (utils/calibrate.py) must also cover the layers the planner runs as
+    fused Conv -> Norm -> LIF kernels (the event-frame layer is one): with raw initialisation they are silent
+     and every output downstream is exactly zero."""
+    import snn_for_object_detection_b200 as pkg
+    from snn_for_object_detection_b200.utils.calibrate import calibrate
+
+    torch.manual_seed(0)
+    model = pkg.TinyYolo(num_classes=2).to(DEV).eval()
+    X = (torch.rand(8, 2, 2, 96, 128, device=DEV) < 0.07).float()
+    with torch.no_grad():
+        _, cls0, _ = model(X)
+        assert float((cls0 != 0).float().mean()) == 0.0      # the premise: reference init is silent
+        calibrate(model, X, gain=5.0)
+        stem_bn = next(m for m in model.modules() if isinstance(m, torch.nn.BatchNorm2d))
+        assert float(stem_bn.weight.mean()) == 5.0 and float(stem_bn.running_var.mean()) != 1.0
+        _, cls, bbox = model(X)
+    assert float((cls != 0).float().mean()) > 0.9 and float((bbox != 0).float().mean()) > 0.9
+    assert torch.isfinite(cls).all() and torch.isfinite(bbox).all()
