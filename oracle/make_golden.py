@@ -297,6 +297,35 @@ def golden_conv_lstm(ref):
     print("conv_lstm: out std", float(torch.stack(outs).std()))
 
 
+def golden_li_from_sli(ref):
+    """Pins the LI update (and the sub-threshold half of LIF) to arithmetic that is IN the reference tree.
+    ``sli_feed_forward_step`` (models/modules/sli.py:110-126) is the author's derivative of norse's LI cell with
+    one extra factor, ``sigmoid(v_st - |v|)``, on the input.  With ``v_st = 1e4`` that factor is exactly 1.0f for
+    every |v| < 9.9e3, ``input * 1.0f`` is exact, and the function IS the LI step: jump, dv with the
+    ``dt * tau_mem_inv`` constant, di with ``-dt * tau_syn_inv``, same fp32 op order.  T = 16 steps with carried
+    state, once with large inputs (LI) and once with inputs small enough that v never reaches v_th = 1 (the LIF
+    cell then never spikes or resets, so its (v, i) must equal LI's)."""
+    import sys
+
+    sli = sys.modules["models.modules.sli"]
+    torch.manual_seed(23)
+    prm = sli.SLIParameters(v_st=torch.as_tensor(1.0e4))
+    res = {}
+    for tag, scale, shift in (("big", 4.0, 1.0), ("sub", 0.12, 0.02)):
+        x = torch.randn(16, 2, 8, 5, 6) * scale + shift
+        state, outs, currents = sli.SLIState(v=torch.zeros_like(x[0]), i=torch.zeros_like(x[0])), [], []
+        for t in range(x.shape[0]):
+            assert bool((torch.sigmoid(prm.v_st - state.v.abs()) == 1.0).all())
+            out, state = sli.sli_feed_forward_step(x[t], state, prm, 0.001)
+            outs.append(out)
+            currents.append(state.i)
+        res["x_" + tag], res["v_" + tag] = x.numpy(), torch.stack(outs).numpy()
+        res["i_" + tag] = torch.stack(currents).numpy()
+    assert float(np.abs(res["v_sub"]).max()) < 0.95, float(np.abs(res["v_sub"]).max())
+    np.savez_compressed(os.path.join(OUT, "li_from_sli.npz"), **res)
+    print("li_from_sli: max |v| big", float(np.abs(res["v_big"]).max()), "sub", float(np.abs(res["v_sub"]).max()))
+
+
 def main():
     os.makedirs(OUT, exist_ok=True)
     ref = load_reference()
@@ -304,6 +333,7 @@ def main():
     golden_box(ref)
     golden_roi(ref)
     golden_sli(ref)
+    golden_li_from_sli(ref)
     golden_synapse(ref)
     golden_conv_lstm(ref)
     golden_vgg(ref)

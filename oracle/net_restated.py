@@ -28,6 +28,20 @@ from . import norse_restated as nr
 _LIF = nr.LIFCell()
 _LI = nr.LICell()
 
+# "fp32": nn.Conv2d.forward as the reference runs it.  "fp64": the convolution is accumulated in float64 and
+# rounded once to fp32 ("the oracle should run convs in fp64 to adjudicate") - the distance
+# between the two runs is the NOISE FLOOR of the comparison: what any two correct fp32 implementations with
+# different summation order may differ by on this net.
+CONV_DTYPE = "fp32"
+
+
+def _conv(layer: nn.Conv2d, Y: torch.Tensor) -> torch.Tensor:
+    if CONV_DTYPE == "fp32":
+        return nn.Conv2d.forward(layer, Y)
+    b = None if layer.bias is None else layer.bias.double()
+    return F.conv2d(Y.double(), layer.weight.double(), b, layer.stride, layer.padding, layer.dilation,
+                    layer.groups).float()
+
 
 def _kind(m: nn.Module) -> str:
     return type(m).__name__
@@ -60,7 +74,7 @@ def block_forward(block, X, state=None, taps: Optional[dict] = None):
             elif name in ("LIFCell", "LICell", "StateStorage"):
                 Y, branch_state[idx] = _cell_step(layer, Y, branch_state[idx], taps)
             elif isinstance(layer, nn.Conv2d):
-                Y = nn.Conv2d.forward(layer, Y)
+                Y = _conv(layer, Y)
             elif isinstance(layer, nn.BatchNorm2d):
                 Y = nn.BatchNorm2d.forward(layer, Y)
             elif name == "SumPool2d":

@@ -158,6 +158,33 @@ def test_li_scan(tanh):
         assert torch.equal(out.cpu(), vo)
 
 
+def test_li_and_subthreshold_lif_kernels_pinned_to_the_reference_sli_cell():
+    """Rows a8/a9: soda_li_fwd, and soda_lif_fwd below threshold, are bit-identical to T = 16 steps of the
+    reference's OWN sli_feed_forward_step with v_st = 1e4 (= the LI update; tests/golden/li_from_sli.npz,
+    models/modules/sli.py:110-126), also when the scan is cut in two with the state carried through HBM."""
+    from helpers import golden
+
+    pkg = _pkg()
+    g = golden("li_from_sli.npz")
+    x = torch.from_numpy(g["x_big"]).to(DEV)
+    T = x.shape[0]
+    v_ref, i_ref = torch.from_numpy(g["v_big"]), torch.from_numpy(g["i_big"])
+    out, v, i, it = pkg.ops.li_scan(x.reshape(T, -1), T, want_trace=True)
+    assert torch.equal(out.cpu().reshape(v_ref.shape), v_ref) and torch.equal(it.cpu().reshape(i_ref.shape), i_ref)
+    assert torch.equal(v.cpu().reshape(v_ref[-1].shape), v_ref[-1])
+    h = 7
+    _, v1, i1, _ = pkg.ops.li_scan(x[:h].reshape(h, -1), h)
+    out2, v2, i2, _ = pkg.ops.li_scan(x[h:].reshape(T - h, -1), T - h, v0=v1, i0=i1)
+    assert torch.equal(out2.cpu().reshape(v_ref[h:].shape), v_ref[h:])
+    assert torch.equal(i2.cpu().reshape(i_ref[-1].shape), i_ref[-1])
+    # LIF below threshold: never spikes, never resets => the same (v, i) trajectory
+    x = torch.from_numpy(g["x_sub"]).to(DEV)
+    v_ref, i_ref = torch.from_numpy(g["v_sub"]), torch.from_numpy(g["i_sub"])
+    z, v, i, _, vt, it = pkg.ops.lif_scan(x.reshape(T, -1), T, want_trace=True)
+    assert float(z.abs().max()) == 0.0
+    assert torch.equal(vt.cpu().reshape(v_ref.shape), v_ref) and torch.equal(it.cpu().reshape(i_ref.shape), i_ref)
+
+
 def test_lif_decay_first_order_switch():
     pkg = _pkg()
     torch.manual_seed(4)

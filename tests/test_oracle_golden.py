@@ -235,3 +235,65 @@ def test_st_sample_stream_matches_live_reference_parse_data():
                     assert np.array_equal(ob.bin_st(np.ascontiguousarray(rec), t0, step_us, T, H, W), data[0].numpy())
                 if not ok:
                     break
+
+
+def _scan_cell(step, cell_state, x):
+    vs, cs, state = [], [], cell_state
+    for t in range(x.shape[0]):
+        out, state = step(x[t], state)
+        vs.append(state.v)
+        cs.append(state.i)
+    return torch.stack(vs), torch.stack(cs), out
+
+
+def test_li_and_subthreshold_lif_pinned_to_the_reference_sli_cell():
+    """Rows a8/a9: ``tests/golden/li_from_sli.npz`` holds T = 16 steps of the reference's OWN
+    ``sli_feed_forward_step`` (models/modules/sli.py:110-126) with ``v_st = 1e4``, where its saturation factor is
+    exactly 1.0f and the function is the LI update.  The norse restatement must reproduce it bit for bit: LI on
+    large inputs, and LIF on inputs that never reach the threshold (no spike, no reset => same (v, i))."""
+    from oracle import norse_restated as nr
+
+    g = golden("li_from_sli.npz")
+    with torch.no_grad():
+        x = torch.from_numpy(g["x_big"])
+        s0 = nr.LIState(v=torch.zeros_like(x[0]), i=torch.zeros_like(x[0]))
+        v, i, _ = _scan_cell(lambda a, s: nr.li_feed_forward_step(a, s), s0, x)
+        assert torch.equal(v, torch.from_numpy(g["v_big"])) and torch.equal(i, torch.from_numpy(g["i_big"]))
+        x = torch.from_numpy(g["x_sub"])
+        s0 = nr.LIFFeedForwardState(v=torch.zeros_like(x[0]), i=torch.zeros_like(x[0]))
+        zs = []
+
+        def lif(a, s):
+            z, s = nr.lif_feed_forward_step(a, s)
+            zs.append(z)
+            return z, s
+
+        v, i, _ = _scan_cell(lif, s0, x)
+        assert float(torch.stack(zs).abs().max()) == 0.0
+        assert torch.equal(v, torch.from_numpy(g["v_sub"])) and torch.equal(i, torch.from_numpy(g["i_sub"]))
+        # the cells' own initial state (v = v_leak = 0, i = 0) gives the same sequence
+        out, st = nr.LICell()(torch.from_numpy(g["x_big"])[0])
+        assert torch.equal(out, torch.from_numpy(g["v_big"])[0])
+
+
+def test_li_pin_live_reference():
+    """Same check against the live reference function on fresh inputs (build container only)."""
+    import sys
+
+    from oracle import norse_restated as nr
+    from oracle import ref_shim
+
+    if not ref_shim.reference_available():
+        pytest.skip("reference tree not present")
+    ref_shim.load_reference()
+    sli = sys.modules["models.modules.sli"]
+    prm = sli.SLIParameters(v_st=torch.as_tensor(1.0e4))
+    torch.manual_seed(99)
+    x = torch.randn(20, 7, 33) * 6.0
+    with torch.no_grad():
+        sr = sli.SLIState(v=torch.zeros_like(x[0]), i=torch.zeros_like(x[0]))
+        so = nr.LIState(v=torch.zeros_like(x[0]), i=torch.zeros_like(x[0]))
+        for t in range(x.shape[0]):
+            vr, sr = sli.sli_feed_forward_step(x[t], sr, prm, 0.001)
+            vo, so = nr.li_feed_forward_step(x[t], so)
+            assert torch.equal(vr, vo) and torch.equal(sr.i, so.i)
