@@ -40,7 +40,7 @@ typedef enum {
   SODA_ERR_CUDA = 3          /* a CUDA runtime/driver call failed (message has the code) */
 } soda_status_t;
 
-#define SODA_ABI_VERSION 1
+#define SODA_ABI_VERSION 2
 
 struct soda_neuron_params_s; /* defined below (LIF / LI section) */
 
@@ -249,6 +249,76 @@ SODA_API int soda_lif_bwd(const soda_neuron_params_t* p, const float* grad_out, 
 SODA_API int soda_li_bwd(const soda_neuron_params_t* p, const float* grad_out, const float* grad_v_T,
                 const float* grad_i_T, int T, int64_t n, float* grad_x, float* grad_v0,
                 float* grad_i0, void* stream);
+
+/* ---------------------------------------------------------------------------------------------
+ * Pre-split ("packed") activation formats and the convolution that consumes them (rows N1 / N2 of the scope table:
+ * "spikes are written as packed maps that the next layer consumes directly", "LIF fused into the conv epilogue")
+ *
+ * Between two layers of a generated net (models/generator.py:184-198: the output of one LayerGen module is the
+ * input of the next) an activation tensor need not be fp32: the PRODUCER's epilogue writes it in the form the
+ * CONSUMER's tensor-core operands have, so the consumer's TMA loads are its MMA operands.
+ *   SODA_ACT_F32  : fp32 pixel-major (the external contract: network inputs / outputs, neuron state, StateStorage)
+ *   SODA_ACT_PAIR : per pixel and 32-channel group, 128 bytes = fp16 hi[32] | fp16 lo[32] with x = hi + lo
+ *                   (hi = rn16(x), lo = rn16(x - hi): 22 significant bits).  Same bytes per value as fp32, hence the
+ *                   same strides: element (n, y, x, c) of a PAIR tensor starts at byte
+ *                   4 * (n * batch_stride + (y * W + x) * pix_stride + (c & ~31)) + 2 * (c & 31)  (+ 64 for lo).
+ *                   Channel counts, channel-slice offsets and strides are multiples of 32; |x| <= 65504.
+ *   SODA_ACT_HALF : fp16 pixel-major, for values exact in fp16: spikes {0,1} (layer_gen.py:217-235), sum-pooled
+ *                   spike counts (common.py:45-49), sums of spike maps - integers <= 2048.  2 bytes per value.
+ * Strides in every descriptor below are in ELEMENTS (channels) of the tensor's own format.
+ * ------------------------------------------------------------------------------------------- */
+#define SODA_ACT_F32 0
+#define SODA_ACT_PAIR 1
+#define SODA_ACT_HALF 2
+/* flags: the PAIR input's lo halves are all zero (an exact tensor stored as PAIR): a_lo * w_hi is skipped */
+#define SODA_PCONV_FLAG_INPUT_EXACT 1
+
+typedef struct {
+  int N, H, W, Cin, Cout, k, stride;
+  int in_fmt, out_fmt, res_fmt;   /* in: PAIR / HALF; out, res: any */
+  int flags;
+  int64_t in_batch_stride, in_pix_stride;
+  int64_t out_batch_stride, out_pix_stride;
+  int64_t res_batch_stride, res_pix_stride;
+} soda_pconv_desc_t;
+
+/* Weights [Cout, Cin, k, k] (the state_dict tensor) * scale[Cout] (folded BatchNorm, NULL = 1) * *mult (device
+ * scalar, a power of two that puts the largest weight near 2^11, NULL = 1) -> fp16 hi | fp16 lo planes in the
+ * k-block order of the input format.  soda_pconv_packed_bytes() bytes, caller-owned.  The convolution multiplies its
+ * accumulators by *descale = 1 / *mult. */
+SODA_API int64_t soda_pconv_packed_bytes(int Cout, int Cin, int k);
+SODA_API int soda_pconv_pack_weights(const float* weight, const float* scale, const float* mult, int Cout, int Cin,
+                                     int k, int in_fmt, void* packed, void* stream);
+/* 1 if soda_pconv_fwd takes this descriptor and these pointers (alignment), else 0. */
+SODA_API int soda_pconv_supported(const soda_pconv_desc_t* d, const void* x, const void* y, const void* residual);
+/*   replaces: nn.Conv2d (layer_gen.py:129-136) + eval BatchNorm (:211-214) + Residual sum (generator.py:146) +
+ *             concat-slice store (:158), as soda_conv2d_fwd, on PAIR / HALF input.
+ *   y = descale * sum(x * w) + shift (+ residual), written as d->out_fmt.  kind::f16 tensor-core products
+ *   a_hi*w_hi + a_hi*w_lo + a_lo*w_hi with fp32 accumulation (PAIR) or a*w_hi + a*w_lo (HALF).
+ *   status: NULL, or a device counter incremented for every output value beyond fp16's range (PAIR / HALF out). */
+SODA_API int soda_pconv_fwd(const soda_pconv_desc_t* d, const void* x, const void* packed, const float* descale,
+                            const float* shift, const void* residual, void* y, unsigned int* status, void* stream);
+/* Fused Conv -> BatchNorm(eval) -> LIF over T steps on PAIR / HALF input (cf. soda_conv_lif_fwd): membrane state in
+ * registers for all T steps, spikes (+ residual) written as d->out_fmt; v0 / i0 / v_out / i_out fp32 [B, Ho, Wo, Cout]. */
+SODA_API int soda_pconv_lif_fwd(const soda_pconv_desc_t* d, const void* x, const void* packed, const float* descale,
+                                const float* shift, const void* residual, int T, const soda_neuron_params_t* np,
+                                const float* v0, const float* i0, void* y, float* v_out, float* i_out,
+                                unsigned int* status, void* stream);
+
+/* Format conversion / strided copy of a pixel-major tensor [n_frames][pix_per_frame][C] between any two formats
+ * (decode to fp32, re-encode): the boundary between the packed region of a net and fp32 callers, and the copy of a
+ * tensor into a concat slice of another format (generator.py:158).  C % 32 == 0 when PAIR is involved, else C % 8. */
+SODA_API int soda_act_convert(const void* src, int src_fmt, int64_t src_batch_stride, int64_t src_pix_stride, void* dst,
+                              int dst_fmt, int64_t dst_batch_stride, int64_t dst_pix_stride, int64_t n_frames,
+                              int64_t pix_per_frame, int C, unsigned int* status, void* stream);
+
+/* LIF scan (soda_lif_fwd's arithmetic) on an fp32 conv output with the Residual sum and the store fused, residual
+ * and output in any format: x [T][n_pix][C] dense fp32; residual / out element (t, q, c) addressed through their
+ * pixel strides (frames of n_pix pixels are dense: batch stride = n_pix * pix_stride); C % 32 == 0. */
+SODA_API int soda_lif_fmt_fwd(const soda_neuron_params_t* p, const float* x, const float* v0, const float* i0, int T,
+                              int64_t n_pix, int C, const void* residual, int res_fmt, int64_t res_pix_stride, void* out,
+                              int out_fmt, int64_t out_pix_stride, float* v_out, float* i_out, unsigned int* status,
+                              void* stream);
 
 /* ---------------------------------------------------------------------------------------------
  * Pooling (K5)

@@ -18,6 +18,10 @@ SODA_CONV_FP32 = 0
 SODA_CONV_TC = 1
 SODA_CONV_FLAG_INPUT_EXACT_TF32 = 1
 SODA_CONV_FLAG_INPUT_EXACT_BF16 = 2
+SODA_ACT_F32 = 0
+SODA_ACT_PAIR = 1
+SODA_ACT_HALF = 2
+SODA_PCONV_FLAG_INPUT_EXACT = 1
 
 
 class SodaError(RuntimeError):
@@ -35,6 +39,28 @@ class ConvDesc(C.Structure):
         ("stride", C.c_int),
         ("in_nchw", C.c_int),
         ("kind", C.c_int),
+        ("flags", C.c_int),
+        ("in_batch_stride", C.c_int64),
+        ("in_pix_stride", C.c_int64),
+        ("out_batch_stride", C.c_int64),
+        ("out_pix_stride", C.c_int64),
+        ("res_batch_stride", C.c_int64),
+        ("res_pix_stride", C.c_int64),
+    ]
+
+
+class PConvDesc(C.Structure):
+    _fields_ = [
+        ("N", C.c_int),
+        ("H", C.c_int),
+        ("W", C.c_int),
+        ("Cin", C.c_int),
+        ("Cout", C.c_int),
+        ("k", C.c_int),
+        ("stride", C.c_int),
+        ("in_fmt", C.c_int),
+        ("out_fmt", C.c_int),
+        ("res_fmt", C.c_int),
         ("flags", C.c_int),
         ("in_batch_stride", C.c_int64),
         ("in_pix_stride", C.c_int64),
@@ -72,6 +98,15 @@ SIGNATURES = {
     "soda_conv2d_fwd": (_i, [C.POINTER(ConvDesc), _vp, _vp, _vp, _vp, _vp, _vp]),
     "soda_conv_lif_fwd": (_i, [C.POINTER(ConvDesc), _vp, _vp, _vp, _vp, _i, C.POINTER(NeuronParams), _vp, _vp, _vp,
                                 _vp, _vp, _vp]),
+    "soda_pconv_packed_bytes": (_i64, [_i, _i, _i]),
+    "soda_pconv_pack_weights": (_i, [_vp, _vp, _vp, _i, _i, _i, _i, _vp, _vp]),
+    "soda_pconv_supported": (_i, [C.POINTER(PConvDesc), _vp, _vp, _vp]),
+    "soda_pconv_fwd": (_i, [C.POINTER(PConvDesc), _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp]),
+    "soda_pconv_lif_fwd": (_i, [C.POINTER(PConvDesc), _vp, _vp, _vp, _vp, _vp, _i, C.POINTER(NeuronParams), _vp, _vp,
+                                 _vp, _vp, _vp, _vp, _vp]),
+    "soda_act_convert": (_i, [_vp, _i, _i64, _i64, _vp, _i, _i64, _i64, _i64, _i64, _i, _vp, _vp]),
+    "soda_lif_fmt_fwd": (_i, [C.POINTER(NeuronParams), _vp, _vp, _vp, _i, _i64, _i, _vp, _i, _i64, _vp, _i, _i64,
+                              _vp, _vp, _vp, _vp]),
     "soda_lif_fwd": (_i, [C.POINTER(NeuronParams), _vp, _vp, _vp, _i, _i64, _vp, _vp, _vp, _vp, _vp, _vp, _vp]),
     "soda_lif_res_fwd": (_i, [C.POINTER(NeuronParams), _vp, _vp, _vp, _i, _i64, _i, _vp, _i64, _vp, _i64, _vp, _vp,
                               _vp]),

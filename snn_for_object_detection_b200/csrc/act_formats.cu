@@ -1,0 +1,208 @@
+// Packed activation formats (include/soda_b200.h: SODA_ACT_F32 / PAIR / HALF): conversion between them
+// (soda_act_convert) and the LIF scan whose residual input and output are in any of them (soda_lif_fmt_fwd).
+//
+// Reference call sites: the tensor handed from one LayerGen module to the next by models/generator.py:184-198;
+// torch.cat into a Dense buffer (:158), the Residual sum (:146), norse LIFCell (models/modules/layer_gen.py:233).
+// Both kernels are pure HBM streams: one thread owns one pixel's 8-channel piece (a 16- or 32-byte vector in every
+// format), consecutive threads take consecutive pieces, so a warp reads and writes whole 128-byte lines.
+#include <cuda_fp16.h>
+
+#include <algorithm>
+
+#include "common.cuh"
+#include "neuron.cuh"
+
+namespace soda {
+
+__device__ __forceinline__ uint32_t h2_pack(float lo, float hi) {
+  uint32_t d;
+  asm("cvt.rn.satfinite.f16x2.f32 %0, %1, %2;" : "=r"(d) : "f"(hi), "f"(lo));
+  return d;
+}
+__device__ __forceinline__ float2 h2_unpack(uint32_t v) {
+  return __half22float2(*reinterpret_cast<const __half2*>(&v));
+}
+
+// byte offset of the 8-channel piece starting at channel c (c % 8 == 0) inside a pixel
+__device__ __forceinline__ int64_t piece_off(int fmt, int c) {
+  if (fmt == SODA_ACT_F32) return (int64_t)c * 4;
+  if (fmt == SODA_ACT_HALF) return (int64_t)c * 2;
+  return (int64_t)(c & ~31) * 4 + (int64_t)(c & 31) * 2;   // PAIR: hi piece; lo piece 64 bytes further
+}
+
+__device__ __forceinline__ void load8(const uint8_t* px, int fmt, int c, float (&v)[8]) {
+  const uint8_t* q = px + piece_off(fmt, c);
+  if (fmt == SODA_ACT_F32) {
+    const float4 a = __ldg(reinterpret_cast<const float4*>(q)), b = __ldg(reinterpret_cast<const float4*>(q + 16));
+    v[0] = a.x, v[1] = a.y, v[2] = a.z, v[3] = a.w, v[4] = b.x, v[5] = b.y, v[6] = b.z, v[7] = b.w;
+  } else {
+    const uint4 h = __ldg(reinterpret_cast<const uint4*>(q));
+    const uint32_t hw[4] = {h.x, h.y, h.z, h.w};
+#pragma unroll
+    for (int k = 0; k < 4; ++k) {
+      const float2 f = h2_unpack(hw[k]);
+      v[2 * k] = f.x, v[2 * k + 1] = f.y;
+    }
+    if (fmt == SODA_ACT_PAIR) {
+      const uint4 l = __ldg(reinterpret_cast<const uint4*>(q + 64));
+      const uint32_t lw[4] = {l.x, l.y, l.z, l.w};
+#pragma unroll
+      for (int k = 0; k < 4; ++k) {
+        const float2 f = h2_unpack(lw[k]);
+        v[2 * k] += f.x, v[2 * k + 1] += f.y;
+      }
+    }
+  }
+}
+
+__device__ __forceinline__ unsigned int store8(uint8_t* px, int fmt, int c, const float (&v)[8]) {
+  uint8_t* q = px + piece_off(fmt, c);
+  if (fmt == SODA_ACT_F32) {
+    *reinterpret_cast<float4*>(q) = make_float4(v[0], v[1], v[2], v[3]);
+    *reinterpret_cast<float4*>(q + 16) = make_float4(v[4], v[5], v[6], v[7]);
+    return 0;
+  }
+  unsigned int over = 0;
+  uint32_t hi[4], lo[4];
+#pragma unroll
+  for (int k = 0; k < 4; ++k) {
+    hi[k] = h2_pack(v[2 * k], v[2 * k + 1]);
+    const float2 f = h2_unpack(hi[k]);
+    lo[k] = h2_pack(v[2 * k] - f.x, v[2 * k + 1] - f.y);
+    over += (fabsf(v[2 * k]) > 65504.f) + (fabsf(v[2 * k + 1]) > 65504.f);
+  }
+  *reinterpret_cast<uint4*>(q) = make_uint4(hi[0], hi[1], hi[2], hi[3]);
+  if (fmt == SODA_ACT_PAIR) *reinterpret_cast<uint4*>(q + 64) = make_uint4(lo[0], lo[1], lo[2], lo[3]);
+  return over;
+}
+
+__global__ void __launch_bounds__(256)
+act_convert_kernel(const uint8_t* __restrict__ src, int src_fmt, int64_t src_bs, int64_t src_ps, uint8_t* __restrict__ dst,
+                   int dst_fmt, int64_t dst_bs, int64_t dst_ps, int64_t n_frames, int64_t pix_per_frame, int C,
+                   unsigned int* status) {
+  pdl_trigger();
+  const int pieces = C >> 3;
+  const int64_t total = n_frames * pix_per_frame * pieces;
+  unsigned int over = 0;
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (int64_t)gridDim.x * blockDim.x) {
+    const int pc = (int)(i % pieces);
+    const int64_t pix = i / pieces;
+    const int64_t f = pix / pix_per_frame, q = pix - f * pix_per_frame;
+    float v[8];
+    load8(src + f * src_bs + q * src_ps, src_fmt, pc * 8, v);
+    over += store8(dst + f * dst_bs + q * dst_ps, dst_fmt, pc * 8, v);
+  }
+  if (status != nullptr && over != 0) atomicAdd(status, over);
+}
+
+// One thread: 8 channels of one pixel for all T steps, state in registers; loads of 4 steps are issued before the
+// first of them is consumed so that 8 x 32 bytes per thread are in flight.
+__global__ void __launch_bounds__(256)
+lif_fmt_fwd_kernel(NP p, const float* __restrict__ x, const float* __restrict__ v0, const float* __restrict__ i0, int T,
+                   int64_t n_pix, int C, const uint8_t* __restrict__ residual, int res_fmt, int64_t res_ps,
+                   uint8_t* __restrict__ out, int out_fmt, int64_t out_ps, float* __restrict__ v_out,
+                   float* __restrict__ i_out, unsigned int* status) {
+  pdl_trigger();
+  const int pieces = C >> 3;
+  const int64_t total = n_pix * pieces;
+  const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= total) return;
+  const int c = (int)(i % pieces) * 8;
+  const int64_t q = i / pieces;
+  const int64_t soff = q * C + c;
+  float v[8], cur[8];
+  if (v0 != nullptr) {
+    const float4 a = __ldg(reinterpret_cast<const float4*>(v0 + soff)), b = __ldg(reinterpret_cast<const float4*>(v0 + soff + 4));
+    const float4 e = __ldg(reinterpret_cast<const float4*>(i0 + soff)), f = __ldg(reinterpret_cast<const float4*>(i0 + soff + 4));
+    v[0] = a.x, v[1] = a.y, v[2] = a.z, v[3] = a.w, v[4] = b.x, v[5] = b.y, v[6] = b.z, v[7] = b.w;
+    cur[0] = e.x, cur[1] = e.y, cur[2] = e.z, cur[3] = e.w, cur[4] = f.x, cur[5] = f.y, cur[6] = f.z, cur[7] = f.w;
+  } else {
+#pragma unroll
+    for (int k = 0; k < 8; ++k) v[k] = p.v_leak, cur[k] = 0.f;
+  }
+  const int64_t step = n_pix * C;   // floats between two time steps of x
+  unsigned int over = 0;
+  for (int t0 = 0; t0 < T; t0 += 4) {
+    float xin[4][8], rin[4][8];
+#pragma unroll
+    for (int u = 0; u < 4; ++u) {
+      if (t0 + u < T) {
+        const float* xp = x + (int64_t)(t0 + u) * step + soff;
+        const float4 a = __ldg(reinterpret_cast<const float4*>(xp)), b = __ldg(reinterpret_cast<const float4*>(xp + 4));
+        xin[u][0] = a.x, xin[u][1] = a.y, xin[u][2] = a.z, xin[u][3] = a.w;
+        xin[u][4] = b.x, xin[u][5] = b.y, xin[u][6] = b.z, xin[u][7] = b.w;
+        if (residual != nullptr) load8(residual + ((int64_t)(t0 + u) * n_pix + q) * res_ps, res_fmt, c, rin[u]);
+      }
+    }
+#pragma unroll
+    for (int u = 0; u < 4; ++u) {
+      if (t0 + u < T) {
+        float o[8];
+#pragma unroll
+        for (int k = 0; k < 8; ++k) {
+          float z, vd;
+          lif_step(p, xin[u][k], v[k], cur[k], z, vd);
+          o[k] = residual != nullptr ? z + rin[u][k] : z;
+        }
+        over += store8(out + ((int64_t)(t0 + u) * n_pix + q) * out_ps, out_fmt, c, o);
+      }
+    }
+  }
+  *reinterpret_cast<float4*>(v_out + soff) = make_float4(v[0], v[1], v[2], v[3]);
+  *reinterpret_cast<float4*>(v_out + soff + 4) = make_float4(v[4], v[5], v[6], v[7]);
+  *reinterpret_cast<float4*>(i_out + soff) = make_float4(cur[0], cur[1], cur[2], cur[3]);
+  *reinterpret_cast<float4*>(i_out + soff + 4) = make_float4(cur[4], cur[5], cur[6], cur[7]);
+  if (status != nullptr && over != 0) atomicAdd(status, over);
+}
+
+static inline int fmt_bytes(int fmt) { return fmt == SODA_ACT_HALF ? 2 : 4; }
+static inline bool fmt_ok(int fmt) { return fmt >= SODA_ACT_F32 && fmt <= SODA_ACT_HALF; }
+// pointer / stride (in elements) alignment a format needs for the vector accesses above
+static inline bool fmt_aligned(const void* p, int fmt, int64_t s0, int64_t s1) {
+  const int al = fmt == SODA_ACT_PAIR ? 128 : 16;
+  const int b = fmt_bytes(fmt);
+  return (reinterpret_cast<uintptr_t>(p) % al) == 0 && (s0 * b) % al == 0 && (s1 * b) % al == 0;
+}
+
+}  // namespace soda
+
+extern "C" int soda_act_convert(const void* src, int src_fmt, int64_t src_batch_stride, int64_t src_pix_stride, void* dst,
+                                int dst_fmt, int64_t dst_batch_stride, int64_t dst_pix_stride, int64_t n_frames,
+                                int64_t pix_per_frame, int C, unsigned int* status, void* stream) {
+  using namespace soda;
+  if (!src || !dst) return fail(SODA_ERR_BAD_ARG, "act_convert: null pointer");
+  if (!fmt_ok(src_fmt) || !fmt_ok(dst_fmt)) return fail(SODA_ERR_BAD_ARG, "act_convert: unknown format");
+  if (n_frames <= 0 || pix_per_frame <= 0 || C <= 0) return fail(SODA_ERR_BAD_ARG, "act_convert: non-positive size");
+  const bool pair = src_fmt == SODA_ACT_PAIR || dst_fmt == SODA_ACT_PAIR;
+  if (C % (pair ? 32 : 8) != 0) return fail(SODA_ERR_UNSUPPORTED, "act_convert: C must be a multiple of 32 (PAIR) / 8");
+  if (!fmt_aligned(src, src_fmt, src_batch_stride, src_pix_stride) || !fmt_aligned(dst, dst_fmt, dst_batch_stride, dst_pix_stride))
+    return fail(SODA_ERR_BAD_ARG, "act_convert: misaligned pointer or stride");
+  const int64_t total = n_frames * pix_per_frame * (C / 8);
+  const unsigned grid = (unsigned)std::min<int64_t>(ceil_div(total, 256), 148 * 16);
+  act_convert_kernel<<<grid, 256, 0, (cudaStream_t)stream>>>(
+      reinterpret_cast<const uint8_t*>(src), src_fmt, src_batch_stride * fmt_bytes(src_fmt), src_pix_stride * fmt_bytes(src_fmt),
+      reinterpret_cast<uint8_t*>(dst), dst_fmt, dst_batch_stride * fmt_bytes(dst_fmt), dst_pix_stride * fmt_bytes(dst_fmt),
+      n_frames, pix_per_frame, C, status);
+  return after_launch("act_convert_kernel");
+}
+
+extern "C" int soda_lif_fmt_fwd(const soda_neuron_params_t* p, const float* x, const float* v0, const float* i0, int T,
+                                int64_t n_pix, int C, const void* residual, int res_fmt, int64_t res_pix_stride, void* out,
+                                int out_fmt, int64_t out_pix_stride, float* v_out, float* i_out, unsigned int* status,
+                                void* stream) {
+  using namespace soda;
+  if (!p || !x || !out || !v_out || !i_out) return fail(SODA_ERR_BAD_ARG, "lif_fmt: null pointer");
+  if ((v0 == nullptr) != (i0 == nullptr)) return fail(SODA_ERR_BAD_ARG, "lif_fmt: v0 / i0 must come together");
+  if (T <= 0 || n_pix <= 0 || C <= 0) return fail(SODA_ERR_BAD_ARG, "lif_fmt: non-positive size");
+  if (!fmt_ok(out_fmt) || (residual != nullptr && !fmt_ok(res_fmt))) return fail(SODA_ERR_BAD_ARG, "lif_fmt: unknown format");
+  if (C % 32 != 0) return fail(SODA_ERR_UNSUPPORTED, "lif_fmt: C must be a multiple of 32");
+  if ((reinterpret_cast<uintptr_t>(x) & 15) || !fmt_aligned(out, out_fmt, out_pix_stride, out_pix_stride) ||
+      (residual != nullptr && !fmt_aligned(residual, res_fmt, res_pix_stride, res_pix_stride)))
+    return fail(SODA_ERR_BAD_ARG, "lif_fmt: misaligned pointer or stride");
+  const int64_t total = n_pix * (C / 8);
+  lif_fmt_fwd_kernel<<<(unsigned)ceil_div(total, 256), 256, 0, (cudaStream_t)stream>>>(
+      to_np(p), x, v0, i0, T, n_pix, C, reinterpret_cast<const uint8_t*>(residual), res_fmt,
+      res_pix_stride * fmt_bytes(res_fmt), reinterpret_cast<uint8_t*>(out), out_fmt, out_pix_stride * fmt_bytes(out_fmt),
+      v_out, i_out, status);
+  return after_launch("lif_fmt_fwd_kernel");
+}

@@ -1,0 +1,914 @@
+// tcgen05 / TMEM / TMA implicit-GEMM convolution over PRE-SPLIT activations (soda_pconv_fwd).
+//
+// Reference arithmetic: nn.Conv2d(bias=False, padding=k/2) models/modules/layer_gen.py:129-136, the eval
+// BatchNorm affine (:211-214), norse LIFCell (:233) iterated over the T steps of models/soda.py:142, the Residual
+// sum (models/generator.py:146) and the concat-slice store (:158) in the epilogue.
+//
+//   D[m, co] = sum_{tap, ci} A_tap[m, ci] * W[tap][co][ci]          m = output pixel, 128 per tile
+//
+// What is different from conv_tc3.cu (fp32 activations, split in shared memory by 8 warps, tf32 + bf16 passes):
+//
+// * Activations live in HBM already split for the tensor core, written that way by the PRODUCING kernel's epilogue:
+//     SODA_ACT_PAIR : per pixel and 32-channel group 128 B = fp16 hi[32] | fp16 lo[32], x = hi + lo (22 significant
+//                     bits; the same 4 bytes per value as fp32, so a PAIR tensor has an fp32 tensor's strides)
+//     SODA_ACT_HALF : fp16, for values that are exact in it (spikes {0,1}, spike counts <= 2048): 2 bytes per value
+//   so TMA's bytes ARE the MMA operands: no split warps, no second shared-memory plane, no tf32 stream.
+// * Products, all kind::f16 with fp32 accumulation in TMEM:
+//     PAIR : a_hi*w_hi + a_hi*w_lo + a_lo*w_hi      (6 MMAs per 32 channels and tap; a_lo*w_lo ~ 2^-22 is dropped)
+//     HALF : a*w_hi + a*w_lo                         (8 MMAs per 64 channels and tap)
+//   Weights are split the same way (fp16 hi | fp16 lo) after multiplication by the folded BatchNorm scale and by a
+//   per-tensor power of two that puts them in fp16's normal range; the epilogue multiplies by its inverse (exact).
+// * One weight k-block is BN x 128 B per 32 channels (was 2 x BN x 128 B): twice as many layers keep their weights
+//   resident in shared memory, streamed layers move half the bytes from L2.
+// * The epilogue emits F32, PAIR or HALF as the consumer wants (fp32 membrane state never leaves the registers in
+//   the LIF variant) through a staged, fully coalesced store: 4 rows x 128 B per instruction.
+//
+// "im2col by descriptor" (one 18 x 10 halo tile per 32-channel slab, the nine taps are nine descriptors into it),
+// the persistent item loop, the weight-stationary / streamed plans and programmatic dependent launch are those of
+// conv_tc3.cu.  11 warps: w0-7 epilogue (two per TMEM lane quarter), w8 A producer (TMA), w9 B producer (TMA),
+// w10 MMA issuer + TMEM owner.
+#include <stdlib.h>
+#include <string.h>
+
+#include <algorithm>
+
+#include <cuda_fp16.h>
+
+#include "common.cuh"
+#include "neuron.cuh"
+#include "tc_common.cuh"
+
+namespace soda {
+
+using namespace tc;
+
+constexpr int T4_BM = 128;
+constexpr int T4_BH = 16, T4_BW = 8;
+constexpr int T4_THREADS = 352;
+constexpr int T4_W_PROD_A = 8, T4_W_PROD_B = 9, T4_W_MMA = 10;
+constexpr int T4_MAX_RING = 8;
+// accumulator stages in TMEM; a stage = main accumulator (hi * hi products) | correction accumulator (hi * lo, lo * hi):
+// the tensor core truncates on every accumulate, an error proportional to the accumulator's magnitude and to the number
+// of MMAs into it - the 2^-11-small corrections, two thirds of the MMAs, must not pay it at the main sum's magnitude
+// (measured: one accumulator 4.1e-6 of the output scale at K = 1152, split 1.2e-6)
+__host__ __device__ constexpr int t4_nacc(int BN) { return BN == 128 ? 2 : 4; }
+constexpr int T4_EPI_BYTES = 2048 + 512;        // per epilogue warp: 16 rows x 128 B staging + 32-row offset table
+constexpr int T4_SMEM_LIMIT = 232448 - 1024 /*alignment slack*/ - 512 /*barriers*/ - 8 * T4_EPI_BYTES;
+
+struct Tc4Params {
+  int H, W, Cin, Cout, k, stride, pad, Ho, Wo;
+  int tiles_x, tiles_y, n_spatial;
+  int mt;                        // M-tiles per work item sharing every streamed weight k-block (1 or 2)
+  int n_sp_items;
+  int it_step_sp, it_step_outer;
+  int taps, cblocks, kblocks;
+  int mode;                      // 0 = HALO (one A stage per channel slab, `taps` k-blocks), 1 = TAP (one stage per k-block)
+  int flat;                      // 1x1 stride-1 over the flattened pixel list
+  int in_fmt;                    // SODA_ACT_PAIR / SODA_ACT_HALF
+  int a_exact;                   // PAIR input whose lo halves are all zero: the a_lo*w_hi product is skipped
+  int rows, WW;
+  uint32_t sbo, plane_bytes, a_tx_bytes;
+  uint32_t b_kb_bytes;           // one weight k-block in shared memory: BN*128 (PAIR) or 2*BN*128 (HALF)
+  int nch, n_outer, T_inner, Bsz, n_items;
+  int b_stationary, b_stages, a_stages;
+  uint32_t b_region_bytes;
+  int64_t total_pix;
+  int out_fmt, res_fmt;
+  int64_t out_bs, out_ps, res_bs, res_ps;   // BYTES
+  const float* shift;
+  const float* descale;          // device scalar: inverse of the weights' power-of-two scale
+  const uint8_t* residual;
+  uint8_t* y;
+  unsigned int* status;          // [0] counts values that left fp16's range when encoded (NULL = not counted)
+  int lif;
+  NP np;
+  const float* v0;
+  const float* i0;
+  float* v_out;
+  float* i_out;
+};
+
+struct Tc4Iter {
+  int sp, outer;
+  __device__ __forceinline__ void init(const Tc4Params& p) {
+    const int r0 = (int)blockIdx.x / p.nch;
+    sp = r0 % p.n_sp_items;
+    outer = r0 / p.n_sp_items;
+  }
+  __device__ __forceinline__ void next(const Tc4Params& p) {
+    sp += p.it_step_sp;
+    outer += p.it_step_outer;
+    if (sp >= p.n_sp_items) sp -= p.n_sp_items, ++outer;
+  }
+};
+
+// kind::f16 with fp16 inputs, fp32 accumulate, both operands K-major
+__host__ __device__ constexpr uint32_t idesc_f16(int M, int N) {
+  return (1u << 4) | (0u << 7) | (0u << 10) | ((uint32_t)(N >> 3) << 17) | ((uint32_t)(M >> 4) << 24);
+}
+
+__device__ __forceinline__ uint32_t pack_h2(float lo, float hi) {   // lo -> bits [0,16)
+  uint32_t d;
+  asm("cvt.rn.satfinite.f16x2.f32 %0, %1, %2;" : "=r"(d) : "f"(hi), "f"(lo));
+  return d;
+}
+__device__ __forceinline__ float2 unpack_h2(uint32_t v) {
+  const __half2 h = *reinterpret_cast<const __half2*>(&v);
+  return __half22float2(h);
+}
+__device__ __forceinline__ uint4 ldg_u4(const uint8_t* p) { return __ldg(reinterpret_cast<const uint4*>(p)); }
+
+// ================================ MMA issuer ===================================================
+template <int BN, int MT>
+__device__ __forceinline__ void tc4_mma_role(const Tc4Params& p, uint32_t tmem_base, uint32_t smem_a_u32,
+                                             uint32_t smem_b_u32, uint64_t* a_full, uint64_t* a_empty,
+                                             uint64_t* b_full, uint64_t* b_empty, uint64_t* acc_full,
+                                             uint64_t* acc_empty) {
+  constexpr uint32_t idesc = idesc_f16(T4_BM, BN);
+  constexpr uint32_t B_TILE16 = (BN * 128) >> 4;   // one BN x 128 B weight tile, in descriptor units
+  const uint64_t a_desc0 = smem_desc_sw128_sbo(smem_a_u32, p.sbo);
+  const uint64_t b_desc0 = smem_desc_sw128(smem_b_u32);
+  const bool stat = p.b_stationary != 0;
+  const bool halo3 = p.mode == 0 && p.k == 3;
+  const bool pair = p.in_fmt == SODA_ACT_PAIR;
+  const bool lo_pass = pair && !p.a_exact;
+  const int stages_per_tile = p.mode == 0 ? p.cblocks : p.kblocks;
+  const int kb_per_stage = p.mode == 0 ? p.taps : 1;
+  const uint32_t a_stage16 = p.plane_bytes >> 4;
+  const uint32_t b_kb16 = p.b_kb_bytes >> 4;
+  constexpr uint32_t NACC = t4_nacc(BN);
+  uint32_t sa = 0, pa = 0, sb = 0, pb = 0, cnt = 0;
+  if (stat) mbar_wait(&b_full[0], 0);
+  for (int item = blockIdx.x; item < p.n_items; item += gridDim.x) {
+    for (int t = 0; t < p.T_inner; ++t) {
+      uint32_t d_acc[2];
+      _Pragma("unroll") for (int m = 0; m < 2; ++m) if (m < MT) {
+        const uint32_t a = (cnt + m) % NACC, ph = ((cnt + m) / NACC) & 1u;
+        mbar_wait(&acc_empty[a], ph ^ 1);
+        d_acc[m] = tmem_base + a * (2 * BN);   // main; correction accumulator BN columns further
+      }
+      tc_fence_after();
+      uint32_t accum = 0;
+      for (int st = 0; st < stages_per_tile; ++st) {
+        uint32_t s_m[2];
+        uint64_t a_st[2];
+        _Pragma("unroll") for (int m = 0; m < 2; ++m) if (m < MT) {
+          mbar_wait(&a_full[sa], pa);
+          a_st[m] = a_desc0 + (uint64_t)(sa * a_stage16);
+          s_m[m] = sa;
+          if (++sa == (uint32_t)p.a_stages) sa = 0, pa ^= 1;
+        }
+        tc_fence_after();
+        int ky = 0, kx = 0;
+        for (int tp = 0; tp < kb_per_stage; ++tp) {
+          uint64_t b_desc;
+          if (stat) {
+            const int bi = p.mode == 0 ? tp * p.cblocks + st : st;   // resident weights are stored (tap, cb)
+            b_desc = b_desc0 + (uint64_t)((uint32_t)bi * b_kb16);
+          } else {
+            mbar_wait(&b_full[sb], pb);
+            tc_fence_after();
+            b_desc = b_desc0 + (uint64_t)(sb * b_kb16);
+          }
+          const uint64_t tap_off = (uint64_t)(halo3 ? (uint32_t)(ky * p.WW + kx) * 8u : 0u);
+          if (elect_one()) {
+            // 32 bytes along the 128-byte row = 16 fp16 K elements; descriptor unit is 16 B
+            _Pragma("unroll") for (int m = 0; m < 2; ++m) if (m < MT) {
+              const uint64_t a_desc = a_st[m] + tap_off;
+              if (pair) {
+                // A row = hi[0..15] hi[16..31] lo[0..15] lo[16..31]; B row = w_hi[0..31] | w_lo[0..31]
+                mma_bf16_ss(d_acc[m], a_desc, b_desc, idesc, accum);               // a_hi * w_hi
+                mma_bf16_ss(d_acc[m], a_desc + 2, b_desc + 2, idesc, 1);
+                mma_bf16_ss(d_acc[m] + BN, a_desc, b_desc + 4, idesc, accum);      // a_hi * w_lo
+                mma_bf16_ss(d_acc[m] + BN, a_desc + 2, b_desc + 6, idesc, 1);
+                if (lo_pass) {
+                  mma_bf16_ss(d_acc[m] + BN, a_desc + 4, b_desc, idesc, 1);        // a_lo * w_hi
+                  mma_bf16_ss(d_acc[m] + BN, a_desc + 6, b_desc + 2, idesc, 1);
+                }
+              } else {
+                // A row = a[0..63]; B tiles = w_hi[0..63], then w_lo[0..63]
+                mma_bf16_ss(d_acc[m], a_desc, b_desc, idesc, accum);
+                mma_bf16_ss(d_acc[m], a_desc + 2, b_desc + 2, idesc, 1);
+                mma_bf16_ss(d_acc[m], a_desc + 4, b_desc + 4, idesc, 1);
+                mma_bf16_ss(d_acc[m], a_desc + 6, b_desc + 6, idesc, 1);
+                mma_bf16_ss(d_acc[m] + BN, a_desc, b_desc + B_TILE16, idesc, accum);
+                mma_bf16_ss(d_acc[m] + BN, a_desc + 2, b_desc + B_TILE16 + 2, idesc, 1);
+                mma_bf16_ss(d_acc[m] + BN, a_desc + 4, b_desc + B_TILE16 + 4, idesc, 1);
+                mma_bf16_ss(d_acc[m] + BN, a_desc + 6, b_desc + B_TILE16 + 6, idesc, 1);
+              }
+            }
+            if (!stat) mma_commit(&b_empty[sb]);
+          }
+          accum = 1;
+          if (++kx == 3) kx = 0, ++ky;
+          if (!stat && ++sb == (uint32_t)p.b_stages) sb = 0, pb ^= 1;
+        }
+        if (elect_one()) {
+          _Pragma("unroll") for (int m = 0; m < 2; ++m) if (m < MT) mma_commit(&a_empty[s_m[m]]);
+        }
+      }
+      if (elect_one()) {
+        _Pragma("unroll") for (int m = 0; m < 2; ++m) if (m < MT) mma_commit(&acc_full[(cnt + m) % NACC]);
+      }
+      cnt += MT;
+    }
+  }
+}
+
+template <int BN, bool LIF>
+__global__ void __launch_bounds__(T4_THREADS, 1)
+conv_tc4_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB, Tc4Params p) {
+  constexpr uint32_t B_TILE = BN * 128;
+  constexpr uint32_t NACC = t4_nacc(BN);
+  constexpr uint32_t TMEM_COLS = NACC * 2 * BN;
+  constexpr bool UNIT_SPLIT = BN == 32;          // the two warps of a lane quarter alternate work units
+  constexpr int NG = BN >= 64 ? BN / 64 : 1;     // 32-channel groups per epilogue warp
+  static_assert(!LIF || NG == 1, "fused LIF keeps 2 x 32 state registers per group");
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+  uint8_t* smem_b = smem;
+  uint8_t* smem_a = smem + p.b_region_bytes;
+  uint64_t* bars = reinterpret_cast<uint64_t*>(smem_a + (size_t)p.a_stages * p.plane_bytes);
+  uint64_t* a_full = bars;             // [8]
+  uint64_t* a_empty = bars + 8;        // [8]
+  uint64_t* b_full = bars + 16;        // [8]
+  uint64_t* b_empty = bars + 24;       // [8]
+  uint64_t* acc_full = bars + 32;      // [4]
+  uint64_t* acc_empty = bars + 36;     // [4]
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 40);
+  uint8_t* epi_base = reinterpret_cast<uint8_t*>(bars) + 512;
+
+  const int warp = threadIdx.x >> 5;
+  const int lane = threadIdx.x & 31;
+
+  if (warp == T4_W_PROD_A && lane == 0) {
+    prefetch_tmap(&tmA);
+    prefetch_tmap(&tmB);
+    for (int s = 0; s < T4_MAX_RING; ++s) {
+      mbar_init(&a_full[s], 1);
+      mbar_init(&a_empty[s], 1);
+      mbar_init(&b_full[s], 1);
+      mbar_init(&b_empty[s], 1);
+    }
+    for (int a = 0; a < 4; ++a) {
+      mbar_init(&acc_full[a], 1);
+      mbar_init(&acc_empty[a], UNIT_SPLIT ? 4 : 8);   // one arrival per epilogue warp that reads the stage
+    }
+    fence_barrier_init();
+  }
+  if (warp == T4_W_MMA) tmem_alloc(tmem_slot, TMEM_COLS);
+  pdl_trigger();
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = *tmem_slot;
+  pdl_wait();
+  const int my_chunk = blockIdx.x % p.nch;   // gridDim.x is a multiple of nch: fixed per CTA
+
+  if (warp == T4_W_PROD_A) {
+    // ================================ A producer (TMA) =========================================
+    uint32_t s = 0, ph = 0;
+    const uint32_t smem_a_u32 = smem_u32(smem_a);
+    const int rowch = p.in_fmt == SODA_ACT_PAIR ? 32 : 64;   // tensor-map elements per 128-byte row
+    Tc4Iter it;
+    it.init(p);
+    for (int item = blockIdx.x; item < p.n_items; item += gridDim.x, it.next(p)) {
+      int x0[2] = {0, 0}, y0[2] = {0, 0};
+      _Pragma("unroll") for (int m = 0; m < 2; ++m) if (m < p.mt) {
+        // a tile index past the last one (odd tile count) loads zeros (out of bounds) and is never stored
+        const int spt = it.sp * p.mt + m;
+        if (p.flat) {
+          x0[m] = spt * T4_BM;
+        } else {
+          const int ty = spt / p.tiles_x, tx = spt - ty * p.tiles_x;
+          y0[m] = ty * T4_BH * p.stride - p.pad;
+          x0[m] = tx * T4_BW * p.stride - p.pad;
+        }
+      }
+      for (int t = 0; t < p.T_inner; ++t) {
+        const int img = p.flat ? 0 : t * p.Bsz + it.outer;
+        const int n_tap = p.mode == 0 ? 1 : p.taps;
+        int ky = 0, kx = 0;
+        for (int tap = 0; tap < n_tap; ++tap) {
+          for (int cb = 0; cb < p.cblocks; ++cb) {
+            _Pragma("unroll") for (int m = 0; m < 2; ++m) if (m < p.mt) {
+              mbar_wait(&a_empty[s], ph ^ 1);
+              if (elect_one()) {
+                mbar_expect_tx(&a_full[s], p.a_tx_bytes);
+                tma_load_4d_s(smem_a_u32 + s * p.plane_bytes, &tmA, &a_full[s], cb * rowch, x0[m] + kx, y0[m] + ky,
+                              img);
+              }
+              __syncwarp();
+              if (++s == (uint32_t)p.a_stages) s = 0, ph ^= 1;
+            }
+          }
+          if (++kx == p.k) kx = 0, ++ky;
+        }
+      }
+    }
+  } else if (warp == T4_W_PROD_B) {
+    // ================================ B producer (TMA) =========================================
+    // packed weights: [tap][Cout_pad][2 * Cin] fp16; PAIR: per 32 channels hi[32] | lo[32] (one 128-byte row);
+    // HALF: per 64 channels hi[64] | lo[64] (two rows -> two BN x 128 B tiles)
+    const uint32_t smem_b_u32 = smem_u32(smem_b);
+    const bool pair = p.in_fmt == SODA_ACT_PAIR;
+    if (p.b_stationary) {
+      if (elect_one()) mbar_expect_tx(&b_full[0], (uint32_t)p.kblocks * p.b_kb_bytes);
+      __syncwarp();
+      for (int tap = 0; tap < p.taps; ++tap)
+        for (int cb = 0; cb < p.cblocks; ++cb) {
+          const uint32_t dst = smem_b_u32 + (uint32_t)(tap * p.cblocks + cb) * p.b_kb_bytes;
+          if (elect_one()) {
+            if (pair) {
+              tma_load_3d_s(dst, &tmB, &b_full[0], cb * 64, my_chunk * BN, tap);
+            } else {
+              tma_load_3d_s(dst, &tmB, &b_full[0], cb * 128, my_chunk * BN, tap);
+              tma_load_3d_s(dst + B_TILE, &tmB, &b_full[0], cb * 128 + 64, my_chunk * BN, tap);
+            }
+          }
+          __syncwarp();
+        }
+    } else {
+      uint32_t s = 0, ph = 0;
+      const int n_o = p.mode == 0 ? p.cblocks : p.taps;   // HALO walks (cb, tap), TAP walks (tap, cb)
+      const int n_i = p.mode == 0 ? p.taps : p.cblocks;
+      for (int item = blockIdx.x; item < p.n_items; item += gridDim.x) {
+        for (int t = 0; t < p.T_inner; ++t) {
+          for (int o = 0; o < n_o; ++o)
+            for (int i = 0; i < n_i; ++i) {
+              const int tap = p.mode == 0 ? i : o, cb = p.mode == 0 ? o : i;
+              mbar_wait(&b_empty[s], ph ^ 1);
+              if (elect_one()) {
+                mbar_expect_tx(&b_full[s], p.b_kb_bytes);
+                const uint32_t dst = smem_b_u32 + s * p.b_kb_bytes;
+                if (pair) {
+                  tma_load_3d_s(dst, &tmB, &b_full[s], cb * 64, my_chunk * BN, tap);
+                } else {
+                  tma_load_3d_s(dst, &tmB, &b_full[s], cb * 128, my_chunk * BN, tap);
+                  tma_load_3d_s(dst + B_TILE, &tmB, &b_full[s], cb * 128 + 64, my_chunk * BN, tap);
+                }
+              }
+              __syncwarp();
+              if (++s == (uint32_t)p.b_stages) s = 0, ph ^= 1;
+            }
+        }
+      }
+    }
+  } else if (warp == T4_W_MMA) {
+    if (p.mt == 2)
+      tc4_mma_role<BN, 2>(p, tmem_base, smem_u32(smem_a), smem_u32(smem_b), a_full, a_empty, b_full, b_empty, acc_full,
+                          acc_empty);
+    else
+      tc4_mma_role<BN, 1>(p, tmem_base, smem_u32(smem_a), smem_u32(smem_b), a_full, a_empty, b_full, b_empty, acc_full,
+                          acc_empty);
+  } else if (warp < 8) {
+    // ================================ epilogue ================================================
+    const int e = warp >> 2;
+    const int q = warp & 3;
+    const uint32_t stage_u32 = smem_u32(epi_base) + (uint32_t)warp * T4_EPI_BYTES;
+    const uint32_t table_u32 = stage_u32 + 2048u;
+    const int row = q * 32 + lane;
+    const int64_t hw = (int64_t)p.Ho * p.Wo;
+    const float descale = __ldg(p.descale);
+    const int out_cb = p.out_fmt == SODA_ACT_HALF ? 2 : 4;          // bytes per output channel
+    const uint32_t gch = p.out_fmt == SODA_ACT_HALF ? 4u : 8u;      // 16-byte chunks per 32-channel group
+    const uint32_t gsh = p.out_fmt == SODA_ACT_HALF ? 2u : 3u;      // log2(gch)
+    unsigned int n_over = 0;
+    uint32_t local = 0, unit = 0;
+    Tc4Iter it;
+    it.init(p);
+    for (int item = blockIdx.x; item < p.n_items; item += gridDim.x, it.next(p)) {
+      for (int m = 0; m < p.mt; ++m) {   // (mt == 2 only without LIF: T_inner == 1)
+        const bool mine = !UNIT_SPLIT || ((unit & 1u) == (uint32_t)e);
+        ++unit;
+        if (!mine) {
+          local += (uint32_t)p.T_inner;
+          continue;
+        }
+        const int spt = it.sp * p.mt + m;
+        bool valid;
+        int64_t rr;      // pixel index inside its frame
+        int64_t frame0;  // frame of step t = 0
+        if (p.flat) {
+          const int64_t pix = (int64_t)spt * T4_BM + row;
+          valid = pix < p.total_pix;
+          frame0 = 0;
+          rr = pix;
+        } else {
+          const int ty = spt / p.tiles_x, tx = spt - ty * p.tiles_x;
+          const int oy = ty * T4_BH + (row >> 3);
+          const int ox = tx * T4_BW + (row & 7);
+          valid = oy < p.Ho && ox < p.Wo;
+          rr = (int64_t)oy * p.Wo + ox;
+          frame0 = it.outer;
+        }
+        const int col_base = UNIT_SPLIT ? 0 : e * (BN / 2);
+        const int co_base = my_chunk * BN + col_base;
+        float sv[LIF ? 32 : 1], si[LIF ? 32 : 1];
+        if constexpr (LIF) {
+          const int64_t soff = ((int64_t)it.outer * hw + rr) * p.Cout + co_base;
+#pragma unroll
+          for (int c = 0; c < 32; c += 4) {
+            float4 a = make_float4(p.np.v_leak, p.np.v_leak, p.np.v_leak, p.np.v_leak);
+            float4 b = make_float4(0.f, 0.f, 0.f, 0.f);
+            if (valid && p.v0 != nullptr && co_base < p.Cout) {
+              a = __ldg(reinterpret_cast<const float4*>(p.v0 + soff + c));
+              b = __ldg(reinterpret_cast<const float4*>(p.i0 + soff + c));
+            }
+            sv[c] = a.x, sv[c + 1] = a.y, sv[c + 2] = a.z, sv[c + 3] = a.w;
+            si[c] = b.x, si[c + 1] = b.y, si[c + 2] = b.z, si[c + 3] = b.w;
+          }
+        }
+        for (int t = 0; t < p.T_inner; ++t, ++local) {
+          const uint32_t acc = local % NACC;
+          const uint32_t acc_ph = (local / NACC) & 1u;
+          const int64_t frame = frame0 + (int64_t)t * p.Bsz;
+          const int64_t out_off = frame * p.out_bs + rr * p.out_ps;
+          const int64_t res_off = frame * p.res_bs + rr * p.res_ps;
+          {
+            // row -> output byte offset (or -1) of this warp's 32 rows, for the staged coalesced stores
+            __syncwarp();
+            const int64_t my_out = valid ? out_off : -1;
+            asm volatile("st.shared.b64 [%0], %1;" ::"r"(table_u32 + (uint32_t)lane * 8u), "l"(my_out) : "memory");
+            __syncwarp();
+          }
+          mbar_wait(&acc_full[acc], acc_ph);
+          tc_fence_after();
+          const uint32_t t_row = tmem_base + ((uint32_t)(q * 32) << 16) + acc * (2 * BN) + (uint32_t)col_base;
+#pragma unroll
+          for (int g = 0; g < NG; ++g) {
+            uint32_t r[32], rc[32];
+            tmem_ld_32x32(t_row + g * 32, r);
+            tmem_ld_32x32(t_row + BN + g * 32, rc);
+            tmem_ld_wait();
+            if (g == NG - 1) {
+              // last TMEM read of this tile: hand the accumulator back before the global traffic
+              tc_fence_before();
+              __syncwarp();
+              if (lane == 0) mbar_arrive(&acc_empty[acc]);
+            }
+            const int co0 = co_base + g * 32;
+            const bool group_live = co0 < p.Cout;   // Cout % 32 == 0: a group is whole or absent
+            float o[32];
+#pragma unroll
+            for (int j = 0; j < 32; ++j) o[j] = (__uint_as_float(r[j]) + __uint_as_float(rc[j])) * descale;
+            if (p.shift != nullptr && group_live) {
+#pragma unroll
+              for (int j = 0; j < 32; j += 4) {
+                const float4 sh = __ldg(reinterpret_cast<const float4*>(p.shift + co0 + j));
+                o[j] += sh.x, o[j + 1] += sh.y, o[j + 2] += sh.z, o[j + 3] += sh.w;
+              }
+            }
+            if constexpr (LIF) {
+#pragma unroll
+              for (int j = 0; j < 32; ++j) {
+                float z, vd;
+                lif_step(p.np, o[j], sv[j], si[j], z, vd);
+                o[j] = z;
+              }
+            }
+            if (p.residual != nullptr && valid && group_live) {
+              if (p.res_fmt == SODA_ACT_F32) {
+                const uint8_t* rp = p.residual + res_off + (int64_t)co0 * 4;
+#pragma unroll
+                for (int j = 0; j < 8; ++j) {
+                  const uint4 u = ldg_u4(rp + j * 16);
+                  o[4 * j] += __uint_as_float(u.x), o[4 * j + 1] += __uint_as_float(u.y);
+                  o[4 * j + 2] += __uint_as_float(u.z), o[4 * j + 3] += __uint_as_float(u.w);
+                }
+              } else if (p.res_fmt == SODA_ACT_PAIR) {
+                const uint8_t* rp = p.residual + res_off + (int64_t)co0 * 4;
+#pragma unroll
+                for (int j = 0; j < 4; ++j) {
+                  const uint4 h = ldg_u4(rp + j * 16), l = ldg_u4(rp + 64 + j * 16);
+                  const uint32_t hw4[4] = {h.x, h.y, h.z, h.w}, lw4[4] = {l.x, l.y, l.z, l.w};
+#pragma unroll
+                  for (int w = 0; w < 4; ++w) {
+                    const float2 a = unpack_h2(hw4[w]), b = unpack_h2(lw4[w]);
+                    o[8 * j + 2 * w] += a.x + b.x;
+                    o[8 * j + 2 * w + 1] += a.y + b.y;
+                  }
+                }
+              } else {
+                const uint8_t* rp = p.residual + res_off + (int64_t)co0 * 2;
+#pragma unroll
+                for (int j = 0; j < 4; ++j) {
+                  const uint4 h = ldg_u4(rp + j * 16);
+                  const uint32_t hw4[4] = {h.x, h.y, h.z, h.w};
+#pragma unroll
+                  for (int w = 0; w < 4; ++w) {
+                    const float2 a = unpack_h2(hw4[w]);
+                    o[8 * j + 2 * w] += a.x, o[8 * j + 2 * w + 1] += a.y;
+                  }
+                }
+              }
+            }
+            // ---- encode this row's 32 channels: 8 (F32 / PAIR) or 4 (HALF) chunks of 16 bytes ----
+            uint32_t w[32];
+            if (p.out_fmt == SODA_ACT_F32) {
+#pragma unroll
+              for (int j = 0; j < 32; ++j) w[j] = __float_as_uint(o[j]);
+            } else {
+#pragma unroll
+              for (int j = 0; j < 16; ++j) {
+                const uint32_t hi = pack_h2(o[2 * j], o[2 * j + 1]);
+                w[j] = hi;
+                if (p.out_fmt == SODA_ACT_PAIR) {
+                  const float2 hf = unpack_h2(hi);
+                  w[16 + j] = pack_h2(o[2 * j] - hf.x, o[2 * j + 1] - hf.y);
+                }
+                if (p.status != nullptr)
+                  n_over += (fabsf(o[2 * j]) > 65504.f) + (fabsf(o[2 * j + 1]) > 65504.f);
+              }
+            }
+            // ---- staged, coalesced store: 16 rows through 2 KB of shared memory at a time ----
+#pragma unroll
+            for (int half = 0; half < 2; ++half) {
+              __syncwarp();
+              if ((lane >> 4) == half) {
+                const uint32_t r16 = lane & 15u;
+                const uint32_t rowa = stage_u32 + r16 * 128u;
+#pragma unroll
+                for (uint32_t j = 0; j < 8; ++j)
+                  if (j < gch)
+                    sts128(rowa + ((j ^ (r16 & 7u)) << 4), __uint_as_float(w[4 * j]), __uint_as_float(w[4 * j + 1]),
+                           __uint_as_float(w[4 * j + 2]), __uint_as_float(w[4 * j + 3]));
+              }
+              __syncwarp();
+              const uint32_t n_it = (16u * gch) >> 5;   // 4 (8 chunks per row) or 2 (4 chunks per row)
+              for (uint32_t i2 = 0; i2 < n_it; ++i2) {
+                const uint32_t rrow = i2 * (32u >> gsh) + ((uint32_t)lane >> gsh);
+                const uint32_t j = (uint32_t)lane & (gch - 1u);
+                const float4 val = lds128(stage_u32 + rrow * 128u + ((j ^ (rrow & 7u)) << 4));
+                int64_t ooff;
+                asm volatile("ld.shared.b64 %0, [%1];" : "=l"(ooff) : "r"(table_u32 + ((uint32_t)half * 16u + rrow) * 8u));
+                if (ooff >= 0 && group_live)
+                  *reinterpret_cast<float4*>(p.y + ooff + (int64_t)co0 * out_cb + j * 16u) = val;
+              }
+            }
+          }
+        }
+        if constexpr (LIF) {
+          if (valid && co_base < p.Cout) {
+            const int64_t soff = ((int64_t)it.outer * hw + rr) * p.Cout + co_base;
+#pragma unroll
+            for (int c = 0; c < 32; c += 4) {
+              *reinterpret_cast<float4*>(p.v_out + soff + c) = make_float4(sv[c], sv[c + 1], sv[c + 2], sv[c + 3]);
+              *reinterpret_cast<float4*>(p.i_out + soff + c) = make_float4(si[c], si[c + 1], si[c + 2], si[c + 3]);
+            }
+          }
+        }
+      }  // m
+    }
+    if (p.status != nullptr && n_over != 0) atomicAdd(p.status, n_over);
+  }
+
+  tc_fence_before();
+  __syncthreads();
+  if (warp == T4_W_MMA) {
+    tc_fence_after();
+    tmem_dealloc(tmem_base, TMEM_COLS);
+  }
+}
+
+// ------------------------------------------------------------------------------------------------
+// host side: weight packing, tensor maps, configuration, dispatch
+// ------------------------------------------------------------------------------------------------
+static inline int tc4_bn_for(int Cout, bool lif) {
+  static const int env_bn = []() { const char* e = getenv("SODA_TC4_BN"); return e ? atoi(e) : 0; }();
+  if (Cout <= 32) return 32;
+  if (env_bn == 32 || env_bn == 64 || (env_bn == 128 && !lif)) return Cout <= 64 ? std::min(env_bn, 64) : env_bn;
+  if (Cout <= 64 || lif) return 64;
+  return 128;
+}
+static inline int tc4_cout_pad(int Cout) {
+  if (Cout <= 32) return 32;
+  if (Cout <= 64) return 64;
+  return (Cout + 127) / 128 * 128;
+}
+
+int64_t conv_tc4_packed_bytes(int Cout, int Cin, int k) {
+  if (Cin % 32 != 0) return 0;
+  return 4LL * k * k * tc4_cout_pad(Cout) * Cin;
+}
+
+// [Cout, Cin, k, k] * scale[co] * mult -> [tap][Cout_pad][2 * Cin] fp16:
+//   PAIR input: per 32 channels  hi[32] | lo[32]      HALF input: per 64 channels  hi[64] | lo[64]
+__global__ void pack_weights_tc4_kernel(const float* __restrict__ w, const float* __restrict__ scale,
+                                        const float* __restrict__ mult, int Cout, int Cin, int taps, int Cout_pad,
+                                        int grp, __half* __restrict__ wp) {
+  const int64_t n = (int64_t)taps * Cout_pad * Cin;
+  const float mu = mult != nullptr ? __ldg(mult) : 1.0f;
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x) {
+    const int ci = (int)(i % Cin);
+    const int64_t r = i / Cin;   // tap * Cout_pad + co
+    const int co = (int)(r % Cout_pad);
+    const int tap = (int)(r / Cout_pad);
+    float v = 0.f;
+    if (co < Cout) {
+      v = w[((int64_t)co * Cin + ci) * taps + tap];
+      if (scale != nullptr) v = __fmul_rn(v, scale[co]);
+      v = __fmul_rn(v, mu);
+    }
+    const __half hi = __float2half_rn(v);
+    const __half lo = __float2half_rn(v - __half2float(hi));
+    const int64_t base = r * (2 * Cin) + (int64_t)(ci / grp) * (2 * grp) + (ci % grp);
+    wp[base] = hi;
+    wp[base + grp] = lo;
+  }
+}
+
+int conv_tc4_pack(const float* w, const float* scale, const float* mult, int Cout, int Cin, int k, int in_fmt,
+                  void* packed, cudaStream_t st) {
+  if (in_fmt != SODA_ACT_PAIR && in_fmt != SODA_ACT_HALF)
+    return fail(SODA_ERR_BAD_ARG, "pconv_pack: input format must be SODA_ACT_PAIR or SODA_ACT_HALF");
+  const int grp = in_fmt == SODA_ACT_PAIR ? 32 : 64;
+  if (Cin % grp != 0) return fail(SODA_ERR_UNSUPPORTED, "pconv_pack: Cin must be a multiple of 32 (PAIR) / 64 (HALF)");
+  const int64_t n = (int64_t)k * k * tc4_cout_pad(Cout) * Cin;
+  pack_weights_tc4_kernel<<<(unsigned)std::min<int64_t>(ceil_div(n, 256), 4096), 256, 0, st>>>(
+      w, scale, mult, Cout, Cin, k * k, tc4_cout_pad(Cout), grp, reinterpret_cast<__half*>(packed));
+  return after_launch("pack_weights_tc4_kernel");
+}
+
+typedef CUresult (*EncodeTiledFn4)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*,
+                                   const cuuint64_t*, const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave,
+                                   CUtensorMapSwizzle, CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+
+static EncodeTiledFn4 get_encode_fn4() {
+  static EncodeTiledFn4 fn = nullptr;
+  if (fn == nullptr) {
+    void* ptr = nullptr;
+    cudaDriverEntryPointQueryResult q;
+    if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &ptr, cudaEnableDefault, &q) == cudaSuccess &&
+        q == cudaDriverEntryPointSuccess)
+      fn = reinterpret_cast<EncodeTiledFn4>(ptr);
+  }
+  return fn;
+}
+
+static int encode_map4(CUtensorMap* m, CUtensorMapDataType dt, const void* base, int rank, const cuuint64_t* dims,
+                       const cuuint64_t* strides_b, const cuuint32_t* box, const cuuint32_t* estr) {
+  EncodeTiledFn4 fn = get_encode_fn4();
+  if (fn == nullptr) return fail(SODA_ERR_CUDA, "pconv: cuTensorMapEncodeTiled entry point not available");
+  CUresult r = fn(m, dt, (cuuint32_t)rank, const_cast<void*>(base), dims, strides_b, box, estr,
+                  CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                  CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  if (r != CUDA_SUCCESS) {
+    set_error("pconv: cuTensorMapEncodeTiled failed (%d)", (int)r);
+    return (int)SODA_ERR_CUDA;
+  }
+  return 0;
+}
+
+template <int BN, bool LIF>
+static int launch_tc4(const CUtensorMap& tmA, const CUtensorMap& tmB, const Tc4Params& p, int grid, size_t smem,
+                      cudaStream_t st) {
+  // the opt-in is per device: set it on every launch (cheap), not once per process
+  cudaError_t e = cudaFuncSetAttribute(conv_tc4_kernel<BN, LIF>, cudaFuncAttributeMaxDynamicSharedMemorySize, 232448);
+  if (e != cudaSuccess) {
+    set_error("pconv: cudaFuncSetAttribute: %s", cudaGetErrorString(e));
+    return (int)SODA_ERR_CUDA;
+  }
+  static const bool pdl = []() { const char* e = getenv("SODA_PDL"); return !(e && atoi(e) == 0); }();
+  if (pdl) {
+    cudaLaunchConfig_t cfg;
+    memset(&cfg, 0, sizeof(cfg));
+    cfg.gridDim = dim3((unsigned)grid), cfg.blockDim = dim3(T4_THREADS);
+    cfg.dynamicSmemBytes = smem, cfg.stream = st;
+    cudaLaunchAttribute at[1];
+    at[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    at[0].val.programmaticStreamSerializationAllowed = 1;
+    cfg.attrs = at, cfg.numAttrs = 1;
+    cudaLaunchKernelEx(&cfg, conv_tc4_kernel<BN, LIF>, tmA, tmB, p);
+  } else {
+    conv_tc4_kernel<BN, LIF><<<grid, T4_THREADS, smem, st>>>(tmA, tmB, p);
+  }
+  return after_launch("conv_tc4_kernel");
+}
+
+static inline int act_bytes(int fmt) { return fmt == SODA_ACT_HALF ? 2 : 4; }
+
+bool conv_tc4_supported(const soda_pconv_desc_t* d, const void* x, const void* y, const void* residual) {
+  if (d->in_fmt != SODA_ACT_PAIR && d->in_fmt != SODA_ACT_HALF) return false;
+  if (d->out_fmt < SODA_ACT_F32 || d->out_fmt > SODA_ACT_HALF) return false;
+  const int grp = d->in_fmt == SODA_ACT_PAIR ? 32 : 64;
+  if (d->Cin % grp != 0 || d->Cout % 32 != 0) return false;
+  if (d->k != 1 && d->k != 3) return false;
+  if (d->stride != 1 && d->stride != 2) return false;
+  const int ib = act_bytes(d->in_fmt), ob = act_bytes(d->out_fmt);
+  // every 32-channel group of a pixel is one aligned 128-byte (64-byte for HALF output) piece
+  if ((reinterpret_cast<uintptr_t>(x) & 127) || (d->in_pix_stride * ib) % 128 || (d->in_batch_stride * ib) % 128) return false;
+  const int oal = d->out_fmt == SODA_ACT_HALF ? 64 : 128;
+  if ((reinterpret_cast<uintptr_t>(y) & (oal - 1)) || (d->out_pix_stride * ob) % oal || (d->out_batch_stride * ob) % oal)
+    return false;
+  if (residual != nullptr) {
+    if (d->res_fmt < SODA_ACT_F32 || d->res_fmt > SODA_ACT_HALF) return false;
+    const int rb = act_bytes(d->res_fmt);
+    const int ral = d->res_fmt == SODA_ACT_HALF ? 64 : 128;
+    if ((reinterpret_cast<uintptr_t>(residual) & (ral - 1)) || (d->res_pix_stride * rb) % ral ||
+        (d->res_batch_stride * rb) % ral)
+      return false;
+  }
+  return true;
+}
+
+struct Tc4Lif {
+  int T;
+  NP np;
+  const float* v0;
+  const float* i0;
+  float* v_out;
+  float* i_out;
+};
+
+int conv_tc4_dispatch(const soda_pconv_desc_t* d, const void* x, const void* packed, const float* descale,
+                      const float* shift, const void* residual, void* y, unsigned int* status, const Tc4Lif* lif,
+                      void* stream) {
+  if (!conv_tc4_supported(d, x, y, residual))
+    return fail(SODA_ERR_UNSUPPORTED,
+                "pconv: needs PAIR / HALF input with Cin % 32 (64) == 0, Cout % 32 == 0, 128-byte aligned channel groups, "
+                "k in {1,3}, stride in {1,2}");
+  Tc4Params p;
+  memset(&p, 0, sizeof(p));
+  p.H = d->H, p.W = d->W, p.Cin = d->Cin, p.Cout = d->Cout, p.k = d->k, p.stride = d->stride;
+  p.pad = d->k / 2;
+  p.Ho = (d->H + 2 * p.pad - d->k) / d->stride + 1;
+  p.Wo = (d->W + 2 * p.pad - d->k) / d->stride + 1;
+  if (p.Ho <= 0 || p.Wo <= 0) return fail(SODA_ERR_BAD_ARG, "pconv: empty output");
+  p.in_fmt = d->in_fmt, p.out_fmt = d->out_fmt, p.res_fmt = d->res_fmt;
+  p.a_exact = (d->flags & SODA_PCONV_FLAG_INPUT_EXACT) ? 1 : 0;
+  const int rowch = d->in_fmt == SODA_ACT_PAIR ? 32 : 64;
+  const int ib = act_bytes(d->in_fmt), ob = act_bytes(d->out_fmt), rb = act_bytes(d->res_fmt);
+  p.taps = d->k * d->k;
+  p.cblocks = d->Cin / rowch;
+  p.kblocks = p.taps * p.cblocks;
+  p.total_pix = (int64_t)d->N * p.Ho * p.Wo;
+  p.out_bs = d->out_batch_stride * ob, p.out_ps = d->out_pix_stride * ob;
+  p.res_bs = d->res_batch_stride * rb, p.res_ps = d->res_pix_stride * rb;
+  p.shift = shift, p.descale = descale;
+  p.residual = reinterpret_cast<const uint8_t*>(residual), p.y = reinterpret_cast<uint8_t*>(y);
+  p.status = status;
+  const bool is_lif = lif != nullptr;
+  if (is_lif) {
+    if (lif->T <= 0 || d->N % lif->T != 0) return fail(SODA_ERR_BAD_ARG, "pconv_lif: N must be T * batch");
+    if (!lif->v_out || !lif->i_out) return fail(SODA_ERR_BAD_ARG, "pconv_lif: null state output");
+    if ((lif->v0 == nullptr) != (lif->i0 == nullptr)) return fail(SODA_ERR_BAD_ARG, "pconv_lif: v0 / i0 must come together");
+    p.lif = 1, p.np = lif->np, p.v0 = lif->v0, p.i0 = lif->i0, p.v_out = lif->v_out, p.i_out = lif->i_out;
+    p.T_inner = lif->T, p.Bsz = d->N / lif->T, p.n_outer = p.Bsz;
+  } else {
+    p.T_inner = 1, p.Bsz = d->N, p.n_outer = d->N;
+  }
+  const int BN = tc4_bn_for(d->Cout, is_lif);
+  const int Cout_pad = tc4_cout_pad(d->Cout);
+  p.nch = (d->Cout + BN - 1) / BN;
+  const uint32_t b_kb = (uint32_t)BN * 128u * (d->in_fmt == SODA_ACT_PAIR ? 1u : 2u);
+  p.b_kb_bytes = b_kb;
+
+  CUtensorMap tmA, tmB;
+  const CUtensorMapDataType adt = d->in_fmt == SODA_ACT_PAIR ? CU_TENSOR_MAP_DATA_TYPE_FLOAT32 : CU_TENSOR_MAP_DATA_TYPE_FLOAT16;
+  const int64_t HW = (int64_t)d->H * d->W;
+  const bool frames_dense = d->N == 1 || d->in_batch_stride == HW * d->in_pix_stride;
+  p.mode = d->stride == 1 ? 0 : 1;
+  const int64_t HWo = (int64_t)p.Ho * p.Wo;
+  const bool out_dense = (d->N == 1 || d->out_batch_stride == HWo * d->out_pix_stride) &&
+                         (residual == nullptr || d->N == 1 || d->res_batch_stride == HWo * d->res_pix_stride);
+  p.flat = (d->k == 1 && d->stride == 1 && frames_dense && out_dense && !is_lif) ? 1 : 0;
+  p.rows = T4_BM, p.WW = T4_BW, p.sbo = 1024;
+  if (p.flat) {
+    p.n_spatial = (int)ceil_div(p.total_pix, T4_BM);
+    p.tiles_x = p.n_spatial, p.tiles_y = 1;
+    p.n_outer = 1;
+    const cuuint64_t dims[4] = {(cuuint64_t)d->Cin, (cuuint64_t)p.total_pix, 1, 1};
+    const cuuint64_t str[3] = {(cuuint64_t)d->in_pix_stride * ib, (cuuint64_t)p.total_pix * d->in_pix_stride * ib,
+                               (cuuint64_t)p.total_pix * d->in_pix_stride * ib};
+    const cuuint32_t box[4] = {(cuuint32_t)rowch, T4_BM, 1, 1};
+    const cuuint32_t es[4] = {1, 1, 1, 1};
+    int rc = encode_map4(&tmA, adt, x, 4, dims, str, box, es);
+    if (rc) return rc;
+  } else {
+    p.tiles_y = (int)ceil_div(p.Ho, T4_BH), p.tiles_x = (int)ceil_div(p.Wo, T4_BW);
+    p.n_spatial = p.tiles_x * p.tiles_y;
+    const cuuint64_t dims[4] = {(cuuint64_t)d->Cin, (cuuint64_t)d->W, (cuuint64_t)d->H, (cuuint64_t)d->N};
+    const cuuint64_t str[3] = {(cuuint64_t)d->in_pix_stride * ib, (cuuint64_t)d->W * d->in_pix_stride * ib,
+                               (cuuint64_t)(d->N == 1 ? HW * d->in_pix_stride : d->in_batch_stride) * ib};
+    if (p.mode == 0) {
+      p.WW = T4_BW + 2 * p.pad;
+      const int HH = T4_BH + 2 * p.pad;
+      p.rows = p.WW * HH;
+      p.sbo = (uint32_t)p.WW * 128u;
+      const cuuint32_t box[4] = {(cuuint32_t)rowch, (cuuint32_t)p.WW, (cuuint32_t)HH, 1};
+      const cuuint32_t es[4] = {1, 1, 1, 1};
+      int rc = encode_map4(&tmA, adt, x, 4, dims, str, box, es);
+      if (rc) return rc;
+    } else {
+      const cuuint32_t box[4] = {(cuuint32_t)rowch, (cuuint32_t)(T4_BW * d->stride), (cuuint32_t)(T4_BH * d->stride), 1};
+      const cuuint32_t es[4] = {1, (cuuint32_t)d->stride, (cuuint32_t)d->stride, 1};
+      int rc = encode_map4(&tmA, adt, x, 4, dims, str, box, es);
+      if (rc) return rc;
+    }
+  }
+  p.a_tx_bytes = (uint32_t)p.rows * 128u;
+  p.plane_bytes = (p.a_tx_bytes + 1023u) & ~1023u;
+  {
+    const cuuint64_t dims[3] = {(cuuint64_t)(2 * d->Cin), (cuuint64_t)Cout_pad, (cuuint64_t)p.taps};
+    const cuuint64_t str[2] = {(cuuint64_t)d->Cin * 4, (cuuint64_t)Cout_pad * d->Cin * 4};
+    const cuuint32_t box[3] = {64, (cuuint32_t)BN, 1};
+    const cuuint32_t es[3] = {1, 1, 1};
+    int rc = encode_map4(&tmB, CU_TENSOR_MAP_DATA_TYPE_FLOAT16, packed, 3, dims, str, box, es);
+    if (rc) return rc;
+  }
+  // shared-memory plan: weights resident if one output-channel chunk fits beside an A ring of >= min_a planes,
+  // else a weight ring as well
+  const int64_t b_total = (int64_t)p.kblocks * b_kb;
+  const bool halo3 = p.mode == 0 && p.k == 3;
+  const int64_t plane = p.plane_bytes;
+  static const int env_min_a = []() { const char* e = getenv("SODA_TC4_MIN_A"); return e ? atoi(e) : 0; }();
+  const int min_a = env_min_a > 0 ? env_min_a : (halo3 ? 2 : 4);
+  if (b_total + min_a * plane <= T4_SMEM_LIMIT) {
+    p.b_stationary = 1, p.b_stages = 1, p.mt = 1;
+    p.b_region_bytes = (uint32_t)b_total;
+    p.a_stages = (int)std::min<int64_t>(T4_MAX_RING, (T4_SMEM_LIMIT - b_total) / plane);
+  } else {
+    // streamed weights: an item takes TWO M-tiles that share each weight k-block (two accumulators of the four)
+    p.b_stationary = 0;
+    static const int env_mt = []() { const char* e = getenv("SODA_TC4_MT"); return e ? atoi(e) : 0; }();
+    const bool want_pair = !is_lif && p.n_spatial > 1 && env_mt != 1;
+    p.mt = want_pair ? 2 : 1;
+    int bs = 4;
+    while (bs > 2 && (int64_t)bs * b_kb + 2 * plane > T4_SMEM_LIMIT) --bs;
+    int64_t a = (T4_SMEM_LIMIT - (int64_t)bs * b_kb) / plane;
+    if (a < 2) return fail(SODA_ERR_UNSUPPORTED, "pconv: shared-memory plan does not fit");
+    const int a_pref = halo3 ? 4 : 6;
+    p.a_stages = (int)std::min<int64_t>(std::min<int64_t>(a, T4_MAX_RING), a_pref);
+    p.b_stages = (int)std::min<int64_t>(T4_MAX_RING, (T4_SMEM_LIMIT - (int64_t)p.a_stages * plane) / b_kb);
+    if (p.b_stages < 2) return fail(SODA_ERR_UNSUPPORTED, "pconv: shared-memory plan does not fit");
+    p.b_region_bytes = (uint32_t)p.b_stages * b_kb;
+  }
+  p.n_sp_items = (p.n_spatial + p.mt - 1) / p.mt;
+  p.n_items = p.nch * p.n_sp_items * p.n_outer;
+  int dev = 0, n_sm = kNumSMs;
+  if (cudaGetDevice(&dev) == cudaSuccess) {
+    static int sm_cache[64] = {0};
+    if (dev >= 0 && dev < 64) {
+      if (sm_cache[dev] == 0) cudaDeviceGetAttribute(&sm_cache[dev], cudaDevAttrMultiProcessorCount, dev);
+      if (sm_cache[dev] > 0) n_sm = sm_cache[dev];
+    }
+  }
+  int grid = p.n_items < n_sm ? p.n_items : n_sm;
+  grid = grid / p.nch * p.nch;
+  if (grid < p.nch) grid = p.nch;
+  p.it_step_sp = (grid / p.nch) % p.n_sp_items;
+  p.it_step_outer = (grid / p.nch) / p.n_sp_items;
+  const size_t smem = (size_t)p.b_region_bytes + (size_t)p.a_stages * p.plane_bytes + 512 + 8 * T4_EPI_BYTES + 1024;
+  cudaStream_t st = (cudaStream_t)stream;
+  if (is_lif) {
+    if (BN == 32) return launch_tc4<32, true>(tmA, tmB, p, grid, smem, st);
+    return launch_tc4<64, true>(tmA, tmB, p, grid, smem, st);
+  }
+  if (BN == 32) return launch_tc4<32, false>(tmA, tmB, p, grid, smem, st);
+  if (BN == 64) return launch_tc4<64, false>(tmA, tmB, p, grid, smem, st);
+  return launch_tc4<128, false>(tmA, tmB, p, grid, smem, st);
+}
+
+}  // namespace soda
+
+extern "C" int64_t soda_pconv_packed_bytes(int Cout, int Cin, int k) {
+  if (Cout <= 0 || Cin <= 0 || k <= 0) return 0;
+  return soda::conv_tc4_packed_bytes(Cout, Cin, k);
+}
+
+extern "C" int soda_pconv_pack_weights(const float* weight, const float* scale, const float* mult, int Cout, int Cin,
+                                       int k, int in_fmt, void* packed, void* stream) {
+  using namespace soda;
+  if (!weight || !packed) return fail(SODA_ERR_BAD_ARG, "pconv_pack: null pointer");
+  if (Cout <= 0 || Cin <= 0 || k <= 0) return fail(SODA_ERR_BAD_ARG, "pconv_pack: non-positive size");
+  return conv_tc4_pack(weight, scale, mult, Cout, Cin, k, in_fmt, packed, (cudaStream_t)stream);
+}
+
+extern "C" int soda_pconv_supported(const soda_pconv_desc_t* d, const void* x, const void* y, const void* residual) {
+  if (!d || !x || !y) return 0;
+  return soda::conv_tc4_supported(d, x, y, residual) ? 1 : 0;
+}
+
+extern "C" int soda_pconv_fwd(const soda_pconv_desc_t* d, const void* x, const void* packed, const float* descale,
+                              const float* shift, const void* residual, void* y, unsigned int* status, void* stream) {
+  using namespace soda;
+  if (!d || !x || !packed || !y || !descale) return fail(SODA_ERR_BAD_ARG, "pconv: null pointer");
+  if (d->N <= 0 || d->H <= 0 || d->W <= 0 || d->Cin <= 0 || d->Cout <= 0 || d->k <= 0 || d->stride <= 0)
+    return fail(SODA_ERR_BAD_ARG, "pconv: non-positive size");
+  return conv_tc4_dispatch(d, x, packed, descale, shift, residual, y, status, nullptr, stream);
+}
+
+extern "C" int soda_pconv_lif_fwd(const soda_pconv_desc_t* d, const void* x, const void* packed, const float* descale,
+                                  const float* shift, const void* residual, int T, const soda_neuron_params_t* np,
+                                  const float* v0, const float* i0, void* y, float* v_out, float* i_out,
+                                  unsigned int* status, void* stream) {
+  using namespace soda;
+  if (!d || !x || !packed || !y || !descale || !np || !v_out || !i_out)
+    return fail(SODA_ERR_BAD_ARG, "pconv_lif: null pointer");
+  if (d->N <= 0 || d->H <= 0 || d->W <= 0 || d->Cin <= 0 || d->Cout <= 0 || d->k <= 0 || d->stride <= 0)
+    return fail(SODA_ERR_BAD_ARG, "pconv_lif: non-positive size");
+  Tc4Lif l;
+  l.T = T, l.np = to_np(np), l.v0 = v0, l.i0 = i0, l.v_out = v_out, l.i_out = i_out;
+  return conv_tc4_dispatch(d, x, packed, descale, shift, residual, y, status, &l, stream);
+}

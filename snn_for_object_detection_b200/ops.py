@@ -404,6 +404,264 @@ def conv_lif(
 
 
 # --------------------------------------------------------------------------------------------
+# packed activation formats (rows N1 / N2): PAIR = fp16 hi | fp16 lo per 32-channel group, HALF = fp16
+# --------------------------------------------------------------------------------------------
+FMT_F32, FMT_PAIR, FMT_HALF = _lib.SODA_ACT_F32, _lib.SODA_ACT_PAIR, _lib.SODA_ACT_HALF
+# The storage dtype IS the format tag (it survives views and channel slices): a PAIR tensor has an fp32 tensor's
+# shape and strides (4 bytes per value) and is held as int32 so that no float arithmetic can be applied to it by
+# accident; a HALF tensor is an ordinary float16 tensor with exact small-integer values.
+_FMT_DTYPE = {FMT_F32: torch.float32, FMT_PAIR: torch.int32, FMT_HALF: torch.float16}
+_DTYPE_FMT = {v: k for k, v in _FMT_DTYPE.items()}
+_STATUS = {}
+
+
+def fmt_of(t: torch.Tensor) -> int:
+    try:
+        return _DTYPE_FMT[t.dtype]
+    except KeyError:
+        raise TypeError(f"unsupported activation dtype {t.dtype}") from None
+
+
+def empty_act(n: int, c: int, h: int, w: int, device, fmt: int) -> torch.Tensor:
+    return torch.empty((n, c, h, w), device=device, dtype=_FMT_DTYPE[fmt], memory_format=torch.channels_last)
+
+
+def _status(device) -> torch.Tensor:
+    """Per-device counter of values that left fp16's range when a kernel encoded them as PAIR / HALF."""
+    key = torch.device(device).index if torch.device(device).index is not None else torch.cuda.current_device()
+    t = _STATUS.get(key)
+    if t is None:
+        t = _STATUS[key] = torch.zeros(1, dtype=torch.int32, device=torch.device("cuda", key))
+    return t
+
+
+def overflow_count(device=None) -> int:
+    """Number of activation values beyond +-65504 met while encoding PAIR / HALF tensors on ``device`` so far
+    (synchronises).  Non-zero means the packed route saturated a value: rerun with ``SODA_PACKED=0``."""
+    return int(_status("cuda" if device is None else device).item())
+
+
+def act_convert(x: torch.Tensor, fmt: int, out: Optional[torch.Tensor] = None) -> torch.Tensor:
+    """Re-encodes a pixel-major activation tensor in another format (or copies it into a slice of the same)."""
+    _need_cuda(x, out)
+    src_fmt = fmt_of(x)
+    if x.dim() != 4:
+        raise ValueError("act_convert: [N, C, H, W] tensors only")
+    if _pm_strides(x) is None:
+        if src_fmt != FMT_F32:
+            raise ValueError("act_convert: packed tensors must be pixel-major")
+        x = x.contiguous(memory_format=torch.channels_last)
+    N, Cc, H, W = x.shape
+    if out is None:
+        out = empty_act(N, Cc, H, W, x.device, fmt)
+    elif out.shape != x.shape or fmt_of(out) != fmt:
+        raise ValueError("act_convert: out has the wrong shape or format")
+    so = _pm_strides(out)
+    if so is None:
+        raise ValueError("act_convert: out must be pixel-major")
+    si = _pm_strides(x)
+    check(
+        lib.soda_act_convert(x.data_ptr(), src_fmt, si[0], si[1], out.data_ptr(), fmt, so[0], so[1], N, H * W, Cc,
+                             _status(x.device).data_ptr(), _stream()),
+        "soda_act_convert",
+    )
+    if src_fmt != FMT_PAIR or fmt != FMT_PAIR:
+        mark_exact(out, exact_bound(x))
+    return out
+
+
+def to_f32(x: torch.Tensor) -> torch.Tensor:
+    """The fp32 view of an activation tensor of any format (a no-op for fp32)."""
+    return x if x.dtype == torch.float32 else act_convert(x, FMT_F32)
+
+
+class PackedPConv(NamedTuple):
+    packed: torch.Tensor
+    descale: torch.Tensor
+    shift: Optional[torch.Tensor]
+    Cout: int
+    Cin: int
+    k: int
+    stride: int
+    in_fmt: int
+
+
+def pconv_shape_ok(Cin: int, Cout: int, k: int, stride: int, in_fmt: int) -> bool:
+    return (Cin % (32 if in_fmt == FMT_PAIR else 64) == 0 and Cout % 32 == 0 and k in (1, 3) and stride in (1, 2)
+            and os.environ.get("SODA_CONV_KIND", "") != "fp32")
+
+
+def pack_pconv(weight: torch.Tensor, stride: int, scale: Optional[torch.Tensor], shift: Optional[torch.Tensor],
+               in_fmt: int) -> PackedPConv:
+    """``weight [Cout,Cin,k,k] * scale`` as fp16 hi | lo planes for soda_pconv_fwd.  The weights are first multiplied
+    by a power of two that puts the largest of them near 2^11 (fp16's normal range then covers 15 binades below it);
+    the kernel's epilogue multiplies by the inverse.  No host synchronisation: the factor stays on the device."""
+    _need_cuda(weight, scale, shift)
+    Cout, Cin, k, k2 = weight.shape
+    if k != k2:
+        raise ValueError("square kernels only")
+    w = weight.detach().contiguous().float()
+    sc = None if scale is None else scale.detach().contiguous().float()
+    m = (w if sc is None else w * sc.view(-1, 1, 1, 1)).abs().max()
+    e = torch.floor(torch.log2(2048.0 / m.clamp_min(1e-30))).clamp(-30.0, 30.0)
+    mult = torch.exp2(e).reshape(1).float()
+    descale = (1.0 / mult).float()
+    n = lib.soda_pconv_packed_bytes(Cout, Cin, k)
+    if n <= 0:
+        raise _lib.SodaError(f"soda_pconv_packed_bytes: unsupported conv {Cout}x{Cin}x{k}")
+    packed = torch.empty(n, device=w.device, dtype=torch.uint8)
+    check(
+        lib.soda_pconv_pack_weights(w.data_ptr(), _ptr(sc), mult.data_ptr(), Cout, Cin, k, in_fmt, packed.data_ptr(),
+                                    _stream()),
+        "soda_pconv_pack_weights",
+    )
+    sh = None if shift is None else shift.detach().contiguous().float()
+    return PackedPConv(packed, descale, sh, Cout, Cin, k, int(stride), in_fmt)
+
+
+def _pconv_desc(x, pc: PackedPConv, residual, out, out_fmt):
+    N, Cin, H, W = x.shape
+    if Cin != pc.Cin:
+        raise ValueError(f"pconv: input has {Cin} channels, weights expect {pc.Cin}")
+    in_fmt = fmt_of(x)
+    if in_fmt != pc.in_fmt:
+        raise ValueError("pconv: weights were packed for another input format")
+    Ho, Wo = conv_out_hw(H, W, pc.k, pc.stride)
+    if out is None:
+        out = empty_act(N, pc.Cout, Ho, Wo, x.device, FMT_F32 if out_fmt is None else out_fmt)
+    elif out.shape != (N, pc.Cout, Ho, Wo):
+        raise ValueError(f"pconv: out has shape {tuple(out.shape)}, expected {(N, pc.Cout, Ho, Wo)}")
+    d = _lib.PConvDesc()
+    d.N, d.H, d.W, d.Cin, d.Cout, d.k, d.stride = N, H, W, Cin, pc.Cout, pc.k, pc.stride
+    d.in_fmt, d.out_fmt = in_fmt, fmt_of(out)
+    d.flags = _lib.SODA_PCONV_FLAG_INPUT_EXACT if (in_fmt == FMT_PAIR and exact_bound(x) is not None
+                                                   and exact_bound(x) <= 2048) else 0
+    si, so = _pm_strides(x), _pm_strides(out)
+    if si is None or so is None:
+        raise ValueError("pconv: tensors must be pixel-major")
+    d.in_batch_stride, d.in_pix_stride = si
+    d.out_batch_stride, d.out_pix_stride = so
+    if residual is not None:
+        if residual.shape != out.shape:
+            raise ValueError("pconv: residual shape mismatch")
+        sr = _pm_strides(residual)
+        if sr is None:
+            raise ValueError("pconv: residual must be pixel-major")
+        d.res_fmt = fmt_of(residual)
+        d.res_batch_stride, d.res_pix_stride = sr
+    return d, out
+
+
+def pconv_ok(x: torch.Tensor, pc_shape, residual=None, out=None) -> bool:
+    """Cheap eligibility test of the packed-format tensor-core convolution for this input / destination."""
+    Cin, Cout, k, stride = pc_shape
+    if x.dtype not in (torch.int32, torch.float16) or not pconv_shape_ok(Cin, Cout, k, stride, fmt_of(x)):
+        return False
+    for t in (x, residual, out):
+        if t is None:
+            continue
+        st = _pm_strides(t)
+        if st is None:
+            return False
+        b = 2 if t.dtype == torch.float16 else 4
+        al = 64 if t.dtype == torch.float16 and t is not x else 128
+        if t.data_ptr() % al or (st[0] * b) % al or (st[1] * b) % al:
+            return False
+    return True
+
+
+@_prof("conv2d")
+def pconv(x: torch.Tensor, pc: PackedPConv, residual: Optional[torch.Tensor] = None,
+          out: Optional[torch.Tensor] = None, out_fmt: Optional[int] = None) -> torch.Tensor:
+    """``conv(x, W*scale) + shift (+ residual)`` on a PAIR / HALF input; the output format is ``out``'s, else
+    ``out_fmt`` (default fp32).  Reference: as :func:`conv2d`."""
+    _need_cuda(x, residual, out)
+    d, out = _pconv_desc(x, pc, residual, out, out_fmt)
+    check(
+        lib.soda_pconv_fwd(C.byref(d), x.data_ptr(), pc.packed.data_ptr(), pc.descale.data_ptr(), _ptr(pc.shift),
+                           _ptr(residual), out.data_ptr(), _status(x.device).data_ptr(), _stream()),
+        "soda_pconv_fwd",
+    )
+    return out
+
+
+@_prof("conv_lif")
+def pconv_lif(x: torch.Tensor, pc: PackedPConv, T: int, p: "NeuronConst", v0: Optional[torch.Tensor] = None,
+              i0: Optional[torch.Tensor] = None, residual: Optional[torch.Tensor] = None,
+              out: Optional[torch.Tensor] = None, out_fmt: Optional[int] = None):
+    """Fused ``LIF_T(conv(x, W*scale) + shift) (+ residual)`` on a PAIR / HALF input, see :func:`conv_lif`."""
+    _need_cuda(x, v0, i0, residual, out)
+    N = x.shape[0]
+    if N % T:
+        raise ValueError("pconv_lif: leading dimension is not a multiple of T")
+    d, out = _pconv_desc(x, pc, residual, out, out_fmt)
+    B = N // T
+    v = empty_pixel_major(B, pc.Cout, out.shape[2], out.shape[3], x.device)
+    i = torch.empty_like(v)
+    if v0 is not None:
+        v0 = _like_block(v0, v)
+        i0 = _like_block(i0, v)
+    npar = p.c()
+    check(
+        lib.soda_pconv_lif_fwd(C.byref(d), x.data_ptr(), pc.packed.data_ptr(), pc.descale.data_ptr(), _ptr(pc.shift),
+                               _ptr(residual), T, C.byref(npar), _ptr(v0), _ptr(i0), out.data_ptr(), v.data_ptr(),
+                               i.data_ptr(), _status(x.device).data_ptr(), _stream()),
+        "soda_pconv_lif_fwd",
+    )
+    mark_exact(out, 1 if residual is None else _plus(exact_bound(residual), 1))
+    return out, v, i
+
+
+def lif_scan_fmt_ok(x: torch.Tensor, residual: Optional[torch.Tensor], out: Optional[torch.Tensor]) -> bool:
+    if x.dim() != 4 or x.dtype != torch.float32 or x.shape[1] % 32 or not x.is_contiguous(memory_format=torch.channels_last):
+        return False
+    for t in (residual, out):
+        if t is None:
+            continue
+        ps = _pix_dense(t)
+        if t.shape != x.shape or ps is None:
+            return False
+        b = 2 if t.dtype == torch.float16 else 4
+        al = 128 if t.dtype == torch.int32 else 16
+        if t.data_ptr() % al or (ps * b) % al:
+            return False
+    return True
+
+
+@_prof("lif_scan")
+def lif_scan_fmt(x: torch.Tensor, T: int, v0=None, i0=None, p: "NeuronConst" = None,
+                 residual: Optional[torch.Tensor] = None, out: Optional[torch.Tensor] = None,
+                 out_fmt: Optional[int] = None):
+    """``LIF_T(x) (+ residual)`` with the residual and the output in any activation format; ``x`` is the dense fp32
+    conv output ``[T*B, C, H, W]``.  Returns ``(out, v_T, i_T)``."""
+    _need_cuda(x, v0, i0, residual, out)
+    p = LIF_DEFAULT if p is None else p
+    N, Cc, H, W = x.shape
+    if N % T:
+        raise ValueError("lif_scan_fmt: leading dimension is not a multiple of T")
+    if out is None:
+        out = empty_act(N, Cc, H, W, x.device, FMT_F32 if out_fmt is None else out_fmt)
+    if not lif_scan_fmt_ok(x, residual, out):
+        raise ValueError("lif_scan_fmt: unsupported layout (see lif_scan_fmt_ok)")
+    v = torch.empty_like(x[: N // T])
+    i = torch.empty_like(v)
+    if v0 is not None:
+        v0 = _like_block(v0, v)
+        i0 = _like_block(i0, v)
+    pc = p.c()
+    n_pix = (N // T) * H * W
+    check(
+        lib.soda_lif_fmt_fwd(C.byref(pc), x.data_ptr(), _ptr(v0), _ptr(i0), T, n_pix, Cc, _ptr(residual),
+                             0 if residual is None else fmt_of(residual),
+                             0 if residual is None else _pix_dense(residual), out.data_ptr(), fmt_of(out),
+                             _pix_dense(out), v.data_ptr(), i.data_ptr(), _status(x.device).data_ptr(), _stream()),
+        "soda_lif_fmt_fwd",
+    )
+    mark_exact(out, 1 if residual is None else _plus(exact_bound(residual), 1))
+    return out, v, i
+
+
+# --------------------------------------------------------------------------------------------
 # neuron scans (K3, K4, K8)
 # --------------------------------------------------------------------------------------------
 class NeuronConst(NamedTuple):

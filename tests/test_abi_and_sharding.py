@@ -24,7 +24,7 @@ def test_library_exports_every_declared_symbol():
     for n in names:
         assert hasattr(lib, n), f"{n} declared in include/soda_b200.h but not exported"
     lib.soda_abi_version.restype = ctypes.c_int
-    assert lib.soda_abi_version() == 1
+    assert lib.soda_abi_version() == 2
 
 
 def test_ctypes_binding_covers_the_header():
