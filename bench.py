@@ -298,7 +298,7 @@ def run_gpu_arm(args):
     # Dominant kernel of the step = conv_tc3_kernel<128, false> (tensor-core conv, Cout > 64, plain epilogue):
     # ALGORITHMIC flops of its launches (dense 2*MAC as the reference executes them) / their summed
     # device time, both from this run's CUDA events.
-    dom = [(m, ms) for fam_, m, ms in conv_launches if fam_ == "conv2d" and m["kind"] == 1 and m["Cout"] > 64]
+    dom = [(m, ms) for fam_, m, ms in conv_launches if fam_ == "conv2d" and m["kind"] in (1, 2) and m["Cout"] > 64]
     dom_flops, dom_ms = sum(flops(m) for m, _ in dom), sum(ms for _, ms in dom)
     achieved = dom_flops / (dom_ms * 1e-3) / 1e12 if dom_ms > 0 else None
     peak = pk["bf16_tflops_sustained"]

@@ -109,6 +109,10 @@ SODA_API int soda_bin_events(const void* events, const int64_t* sample_offsets, 
  * 16+ significant weight bits, half the tensor-core work and half the weight bytes of the tf32 + correction
  * scheme.  Implies SODA_CONV_FLAG_INPUT_EXACT_TF32. */
 #define SODA_CONV_FLAG_INPUT_EXACT_BF16 2
+/* flags (soda_conv_lif_fwd, direct event-frame kernel only): write the spikes as SODA_ACT_HALF / SODA_ACT_PAIR
+ * (see "packed activation formats" below) instead of fp32; `y` and the out strides are then those of that format. */
+#define SODA_CONV_FLAG_OUT_HALF 4
+#define SODA_CONV_FLAG_OUT_PAIR 8
 
 typedef struct {
   int N, H, W, Cin, Cout, k, stride;

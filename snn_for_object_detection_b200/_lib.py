@@ -18,6 +18,8 @@ SODA_CONV_FP32 = 0
 SODA_CONV_TC = 1
 SODA_CONV_FLAG_INPUT_EXACT_TF32 = 1
 SODA_CONV_FLAG_INPUT_EXACT_BF16 = 2
+SODA_CONV_FLAG_OUT_HALF = 4
+SODA_CONV_FLAG_OUT_PAIR = 8
 SODA_ACT_F32 = 0
 SODA_ACT_PAIR = 1
 SODA_ACT_HALF = 2

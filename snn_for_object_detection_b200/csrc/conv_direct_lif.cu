@@ -11,6 +11,8 @@
 // folded, [K][Cout_pad] = conv_ffma's packed layout) and the BN shift sit in shared memory.
 // Accumulation is a sequential fmaf chain in k = (ky*k + kx)*Cin + ci order - the order of
 // conv_ffma_kernel - so results are bit-identical to soda_conv2d_fwd(FP32) + soda_lif_fwd.
+#include <cuda_fp16.h>
+
 #include "common.cuh"
 #include "neuron.cuh"
 
@@ -18,14 +20,33 @@ namespace soda {
 
 struct DirectP {
   int T, B, H, W, Cin, Cout, Cout_pad, k, stride, pad, Ho, Wo, Ktot;
-  int64_t out_bs, out_ps;
+  int64_t out_bs, out_ps;   // BYTES
+  int out_fmt;              // SODA_ACT_F32 / PAIR / HALF (spikes are exact in all of them)
   NP np;
 };
 
+// byte offset of channel c (c % 4 == 0) inside a pixel of the output format
+__device__ __forceinline__ int64_t direct_ch_off(int fmt, int c) {
+  if (fmt == SODA_ACT_F32) return (int64_t)c * 4;
+  if (fmt == SODA_ACT_HALF) return (int64_t)c * 2;
+  return (int64_t)(c & ~31) * 4 + (int64_t)(c & 31) * 2;
+}
+__device__ __forceinline__ void direct_store4(uint8_t* dst, int fmt, float a, float b, float c, float d) {
+  if (fmt == SODA_ACT_F32) {
+    __stcs(reinterpret_cast<float4*>(dst), make_float4(a, b, c, d));
+    return;
+  }
+  const __half2 h0 = __floats2half2_rn(a, b), h1 = __floats2half2_rn(c, d);
+  uint2 u;
+  u.x = *reinterpret_cast<const uint32_t*>(&h0), u.y = *reinterpret_cast<const uint32_t*>(&h1);
+  __stcs(reinterpret_cast<uint2*>(dst), u);
+  if (fmt == SODA_ACT_PAIR) __stcs(reinterpret_cast<uint2*>(dst + 64), make_uint2(0u, 0u));   // lo halves: exact zero
+}
+
 template <int CPT>
 __device__ __forceinline__ void direct_neuron_store(const NP& np, const float (&acc)[CPT], const float (&sh)[CPT],
-                                                    float (&v)[CPT], float (&cur)[CPT], float* __restrict__ dst,
-                                                    int chalf) {
+                                                    float (&v)[CPT], float (&cur)[CPT], uint8_t* __restrict__ dst,
+                                                    int64_t off_hi, int fmt) {
   float z[CPT];
 #pragma unroll
   for (int c = 0; c < CPT; ++c) {
@@ -34,7 +55,7 @@ __device__ __forceinline__ void direct_neuron_store(const NP& np, const float (&
   }
 #pragma unroll
   for (int c = 0; c < CPT; c += 4)
-    __stcs(reinterpret_cast<float4*>(dst + (c ? chalf : 0)), make_float4(z[c], z[c + 1], z[c + 2], z[c + 3]));
+    direct_store4(dst + (c ? off_hi : 0), fmt, z[c], z[c + 1], z[c + 2], z[c + 3]);
 }
 
 // KS / CIN > 0: compile-time filter size and input channels (fully unrolled taps, input offsets
@@ -44,7 +65,7 @@ template <int CPT, int KS, int CIN>
 __global__ void __launch_bounds__(256, 2)
 conv_direct_lif_kernel(DirectP p, const float* __restrict__ x, const float* __restrict__ wp,
                        const float* __restrict__ shift, const float* __restrict__ v0,
-                       const float* __restrict__ i0, float* __restrict__ y, float* __restrict__ v_out,
+                       const float* __restrict__ i0, uint8_t* __restrict__ y, float* __restrict__ v_out,
                        float* __restrict__ i_out) {
   pdl_trigger();   // lets a dependent tensor-core conv start its prologue in this grid's tail
   extern __shared__ float smem_w[];  // [Ktot][Cout] weights, then [Cout] shift
@@ -93,8 +114,9 @@ conv_direct_lif_kernel(DirectP p, const float* __restrict__ x, const float* __re
   const int64_t frame_elems = (int64_t)p.Cin * p.H * p.W;
   const int64_t step_elems = frame_elems * p.B;
   const float* xb = x + (int64_t)b * frame_elems;          // frame (t, b) = xb + t * step_elems
-  float* yb = y + (int64_t)b * p.out_bs + (int64_t)rr * p.out_ps + c0;
+  uint8_t* yb = y + (int64_t)b * p.out_bs + (int64_t)rr * p.out_ps + direct_ch_off(p.out_fmt, c0);
   const int64_t y_step = (int64_t)p.B * p.out_bs;
+  const int64_t off_hi = direct_ch_off(p.out_fmt, chalf + c0) - direct_ch_off(p.out_fmt, c0);
 
   if constexpr (KS > 0) {
     constexpr int NT = KS * KS * CIN;
@@ -145,7 +167,7 @@ conv_direct_lif_kernel(DirectP p, const float* __restrict__ x, const float* __re
           }
         }
       }
-      direct_neuron_store<CPT>(p.np, acc, sh, v, cur, yb + (int64_t)t * y_step, chalf);
+      direct_neuron_store<CPT>(p.np, acc, sh, v, cur, yb + (int64_t)t * y_step, off_hi, p.out_fmt);
     }
   } else {
     for (int t = 0; t < p.T; ++t) {
@@ -173,7 +195,7 @@ conv_direct_lif_kernel(DirectP p, const float* __restrict__ x, const float* __re
           }
         }
       }
-      direct_neuron_store<CPT>(p.np, acc, sh, v, cur, yb + (int64_t)t * y_step, chalf);
+      direct_neuron_store<CPT>(p.np, acc, sh, v, cur, yb + (int64_t)t * y_step, off_hi, p.out_fmt);
     }
   }
 #pragma unroll
@@ -183,11 +205,23 @@ conv_direct_lif_kernel(DirectP p, const float* __restrict__ x, const float* __re
   }
 }
 
+static inline int direct_out_fmt(const soda_conv_desc_t* d) {
+  if (d->flags & SODA_CONV_FLAG_OUT_HALF) return SODA_ACT_HALF;
+  if (d->flags & SODA_CONV_FLAG_OUT_PAIR) return SODA_ACT_PAIR;
+  return SODA_ACT_F32;
+}
+
 bool conv_direct_lif_supported(const soda_conv_desc_t* d, const float* y) {
   if (!d->in_nchw || d->Cout % 8 != 0) return false;
   if ((int64_t)d->Cin * d->k * d->k * d->Cout > 11000) return false;  // weights + shift <= 48 KB of smem
+  const int fmt = direct_out_fmt(d);
+  if (fmt == SODA_ACT_PAIR) {
+    if (d->Cout % 32 != 0 || d->out_pix_stride % 32 != 0 || d->out_batch_stride % 32 != 0) return false;
+    if ((reinterpret_cast<uintptr_t>(y) & 127) != 0) return false;
+    return true;
+  }
   if (d->out_pix_stride % 4 != 0 || d->out_batch_stride % 4 != 0) return false;
-  if ((reinterpret_cast<uintptr_t>(y) & 15) != 0) return false;
+  if ((reinterpret_cast<uintptr_t>(y) & (fmt == SODA_ACT_HALF ? 7 : 15)) != 0) return false;
   return true;
 }
 
@@ -206,7 +240,9 @@ int conv_direct_lif_dispatch(const soda_conv_desc_t* d, const float* x, const fl
   p.Wo = (d->W + 2 * p.pad - d->k) / d->stride + 1;
   if (p.Ho <= 0 || p.Wo <= 0) return fail(SODA_ERR_BAD_ARG, "conv: empty output");
   p.Ktot = d->Cin * d->k * d->k;
-  p.out_bs = d->out_batch_stride, p.out_ps = d->out_pix_stride;
+  p.out_fmt = direct_out_fmt(d);
+  const int ob = p.out_fmt == SODA_ACT_HALF ? 2 : 4;
+  p.out_bs = d->out_batch_stride * ob, p.out_ps = d->out_pix_stride * ob;
   p.np = to_np(np);
   constexpr int CPT = 8;
   const int64_t threads = (int64_t)p.B * p.Ho * p.Wo * (p.Cout / CPT);
@@ -214,9 +250,9 @@ int conv_direct_lif_dispatch(const soda_conv_desc_t* d, const float* x, const fl
   const unsigned grid = (unsigned)ceil_div(threads, 256);
   cudaStream_t st = (cudaStream_t)stream;
   if (d->k == 3 && d->Cin == 2 && (int64_t)d->Cin * d->H * d->W < (1LL << 31))
-    conv_direct_lif_kernel<CPT, 3, 2><<<grid, 256, smem, st>>>(p, x, wp, shift, v0, i0, y, v_out, i_out);
+    conv_direct_lif_kernel<CPT, 3, 2><<<grid, 256, smem, st>>>(p, x, wp, shift, v0, i0, reinterpret_cast<uint8_t*>(y), v_out, i_out);
   else
-    conv_direct_lif_kernel<CPT, 0, 0><<<grid, 256, smem, st>>>(p, x, wp, shift, v0, i0, y, v_out, i_out);
+    conv_direct_lif_kernel<CPT, 0, 0><<<grid, 256, smem, st>>>(p, x, wp, shift, v0, i0, reinterpret_cast<uint8_t*>(y), v_out, i_out);
   return after_launch("conv_direct_lif_kernel");
 }
 

@@ -137,14 +137,27 @@ __device__ __forceinline__ void tc4_mma_role(const Tc4Params& p, uint32_t tmem_b
   const uint32_t a_stage16 = p.plane_bytes >> 4;
   const uint32_t b_kb16 = p.b_kb_bytes >> 4;
   constexpr uint32_t NACC = t4_nacc(BN);
+  // BN = 32: the two epilogue warps of a lane quarter alternate WORK UNITS (item x m-tile), and a warp must see every
+  // phase of a barrier it waits on - so the units of warpgroup e cycle through their own two stages {2e, 2e + 1}
+  constexpr bool UNIT_SPLIT = BN == 32;
   uint32_t sa = 0, pa = 0, sb = 0, pb = 0, cnt = 0;
+  uint32_t unit = 0, ce0 = 0, ce1 = 0;
   if (stat) mbar_wait(&b_full[0], 0);
-  for (int item = blockIdx.x; item < p.n_items; item += gridDim.x) {
+  for (int item = blockIdx.x; item < p.n_items; item += gridDim.x, unit += MT) {
     for (int t = 0; t < p.T_inner; ++t) {
-      uint32_t d_acc[2];
+      uint32_t d_acc[2], acc_i[2];
       _Pragma("unroll") for (int m = 0; m < 2; ++m) if (m < MT) {
-        const uint32_t a = (cnt + m) % NACC, ph = ((cnt + m) / NACC) & 1u;
+        uint32_t a, ph;
+        if (UNIT_SPLIT) {
+          const uint32_t e = (unit + m) & 1u;
+          const uint32_t c = e ? ce1 : ce0;
+          a = 2u * e + (c & 1u), ph = (c >> 1) & 1u;
+          if (e) ++ce1; else ++ce0;
+        } else {
+          a = (cnt + m) % NACC, ph = ((cnt + m) / NACC) & 1u;
+        }
         mbar_wait(&acc_empty[a], ph ^ 1);
+        acc_i[m] = a;
         d_acc[m] = tmem_base + a * (2 * BN);   // main; correction accumulator BN columns further
       }
       tc_fence_after();
@@ -208,7 +221,7 @@ __device__ __forceinline__ void tc4_mma_role(const Tc4Params& p, uint32_t tmem_b
         }
       }
       if (elect_one()) {
-        _Pragma("unroll") for (int m = 0; m < 2; ++m) if (m < MT) mma_commit(&acc_full[(cnt + m) % NACC]);
+        _Pragma("unroll") for (int m = 0; m < 2; ++m) if (m < MT) mma_commit(&acc_full[acc_i[m]]);
       }
       cnt += MT;
     }
@@ -374,7 +387,7 @@ conv_tc4_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__
     const uint32_t gch = p.out_fmt == SODA_ACT_HALF ? 4u : 8u;      // 16-byte chunks per 32-channel group
     const uint32_t gsh = p.out_fmt == SODA_ACT_HALF ? 2u : 3u;      // log2(gch)
     unsigned int n_over = 0;
-    uint32_t local = 0, unit = 0;
+    uint32_t local = 0, unit = 0, mine_cnt = 0;
     Tc4Iter it;
     it.init(p);
     for (int item = blockIdx.x; item < p.n_items; item += gridDim.x, it.next(p)) {
@@ -419,9 +432,10 @@ conv_tc4_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__
             si[c] = b.x, si[c + 1] = b.y, si[c + 2] = b.z, si[c + 3] = b.w;
           }
         }
-        for (int t = 0; t < p.T_inner; ++t, ++local) {
-          const uint32_t acc = local % NACC;
-          const uint32_t acc_ph = (local / NACC) & 1u;
+        for (int t = 0; t < p.T_inner; ++t, ++local, ++mine_cnt) {
+          // (see tc4_mma_role: with BN = 32 this warpgroup's units use its own two stages)
+          const uint32_t acc = UNIT_SPLIT ? 2u * (uint32_t)e + (mine_cnt & 1u) : local % NACC;
+          const uint32_t acc_ph = UNIT_SPLIT ? (mine_cnt >> 1) & 1u : (local / NACC) & 1u;
           const int64_t frame = frame0 + (int64_t)t * p.Bsz;
           const int64_t out_off = frame * p.out_bs + rr * p.out_ps;
           const int64_t res_off = frame * p.res_bs + rr * p.res_ps;

@@ -49,13 +49,92 @@ def _has_state(block: "BlockGen") -> bool:
     return False
 
 
+def _packed() -> bool:
+    """Inference keeps inter-layer activations in the tensor core's own operand formats (ops.FMT_PAIR /
+    FMT_HALF, rows N1 / N2 of the scope table) unless ``SODA_PACKED=0``; a recorded (training) graph is fp32."""
+    if os.environ.get("SODA_CONV_KIND", "") == "fp32":
+        return False   # the bit-faithful FP32-pipe cross-check route keeps fp32 activations end to end
+    return os.environ.get("SODA_PACKED", "1") != "0" and not torch.is_grad_enabled()
+
+
+def _real_fmt(C: int) -> int:
+    return ops.FMT_PAIR if (_packed() and C % 32 == 0) else ops.FMT_F32
+
+
+def _spike_fmt(C: int) -> int:
+    if not _packed() or C % 32:
+        return ops.FMT_F32
+    return ops.FMT_HALF if C % 64 == 0 else ops.FMT_PAIR
+
+
+def _wants_f32(layer) -> bool:
+    """Layers that read fp32: neuron cells (their scans take the conv output at full precision), stand-alone
+    BatchNorm, pooling, activations, user modules.  Convs, nested blocks, taps and Pass take any format."""
+    return not isinstance(layer, (SodaConv2d, BlockGen, Storage, nn.Identity))
+
+
 def _copy_into(src: torch.Tensor, dst: torch.Tensor) -> None:
     """Strided pixel-major copy on our own kernel (concat-slice store, generator.py:158)."""
     if torch.is_grad_enabled() and src.requires_grad:
         dst.copy_(src)   # training: differentiable slice store
         return
+    if src.dtype != torch.float32 or dst.dtype != torch.float32:
+        ops.act_convert(src, ops.fmt_of(dst), out=dst)
+        return
     ops.channel_affine(src, None, None, out=dst)
     ops.mark_exact(dst, ops.exact_bound(src))
+
+
+def _conv_eligible(conv: SodaConv2d) -> bool:
+    return conv.bias is None and conv.groups == 1 and conv.dilation == (1, 1)
+
+
+def _packed_input(Y: torch.Tensor, conv: SodaConv2d) -> Optional[torch.Tensor]:
+    """``Y`` in the format the packed-activation convolution reads (converted if it arrives as fp32), or None
+    when this convolution cannot take that route."""
+    Cin, Cout, k, s = conv.in_channels, conv.out_channels, conv.kernel_size[0], conv.stride[0]
+    if not _packed() or not _conv_eligible(conv) or Y.dim() != 4:
+        return None
+    if Y.dtype == torch.int32:
+        return Y if ops.pconv_shape_ok(Cin, Cout, k, s, ops.FMT_PAIR) else None
+    if Y.dtype == torch.float16:
+        if ops.pconv_shape_ok(Cin, Cout, k, s, ops.FMT_HALF):
+            return Y
+        return ops.act_convert(Y, ops.FMT_PAIR) if ops.pconv_shape_ok(Cin, Cout, k, s, ops.FMT_PAIR) else None
+    if Y.dtype != torch.float32 or not ops.pconv_shape_ok(Cin, Cout, k, s, ops.FMT_PAIR):
+        return None
+    b = ops.exact_bound(Y)
+    if b is not None and b <= 2048 and ops.pconv_shape_ok(Cin, Cout, k, s, ops.FMT_HALF):
+        return ops.act_convert(Y, ops.FMT_HALF)
+    return ops.act_convert(Y, ops.FMT_PAIR)
+
+
+def _run_conv(conv: SodaConv2d, norm, Y: torch.Tensor, out: Optional[torch.Tensor], out_fmt: int,
+              residual: Optional[torch.Tensor] = None) -> torch.Tensor:
+    """Conv (+ folded eval BatchNorm) on an input of any format; result in ``out`` (its format) or a new tensor of
+    ``out_fmt``."""
+    Yp = _packed_input(Y, conv)
+    if Yp is not None:
+        shape = (conv.in_channels, conv.out_channels, conv.kernel_size[0], conv.stride[0])
+        if ops.pconv_ok(Yp, shape, residual, out):
+            return ops.pconv(Yp, conv.packed_p(norm, ops.fmt_of(Yp)), residual=residual, out=out, out_fmt=out_fmt)
+    Yf = ops.to_f32(Y)
+    rf = None if residual is None else ops.to_f32(residual)
+    if out is not None and out.dtype != torch.float32:
+        tmp = conv(Yf, norm=norm, residual=rf)
+        ops.act_convert(tmp, ops.fmt_of(out), out=out)
+        return out
+    y = conv(Yf, norm=norm, residual=rf, out=out)
+    if out is None and out_fmt != ops.FMT_F32 and not torch.is_grad_enabled():
+        y = ops.act_convert(y, out_fmt)
+    return y
+
+
+def _fuse_items_ok(Cout: int, Ho: int, Wo: int, B: int, T: int) -> bool:
+    """The fused kernel walks the T steps inside one work item, so it needs (channel chunks x spatial tiles x
+    samples) >= about one wave of CTAs; small maps at small batch stay unfused."""
+    items = -(-Cout // (32 if Cout <= 32 else 64)) * (-(-Ho // 16)) * (-(-Wo // 8)) * B
+    return T == 1 or items >= int(os.environ.get("SODA_FUSE_LIF_MIN_ITEMS", "96"))
 
 
 def _fused_lif_plan(conv: SodaConv2d, norm: SodaBatchNorm2d, x: torch.Tensor, T: int):
@@ -143,10 +222,29 @@ class BlockGen(nn.Module):
         return self.forward_seq(X, 1, state)
 
     def forward_seq(
-        self, X: torch.Tensor, T: int, state: Optional[ListState] = None, out: Optional[torch.Tensor] = None
+        self, X: torch.Tensor, T: int, state: Optional[ListState] = None, out: Optional[torch.Tensor] = None,
+        packed_out: bool = False,
     ) -> Tuple[torch.Tensor, ListState]:
         """All T steps of the block; ``X`` is ``[T*B, C, H, W]`` time-major.  ``out``: optional
-        pre-allocated (possibly channel-sliced) destination for the block's result."""
+        pre-allocated (possibly channel-sliced) destination for the block's result.  ``packed_out``: the caller
+        is another planner and takes the result in whatever activation format it was produced in; otherwise
+        (the public call) the result is fp32."""
+        Y, out_state = self._forward_seq(X, T, state, out, f32_out=not packed_out and out is None)
+        if not packed_out and Y.dtype != torch.float32:
+            Y = ops.to_f32(Y)
+        return Y, out_state
+
+    def _ch32(self) -> bool:
+        """Every channel count inside this block (hence every concat-slice offset) is a multiple of 32."""
+        hit = getattr(self, "_ch32_cache", None)
+        if hit is None:
+            hit = all(c % 32 == 0 for c in self.branch_channels) and all(
+                m._ch32() for br in self.net for m in br if isinstance(m, BlockGen))
+            self._ch32_cache = hit
+        return hit
+
+    def _forward_seq(self, X, T, state, out, f32_out=False):
+        """``f32_out``: the result leaves the planner (public call): whatever produces it writes fp32 directly."""
         outs = []
         out_state = []
         state = [None] * len(self.net) if state is None else state
@@ -158,8 +256,9 @@ class BlockGen(nn.Module):
             out = None
         if self.merge == "dense" and not recording:
             Ho, Wo = self.out_hw(X.shape[2], X.shape[3])
-            dense_buf = out if out is not None else ops.empty_pixel_major(
-                X.shape[0], self.out_channels, Ho, Wo, X.device
+            dense_buf = out if out is not None else ops.empty_act(
+                X.shape[0], self.out_channels, Ho, Wo, X.device,
+                ops.FMT_PAIR if (_packed() and self._ch32() and not f32_out) else ops.FMT_F32,
             )
         c0 = 0
         for bi, (branch, flags, branch_state) in enumerate(zip(self.net, self.branch_state, state)):
@@ -175,7 +274,8 @@ class BlockGen(nn.Module):
             fuse_res = None
             if self.merge == "residual" and len(self.net) == 2 and self._is_identity(self.net[1 - bi]):
                 fuse_res = X
-            Y, consumed = self._run_branch(X, T, branch, flags, branch_state, dst, fuse_res, out)
+            Y, consumed = self._run_branch(X, T, branch, flags, branch_state, dst, fuse_res, out,
+                                           f32_out=f32_out and self.merge != "dense")
             out_state.append(branch_state)
             if consumed:
                 # the other branch is the identity: its state list is all None
@@ -197,7 +297,7 @@ class BlockGen(nn.Module):
                 for o in outs[1:]:
                     Y = Y + o                  # training: differentiable merge (= torch.stack(out).sum(0) for two branches)
             else:
-                Y = ops.add_n(outs)
+                Y = ops.add_n([ops.to_f32(o) for o in outs])
             if out is not None:
                 _copy_into(Y, out)
                 Y = out
@@ -244,19 +344,52 @@ class BlockGen(nn.Module):
         sl = nxt._identity_slice()
         if sl is None or sl[1] - sl[0] != C or nxt.out_hw(H, W) != (H, W):
             return None
-        buf = dst if (end_idx + 1 == n - 1 and dst is not None) else ops.empty_pixel_major(N, nxt.out_channels, H, W, device)
+        buf = dst if (end_idx + 1 == n - 1 and dst is not None) else ops.empty_act(
+            N, nxt.out_channels, H, W, device, ops.FMT_PAIR if (_packed() and nxt._ch32()) else ops.FMT_F32)
         prealloc[end_idx + 1] = buf
         return buf[:, sl[0] : sl[1]]
 
-    def _run_branch(self, X, T, branch, flags, branch_state, dst, residual=None, residual_dst=None):
+    def _next_fmt(self, branch, end_idx: int, n: int, C: int, spikes: bool, f32_out: bool = False) -> int:
+        """Format of the output of the layer group ending at ``end_idx`` when no destination buffer dictates it:
+        fp32 for a consumer that reads fp32 (or the public caller), else the tensor core's operand format."""
+        if end_idx + 1 < n and _wants_f32(branch[end_idx + 1]):
+            return ops.FMT_F32
+        if f32_out and all(isinstance(m, (nn.Identity, Storage)) for m in branch[end_idx + 1:]):
+            return ops.FMT_F32
+        return _spike_fmt(C) if spikes else _real_fmt(C)
+
+    def _fused_conv_lif(self, conv, norm, cell, Y, T, v0, i0, res, o, ofmt, Ho, Wo):
+        """ONE kernel for Conv -> Norm(eval) -> LIF over all T steps (membrane state on-chip, Residual identity
+        added, result stored in the destination's format), or None when no fused kernel takes this case."""
+        if Y.dtype == torch.float32:
+            pc = _fused_lif_plan(conv, norm, Y, T)
+            if pc is None:
+                return None
+            if pc.kind != _lib.SODA_CONV_TC:
+                # direct small-K kernel on the NCHW event frames: writes spikes in any format, takes no residual
+                if res is not None:
+                    return None
+                return ops.conv_lif(Y, pc, T, cell._const, v0, i0, out=o, out_fmt=ofmt)
+            if ofmt != ops.FMT_F32 or (res is not None and res.dtype != torch.float32):
+                return None
+            return ops.conv_lif(Y, pc, T, cell._const, v0, i0, residual=res, out=o)
+        shape = (conv.in_channels, conv.out_channels, conv.kernel_size[0], conv.stride[0])
+        if not ops.pconv_ok(Y, shape, res, o) or not _fuse_items_ok(conv.out_channels, Ho, Wo, Y.shape[0] // T, T):
+            return None
+        return ops.pconv_lif(Y, conv.packed_p(norm, ops.fmt_of(Y)), T, cell._const, v0, i0, residual=res, out=o,
+                             out_fmt=ofmt)
+
+    def _run_branch(self, X, T, branch, flags, branch_state, dst, residual=None, residual_dst=None, f32_out=False):
         """Runs one branch; fuses Conv+Norm(eval)(+LIF) and LI+Tanh; the branch's last layer writes
         straight into ``dst`` (concat slice / caller's buffer) when it can.  ``residual``: tensor the
         caller wants added to the branch result (then written to ``residual_dst`` if given); returns
-        ``(Y, residual_consumed)``."""
+        ``(Y, residual_consumed)``.  Activations travel in the format their consumer reads (ops.FMT_*)."""
         n = len(branch)
         Y = X
         idx = 0
         prealloc = {}  # index of a Dense block -> its concat buffer, allocated early by _lookahead_dst
+        pending_dst = None  # (index of a LIF cell, destination its scan should write) set by an unfused Conv/Norm/LIF
+        nograd = not torch.is_grad_enabled()
         while idx < n:
             layer = branch[idx]
             if isinstance(layer, SodaConv2d):
@@ -266,35 +399,46 @@ class BlockGen(nn.Module):
                     norm = branch[idx + 1]
                     last = idx + 1
                 cell = branch[last + 1] if last + 1 < n else None
-                if norm is not None and type(cell) is LIFCell and not torch.is_grad_enabled():
-                    pc = _fused_lif_plan(layer, norm, Y, T)
-                    if pc is not None:
-                        # Conv -> Norm -> LIF over all T steps in one kernel, membrane state on-chip
-                        last += 1
-                        is_last = last == n - 1
-                        st = branch_state[last]
-                        v0, i0 = (None, None) if st is None else (st.v, st.i)
-                        if is_last:
-                            o = dst if residual is None else residual_dst
-                        else:
-                            Ho, Wo = ops.conv_out_hw(Y.shape[2], Y.shape[3], pc.k, pc.stride)
-                            o = self._lookahead_dst(branch, last, n, Y.shape[0], pc.Cout, Ho, Wo, dst, Y.device, prealloc)
-                        Y, v, i = ops.conv_lif(Y, pc, T, cell._const, v0, i0,
-                                               residual=residual if is_last else None, out=o)
-                        branch_state[last] = LIFFeedForwardState(v, i)
-                        idx = last + 1
+                Yp = _packed_input(Y, layer)   # one conversion at most; later uses see the packed tensor
+                if Yp is not None:
+                    Y = Yp
+                Cout = layer.out_channels
+                Ho, Wo = ops.conv_out_hw(Y.shape[2], Y.shape[3], layer.kernel_size[0], layer.stride[0])
+                if (norm is not None and type(cell) is LIFCell and nograd and _conv_eligible(layer)
+                        and os.environ.get("SODA_FUSE_LIF", "1") != "0"):
+                    lif_idx = last + 1
+                    is_last = lif_idx == n - 1
+                    res = residual if is_last else None
+                    if is_last:
+                        o = dst if residual is None else residual_dst
+                    else:
+                        o = self._lookahead_dst(branch, lif_idx, n, Y.shape[0], Cout, Ho, Wo, dst, Y.device, prealloc)
+                    ofmt = ops.fmt_of(o) if o is not None else self._next_fmt(branch, lif_idx, n, Cout, res is None, f32_out)
+                    st = branch_state[lif_idx]
+                    v0, i0 = (None, None) if st is None else (st.v, st.i)
+                    done = self._fused_conv_lif(layer, norm, cell, Y, T, v0, i0, res, o, ofmt, Ho, Wo)
+                    if done is not None:
+                        Y, v, i = done
+                        branch_state[lif_idx] = LIFFeedForwardState(v, i)
+                        idx = lif_idx + 1
                         if is_last:
                             return Y, residual is not None
                         continue
-                if last == n - 1:
+                    # unfused: fp32 currents, then the cell's own branch below scans them (+ residual, + store into the
+                    # look-ahead destination chosen above)
+                    Y = _run_conv(layer, norm, Y, None, ops.FMT_F32)
+                    pending_dst = (lif_idx, o) if (o is not None and not is_last) else None
+                    idx = lif_idx
+                    continue
+                is_last = last == n - 1
+                if is_last:
                     o = dst
                 else:
-                    Ho, Wo = ops.conv_out_hw(Y.shape[2], Y.shape[3], layer.kernel_size[0], layer.stride[0])
-                    o = self._lookahead_dst(branch, last, n, Y.shape[0], layer.out_channels, Ho, Wo, dst, Y.device,
-                                            prealloc)
-                Y = layer(Y, norm=norm, out=o)
+                    o = self._lookahead_dst(branch, last, n, Y.shape[0], Cout, Ho, Wo, dst, Y.device, prealloc)
+                ofmt = ops.fmt_of(o) if o is not None else self._next_fmt(branch, last, n, Cout, False, f32_out)
+                Y = _run_conv(layer, norm, Y, o, ofmt)
                 idx = last + 1
-                if last == n - 1 and o is not None:
+                if is_last and o is not None:
                     return Y, False
                 continue
             if isinstance(layer, BlockGen):
@@ -306,49 +450,67 @@ class BlockGen(nn.Module):
                     Ho, Wo = layer.out_hw(Y.shape[2], Y.shape[3])
                     o = self._lookahead_dst(branch, idx, n, Y.shape[0], layer.out_channels, Ho, Wo, dst, Y.device,
                                             prealloc)
-                Y, branch_state[idx] = layer.forward_seq(Y, T, branch_state[idx], out=o)
+                Y, branch_state[idx] = layer.forward_seq(Y, T, branch_state[idx], out=o,
+                                                         packed_out=not (f32_out and idx == n - 1 and o is None))
                 idx += 1
                 if idx == n and o is not None:
                     return Y, False
                 continue
-            if type(layer) is LIFCell and idx + 1 < n and not torch.is_grad_enabled():
-                # Conv, Norm, LIF, Pool block: 2x2 / stride-2 pooling of the spikes fused into the scan's store
-                pool = branch[idx + 1]
-                mode = None
-                if isinstance(pool, SumPool2d) and pool.kernel_size == 2 and pool.stride == 2:
-                    mode = "S"
-                elif isinstance(pool, SodaPool2d) and pool.kernel_size == 2 and pool.stride == 2:
-                    mode = pool.mode
-                if mode is not None and Y.is_contiguous(memory_format=torch.channels_last):
-                    is_last = idx + 1 == n - 1
-                    o = (dst if residual is None else None) if is_last else None
-                    if ops.lif_pool_ok(Y, o):
-                        st = branch_state[idx]
-                        v0, i0 = (None, None) if st is None else (st.v, st.i)
-                        Y, v, i = ops.lif_pool_scan(Y, T, mode, v0, i0, layer._const, out=o)
-                        branch_state[idx] = LIFFeedForwardState(v, i)
-                        idx += 2
-                        if is_last and o is not None:
-                            return Y, False
-                        continue
-            if (type(layer) is LIFCell and idx == n - 1 and not torch.is_grad_enabled()
-                    and (residual is not None or dst is not None)):
-                # last layer of the branch: the scan adds the Residual identity and stores straight
-                # into the destination (concat slice) in the same pass
-                o = dst if residual is None else residual_dst
-                Yc = Y if Y.is_contiguous(memory_format=torch.channels_last) else None
-                if Yc is not None and ops.lif_scan_out_ok(Yc, residual, o):
+            if type(layer) is LIFCell and nograd:
+                Yf = ops.to_f32(Y)
+                if idx + 1 < n:
+                    # Conv, Norm, LIF, Pool block: 2x2 / stride-2 pooling of the spikes fused into the scan's store
+                    pool = branch[idx + 1]
+                    mode = None
+                    if isinstance(pool, SumPool2d) and pool.kernel_size == 2 and pool.stride == 2:
+                        mode = "S"
+                    elif isinstance(pool, SodaPool2d) and pool.kernel_size == 2 and pool.stride == 2:
+                        mode = pool.mode
+                    if mode is not None and Yf.is_contiguous(memory_format=torch.channels_last):
+                        is_last = idx + 1 == n - 1
+                        o = (dst if residual is None else None) if is_last else None
+                        if (o is None or o.dtype == torch.float32) and ops.lif_pool_ok(Yf, o):
+                            st = branch_state[idx]
+                            v0, i0 = (None, None) if st is None else (st.v, st.i)
+                            Y, v, i = ops.lif_pool_scan(Yf, T, mode, v0, i0, layer._const, out=o)
+                            branch_state[idx] = LIFFeedForwardState(v, i)
+                            idx += 2
+                            if is_last and o is not None:
+                                return Y, False
+                            continue
+                # the scan adds the Residual identity and stores straight into the destination (concat slice), in
+                # the destination's / the consumer's format, in the same pass
+                is_last = idx == n - 1
+                res = residual if is_last else None
+                pend, pending_dst = pending_dst, None
+                if is_last:
+                    o = dst if residual is None else residual_dst
+                elif pend is not None and pend[0] == idx:
+                    o = pend[1]
+                else:
+                    o = self._lookahead_dst(branch, idx, n, Yf.shape[0], Yf.shape[1], Yf.shape[2], Yf.shape[3], dst,
+                                            Yf.device, prealloc)
+                Yc = Yf if Yf.is_contiguous(memory_format=torch.channels_last) else None
+                if Yc is not None and ops.lif_scan_fmt_ok(Yc, res, o):
+                    ofmt = ops.fmt_of(o) if o is not None else self._next_fmt(branch, idx, n, Yf.shape[1], res is None, f32_out)
                     st = branch_state[idx]
                     v0, i0 = (None, None) if st is None else (st.v, st.i)
-                    Y, v, i = ops.lif_scan_out(Yc, T, v0, i0, layer._const, residual=residual, out=o)
+                    Y, v, i = ops.lif_scan_fmt(Yc, T, v0, i0, layer._const, residual=res, out=o, out_fmt=ofmt)
                     branch_state[idx] = LIFFeedForwardState(v, i)
-                    return Y, residual is not None
+                    idx += 1
+                    if is_last and res is not None:
+                        return Y, True
+                    continue
+                # the scan kernel does not take this layout: the generic cell path below produces a new tensor (a
+                # look-ahead buffer stays valid - the Dense block's own [Pass] branch then copies into its slice)
+                Y = Yf
             if isinstance(layer, (SNNCell, StateStorage)):
+                Y = ops.to_f32(Y)
                 fuse = (
                     isinstance(layer, LICell)
                     and idx + 1 < n
                     and isinstance(branch[idx + 1], nn.Tanh)
-                    and not torch.is_grad_enabled()
+                    and nograd
                 )
                 if fuse:
                     Y, branch_state[idx] = layer.forward_seq(Y, T, branch_state[idx], fuse_tanh=True)
@@ -358,15 +520,16 @@ class BlockGen(nn.Module):
                     idx += 1
                 continue
             if isinstance(layer, SodaBatchNorm2d):
-                Y = layer.forward_seq(Y, T)
+                Y = layer.forward_seq(ops.to_f32(Y), T)
                 idx += 1
                 continue
             if isinstance(layer, ConvLSTM):
-                Y, branch_state[idx] = layer.forward_seq(Y, T, branch_state[idx])
+                Y, branch_state[idx] = layer.forward_seq(ops.to_f32(Y), T, branch_state[idx])
                 idx += 1
                 continue
             if flags[idx]:
                 # unknown stateful module: per-step protocol, one call per time step
+                Y = ops.to_f32(Y)
                 if T == 1:
                     Y, branch_state[idx] = layer(Y, branch_state[idx])
                 else:
@@ -377,6 +540,8 @@ class BlockGen(nn.Module):
                         ys.append(y)
                     Y, branch_state[idx] = torch.cat(ys), s
             else:
+                if _wants_f32(layer):
+                    Y = ops.to_f32(Y)
                 b = ops.exact_bound(Y) if isinstance(layer, (nn.Identity, nn.Upsample)) else None
                 Y = layer(Y)
                 if b is not None and not (isinstance(layer, nn.Upsample) and layer.mode != "nearest"):
@@ -427,8 +592,8 @@ class BackboneGen(ModelGen):
     def forward(self, X: torch.Tensor, state: Optional[ListState] = None) -> Tuple[torch.Tensor, ListState]:
         return self.net(X, state)
 
-    def forward_seq(self, X: torch.Tensor, T: int, state: Optional[ListState] = None):
-        return self.net.forward_seq(X, T, state)
+    def forward_seq(self, X: torch.Tensor, T: int, state: Optional[ListState] = None, packed_out: bool = False):
+        return self.net.forward_seq(X, T, state, packed_out=packed_out)
 
 
 class NeckGen(ModelGen):
@@ -455,11 +620,12 @@ class NeckGen(ModelGen):
 
     def forward(self, X: torch.Tensor, state: Optional[ListState] = None):
         _, state = self.net(X, state)
-        return self._taps(), state
+        return [ops.to_f32(t) for t in self._taps()], state
 
-    def forward_seq(self, X: torch.Tensor, T: int, state: Optional[ListState] = None):
-        _, state = self.net.forward_seq(X, T, state)
-        return self._taps(), state
+    def forward_seq(self, X: torch.Tensor, T: int, state: Optional[ListState] = None, packed_out: bool = False):
+        _, state = self.net.forward_seq(X, T, state, packed_out=True)
+        taps = self._taps()
+        return (taps if packed_out else [ops.to_f32(t) for t in taps]), state
 
 
 class Head(nn.Module):
@@ -530,7 +696,7 @@ class HeadGen(ModelGen):
 
     def forward_seq(self, X: torch.Tensor, T: int, state: Optional[ListState] = None):
         state = [None] * 3 if state is None else list(state)
-        Y, state[0] = self.base_net.forward_seq(X, T, state[0])
+        Y, state[0] = self.base_net.forward_seq(X, T, state[0])   # X: any activation format (a neck tap)
         B = Y.shape[0] // T
         outs = []
         for k, net in ((1, self.box_net), (2, self.cls_net)):

@@ -56,6 +56,22 @@ class SodaConv2d(nn.Conv2d):
             self._pack_cache[kind] = hit
         return hit[1]
 
+    def packed_p(self, norm: Optional["SodaBatchNorm2d"], in_fmt: int) -> "ops.PackedPConv":
+        """fp16 hi | lo weight planes (BatchNorm folded) for the packed-activation convolution, cached like
+        :meth:`packed`."""
+        key = (self.weight.data_ptr(), self.weight._version, self.weight.device)
+        scale = shift = None
+        if norm is not None:
+            key = key + norm.fold_key()
+        slot = ("p", in_fmt)
+        hit = self._pack_cache.get(slot)
+        if hit is None or hit[0] != key:
+            if norm is not None:
+                scale, shift = norm.fold()
+            hit = (key, ops.pack_pconv(self.weight, self.stride[0], scale, shift, in_fmt))
+            self._pack_cache[slot] = hit
+        return hit[1]
+
     def packed_dgrad(self) -> ops.PackedConv:
         """Packed filter of the data-gradient convolution of a stride-1 layer: ``W'[ci, co, ky, kx] =
         W[co, ci, k-1-ky, k-1-kx]`` (tensor-core kind), cached on the weight version."""
@@ -83,9 +99,13 @@ class SodaBatchNorm2d(nn.BatchNorm2d):
 
     def fold_key(self):
         b = self.bias
+        # the train-mode kernels update the running statistics through raw pointers (no version bump): they bump
+        # `_stats_gen` instead (autograd.batchnorm_train), and num_batches_tracked moves with every train step
+        nbt = self.num_batches_tracked
         return (
             self.weight.data_ptr(), self.weight._version, self.running_mean._version, self.running_var._version,
             None if b is None else (b.data_ptr(), b._version),
+            getattr(self, "_stats_gen", 0), None if nbt is None else nbt._version,
         )
 
     def fold(self):

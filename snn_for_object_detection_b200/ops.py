@@ -64,10 +64,10 @@ def _prof(name):
             if name in ("conv2d", "conv_lif"):
                 x, pc = a[0], a[1]
                 PROFILE.setdefault(name + "_tags", []).append(
-                    f"{tuple(x.shape)}->{pc.Cout} k{pc.k} s{pc.stride} kind{pc.kind} exact{exact_bound(x)}")
+                    f"{tuple(x.shape)}->{pc.Cout} k{pc.k} s{pc.stride} kind{getattr(pc, 'kind', 'P')} exact{exact_bound(x)}")
                 PROFILE.setdefault(name + "_meta", []).append(
                     dict(N=x.shape[0], Cin=x.shape[1], H=x.shape[2], W=x.shape[3], Cout=pc.Cout, k=pc.k,
-                         stride=pc.stride, kind=pc.kind))
+                         stride=pc.stride, kind=getattr(pc, 'kind', 2)))   # 2 = packed-activation tensor-core route
             return r
 
         wrapped.__name__, wrapped.__doc__ = fn.__name__, fn.__doc__
@@ -350,6 +350,7 @@ def conv_lif(
     i0: Optional[torch.Tensor] = None,
     residual: Optional[torch.Tensor] = None,
     out: Optional[torch.Tensor] = None,
+    out_fmt: Optional[int] = None,
 ):
     """Fused ``LIF_T(conv(x, W*scale) + shift) (+ residual)`` over ``x [T*B, Cin, H, W]``.
 
@@ -375,9 +376,13 @@ def conv_lif(
         d.in_nchw = 0
         d.in_batch_stride, d.in_pix_stride = _pm_strides(x)
     if out is None:
-        out = empty_pixel_major(N, pc.Cout, Ho, Wo, x.device)
+        out = empty_act(N, pc.Cout, Ho, Wo, x.device, FMT_F32 if out_fmt is None else out_fmt)
     elif out.shape != (N, pc.Cout, Ho, Wo):
         raise ValueError(f"conv_lif: out has shape {tuple(out.shape)}, expected {(N, pc.Cout, Ho, Wo)}")
+    if out.dtype != torch.float32:
+        if not d.in_nchw:
+            raise ValueError("conv_lif: only the direct (NCHW frames) kernel writes packed spikes; use pconv_lif")
+        d.flags |= _lib.SODA_CONV_FLAG_OUT_HALF if out.dtype == torch.float16 else _lib.SODA_CONV_FLAG_OUT_PAIR
     os_ = _pm_strides(out)
     if os_ is None:
         raise ValueError("conv_lif: out must be pixel-major (channels_last) addressable")
@@ -465,8 +470,7 @@ def act_convert(x: torch.Tensor, fmt: int, out: Optional[torch.Tensor] = None) -
                              _status(x.device).data_ptr(), _stream()),
         "soda_act_convert",
     )
-    if src_fmt != FMT_PAIR or fmt != FMT_PAIR:
-        mark_exact(out, exact_bound(x))
+    mark_exact(out, exact_bound(x))
     return out
 
 

@@ -76,17 +76,20 @@ class SODa(nn.Module):
         T, B = X.shape[0], X.shape[1]
         state = [None] * 3 if state is None else list(state)
         Xf = X.reshape(T * B, *X.shape[2:])
-        base_out, state[0] = self.base_net.forward_seq(Xf, T, state[0])
-        neck_out, state[1] = self.neck_net.forward_seq(base_out, T, state[1])
+        # between the three generators the feature maps stay in the planner's own activation formats
+        base_out, state[0] = self.base_net.forward_seq(Xf, T, state[0], packed_out=True)
+        neck_out, state[1] = self.neck_net.forward_seq(base_out, T, state[1], packed_out=True)
         anchors, cls_preds, bbox_preds, state[2] = self.head_net.forward_seq(neck_out, T, state[2])
         return (anchors, cls_preds, bbox_preds), state
 
     def _forward_impl(self, X: torch.Tensor, state: Optional[ListState]):
         """One time step, state in / state out (reference soda.py:235-244)."""
         state = [None] * 3 if state is None else list(state)
-        base_out, state[0] = self.base_net.forward(X, state[0])
-        neck_out, state[1] = self.neck_net.forward(base_out, state[1])
-        anchors, cls_preds, bbox_preds, state[2] = self.head_net.forward(neck_out, state[2])
+        # = the generators' forward(X, state) with T = 1; the feature maps between them stay in the planner's
+        # activation formats exactly as in forward_seq, so both protocols give bit-identical results
+        base_out, state[0] = self.base_net.forward_seq(X, 1, state[0], packed_out=True)
+        neck_out, state[1] = self.neck_net.forward_seq(base_out, 1, state[1], packed_out=True)
+        anchors, cls_preds, bbox_preds, state[2] = self.head_net.forward_seq(neck_out, 1, state[2])
         return (anchors, cls_preds, bbox_preds), state
 
     def predict(self, X: torch.Tensor, state: Optional[ListState]):

@@ -38,9 +38,18 @@ def calibrate(model: torch.nn.Module, X: torch.Tensor, gain: float = 5.0) -> Non
     # or the layers they cover keep identity statistics and stay silent (and with them everything downstream)
     fused_plan = generator._fused_lif_plan
     generator._fused_lif_plan = lambda *a, **k: None
+    # ... and neither does the packed-activation route (ops.pconv): measure on the fp32 route
+    import os
+
+    packed_env = os.environ.get("SODA_PACKED")
+    os.environ["SODA_PACKED"] = "0"
     try:
         model(X)
     finally:
         SodaConv2d.forward = orig
         generator._fused_lif_plan = fused_plan
+        if packed_env is None:
+            del os.environ["SODA_PACKED"]
+        else:
+            os.environ["SODA_PACKED"] = packed_env
         model.train(was_training)

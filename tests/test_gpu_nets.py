@@ -387,7 +387,7 @@ def test_vgg_planner_fuses_lif_and_pool():
         n = _lib.launch_count() - n0
     Y = Y.reshape(T, B, *Y.shape[1:]).cpu()
     assert float((Y != torch.from_numpy(g["Y"])).float().mean()) <= SPIKE_TOL
-    assert n <= 6, n   # conv, lif+pool, conv, lif+pool, conv(+lif)
+    assert n <= 7, n   # conv+lif, pool, conv, lif+pool, [pooled counts -> tensor-core operand format], conv+lif
 
 
 @pytest.mark.gpu
