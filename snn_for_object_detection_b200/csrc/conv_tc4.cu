@@ -80,6 +80,8 @@ struct Tc4Params {
   const uint8_t* residual;
   uint8_t* y;
   unsigned int* status;          // [0] counts values that left fp16's range when encoded (NULL = not counted)
+  int dbg;                       // SODA_TC4_DBG timing experiments (results are garbage when set): 1 = no MMAs, 2 = no stores,
+                                 // 4 = no epilogue arithmetic / stores, 8 = no A loads, 16 = no (streamed) B loads
   int lif;
   NP np;
   const float* v0;
@@ -119,30 +121,81 @@ __device__ __forceinline__ float2 unpack_h2(uint32_t v) {
 __device__ __forceinline__ uint4 ldg_u4(const uint8_t* p) { return __ldg(reinterpret_cast<const uint4*>(p)); }
 
 // ================================ MMA issuer ===================================================
-template <int BN, int MT>
+// The issuer is ONE warp and every tcgen05.mma needs its two 64-bit descriptors in uniform registers: measured
+// (SODA_TC4_DBG=32), a k-block of 6 MMAs cost ~600 clk of issue time when the descriptors were assembled with 64-bit
+// adds inside the elected-lane region - 2.5 x the 240 clk the tensor core needs for them at N = 32.  So: the upper
+// descriptor words are kernel constants, the lower words (start address | leading byte offset) are 32-bit values
+// that only ever get small immediates added (an address field never carries out of its 14 bits for offsets inside
+// the shared-memory window), the tap loop is unrolled with compile-time tap offsets, and the operand format is a
+// template parameter.
+__device__ __forceinline__ void mma_f16_lo(uint32_t tmem_d, uint32_t a_lo, uint32_t a_hi, uint32_t b_lo, uint32_t b_hi,
+                                           uint32_t idesc, uint32_t accumulate) {
+  asm volatile(
+      "{\n\t.reg .pred p;\n\t.reg .b64 da, db;\n\t"
+      "setp.ne.b32 p, %6, 0;\n\t"
+      "mov.b64 da, {%1, %2};\n\t"
+      "mov.b64 db, {%3, %4};\n\t"
+      "tcgen05.mma.cta_group::1.kind::f16 [%0], da, db, %5, p;\n\t}"
+      ::"r"(tmem_d), "r"(a_lo), "r"(a_hi), "r"(b_lo), "r"(b_hi), "r"(idesc), "r"(accumulate)
+      : "memory");
+}
+
+// one k-block (one 128-byte A row slab x one filter tap) of one tile: 6 (PAIR) / 8 (HALF) MMAs
+template <int BN, bool PAIR>
+__device__ __forceinline__ void tc4_issue_kblock(uint32_t d_main, uint32_t a_lo, uint32_t a_hi, uint32_t b_lo,
+                                                 uint32_t b_hi, uint32_t accum, bool lo_pass) {
+  constexpr uint32_t idesc = idesc_f16(T4_BM, BN);
+  constexpr uint32_t B_TILE16 = (BN * 128) >> 4;
+  const uint32_t d_corr = d_main + BN;
+  if constexpr (PAIR) {
+    // A row = hi[0..15] hi[16..31] lo[0..15] lo[16..31]; B row = w_hi[0..31] | w_lo[0..31]
+    mma_f16_lo(d_main, a_lo, a_hi, b_lo, b_hi, idesc, accum);               // a_hi * w_hi
+    mma_f16_lo(d_main, a_lo + 2, a_hi, b_lo + 2, b_hi, idesc, 1);
+    mma_f16_lo(d_corr, a_lo, a_hi, b_lo + 4, b_hi, idesc, accum);           // a_hi * w_lo
+    mma_f16_lo(d_corr, a_lo + 2, a_hi, b_lo + 6, b_hi, idesc, 1);
+    if (lo_pass) {
+      mma_f16_lo(d_corr, a_lo + 4, a_hi, b_lo, b_hi, idesc, 1);             // a_lo * w_hi
+      mma_f16_lo(d_corr, a_lo + 6, a_hi, b_lo + 2, b_hi, idesc, 1);
+    }
+  } else {
+    // A row = a[0..63]; B tiles = w_hi[0..63], then w_lo[0..63]
+    mma_f16_lo(d_main, a_lo, a_hi, b_lo, b_hi, idesc, accum);
+    mma_f16_lo(d_main, a_lo + 2, a_hi, b_lo + 2, b_hi, idesc, 1);
+    mma_f16_lo(d_main, a_lo + 4, a_hi, b_lo + 4, b_hi, idesc, 1);
+    mma_f16_lo(d_main, a_lo + 6, a_hi, b_lo + 6, b_hi, idesc, 1);
+    mma_f16_lo(d_corr, a_lo, a_hi, b_lo + B_TILE16, b_hi, idesc, accum);
+    mma_f16_lo(d_corr, a_lo + 2, a_hi, b_lo + B_TILE16 + 2, b_hi, idesc, 1);
+    mma_f16_lo(d_corr, a_lo + 4, a_hi, b_lo + B_TILE16 + 4, b_hi, idesc, 1);
+    mma_f16_lo(d_corr, a_lo + 6, a_hi, b_lo + B_TILE16 + 6, b_hi, idesc, 1);
+  }
+}
+
+// HALO3: 3x3 stride-1 layers (one A stage = one channel slab with its halo, nine taps = nine descriptor offsets);
+// otherwise one A stage = one k-block (1x1 layers, stride-2 tap tiles).
+template <int BN, int MT, bool PAIR, bool HALO3>
 __device__ __forceinline__ void tc4_mma_role(const Tc4Params& p, uint32_t tmem_base, uint32_t smem_a_u32,
                                              uint32_t smem_b_u32, uint64_t* a_full, uint64_t* a_empty,
                                              uint64_t* b_full, uint64_t* b_empty, uint64_t* acc_full,
                                              uint64_t* acc_empty) {
-  constexpr uint32_t idesc = idesc_f16(T4_BM, BN);
-  constexpr uint32_t B_TILE16 = (BN * 128) >> 4;   // one BN x 128 B weight tile, in descriptor units
-  const uint64_t a_desc0 = smem_desc_sw128_sbo(smem_a_u32, p.sbo);
-  const uint64_t b_desc0 = smem_desc_sw128(smem_b_u32);
-  const bool stat = p.b_stationary != 0;
-  const bool halo3 = p.mode == 0 && p.k == 3;
-  const bool pair = p.in_fmt == SODA_ACT_PAIR;
-  const bool lo_pass = pair && !p.a_exact;
-  const int stages_per_tile = p.mode == 0 ? p.cblocks : p.kblocks;
-  const int kb_per_stage = p.mode == 0 ? p.taps : 1;
-  const uint32_t a_stage16 = p.plane_bytes >> 4;
-  const uint32_t b_kb16 = p.b_kb_bytes >> 4;
   constexpr uint32_t NACC = t4_nacc(BN);
+  constexpr uint32_t B_KB16 = ((BN * 128) >> 4) * (PAIR ? 1 : 2);   // one weight k-block, in descriptor units
+  constexpr int WW = T4_BW + 2;                                      // halo row pitch in pixels
   // BN = 32: the two epilogue warps of a lane quarter alternate WORK UNITS (item x m-tile), and a warp must see every
   // phase of a barrier it waits on - so the units of warpgroup e cycle through their own two stages {2e, 2e + 1}
   constexpr bool UNIT_SPLIT = BN == 32;
+  const uint64_t a_desc0 = smem_desc_sw128_sbo(smem_a_u32, p.sbo);
+  const uint64_t b_desc0 = smem_desc_sw128(smem_b_u32);
+  const uint32_t a_hi = (uint32_t)(a_desc0 >> 32), b_hi = (uint32_t)(b_desc0 >> 32);
+  const uint32_t a_lo0 = (uint32_t)a_desc0, b_lo0 = (uint32_t)b_desc0;
+  const bool stat = p.b_stationary != 0;
+  const bool lo_pass = PAIR && !p.a_exact;
+  const int stages_per_tile = HALO3 ? p.cblocks : p.kblocks;
+  const uint32_t a_stage16 = p.plane_bytes >> 4;
+  const uint32_t b_tap16 = (uint32_t)p.cblocks * B_KB16;   // resident weights are stored (tap, cb)
   uint32_t sa = 0, pa = 0, sb = 0, pb = 0, cnt = 0;
   uint32_t unit = 0, ce0 = 0, ce1 = 0;
-  if (stat) mbar_wait(&b_full[0], 0);
+  if (stat) mbar_wait_uniform(&b_full[0], 0);
+  const long long dbg_t0 = clock64();
   for (int item = blockIdx.x; item < p.n_items; item += gridDim.x, unit += MT) {
     for (int t = 0; t < p.T_inner; ++t) {
       uint32_t d_acc[2], acc_i[2];
@@ -156,64 +209,54 @@ __device__ __forceinline__ void tc4_mma_role(const Tc4Params& p, uint32_t tmem_b
         } else {
           a = (cnt + m) % NACC, ph = ((cnt + m) / NACC) & 1u;
         }
-        mbar_wait(&acc_empty[a], ph ^ 1);
+        mbar_wait_uniform(&acc_empty[a], ph ^ 1);
         acc_i[m] = a;
         d_acc[m] = tmem_base + a * (2 * BN);   // main; correction accumulator BN columns further
       }
       tc_fence_after();
-      uint32_t accum = 0;
       for (int st = 0; st < stages_per_tile; ++st) {
-        uint32_t s_m[2];
-        uint64_t a_st[2];
+        uint32_t s_m[2], a_lo[2];
         _Pragma("unroll") for (int m = 0; m < 2; ++m) if (m < MT) {
-          mbar_wait(&a_full[sa], pa);
-          a_st[m] = a_desc0 + (uint64_t)(sa * a_stage16);
+          mbar_wait_uniform(&a_full[sa], pa);
+          a_lo[m] = a_lo0 + sa * a_stage16;
           s_m[m] = sa;
           if (++sa == (uint32_t)p.a_stages) sa = 0, pa ^= 1;
         }
         tc_fence_after();
-        int ky = 0, kx = 0;
-        for (int tp = 0; tp < kb_per_stage; ++tp) {
-          uint64_t b_desc;
-          if (stat) {
-            const int bi = p.mode == 0 ? tp * p.cblocks + st : st;   // resident weights are stored (tap, cb)
-            b_desc = b_desc0 + (uint64_t)((uint32_t)bi * b_kb16);
-          } else {
-            mbar_wait(&b_full[sb], pb);
-            tc_fence_after();
-            b_desc = b_desc0 + (uint64_t)(sb * b_kb16);
-          }
-          const uint64_t tap_off = (uint64_t)(halo3 ? (uint32_t)(ky * p.WW + kx) * 8u : 0u);
-          if (elect_one()) {
-            // 32 bytes along the 128-byte row = 16 fp16 K elements; descriptor unit is 16 B
-            _Pragma("unroll") for (int m = 0; m < 2; ++m) if (m < MT) {
-              const uint64_t a_desc = a_st[m] + tap_off;
-              if (pair) {
-                // A row = hi[0..15] hi[16..31] lo[0..15] lo[16..31]; B row = w_hi[0..31] | w_lo[0..31]
-                mma_bf16_ss(d_acc[m], a_desc, b_desc, idesc, accum);               // a_hi * w_hi
-                mma_bf16_ss(d_acc[m], a_desc + 2, b_desc + 2, idesc, 1);
-                mma_bf16_ss(d_acc[m] + BN, a_desc, b_desc + 4, idesc, accum);      // a_hi * w_lo
-                mma_bf16_ss(d_acc[m] + BN, a_desc + 2, b_desc + 6, idesc, 1);
-                if (lo_pass) {
-                  mma_bf16_ss(d_acc[m] + BN, a_desc + 4, b_desc, idesc, 1);        // a_lo * w_hi
-                  mma_bf16_ss(d_acc[m] + BN, a_desc + 6, b_desc + 2, idesc, 1);
-                }
-              } else {
-                // A row = a[0..63]; B tiles = w_hi[0..63], then w_lo[0..63]
-                mma_bf16_ss(d_acc[m], a_desc, b_desc, idesc, accum);
-                mma_bf16_ss(d_acc[m], a_desc + 2, b_desc + 2, idesc, 1);
-                mma_bf16_ss(d_acc[m], a_desc + 4, b_desc + 4, idesc, 1);
-                mma_bf16_ss(d_acc[m], a_desc + 6, b_desc + 6, idesc, 1);
-                mma_bf16_ss(d_acc[m] + BN, a_desc, b_desc + B_TILE16, idesc, accum);
-                mma_bf16_ss(d_acc[m] + BN, a_desc + 2, b_desc + B_TILE16 + 2, idesc, 1);
-                mma_bf16_ss(d_acc[m] + BN, a_desc + 4, b_desc + B_TILE16 + 4, idesc, 1);
-                mma_bf16_ss(d_acc[m] + BN, a_desc + 6, b_desc + B_TILE16 + 6, idesc, 1);
-              }
+        const uint32_t acc0 = st != 0;
+        if constexpr (HALO3) {
+          uint32_t b_lo = b_lo0 + (uint32_t)st * B_KB16;   // resident: k-block (tap 0, slab st)
+          _Pragma("unroll") for (int tp = 0; tp < 9; ++tp) {
+            if (!stat) {
+              mbar_wait_uniform(&b_full[sb], pb);
+              tc_fence_after();
+              b_lo = b_lo0 + sb * B_KB16;
             }
+            constexpr int dummy = 0;
+            (void)dummy;
+            const uint32_t tap_off = (uint32_t)((tp / 3) * WW + (tp % 3)) * 8u;
+            if (elect_one()) {
+              _Pragma("unroll") for (int m = 0; m < 2; ++m) if (m < MT)
+                tc4_issue_kblock<BN, PAIR>(d_acc[m], a_lo[m] + tap_off, a_hi, b_lo, b_hi, tp == 0 ? acc0 : 1u, lo_pass);
+              if (!stat) mma_commit(&b_empty[sb]);
+            }
+            if (stat) b_lo += b_tap16;
+            else if (++sb == (uint32_t)p.b_stages) sb = 0, pb ^= 1;
+          }
+        } else {
+          uint32_t b_lo;
+          if (stat) {
+            b_lo = b_lo0 + (uint32_t)st * B_KB16;
+          } else {
+            mbar_wait_uniform(&b_full[sb], pb);
+            tc_fence_after();
+            b_lo = b_lo0 + sb * B_KB16;
+          }
+          if (elect_one()) {
+            _Pragma("unroll") for (int m = 0; m < 2; ++m) if (m < MT)
+              tc4_issue_kblock<BN, PAIR>(d_acc[m], a_lo[m], a_hi, b_lo, b_hi, acc0, lo_pass);
             if (!stat) mma_commit(&b_empty[sb]);
           }
-          accum = 1;
-          if (++kx == 3) kx = 0, ++ky;
           if (!stat && ++sb == (uint32_t)p.b_stages) sb = 0, pb ^= 1;
         }
         if (elect_one()) {
@@ -226,6 +269,8 @@ __device__ __forceinline__ void tc4_mma_role(const Tc4Params& p, uint32_t tmem_b
       cnt += MT;
     }
   }
+  if ((p.dbg & 32) && blockIdx.x == 0 && (threadIdx.x & 31) == 0)
+    printf("tc4 mma warp: %lld clk total, %u tiles, BN=%d MT=%d\n", clock64() - dbg_t0, cnt, BN, MT);
 }
 
 template <int BN, bool LIF>
@@ -251,7 +296,9 @@ conv_tc4_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 40);
   uint8_t* epi_base = reinterpret_cast<uint8_t*>(bars) + 512;
 
-  const int warp = threadIdx.x >> 5;
+  // the shuffle tells ptxas that the warp index is warp-uniform: the role branches below are then uniform branches
+  // and each role's scalar state (ring positions, descriptor words, barrier addresses) can live in uniform registers
+  const int warp = __shfl_sync(0xffffffffu, (int)(threadIdx.x >> 5), 0);
   const int lane = threadIdx.x & 31;
 
   if (warp == T4_W_PROD_A && lane == 0) {
@@ -305,11 +352,15 @@ conv_tc4_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__
         for (int tap = 0; tap < n_tap; ++tap) {
           for (int cb = 0; cb < p.cblocks; ++cb) {
             _Pragma("unroll") for (int m = 0; m < 2; ++m) if (m < p.mt) {
-              mbar_wait(&a_empty[s], ph ^ 1);
+              mbar_wait_uniform(&a_empty[s], ph ^ 1);
               if (elect_one()) {
-                mbar_expect_tx(&a_full[s], p.a_tx_bytes);
-                tma_load_4d_s(smem_a_u32 + s * p.plane_bytes, &tmA, &a_full[s], cb * rowch, x0[m] + kx, y0[m] + ky,
-                              img);
+                if (p.dbg & 8) {
+                  mbar_arrive(&a_full[s]);
+                } else {
+                  mbar_expect_tx(&a_full[s], p.a_tx_bytes);
+                  tma_load_4d_s(smem_a_u32 + s * p.plane_bytes, &tmA, &a_full[s], cb * rowch, x0[m] + kx, y0[m] + ky,
+                                img);
+                }
               }
               __syncwarp();
               if (++s == (uint32_t)p.a_stages) s = 0, ph ^= 1;
@@ -350,8 +401,9 @@ conv_tc4_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__
           for (int o = 0; o < n_o; ++o)
             for (int i = 0; i < n_i; ++i) {
               const int tap = p.mode == 0 ? i : o, cb = p.mode == 0 ? o : i;
-              mbar_wait(&b_empty[s], ph ^ 1);
-              if (elect_one()) {
+              mbar_wait_uniform(&b_empty[s], ph ^ 1);
+              if (elect_one() && (p.dbg & 16)) mbar_arrive(&b_full[s]);
+              if (elect_one() && !(p.dbg & 16)) {
                 mbar_expect_tx(&b_full[s], p.b_kb_bytes);
                 const uint32_t dst = smem_b_u32 + s * p.b_kb_bytes;
                 if (pair) {
@@ -368,12 +420,18 @@ conv_tc4_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__
       }
     }
   } else if (warp == T4_W_MMA) {
-    if (p.mt == 2)
-      tc4_mma_role<BN, 2>(p, tmem_base, smem_u32(smem_a), smem_u32(smem_b), a_full, a_empty, b_full, b_empty, acc_full,
-                          acc_empty);
-    else
-      tc4_mma_role<BN, 1>(p, tmem_base, smem_u32(smem_a), smem_u32(smem_b), a_full, a_empty, b_full, b_empty, acc_full,
-                          acc_empty);
+    const uint32_t sa_u32 = smem_u32(smem_a), sb_u32 = smem_u32(smem_b);
+    const bool pair = p.in_fmt == SODA_ACT_PAIR, halo3 = p.mode == 0 && p.k == 3;
+#define TC4_ROLE(MT_, PAIR_, HALO_) \
+    tc4_mma_role<BN, MT_, PAIR_, HALO_>(p, tmem_base, sa_u32, sb_u32, a_full, a_empty, b_full, b_empty, acc_full, acc_empty)
+    if (p.mt == 2) {
+      if (pair) { if (halo3) TC4_ROLE(2, true, true); else TC4_ROLE(2, true, false); }
+      else      { if (halo3) TC4_ROLE(2, false, true); else TC4_ROLE(2, false, false); }
+    } else {
+      if (pair) { if (halo3) TC4_ROLE(1, true, true); else TC4_ROLE(1, true, false); }
+      else      { if (halo3) TC4_ROLE(1, false, true); else TC4_ROLE(1, false, false); }
+    }
+#undef TC4_ROLE
   } else if (warp < 8) {
     // ================================ epilogue ================================================
     const int e = warp >> 2;
@@ -461,6 +519,7 @@ conv_tc4_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__
               __syncwarp();
               if (lane == 0) mbar_arrive(&acc_empty[acc]);
             }
+            if (p.dbg & 4) continue;
             const int co0 = co_base + g * 32;
             const bool group_live = co0 < p.Cout;   // Cout % 32 == 0: a group is whole or absent
             float o[32];
@@ -556,7 +615,7 @@ conv_tc4_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__
                 const float4 val = lds128(stage_u32 + rrow * 128u + ((j ^ (rrow & 7u)) << 4));
                 int64_t ooff;
                 asm volatile("ld.shared.b64 %0, [%1];" : "=l"(ooff) : "r"(table_u32 + ((uint32_t)half * 16u + rrow) * 8u));
-                if (ooff >= 0 && group_live)
+                if (ooff >= 0 && group_live && !(p.dbg & 2))
                   *reinterpret_cast<float4*>(p.y + ooff + (int64_t)co0 * out_cb + j * 16u) = val;
               }
             }
@@ -744,6 +803,10 @@ int conv_tc4_dispatch(const soda_pconv_desc_t* d, const void* x, const void* pac
                 "k in {1,3}, stride in {1,2}");
   Tc4Params p;
   memset(&p, 0, sizeof(p));
+  {
+    static const int env_dbg = []() { const char* e = getenv("SODA_TC4_DBG"); return e ? atoi(e) : 0; }();
+    p.dbg = env_dbg;
+  }
   p.H = d->H, p.W = d->W, p.Cin = d->Cin, p.Cout = d->Cout, p.k = d->k, p.stride = d->stride;
   p.pad = d->k / 2;
   p.Ho = (d->H + 2 * p.pad - d->k) / d->stride + 1;

@@ -43,6 +43,14 @@ __device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
   }
 }
 
+// Whole-warp wait whose loop branch is WARP-UNIFORM (a vote): ptxas then keeps everything the loop does not touch -
+// ring positions, descriptor words, TMEM addresses - in uniform registers, where tcgen05.mma / TMA need them; with
+// the plain per-thread loop above they live in vector registers and every use costs an R2UR.
+__device__ __forceinline__ void mbar_wait_uniform(uint64_t* bar, uint32_t parity) {
+  while (!__all_sync(0xffffffffu, mbar_try_wait(bar, parity))) {
+  }
+}
+
 // try_wait with a suspend-time hint (ns): the hardware parks the thread for up to that long instead of
 // returning to the polling loop, which keeps ~20 waiting warps from flooding the shared-memory pipe
 __device__ __forceinline__ void mbar_wait_hint(uint64_t* bar, uint32_t parity, uint32_t hint_ns) {
