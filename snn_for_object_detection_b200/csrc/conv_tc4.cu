@@ -25,8 +25,8 @@
 //
 // "im2col by descriptor" (one 18 x 10 halo tile per 32-channel slab, the nine taps are nine descriptors into it),
 // the persistent item loop, the weight-stationary / streamed plans and programmatic dependent launch are those of
-// conv_tc3.cu.  11 warps: w0-7 epilogue (two per TMEM lane quarter), w8 A producer (TMA), w9 B producer (TMA),
-// w10 MMA issuer + TMEM owner.
+// conv_tc3.cu.  12 warps: w0-7 epilogue (two per TMEM lane quarter), w8 A producer (TMA), w9 B producer (TMA),
+// w10 MMA issuer + TMEM owner, w11 idle (setmaxnreg moves registers between whole warpgroups).
 #include <stdlib.h>
 #include <string.h>
 
@@ -44,7 +44,7 @@ using namespace tc;
 
 constexpr int T4_BM = 128;
 constexpr int T4_BH = 16, T4_BW = 8;
-constexpr int T4_THREADS = 352;
+constexpr int T4_THREADS = 384;             // 12 warps: three whole warpgroups, as setmaxnreg wants
 constexpr int T4_W_PROD_A = 8, T4_W_PROD_B = 9, T4_W_MMA = 10;
 constexpr int T4_MAX_RING = 8;
 // accumulator stages in TMEM; a stage = main accumulator (hi * hi products) | correction accumulator (hi * lo, lo * hi):
@@ -52,8 +52,8 @@ constexpr int T4_MAX_RING = 8;
 // of MMAs into it - the 2^-11-small corrections, two thirds of the MMAs, must not pay it at the main sum's magnitude
 // (measured: one accumulator 4.1e-6 of the output scale at K = 1152, split 1.2e-6)
 __host__ __device__ constexpr int t4_nacc(int BN) { return BN == 128 ? 2 : 4; }
-constexpr int T4_EPI_BYTES = 2048 + 512;        // per epilogue warp: 16 rows x 128 B staging + 32-row offset table
-constexpr int T4_SMEM_LIMIT = 232448 - 1024 /*alignment slack*/ - 512 /*barriers*/ - 8 * T4_EPI_BYTES;
+constexpr int T4_EPI_BYTES = 4096;              // per epilogue warp: 32 rows x 128 B staging for the TMA store
+constexpr int T4_SMEM_LIMIT = 232448 - 1024 /*alignment slack*/ - 1024 /*barriers*/ - 8 * T4_EPI_BYTES;
 
 struct Tc4Params {
   int H, W, Cin, Cout, k, stride, pad, Ho, Wo;
@@ -119,6 +119,17 @@ __device__ __forceinline__ float2 unpack_h2(uint32_t v) {
   return __half22float2(h);
 }
 __device__ __forceinline__ uint4 ldg_u4(const uint8_t* p) { return __ldg(reinterpret_cast<const uint4*>(p)); }
+
+// TMA store of a staged tile (shared -> global), bulk-group completion
+__device__ __forceinline__ void tma_store_4d(const CUtensorMap* m, uint32_t smem_src, int c0, int c1, int c2, int c3) {
+  asm volatile("cp.async.bulk.tensor.4d.global.shared::cta.bulk_group [%0, {%2, %3, %4, %5}], [%1];"
+               ::"l"(reinterpret_cast<uint64_t>(m)), "r"(smem_src), "r"(c0), "r"(c1), "r"(c2), "r"(c3)
+               : "memory");
+}
+__device__ __forceinline__ void bulk_commit() { asm volatile("cp.async.bulk.commit_group;" ::: "memory"); }
+// all but the newest N bulk groups of this thread have finished READING their shared-memory source
+__device__ __forceinline__ void bulk_wait_read0() { asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory"); }
+__device__ __forceinline__ void bulk_wait_all() { asm volatile("cp.async.bulk.wait_group 0;" ::: "memory"); }
 
 // ================================ MMA issuer ===================================================
 // The issuer is ONE warp and every tcgen05.mma needs its two 64-bit descriptors in uniform registers: measured
@@ -275,7 +286,8 @@ __device__ __forceinline__ void tc4_mma_role(const Tc4Params& p, uint32_t tmem_b
 
 template <int BN, bool LIF>
 __global__ void __launch_bounds__(T4_THREADS, 1)
-conv_tc4_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB, Tc4Params p) {
+conv_tc4_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
+                const __grid_constant__ CUtensorMap tmY, Tc4Params p) {
   constexpr uint32_t B_TILE = BN * 128;
   constexpr uint32_t NACC = t4_nacc(BN);
   constexpr uint32_t TMEM_COLS = NACC * 2 * BN;
@@ -294,7 +306,7 @@ conv_tc4_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__
   uint64_t* acc_full = bars + 32;      // [4]
   uint64_t* acc_empty = bars + 36;     // [4]
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 40);
-  uint8_t* epi_base = reinterpret_cast<uint8_t*>(bars) + 512;
+  uint8_t* epi_base = reinterpret_cast<uint8_t*>(bars) + 1024;   // 1024-aligned: the store's swizzle is address-based
 
   // the shuffle tells ptxas that the warp index is warp-uniform: the role branches below are then uniform branches
   // and each role's scalar state (ring positions, descriptor words, barrier addresses) can live in uniform registers
@@ -304,6 +316,7 @@ conv_tc4_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__
   if (warp == T4_W_PROD_A && lane == 0) {
     prefetch_tmap(&tmA);
     prefetch_tmap(&tmB);
+    prefetch_tmap(&tmY);
     for (int s = 0; s < T4_MAX_RING; ++s) {
       mbar_init(&a_full[s], 1);
       mbar_init(&a_empty[s], 1);
@@ -324,6 +337,8 @@ conv_tc4_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__
   const uint32_t tmem_base = *tmem_slot;
   pdl_wait();
   const int my_chunk = blockIdx.x % p.nch;   // gridDim.x is a multiple of nch: fixed per CTA
+  // (setmaxnreg re-balancing between the warpgroups was tried: this ptxas keeps the kernel-wide cap of 168 for the
+  // epilogue and only adds spills to the de-allocated roles - measured with -Xptxas -v, not kept)
 
   if (warp == T4_W_PROD_A) {
     // ================================ A producer (TMA) =========================================
@@ -434,16 +449,21 @@ conv_tc4_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__
 #undef TC4_ROLE
   } else if (warp < 8) {
     // ================================ epilogue ================================================
+    // Two warps per TMEM lane quarter.  BN >= 64: warpgroup e owns columns [e*BN/2, (e+1)*BN/2) of every tile;
+    // BN = 32: the warpgroups alternate work units.  Per 32-channel group a warp reads main + correction accumulator,
+    // finishes the values (descale, shift, LIF step, residual), encodes its 32 rows x 128 (64) bytes into a swizzled
+    // 4 KB staging tile and hands it to TMA: the store engine clips the tile at the frame border and un-swizzles, no
+    // per-row addressing, predicates or global store instructions in the warp.
     const int e = warp >> 2;
     const int q = warp & 3;
     const uint32_t stage_u32 = smem_u32(epi_base) + (uint32_t)warp * T4_EPI_BYTES;
-    const uint32_t table_u32 = stage_u32 + 2048u;
     const int row = q * 32 + lane;
     const int64_t hw = (int64_t)p.Ho * p.Wo;
     const float descale = __ldg(p.descale);
-    const int out_cb = p.out_fmt == SODA_ACT_HALF ? 2 : 4;          // bytes per output channel
-    const uint32_t gch = p.out_fmt == SODA_ACT_HALF ? 4u : 8u;      // 16-byte chunks per 32-channel group
-    const uint32_t gsh = p.out_fmt == SODA_ACT_HALF ? 2u : 3u;      // log2(gch)
+    const bool half_out = p.out_fmt == SODA_ACT_HALF;
+    // byte address of 16-byte chunk j of this lane's row inside the staging tile (TMA SWIZZLE_128B / SWIZZLE_64B)
+    const uint32_t st_row = stage_u32 + (uint32_t)lane * (half_out ? 64u : 128u);
+    const uint32_t st_xor = half_out ? (((uint32_t)lane >> 1) & 3u) : ((uint32_t)lane & 7u);
     unsigned int n_over = 0;
     uint32_t local = 0, unit = 0, mine_cnt = 0;
     Tc4Iter it;
@@ -458,13 +478,15 @@ conv_tc4_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__
         }
         const int spt = it.sp * p.mt + m;
         bool valid;
-        int64_t rr;      // pixel index inside its frame
-        int64_t frame0;  // frame of step t = 0
+        int64_t rr;        // pixel index inside its frame
+        int64_t frame0;    // frame of step t = 0
+        int sx, sy;        // store coordinates of this warp's 32 rows: (x0, y0) of its 8 x 4 patch, or (first pixel, 0)
         if (p.flat) {
           const int64_t pix = (int64_t)spt * T4_BM + row;
           valid = pix < p.total_pix;
           frame0 = 0;
           rr = pix;
+          sx = spt * T4_BM + q * 32, sy = 0;
         } else {
           const int ty = spt / p.tiles_x, tx = spt - ty * p.tiles_x;
           const int oy = ty * T4_BH + (row >> 3);
@@ -472,6 +494,7 @@ conv_tc4_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__
           valid = oy < p.Ho && ox < p.Wo;
           rr = (int64_t)oy * p.Wo + ox;
           frame0 = it.outer;
+          sx = tx * T4_BW, sy = ty * T4_BH + q * 4;
         }
         const int col_base = UNIT_SPLIT ? 0 : e * (BN / 2);
         const int co_base = my_chunk * BN + col_base;
@@ -495,43 +518,52 @@ conv_tc4_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__
           const uint32_t acc = UNIT_SPLIT ? 2u * (uint32_t)e + (mine_cnt & 1u) : local % NACC;
           const uint32_t acc_ph = UNIT_SPLIT ? (mine_cnt >> 1) & 1u : (local / NACC) & 1u;
           const int64_t frame = frame0 + (int64_t)t * p.Bsz;
-          const int64_t out_off = frame * p.out_bs + rr * p.out_ps;
-          const int64_t res_off = frame * p.res_bs + rr * p.res_ps;
-          {
-            // row -> output byte offset (or -1) of this warp's 32 rows, for the staged coalesced stores
-            __syncwarp();
-            const int64_t my_out = valid ? out_off : -1;
-            asm volatile("st.shared.b64 [%0], %1;" ::"r"(table_u32 + (uint32_t)lane * 8u), "l"(my_out) : "memory");
-            __syncwarp();
+          const bool has_res = p.residual != nullptr && valid;
+          const uint8_t* res_row = p.residual + frame * p.res_bs + rr * p.res_ps;
+          // the residual row of the first group is fetched BEFORE the wait for the accumulator: its latency then
+          // overlaps the MMAs of this tile instead of sitting between the TMEM read and the store
+          uint4 rp[8];
+          if (has_res && co_base < p.Cout) {
+            const uint8_t* rp0 = res_row + (int64_t)co_base * (p.res_fmt == SODA_ACT_HALF ? 2 : 4);
+#pragma unroll
+            for (int j = 0; j < 8; ++j)
+              if (j < 4 || p.res_fmt != SODA_ACT_HALF) rp[j] = ldg_u4(rp0 + j * 16);
           }
           mbar_wait(&acc_full[acc], acc_ph);
           tc_fence_after();
           const uint32_t t_row = tmem_base + ((uint32_t)(q * 32) << 16) + acc * (2 * BN) + (uint32_t)col_base;
 #pragma unroll
           for (int g = 0; g < NG; ++g) {
-            uint32_t r[32], rc[32];
-            tmem_ld_32x32(t_row + g * 32, r);
-            tmem_ld_32x32(t_row + BN + g * 32, rc);
-            tmem_ld_wait();
-            if (g == NG - 1) {
-              // last TMEM read of this tile: hand the accumulator back before the global traffic
-              tc_fence_before();
-              __syncwarp();
-              if (lane == 0) mbar_arrive(&acc_empty[acc]);
-            }
-            if (p.dbg & 4) continue;
             const int co0 = co_base + g * 32;
             const bool group_live = co0 < p.Cout;   // Cout % 32 == 0: a group is whole or absent
             float o[32];
 #pragma unroll
-            for (int j = 0; j < 32; ++j) o[j] = (__uint_as_float(r[j]) + __uint_as_float(rc[j])) * descale;
-            if (p.shift != nullptr && group_live) {
+            for (int h = 0; h < 2; ++h) {   // 16 columns of main + correction at a time: 32 transient registers
+              uint32_t r[16], rc[16];
+              tmem_ld_32x16(t_row + g * 32 + h * 16, r);
+              tmem_ld_32x16(t_row + BN + g * 32 + h * 16, rc);
+              tmem_ld_wait();
+              if (g == NG - 1 && h == 1) {
+                // last TMEM read of this tile: hand the accumulator back before the rest
+                tc_fence_before();
+                __syncwarp();
+                if (lane == 0) mbar_arrive(&acc_empty[acc]);
+              }
+              if (p.shift != nullptr && group_live) {
 #pragma unroll
-              for (int j = 0; j < 32; j += 4) {
-                const float4 sh = __ldg(reinterpret_cast<const float4*>(p.shift + co0 + j));
-                o[j] += sh.x, o[j + 1] += sh.y, o[j + 2] += sh.z, o[j + 3] += sh.w;
+                for (int j = 0; j < 16; j += 4) {
+                  const float4 sh = __ldg(reinterpret_cast<const float4*>(p.shift + co0 + h * 16 + j));
+                  o[h * 16 + j] = fmaf(__uint_as_float(r[j]) + __uint_as_float(rc[j]), descale, sh.x);
+                  o[h * 16 + j + 1] = fmaf(__uint_as_float(r[j + 1]) + __uint_as_float(rc[j + 1]), descale, sh.y);
+                  o[h * 16 + j + 2] = fmaf(__uint_as_float(r[j + 2]) + __uint_as_float(rc[j + 2]), descale, sh.z);
+                  o[h * 16 + j + 3] = fmaf(__uint_as_float(r[j + 3]) + __uint_as_float(rc[j + 3]), descale, sh.w);
+                }
+              } else {
+#pragma unroll
+                for (int j = 0; j < 16; ++j) o[h * 16 + j] = (__uint_as_float(r[j]) + __uint_as_float(rc[j])) * descale;
               }
             }
+            if (p.dbg & 4) continue;
             if constexpr (LIF) {
 #pragma unroll
               for (int j = 0; j < 32; ++j) {
@@ -540,21 +572,24 @@ conv_tc4_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__
                 o[j] = z;
               }
             }
-            if (p.residual != nullptr && valid && group_live) {
+            if (has_res && group_live) {
+              if (g > 0) {
+                const uint8_t* rpg = res_row + (int64_t)co0 * (p.res_fmt == SODA_ACT_HALF ? 2 : 4);
+#pragma unroll
+                for (int j = 0; j < 8; ++j)
+                  if (j < 4 || p.res_fmt != SODA_ACT_HALF) rp[j] = ldg_u4(rpg + j * 16);
+              }
               if (p.res_fmt == SODA_ACT_F32) {
-                const uint8_t* rp = p.residual + res_off + (int64_t)co0 * 4;
 #pragma unroll
                 for (int j = 0; j < 8; ++j) {
-                  const uint4 u = ldg_u4(rp + j * 16);
-                  o[4 * j] += __uint_as_float(u.x), o[4 * j + 1] += __uint_as_float(u.y);
-                  o[4 * j + 2] += __uint_as_float(u.z), o[4 * j + 3] += __uint_as_float(u.w);
+                  o[4 * j] += __uint_as_float(rp[j].x), o[4 * j + 1] += __uint_as_float(rp[j].y);
+                  o[4 * j + 2] += __uint_as_float(rp[j].z), o[4 * j + 3] += __uint_as_float(rp[j].w);
                 }
               } else if (p.res_fmt == SODA_ACT_PAIR) {
-                const uint8_t* rp = p.residual + res_off + (int64_t)co0 * 4;
 #pragma unroll
                 for (int j = 0; j < 4; ++j) {
-                  const uint4 h = ldg_u4(rp + j * 16), l = ldg_u4(rp + 64 + j * 16);
-                  const uint32_t hw4[4] = {h.x, h.y, h.z, h.w}, lw4[4] = {l.x, l.y, l.z, l.w};
+                  const uint32_t hw4[4] = {rp[j].x, rp[j].y, rp[j].z, rp[j].w};
+                  const uint32_t lw4[4] = {rp[j + 4].x, rp[j + 4].y, rp[j + 4].z, rp[j + 4].w};
 #pragma unroll
                   for (int w = 0; w < 4; ++w) {
                     const float2 a = unpack_h2(hw4[w]), b = unpack_h2(lw4[w]);
@@ -563,11 +598,9 @@ conv_tc4_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__
                   }
                 }
               } else {
-                const uint8_t* rp = p.residual + res_off + (int64_t)co0 * 2;
 #pragma unroll
                 for (int j = 0; j < 4; ++j) {
-                  const uint4 h = ldg_u4(rp + j * 16);
-                  const uint32_t hw4[4] = {h.x, h.y, h.z, h.w};
+                  const uint32_t hw4[4] = {rp[j].x, rp[j].y, rp[j].z, rp[j].w};
 #pragma unroll
                   for (int w = 0; w < 4; ++w) {
                     const float2 a = unpack_h2(hw4[w]);
@@ -582,6 +615,7 @@ conv_tc4_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__
 #pragma unroll
               for (int j = 0; j < 32; ++j) w[j] = __float_as_uint(o[j]);
             } else {
+              float amax = 0.f;
 #pragma unroll
               for (int j = 0; j < 16; ++j) {
                 const uint32_t hi = pack_h2(o[2 * j], o[2 * j + 1]);
@@ -590,34 +624,23 @@ conv_tc4_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__
                   const float2 hf = unpack_h2(hi);
                   w[16 + j] = pack_h2(o[2 * j] - hf.x, o[2 * j + 1] - hf.y);
                 }
-                if (p.status != nullptr)
-                  n_over += (fabsf(o[2 * j]) > 65504.f) + (fabsf(o[2 * j + 1]) > 65504.f);
+                amax = fmaxf(amax, fmaxf(fabsf(o[2 * j]), fabsf(o[2 * j + 1])));
               }
+              n_over += amax > 65504.f;
             }
-            // ---- staged, coalesced store: 16 rows through 2 KB of shared memory at a time ----
+            // ---- stage (swizzled) and let TMA store it ----
+            if (lane == 0) bulk_wait_read0();   // this warp's previous store has read the staging tile
+            __syncwarp();
 #pragma unroll
-            for (int half = 0; half < 2; ++half) {
-              __syncwarp();
-              if ((lane >> 4) == half) {
-                const uint32_t r16 = lane & 15u;
-                const uint32_t rowa = stage_u32 + r16 * 128u;
-#pragma unroll
-                for (uint32_t j = 0; j < 8; ++j)
-                  if (j < gch)
-                    sts128(rowa + ((j ^ (r16 & 7u)) << 4), __uint_as_float(w[4 * j]), __uint_as_float(w[4 * j + 1]),
-                           __uint_as_float(w[4 * j + 2]), __uint_as_float(w[4 * j + 3]));
-              }
-              __syncwarp();
-              const uint32_t n_it = (16u * gch) >> 5;   // 4 (8 chunks per row) or 2 (4 chunks per row)
-              for (uint32_t i2 = 0; i2 < n_it; ++i2) {
-                const uint32_t rrow = i2 * (32u >> gsh) + ((uint32_t)lane >> gsh);
-                const uint32_t j = (uint32_t)lane & (gch - 1u);
-                const float4 val = lds128(stage_u32 + rrow * 128u + ((j ^ (rrow & 7u)) << 4));
-                int64_t ooff;
-                asm volatile("ld.shared.b64 %0, [%1];" : "=l"(ooff) : "r"(table_u32 + ((uint32_t)half * 16u + rrow) * 8u));
-                if (ooff >= 0 && group_live && !(p.dbg & 2))
-                  *reinterpret_cast<float4*>(p.y + ooff + (int64_t)co0 * out_cb + j * 16u) = val;
-              }
+            for (uint32_t j = 0; j < 8; ++j)
+              if (j < 4 || !half_out)
+                sts128(st_row + ((j ^ st_xor) << 4), __uint_as_float(w[4 * j]), __uint_as_float(w[4 * j + 1]),
+                       __uint_as_float(w[4 * j + 2]), __uint_as_float(w[4 * j + 3]));
+            fence_proxy_async_smem();
+            __syncwarp();
+            if (lane == 0 && group_live && !(p.dbg & 2)) {
+              tma_store_4d(&tmY, stage_u32, co0, sx, sy, p.flat ? 0 : (int)frame);
+              bulk_commit();
             }
           }
         }
@@ -633,6 +656,7 @@ conv_tc4_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__
         }
       }  // m
     }
+    if (lane == 0) bulk_wait_all();
     if (p.status != nullptr && n_over != 0) atomicAdd(p.status, n_over);
   }
 
@@ -720,11 +744,12 @@ static EncodeTiledFn4 get_encode_fn4() {
 }
 
 static int encode_map4(CUtensorMap* m, CUtensorMapDataType dt, const void* base, int rank, const cuuint64_t* dims,
-                       const cuuint64_t* strides_b, const cuuint32_t* box, const cuuint32_t* estr) {
+                       const cuuint64_t* strides_b, const cuuint32_t* box, const cuuint32_t* estr,
+                       CUtensorMapSwizzle swz = CU_TENSOR_MAP_SWIZZLE_128B) {
   EncodeTiledFn4 fn = get_encode_fn4();
   if (fn == nullptr) return fail(SODA_ERR_CUDA, "pconv: cuTensorMapEncodeTiled entry point not available");
   CUresult r = fn(m, dt, (cuuint32_t)rank, const_cast<void*>(base), dims, strides_b, box, estr,
-                  CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                  CU_TENSOR_MAP_INTERLEAVE_NONE, swz, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
                   CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
   if (r != CUDA_SUCCESS) {
     set_error("pconv: cuTensorMapEncodeTiled failed (%d)", (int)r);
@@ -734,8 +759,8 @@ static int encode_map4(CUtensorMap* m, CUtensorMapDataType dt, const void* base,
 }
 
 template <int BN, bool LIF>
-static int launch_tc4(const CUtensorMap& tmA, const CUtensorMap& tmB, const Tc4Params& p, int grid, size_t smem,
-                      cudaStream_t st) {
+static int launch_tc4(const CUtensorMap& tmA, const CUtensorMap& tmB, const CUtensorMap& tmY, const Tc4Params& p, int grid,
+                      size_t smem, cudaStream_t st) {
   // the opt-in is per device: set it on every launch (cheap), not once per process
   cudaError_t e = cudaFuncSetAttribute(conv_tc4_kernel<BN, LIF>, cudaFuncAttributeMaxDynamicSharedMemorySize, 232448);
   if (e != cudaSuccess) {
@@ -752,9 +777,9 @@ static int launch_tc4(const CUtensorMap& tmA, const CUtensorMap& tmB, const Tc4P
     at[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
     at[0].val.programmaticStreamSerializationAllowed = 1;
     cfg.attrs = at, cfg.numAttrs = 1;
-    cudaLaunchKernelEx(&cfg, conv_tc4_kernel<BN, LIF>, tmA, tmB, p);
+    cudaLaunchKernelEx(&cfg, conv_tc4_kernel<BN, LIF>, tmA, tmB, tmY, p);
   } else {
-    conv_tc4_kernel<BN, LIF><<<grid, T4_THREADS, smem, st>>>(tmA, tmB, p);
+    conv_tc4_kernel<BN, LIF><<<grid, T4_THREADS, smem, st>>>(tmA, tmB, tmY, p);
   }
   return after_launch("conv_tc4_kernel");
 }
@@ -894,6 +919,28 @@ int conv_tc4_dispatch(const soda_pconv_desc_t* d, const void* x, const void* pac
     int rc = encode_map4(&tmB, CU_TENSOR_MAP_DATA_TYPE_FLOAT16, packed, 3, dims, str, box, es);
     if (rc) return rc;
   }
+  CUtensorMap tmY;
+  {
+    // the epilogue's TMA store: 32 channels x (8 x 4 pixels | 32 pixels) per instruction, clipped at the frame border
+    const CUtensorMapDataType ydt = d->out_fmt == SODA_ACT_HALF ? CU_TENSOR_MAP_DATA_TYPE_FLOAT16 : CU_TENSOR_MAP_DATA_TYPE_FLOAT32;
+    const CUtensorMapSwizzle yswz = d->out_fmt == SODA_ACT_HALF ? CU_TENSOR_MAP_SWIZZLE_64B : CU_TENSOR_MAP_SWIZZLE_128B;
+    const cuuint32_t es[4] = {1, 1, 1, 1};
+    int rc;
+    if (p.flat) {
+      const cuuint64_t dims[4] = {(cuuint64_t)d->Cout, (cuuint64_t)p.total_pix, 1, 1};
+      const cuuint64_t str[3] = {(cuuint64_t)d->out_pix_stride * ob, (cuuint64_t)p.total_pix * d->out_pix_stride * ob,
+                                 (cuuint64_t)p.total_pix * d->out_pix_stride * ob};
+      const cuuint32_t box[4] = {32, 32, 1, 1};
+      rc = encode_map4(&tmY, ydt, y, 4, dims, str, box, es, yswz);
+    } else {
+      const cuuint64_t dims[4] = {(cuuint64_t)d->Cout, (cuuint64_t)p.Wo, (cuuint64_t)p.Ho, (cuuint64_t)d->N};
+      const cuuint64_t str[3] = {(cuuint64_t)d->out_pix_stride * ob, (cuuint64_t)p.Wo * d->out_pix_stride * ob,
+                                 (cuuint64_t)(d->N == 1 ? HWo * d->out_pix_stride : d->out_batch_stride) * ob};
+      const cuuint32_t box[4] = {32, T4_BW, 4, 1};
+      rc = encode_map4(&tmY, ydt, y, 4, dims, str, box, es, yswz);
+    }
+    if (rc) return rc;
+  }
   // shared-memory plan: weights resident if one output-channel chunk fits beside an A ring of >= min_a planes,
   // else a weight ring as well
   const int64_t b_total = (int64_t)p.kblocks * b_kb;
@@ -936,15 +983,15 @@ int conv_tc4_dispatch(const soda_pconv_desc_t* d, const void* x, const void* pac
   if (grid < p.nch) grid = p.nch;
   p.it_step_sp = (grid / p.nch) % p.n_sp_items;
   p.it_step_outer = (grid / p.nch) / p.n_sp_items;
-  const size_t smem = (size_t)p.b_region_bytes + (size_t)p.a_stages * p.plane_bytes + 512 + 8 * T4_EPI_BYTES + 1024;
+  const size_t smem = (size_t)p.b_region_bytes + (size_t)p.a_stages * p.plane_bytes + 1024 + 8 * T4_EPI_BYTES + 1024;
   cudaStream_t st = (cudaStream_t)stream;
   if (is_lif) {
-    if (BN == 32) return launch_tc4<32, true>(tmA, tmB, p, grid, smem, st);
-    return launch_tc4<64, true>(tmA, tmB, p, grid, smem, st);
+    if (BN == 32) return launch_tc4<32, true>(tmA, tmB, tmY, p, grid, smem, st);
+    return launch_tc4<64, true>(tmA, tmB, tmY, p, grid, smem, st);
   }
-  if (BN == 32) return launch_tc4<32, false>(tmA, tmB, p, grid, smem, st);
-  if (BN == 64) return launch_tc4<64, false>(tmA, tmB, p, grid, smem, st);
-  return launch_tc4<128, false>(tmA, tmB, p, grid, smem, st);
+  if (BN == 32) return launch_tc4<32, false>(tmA, tmB, tmY, p, grid, smem, st);
+  if (BN == 64) return launch_tc4<64, false>(tmA, tmB, tmY, p, grid, smem, st);
+  return launch_tc4<128, false>(tmA, tmB, tmY, p, grid, smem, st);
 }
 
 }  // namespace soda
