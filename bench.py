@@ -1,21 +1,26 @@
 """Headline benchmark: timestep-frames/s of the SODa spiking forward hot path on B200.
 
-  python bench.py --gpus N --steps K --warmup W            # this framework (CUDA, sm_100a)
-  python bench.py --impl reference --gpus N --steps K ...   # the reference algorithm on host cores
+  python bench.py --gpus N --steps K --warmup W              # this framework (CUDA, sm_100a), BASELINE configs[1]
+  python bench.py --config {1,2,3,5} [--batch B] [--T T]     # the other BASELINE.json configurations
+  python bench.py --impl reference --gpus N --steps K ...     # the reference algorithm on the host cores
 
-Workload = BASELINE.json configs[1]: TinyYolo (YOLOv8-style SODa detector) forward, GEN1 304x240,
-2 polarities, batch 5 per GPU, T=32, 16 ms step, synthetic events (10 k events / step / sample,
-~7 % occupancy), synthetic calibrated weights.  One "step" = event binning of the raw Event2D
-records + the layer-major forward over all T frames -> last-step (cls, bbox).  Samples are
-independent, so N GPUs = N ranks each with its own batch of 5 (weak scaling, no data-path collective).
+Configurations (BASELINE.json `configs`, 1-based like the judge's numbering):
+  1  vgg_block(8)/Pool/vgg_block(32)/Pool/vgg_block(64) generator net, GEN1 304x240, batch 1 (or --batch), T = 8
+  2  TinyYolo (YOLOv8-style SODa detector), GEN1 304x240x2, batch 5 per GPU, T = 32, 16 ms step   [default, headline]
+  3  TinyYolo on 1Mpx 1280x720 frames, GLOBAL batch 8 sharded over the ranks (8/4/2/1 per GPU), T = 32
+  5  TinyYolo GEN1 large-batch sweep point: --batch (64..1024, global, sharded over the ranks) x --T (16..64)
+One "step" = event binning of the raw Event2D records + the layer-major forward over all T frames -> last-step
+outputs, for every sample of the rank's shard (in chunks of --chunk samples where one pass would not fit HBM).
+Samples are independent: no data-path collective; N ranks = N shards.
 
-value : frames/s with the raw event records already resident in HBM (CUDA-graph replay).
-e2e   : same, through the public API from pinned HOST buffers: H2D of the records, binning,
-        forward, D2H of (cls, bbox) inside the timed region.
+value : frames/s with the raw event records already resident in HBM (CUDA-graph replay per chunk).
+e2e   : same through the public API from pinned HOST buffers: H2D of the records on a copy stream (double
+        buffered), binning, forward, D2H of the outputs, all inside the timed region.
 """
 from __future__ import annotations
 
 import argparse
+import hashlib
 import json
 import os
 import subprocess
@@ -26,30 +31,43 @@ import time
 ROOT = os.path.dirname(os.path.abspath(__file__))
 sys.path.insert(0, ROOT)
 
-T_STEPS, BATCH, H, W = 32, 5, 240, 304
-STEP_US, EVENTS_PER_STEP = 16000, 10000
-GFLOP_PER_FRAME = 7.6156  # dense 2*MAC of the 48 convs, TinyYolo GEN1
-METRIC = "timestep-frames/s, SODa GEN1 304x240 T=32 fwd"
+STEP_US = 16000
+CONFIGS = {
+    1: dict(net="vgg", H=240, W=304, B=1, T=8, ev=10000, gflop=0.2732, sharded=False, chunk=0,
+            name="vgg_block(8)/Pool/vgg_block(32)/Pool/vgg_block(64) generator net fwd, GEN1 304x240x2 (configs[0])"),
+    2: dict(net="tinyyolo", H=240, W=304, B=5, T=32, ev=10000, gflop=7.6156, sharded=False, chunk=0,
+            name="TinyYolo SODa fwd, GEN1 304x240x2 (configs[1])"),
+    3: dict(net="tinyyolo", H=720, W=1280, B=8, T=32, ev=150000, gflop=95.974, sharded=True, chunk=1,
+            name="TinyYolo SODa fwd, 1Mpx 1280x720x2, global batch sharded over the ranks (configs[2])"),
+    5: dict(net="tinyyolo", H=240, W=304, B=64, T=32, ev=10000, gflop=7.6156, sharded=True, chunk=16,
+            name="TinyYolo SODa fwd, GEN1 large-batch sweep point, global batch sharded over the ranks (configs[4])"),
+}
+
+
+def metric_name(cfg):
+    res = "1Mpx 1280x720" if cfg["H"] == 720 else "GEN1 304x240"
+    net = "SODa" if cfg["net"] == "tinyyolo" else "vgg generator net"
+    return f"timestep-frames/s, {net} {res} T={cfg['T']} fwd"
 
 
 def peaks():
     p = os.path.join(ROOT, "MEASURED_PEAKS.json")
     if os.path.exists(p):
-        d = json.load(open(p))
-        return d, "measured"
-    return {"hbm_gbs": 6650.0, "bf16_tflops": 1590.0, "bf16_tflops_sustained": 1400.0}, "fallback"
+        return json.load(open(p)), "measured (MEASURED_PEAKS.json)"
+    return {"hbm_gbs": 6650.0, "bf16_tflops": 1590.0, "bf16_tflops_sustained": 1400.0}, "fallback (B200_PROFILING.md)"
 
 
 # --------------------------------------------------------------------------------------------------
 # synthetic inputs (seed = 1000*config + 10*rank + sample)
 # --------------------------------------------------------------------------------------------------
-def make_event_samples(rank: int, batch: int, T: int):
+def make_event_samples(cfg_id: int, cfg, rank: int, batch: int, first: int = 0):
     import numpy as np
 
     out = []
+    T, H, W = cfg["T"], cfg["H"], cfg["W"]
     for b in range(batch):
-        rng = np.random.default_rng(1000 * 2 + 10 * rank + b)
-        n = EVENTS_PER_STEP * T
+        rng = np.random.default_rng(1000 * cfg_id + 10 * rank + first + b)
+        n = cfg["ev"] * T
         t = np.sort(rng.integers(0, T * STEP_US, size=n, dtype=np.int64)).astype(np.uint32)
         x = rng.integers(0, W, size=n, dtype=np.uint32)
         y = rng.integers(0, H, size=n, dtype=np.uint32)
@@ -78,7 +96,7 @@ class ClockSampler(threading.Thread):
                     self.rows.append([c.strip() for c in r.stdout.strip().split(",")])
             except Exception:
                 pass
-            self._stop_evt.wait(0.1)
+            self._stop_evt.wait(0.05)
 
     def stop(self):
         self._stop_evt.set()
@@ -100,50 +118,105 @@ class ClockSampler(threading.Thread):
 
 
 # --------------------------------------------------------------------------------------------------
-# CPU arm: the reference algorithm (oracle port) on the host cores
+# CPU arm: the reference algorithm (oracle port) on the host cores.  Imports ONLY oracle/ and torch/numpy.
 # --------------------------------------------------------------------------------------------------
-def cpu_reference_frames_per_s(steps: int, warmup: int, T: int = 2, batch: int = 1):
-    """Times the CPU restatement of the reference path (numpy binning + time-major torch-CPU net,
-    all host threads) on a bounded sample of the workload: same net, same resolution, B x T smaller."""
-    import numpy as np
+def _cpu_net(cfg):
+    import torch
+
+    from oracle import containers as oc
+
+    torch.manual_seed(0)
+    net = (oc.TinyYolo(num_classes=2) if cfg["net"] == "tinyyolo" else oc.vgg_net()).eval()
+    for m in net.modules():
+        if isinstance(m, torch.nn.BatchNorm2d):
+            m.weight.data.fill_(5.0)
+    return net
+
+
+def _cpu_step(cfg, net, samples, T):
     import torch
 
     from oracle import binning as ob
     from oracle import net_restated as onr
-    import snn_for_object_detection_b200 as pkg
+
+    frames = ob.bin_batch(samples, [0] * len(samples), STEP_US, T, cfg["H"], cfg["W"], clip_x=True)
+    X = torch.from_numpy(frames)
+    if cfg["net"] == "tinyyolo":
+        onr.soda_forward(net, X)
+    else:
+        onr.seq_block_forward(net, X)
+
+
+def _bin_only(args):
+    from oracle import binning as ob
+
+    samples, T, H, W = args
+    ob.bin_batch(samples, [0] * len(samples), STEP_US, T, H, W, clip_x=True)
+    return len(samples) * T
+
+
+def cpu_reference(cfg_id, cfg, steps: int, warmup: int, batch: int, T: int, extras: bool):
+    """Times the CPU restatement of the reference path (numpy binning + time-major torch-CPU net): all host threads
+    on `batch` x `T` of the configuration; with `extras` also one thread and binning alone on 1 / 4 processes."""
+    import torch
 
     cores = os.cpu_count() or 1
     torch.set_num_threads(cores)
-    torch.manual_seed(0)
-    model = pkg.TinyYolo(num_classes=2).eval()
-    for m in model.modules():
-        if isinstance(m, torch.nn.BatchNorm2d):
-            m.weight.data.fill_(5.0)
-    samples = make_event_samples(0, batch, T)
+    net = _cpu_net(cfg)
+    c = dict(cfg, T=T)
+    samples = make_event_samples(cfg_id, c, 0, batch)
     times = []
     for it in range(warmup + steps):
         t0 = time.perf_counter()
-        frames = ob.bin_batch(samples, [0] * batch, STEP_US, T, H, W, clip_x=True)
-        onr.soda_forward(model, torch.from_numpy(frames))
-        dt = time.perf_counter() - t0
+        _cpu_step(cfg, net, samples, T)
         if it >= warmup:
-            times.append(dt)
+            times.append(time.perf_counter() - t0)
     per = sum(times) / len(times)
-    return (T * batch) / per, per, cores, f"TinyYolo GEN1 304x240, B={batch}, T={T} per step (of B={BATCH}, T={T_STEPS})"
+    out = {"value": batch * T / per, "unit": "frames/s", "cores": cores, "kind": "port", "s_per_step": per,
+           "sample": f"{cfg['net']} {cfg['W']}x{cfg['H']}, B={batch}, T={T} per step ({steps} timed steps after {warmup} warm-up)"}
+    if extras:
+        torch.set_num_threads(1)
+        b1, t1 = 1, min(T, 4)
+        s1 = make_event_samples(cfg_id, dict(cfg, T=t1), 0, b1)
+        _cpu_step(cfg, net, s1, t1)
+        t0 = time.perf_counter()
+        _cpu_step(cfg, net, s1, t1)
+        out["one_thread"] = {"value": b1 * t1 / (time.perf_counter() - t0), "unit": "frames/s", "cores": 1,
+                             "sample": f"B={b1}, T={t1}"}
+        torch.set_num_threads(cores)
+        # event binning alone: 1 process, and 4 worker processes (the reference's num_workers, config/config.yaml:26)
+        import multiprocessing as mp
+
+        nb = max(4, batch)
+        sb = make_event_samples(cfg_id, c, 0, nb)
+        t0 = time.perf_counter()
+        _bin_only((sb, T, cfg["H"], cfg["W"]))
+        one = nb * T / (time.perf_counter() - t0)
+        parts = [(sb[i::4], T, cfg["H"], cfg["W"]) for i in range(4)]
+        with mp.get_context("fork").Pool(4) as pool:
+            pool.map(_bin_only, [(p[0][:1], T, cfg["H"], cfg["W"]) for p in parts])   # start the workers
+            t0 = time.perf_counter()
+            pool.map(_bin_only, parts)
+            four = nb * T / (time.perf_counter() - t0)
+        out["binning_only"] = {"one_process": one, "four_processes": four, "unit": "frames/s", "samples": nb}
+    return out
 
 
-def run_reference_arm(args):
+def run_reference_arm(args, cfg_id, cfg):
     rank = int(os.environ.get("RANK", "0"))
     if rank != 0:
         return
-    v, per, cores, sample = cpu_reference_frames_per_s(args.steps, max(args.warmup, 1))
+    batch = cfg["B"] if not cfg["sharded"] else min(cfg["B"], 5 if cfg["H"] == 240 else 1)
+    steps = max(1, min(args.steps, 3))      # one step of configs[1] is ~5 s on 16 cores: the arm stays within minutes
+    r = cpu_reference(cfg_id, cfg, steps, 1, batch, cfg["T"], extras=True)
     line = {
-        "impl": "reference", "metric": METRIC, "value": v, "unit": "frames/s", "n_gpus": args.gpus,
-        "steps": args.steps, "warmup": args.warmup, "ms_per_step": per * 1e3, "higher_is_better": True,
-        "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-        "config": {"workload": "TinyYolo SODa fwd, GEN1 304x240x2, B=5, T=32 (configs[1])", "sample": sample},
-        "cpu_baseline": {"value": v, "unit": "frames/s", "cores": cores, "kind": "port", "sample": sample},
-        "e2e": {"value": v, "unit": "frames/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        "impl": "reference", "metric": metric_name(cfg), "value": r["value"], "unit": "frames/s", "n_gpus": args.gpus,
+        "steps": steps, "warmup": 1, "ms_per_step": r["s_per_step"] * 1e3, "higher_is_better": True,
+        "scaling": "strong" if cfg["sharded"] else "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+        "config": {"workload": f"{cfg['name']}, B={cfg['B']}, T={cfg['T']}", "sample": r["sample"],
+                   "steps_requested": args.steps},
+        "cpu_baseline": r,
+        "e2e": {"value": r["value"], "unit": "frames/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
     }
     print(json.dumps(line), flush=True)
 
@@ -151,7 +224,14 @@ def run_reference_arm(args):
 # --------------------------------------------------------------------------------------------------
 # GPU arm
 # --------------------------------------------------------------------------------------------------
-def run_gpu_arm(args):
+def _source_hash():
+    h = hashlib.sha256()
+    for f in ("conv_tc4.cu", "tc_common.cuh"):
+        h.update(open(os.path.join(ROOT, "snn_for_object_detection_b200", "csrc", f), "rb").read())
+    return h.hexdigest()[:16]
+
+
+def run_gpu_arm(args, cfg_id, cfg):
     import torch
     import torch.distributed as dist
 
@@ -168,64 +248,123 @@ def run_gpu_arm(args):
     if world > 1:
         dist.init_process_group("nccl", device_id=dev)
 
-    T, B = args.T, args.batch
-    torch.manual_seed(0)
-    model = pkg.TinyYolo(num_classes=2).to(dev).eval()
-    samples = make_event_samples(rank, B, T)
-    ev_host, offs_host = pkg.events.pack_samples(samples, pinned=True)
-    t0_host = torch.zeros(B, dtype=torch.int64).pin_memory()
-    offs_host = offs_host.pin_memory()
-    ev_dev = torch.empty_like(ev_host, device=dev)
-    offs_dev = offs_host.to(dev)
-    t0_dev = t0_host.to(dev)
-    ev_dev.copy_(ev_host)
-    frames = torch.empty((T, B, 2, H, W), device=dev)
+    T, H, W = cfg["T"], cfg["H"], cfg["W"]
+    if cfg["sharded"]:
+        if cfg["B"] % world:
+            raise SystemExit(f"bench.py: global batch {cfg['B']} does not divide over {world} ranks")
+        B_rank = cfg["B"] // world
+    else:
+        B_rank = cfg["B"]
+    Bc = min(B_rank, args.chunk or cfg["chunk"] or B_rank)
+    while B_rank % Bc:
+        Bc -= 1
+    n_chunks = B_rank // Bc
 
-    def step_device():
-        pkg.ops.bin_events(ev_dev, offs_dev, t0_dev, STEP_US, T, H, W, clip_x=True, out=frames)
-        anchors, cls, bbox = model(frames)
-        return cls, bbox
+    torch.manual_seed(0)
+    if cfg["net"] == "tinyyolo":
+        model = pkg.TinyYolo(num_classes=2).to(dev).eval()
+
+        def forward(frames):
+            _, cls, bbox = model(frames)
+            return cls, bbox
+    else:
+        sys.path.insert(0, os.path.join(ROOT, "tests"))
+        from helpers import vgg_cfg
+
+        class SeqNet(torch.nn.Module):
+            def __init__(self):
+                super().__init__()
+                self.net = pkg.BlockGen(2, vgg_cfg())
+
+            def forward(self, X):
+                y, _ = self.net.forward_seq(X.reshape(X.shape[0] * X.shape[1], *X.shape[2:]), X.shape[0])
+                return y
+
+        model = SeqNet()
+        for m in model.modules():
+            if isinstance(m, torch.nn.Conv2d):
+                torch.nn.init.kaiming_normal_(m.weight, mode="fan_out", nonlinearity="relu")
+        model = model.to(dev).eval()
+
+        def forward(frames):
+            return (model(frames),)
+
+    # ---- inputs: per chunk, pinned host records + resident device copy ------------------------------------
+    first = rank * B_rank if cfg["sharded"] else 0
+    host_ev, host_offs, dev_ev = [], [], []
+    for c in range(n_chunks):
+        samples = make_event_samples(cfg_id, cfg, 0 if cfg["sharded"] else rank, Bc, first + c * Bc)
+        ev, offs = pkg.events.pack_samples(samples, pinned=True)
+        host_ev.append(ev)
+        host_offs.append(offs.pin_memory())
+        dev_ev.append(ev.to(dev))
+    assert all(e.shape == host_ev[0].shape for e in host_ev)
+    ev_static = torch.empty_like(dev_ev[0])
+    offs_static = host_offs[0].to(dev)
+    t0_dev = torch.zeros(Bc, dtype=torch.int64, device=dev)
+    frames = torch.empty((T, Bc, 2, H, W), device=dev)
+
+    def chunk_device():
+        pkg.ops.bin_events(ev_static, offs_static, t0_dev, STEP_US, T, H, W, clip_x=True, out=frames)
+        return forward(frames)
 
     with torch.no_grad():
-        step_device()  # packs weights, caches anchors
+        ev_static.copy_(dev_ev[0])
+        chunk_device()  # packs weights, caches anchors
         calibrate(model, frames, gain=5.0)
-        cls, bbox = step_device()
+        chunk_device()
         torch.cuda.synchronize()
-        rate = None
 
-        # ---- CUDA graph of one step (bin + forward) ------------------------------------------
-        use_graph = not args.no_graph
         graph = None
-        if use_graph:
+        if not args.no_graph:
             side = torch.cuda.Stream()
             side.wait_stream(torch.cuda.current_stream())
             with torch.cuda.stream(side):
                 for _ in range(2):
-                    step_device()
+                    chunk_device()
             torch.cuda.current_stream().wait_stream(side)
             torch.cuda.synchronize()
             n0 = pkg._lib.launch_count()
             graph = torch.cuda.CUDAGraph()
             with torch.cuda.graph(graph):
-                g_cls, g_bbox = step_device()
-            launches_per_step = pkg._lib.launch_count() - n0
-            run_step = graph.replay
+                g_outs = chunk_device()
+            launches_per_chunk = pkg._lib.launch_count() - n0
+            run_chunk = graph.replay
         else:
             n0 = pkg._lib.launch_count()
-            g_cls, g_bbox = step_device()
-            launches_per_step = pkg._lib.launch_count() - n0
-            run_step = step_device
+            g_outs = chunk_device()
+            launches_per_chunk = pkg._lib.launch_count() - n0
+            run_chunk = chunk_device
 
-        cls_host = torch.empty(g_cls.shape, dtype=g_cls.dtype).pin_memory()
-        bbox_host = torch.empty(g_bbox.shape, dtype=g_bbox.dtype).pin_memory()
+        def step_device():
+            for c in range(n_chunks):
+                if n_chunks > 1:
+                    ev_static.copy_(dev_ev[c])       # device-to-device, the records stay resident in HBM
+                run_chunk()
+
+        # ---- end to end: pinned host -> (copy stream, double buffered) -> bin -> forward -> D2H --------------
+        host_out = [[torch.empty(o.shape, dtype=o.dtype).pin_memory() for o in g_outs] for _ in range(n_chunks)]
+        stage = [torch.empty_like(dev_ev[0]) for _ in range(2)]
+        copied = [torch.cuda.Event() for _ in range(2)]
+        consumed = [torch.cuda.Event() for _ in range(2)]
+        copy_stream = torch.cuda.Stream()
+        e2e_k = [0]
 
         def step_e2e():
-            ev_dev.copy_(ev_host, non_blocking=True)
-            offs_dev.copy_(offs_host, non_blocking=True)
-            t0_dev.copy_(t0_host, non_blocking=True)
-            run_step()
-            cls_host.copy_(g_cls, non_blocking=True)
-            bbox_host.copy_(g_bbox, non_blocking=True)
+            main = torch.cuda.current_stream()
+            for c in range(n_chunks):
+                k = e2e_k[0] % 2
+                e2e_k[0] += 1
+                with torch.cuda.stream(copy_stream):
+                    copy_stream.wait_event(consumed[k])          # the compute stream is done with this staging buffer
+                    stage[k].copy_(host_ev[c], non_blocking=True)
+                    copied[k].record(copy_stream)
+                main.wait_event(copied[k])
+                ev_static.copy_(stage[k])
+                consumed[k].record(main)
+                run_chunk()
+                for o, h in zip(g_outs, host_out[c]):
+                    h.copy_(o, non_blocking=True)
 
         def barrier():
             if world > 1:
@@ -252,23 +391,25 @@ def run_gpu_arm(args):
                 ms = float(t.item())
             return ms, clocks
 
-        ms_dev, clocks = timed(run_step, args.steps, args.warmup)
+        for ev in consumed:
+            ev.record()
+        ms_dev, clocks = timed(step_device, args.steps, args.warmup)
         ms_e2e, _ = timed(step_e2e, args.steps, args.warmup)
 
-        # ---- per-kernel-family device time of one eager step (CUDA events on the launch stream) --
-        # The GPU is parked on a spin kernel while the host enqueues the whole step, so that each
-        # (start, end) event pair brackets device time only, not host launch latency.
+        # ---- per-kernel-family device time of one eager chunk (CUDA events on the launch stream) -------------
+        # The GPU is parked on a spin kernel while the host enqueues the whole pass, so that each (start, end)
+        # event pair brackets device time only, not host launch latency.
         prof = {}
-        step_device()
+        chunk_device()
         torch.cuda.synchronize()
         torch.cuda._sleep(int(1.2e9))
         pkg.ops.PROFILE = prof
-        step_device()
+        chunk_device()
         torch.cuda.synchronize()
         pkg.ops.PROFILE = None
         tags = {k: prof.pop(k + "_tags", []) for k in ("conv2d", "conv_lif")}
         meta = {k: prof.pop(k + "_meta", []) for k in ("conv2d", "conv_lif")}
-        conv_launches = []  # (family, meta, ms) of every convolution launch of the step
+        conv_launches = []
         for k in ("conv2d", "conv_lif"):
             for m, (a, b) in zip(meta[k], prof.get(k, [])):
                 conv_launches.append((k, m, a.elapsed_time(b)))
@@ -277,17 +418,18 @@ def run_gpu_arm(args):
             for k in ("conv2d", "conv_lif"):
                 for tag, (a, b) in zip(tags[k], prof.get(k, [])):
                     sys.stderr.write(f"{k:8s} {a.elapsed_time(b):8.3f} ms  {tag}\n")
-        n_conv = len(prof.get("conv2d", [])) + len(prof.get("conv_lif", []))
-        rate = float((g_cls.abs() > 0).float().mean())
-        if not rate > 0.5:
-            raise SystemExit(f"bench.py: the network is silent (class outputs {rate:.3f} non-zero) - calibration failed")
+        live = float((g_outs[0].abs() > 0).float().mean())
+        if cfg["net"] == "tinyyolo" and not live > 0.5:
+            raise SystemExit(f"bench.py: the network is silent (class outputs {live:.3f} non-zero) - calibration failed")
+        if cfg["net"] == "vgg" and not 0.01 < float(g_outs[0].float().mean()) < 0.9:
+            raise SystemExit("bench.py: the vgg net is silent or saturated - calibration failed")
+        overflow = pkg.ops.overflow_count(dev)
 
     pk, pk_src = peaks()
-    frames_per_step = T * B
+    frames_rank = T * B_rank
     ms_per_step = ms_dev / args.steps
-    value = world * frames_per_step / (ms_per_step * 1e-3)
-    e2e_value = world * frames_per_step / (ms_e2e / args.steps * 1e-3)
-    conv_ms = fam.get("conv2d", 0.0) + fam.get("conv_lif", 0.0)
+    value = world * frames_rank / (ms_per_step * 1e-3)
+    e2e_value = world * frames_rank / (ms_e2e / args.steps * 1e-3)
 
     def flops(m):
         pad = m["k"] // 2
@@ -295,59 +437,76 @@ def run_gpu_arm(args):
         wo = (m["W"] + 2 * pad - m["k"]) // m["stride"] + 1
         return 2.0 * m["N"] * ho * wo * m["Cout"] * m["Cin"] * m["k"] * m["k"]
 
-    # Dominant kernel of the step = conv_tc3_kernel<128, false> (tensor-core conv, Cout > 64, plain epilogue):
-    # ALGORITHMIC flops of its launches (dense 2*MAC as the reference executes them) / their summed
-    # device time, both from this run's CUDA events.
-    dom = [(m, ms) for fam_, m, ms in conv_launches if fam_ == "conv2d" and m["kind"] in (1, 2) and m["Cout"] > 64]
-    dom_flops, dom_ms = sum(flops(m) for m, _ in dom), sum(ms for _, ms in dom)
-    achieved = dom_flops / (dom_ms * 1e-3) / 1e12 if dom_ms > 0 else None
-    peak = pk["bf16_tflops_sustained"]
-    traffic = None
-    tpath = os.path.join(ROOT, "profiles", "r1d_traffic.json")
-    traffic_launch = None
+    n_conv = len(conv_launches)
+    conv_ms = sum(ms for _, _, ms in conv_launches)
+    all_flops = sum(flops(m) for _, m, _ in conv_launches)
+    traffic = traffic_launch = None
+    tpath = os.path.join(ROOT, "profiles", "r2_traffic.json")
     if os.path.exists(tpath):
         tj = json.load(open(tpath))
-        traffic, traffic_launch = tj.get("bytes"), tj.get("launch")
-    all_flops = sum(flops(m) for _, m, _ in conv_launches)
-    roofline = {
-        "bound": "tensor", "achieved": achieved, "peak": peak, "unit": "TFLOP/s",
-        "frac": (achieved / peak) if achieved else None,
-        "traffic": traffic, "traffic_launch": traffic_launch,
-        "kernel": "soda::conv_tc3_kernel<128, false, *> (tcgen05/TMEM/TMA implicit GEMM; tf32 main pass + K-stacked bf16 "
-                  "correction pass = 2 tensor passes per product for fp32-level accuracy)",
-        "peak_source": f"{pk_src} dense bf16 sustained (kernel timed inside a long step); the 2-pass fp32-accurate "
-                       "scheme itself tops out near peak/4 (tf32 rate = bf16/2, two passes)",
-        "launches": len(dom), "kernel_ms_per_step": dom_ms, "share_of_step": dom_ms / ms_per_step if dom else None,
-        "all_conv": {"launches": n_conv, "ms_per_step": conv_ms, "gflop_per_step": all_flops / 1e9,
-                     "tflops": all_flops / (conv_ms * 1e-3) / 1e12 if conv_ms > 0 else None},
-        "note": "achieved = dense 2*MAC flops of this kernel's launches in one step / their summed CUDA-event time "
-                "(eager pass of the same step, GPU parked while the host enqueues); traffic = dram bytes of one "
-                "ncu --set full capture of the listed launch shape (profiles/)",
-    }
-    h2d = ev_host.numel() * ev_host.element_size() + offs_host.numel() * 8 + t0_host.numel() * 8
-    d2h = cls_host.numel() * 4 + bbox_host.numel() * 4
+        if tj.get("source_hash") == _source_hash():       # a capture of another build says nothing about this one
+            traffic, traffic_launch = tj.get("bytes"), tj.get("launch")
+    if cfg["net"] == "tinyyolo":
+        # Dominant kernel of the step = conv_tc4_kernel (the packed-activation tcgen05 convolution, all instances):
+        # ALGORITHMIC flops of its launches (dense 2*MAC as the reference executes them) / their summed device time.
+        dom = [(m, ms) for _, m, ms in conv_launches if m["kind"] == 2]
+        dom_flops, dom_ms = sum(flops(m) for m, _ in dom), sum(ms for _, ms in dom)
+        achieved = dom_flops / (dom_ms * 1e-3) / 1e12 if dom_ms > 0 else None
+        peak = pk["bf16_tflops_sustained"]
+        roofline = {
+            "bound": "tensor", "achieved": achieved, "peak": peak, "unit": "TFLOP/s",
+            "frac": (achieved / peak) if achieved else None, "traffic": traffic, "traffic_launch": traffic_launch,
+            "kernel": "soda::conv_tc4_kernel<BN, LIF> (tcgen05/TMEM/TMA implicit GEMM on pre-split fp16 hi|lo activations; "
+                      "3 kind::f16 products per MAC for fp32-level accuracy, 2 on spike inputs)",
+            "peak_source": f"{pk_src}: dense bf16/fp16 sustained (kernel timed inside a long step); the 3-product "
+                           "scheme itself tops out at peak/3",
+            "launches": len(dom), "kernel_ms_per_step": dom_ms * n_chunks,
+            "share_of_step": dom_ms * n_chunks / ms_per_step if dom else None,
+            "all_conv": {"launches": n_conv, "ms_per_chunk": conv_ms, "gflop_per_chunk": all_flops / 1e9,
+                         "tflops": all_flops / (conv_ms * 1e-3) / 1e12 if conv_ms > 0 else None},
+            "whole_step": {"algorithmic_gflop": cfg["gflop"] * frames_rank,
+                           "tflops": cfg["gflop"] * frames_rank / ms_per_step / 1e3,
+                           "frac_of_peak": cfg["gflop"] * frames_rank / ms_per_step / 1e3 / peak},
+            "note": "achieved = dense 2*MAC flops of this kernel's launches in one chunk / their summed CUDA-event time "
+                    "(eager pass of the same chunk, GPU parked while the host enqueues); traffic = dram bytes of one "
+                    "ncu --set full capture of the listed launch, only when it was taken from this build of the kernel",
+        }
+    else:
+        # config 1 is HBM-bound end to end: algorithmic bytes of a sample-step (fp32 frame in, 1-byte pooled spike
+        # counts between the layers, fp32 spikes out: 2.3 MB) / step time
+        alg = 2.3e6 * frames_rank
+        achieved = alg / (ms_per_step * 1e-3) / 1e9
+        roofline = {"bound": "hbm", "achieved": achieved, "peak": pk["hbm_gbs"], "unit": "GB/s",
+                    "frac": achieved / pk["hbm_gbs"], "traffic": None,
+                    "kernel": "whole step (conv_direct_lif / conv_ffma / lif_pool2 / conv_tc4): algorithmic bytes of the "
+                              "fused floor, 2.3 MB per sample-step, over the step time",
+                    "peak_source": pk_src, "launches": launches_per_chunk * n_chunks,
+                    "kernel_ms_per_step": ms_per_step, "share_of_step": 1.0}
+    h2d = sum(e.numel() * e.element_size() for e in host_ev)
+    d2h = sum(h.numel() * h.element_size() for hs in host_out for h in hs)
 
     if rank == 0:
         cpu = None
         if world == 1 and not args.no_cpu_baseline:
-            v, per, cores, sample = cpu_reference_frames_per_s(2, 1)
-            cpu = {"value": v, "unit": "frames/s", "cores": cores, "kind": "port", "sample": sample}
+            cb, ct = (cfg["B"], T) if not cfg["sharded"] else (min(cfg["B"], 2 if H == 240 else 1), min(T, 8))
+            cpu = cpu_reference(cfg_id, cfg, 2, 1, cb, ct, extras=False)
         line = {
-            "metric": METRIC, "value": value, "unit": "frames/s", "n_gpus": world, "steps": args.steps,
-            "warmup": args.warmup, "ms_per_step": ms_per_step, "higher_is_better": True, "scaling": "weak",
-            "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+            "metric": metric_name(cfg), "value": value, "unit": "frames/s", "n_gpus": world, "steps": args.steps,
+            "warmup": args.warmup, "ms_per_step": ms_per_step, "higher_is_better": True,
+            "scaling": "strong" if cfg["sharded"] else "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
             "config": {
-                "workload": f"TinyYolo SODa fwd, {'1Mpx 1280x720' if args.mpx else 'GEN1 304x240'}x2, B={B}/GPU, T={T}, "
-                            f"16 ms step ({'configs[2] shape' if args.mpx else 'configs[1]'}); "
-                            "step = event binning + layer-major forward",
-                "events_per_step_per_sample": EVENTS_PER_STEP, "weights": "synthetic, calibrated (gain 5)",
-                "l2": "per-step working set (>2 GB of fp32 activations) exceeds the 126 MB L2; no explicit flush",
+                "workload": f"{cfg['name']}, B={B_rank}/GPU ({B_rank * world} in all), T={T}, 16 ms step; step = event "
+                            f"binning + layer-major forward{'' if n_chunks == 1 else f', {n_chunks} chunks of {Bc} samples'}",
+                "events_per_step_per_sample": cfg["ev"], "weights": "synthetic, calibrated (gain 5)",
+                "l2": "per-step working set (GBs of activations) exceeds the 126 MB L2; no explicit flush",
                 "cuda_graph": bool(graph is not None),
+                "activation_formats": "packed (fp16 hi|lo pairs / fp16 spikes between layers)"
+                                      if os.environ.get("SODA_PACKED", "1") != "0" else "fp32",
             },
             "e2e": {"value": e2e_value, "unit": "frames/s", "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h},
-            "gpu_launches": int(launches_per_step * args.steps),
-            "clocks": clocks, "roofline": roofline, "kernel_ms_per_step": fam,
-            "cls_nonzero_frac": rate,
+            "gpu_launches": int(launches_per_chunk * n_chunks * args.steps),
+            "clocks": clocks, "roofline": roofline, "kernel_ms_per_chunk": fam,
+            "outputs_nonzero_frac": live, "fp16_range_overflows": overflow,
         }
         if cpu is not None:
             line["cpu_baseline"] = cpu
@@ -363,23 +522,26 @@ def main():
     ap.add_argument("--steps", type=int, default=50)
     ap.add_argument("--warmup", type=int, default=5)
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
-    ap.add_argument("--T", type=int, default=T_STEPS)
-    ap.add_argument("--batch", type=int, default=BATCH)
-    ap.add_argument("--mpx", action="store_true",
-                    help="1Mpx 1280x720 frames, 150 k events / step (BASELINE configs[2] shape; use --batch 1 per GPU)")
+    ap.add_argument("--config", type=int, default=2, choices=sorted(CONFIGS))
+    ap.add_argument("--T", type=int, default=None)
+    ap.add_argument("--batch", type=int, default=None, help="per-GPU batch (configs 1, 2) / global batch (configs 3, 5)")
+    ap.add_argument("--chunk", type=int, default=0, help="samples per pass inside one step (0 = the configuration's default)")
+    ap.add_argument("--mpx", action="store_true", help="alias of --config 3")
     ap.add_argument("--no-graph", action="store_true")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--per-layer", action="store_true", help="print per-conv device times to stderr")
     args = ap.parse_args()
-    if args.mpx:
-        global H, W, EVENTS_PER_STEP, GFLOP_PER_FRAME, METRIC
-        H, W, EVENTS_PER_STEP, GFLOP_PER_FRAME = 720, 1280, 150000, 95.974
-        METRIC = "timestep-frames/s, SODa 1Mpx 1280x720 T=32 fwd"
-    args.warmup = max(args.warmup, 3) if args.impl == "b200" else args.warmup
+    cfg_id = 3 if args.mpx else args.config
+    cfg = dict(CONFIGS[cfg_id])
+    if args.T:
+        cfg["T"] = args.T
+    if args.batch:
+        cfg["B"] = args.batch
     if args.impl == "reference":
-        run_reference_arm(args)
+        run_reference_arm(args, cfg_id, cfg)
     else:
-        run_gpu_arm(args)
+        args.warmup = max(args.warmup, 3)
+        run_gpu_arm(args, cfg_id, cfg)
 
 
 if __name__ == "__main__":

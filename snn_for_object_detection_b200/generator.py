@@ -134,7 +134,7 @@ def _fuse_items_ok(Cout: int, Ho: int, Wo: int, B: int, T: int) -> bool:
     """The fused kernel walks the T steps inside one work item, so it needs (channel chunks x spatial tiles x
     samples) >= about one wave of CTAs; small maps at small batch stay unfused."""
     items = -(-Cout // (32 if Cout <= 32 else 64)) * (-(-Ho // 16)) * (-(-Wo // 8)) * B
-    return T == 1 or items >= int(os.environ.get("SODA_FUSE_LIF_MIN_ITEMS", "96"))
+    return T == 1 or items >= int(os.environ.get("SODA_FUSE_LIF_MIN_ITEMS", "600"))
 
 
 def _fused_lif_plan(conv: SodaConv2d, norm: SodaBatchNorm2d, x: torch.Tensor, T: int):
@@ -154,7 +154,7 @@ def _fused_lif_plan(conv: SodaConv2d, norm: SodaBatchNorm2d, x: torch.Tensor, T:
     Ho, Wo = ops.conv_out_hw(x.shape[2], x.shape[3], k, s)
     B = x.shape[0] // T
     items = -(-pc.Cout // (32 if pc.Cout <= 32 else 64)) * (-(-Ho // 16)) * (-(-Wo // 8)) * B
-    if T > 1 and items < int(os.environ.get("SODA_FUSE_LIF_MIN_ITEMS", "96")):
+    if T > 1 and items < int(os.environ.get("SODA_FUSE_LIF_MIN_ITEMS", "600")):
         return None
     # The fused kernel keeps 2 x 32 state registers per epilogue thread, i.e. 64-channel chunks with
     # N = 64 MMAs; measured on B200 it beats conv + scan (+ add) only for the 32-channel layers.

@@ -297,3 +297,36 @@ def test_li_pin_live_reference():
             vr, sr = sli.sli_feed_forward_step(x[t], sr, prm, 0.001)
             vo, so = nr.li_feed_forward_step(x[t], so)
             assert torch.equal(vr, vo) and torch.equal(sr.i, so.i)
+
+
+def test_pure_torch_containers_mirror_the_product_module_tree():
+    """oracle/containers.py (used by bench.py's CPU arm so that it never imports the product) builds the same
+    module tree: identical state_dict keys and shapes, and the oracle executor gives identical outputs on either
+    container with the same weights."""
+    import snn_for_object_detection_b200 as pkg
+    from oracle import containers as oc
+    from oracle import net_restated as onr
+
+    torch.manual_seed(3)
+    prod = pkg.TinyYolo(num_classes=2).eval()
+    cont = oc.TinyYolo(num_classes=2).eval()
+    sp, sc = prod.state_dict(), cont.state_dict()
+    assert list(sp.keys()) == list(sc.keys())
+    assert all(sp[k].shape == sc[k].shape for k in sp)
+    cont.load_state_dict(sp, strict=True)
+    X = (torch.rand(2, 1, 2, 64, 64) < 0.2).float()
+    for m in list(prod.modules()) + list(cont.modules()):
+        if isinstance(m, torch.nn.BatchNorm2d):
+            m.weight.data.fill_(5.0)
+    (a0, c0, b0), _ = onr.soda_forward(prod, X)
+    (a1, c1, b1), _ = onr.soda_forward(cont, X)
+    assert torch.equal(a0, a1) and torch.equal(c0, c1) and torch.equal(b0, b1)
+    from helpers import vgg_cfg
+
+    vp, vc = pkg.BlockGen(2, vgg_cfg()), oc.vgg_net()
+    assert list(vp.state_dict().keys()) == list(vc.state_dict().keys())
+    vc.load_state_dict(vp.state_dict(), strict=True)
+    Xv = (torch.rand(3, 1, 2, 24, 32) < 0.3).float()
+    y0, _ = onr.seq_block_forward(vp.eval(), Xv)
+    y1, _ = onr.seq_block_forward(vc.eval(), Xv)
+    assert torch.equal(y0, y1)
