@@ -89,11 +89,20 @@ def _conv_eligible(conv: SodaConv2d) -> bool:
     return conv.bias is None and conv.groups == 1 and conv.dilation == (1, 1)
 
 
-def _packed_input(Y: torch.Tensor, conv: SodaConv2d) -> Optional[torch.Tensor]:
+def _conv_shape(conv: SodaConv2d):
+    return conv.in_channels, conv.out_channels, conv.kernel_size[0], conv.stride[0]
+
+
+def _packed_input(Y: torch.Tensor, conv) -> Optional[torch.Tensor]:
     """``Y`` in the format the packed-activation convolution reads (converted if it arrives as fp32), or None
-    when this convolution cannot take that route."""
-    Cin, Cout, k, s = conv.in_channels, conv.out_channels, conv.kernel_size[0], conv.stride[0]
-    if not _packed() or not _conv_eligible(conv) or Y.dim() != 4:
+    when this convolution (a module, or a ``(Cin, Cout, k, stride)`` tuple) cannot take that route."""
+    if isinstance(conv, tuple):
+        Cin, Cout, k, s = conv
+    else:
+        Cin, Cout, k, s = _conv_shape(conv)
+        if not _conv_eligible(conv):
+            return None
+    if not _packed() or Y.dim() != 4:
         return None
     if Y.dtype == torch.int32:
         return Y if ops.pconv_shape_ok(Cin, Cout, k, s, ops.FMT_PAIR) else None
@@ -223,13 +232,13 @@ class BlockGen(nn.Module):
 
     def forward_seq(
         self, X: torch.Tensor, T: int, state: Optional[ListState] = None, out: Optional[torch.Tensor] = None,
-        packed_out: bool = False,
+        packed_out: bool = False, fold: Optional[SodaConv2d] = None,
     ) -> Tuple[torch.Tensor, ListState]:
         """All T steps of the block; ``X`` is ``[T*B, C, H, W]`` time-major.  ``out``: optional
         pre-allocated (possibly channel-sliced) destination for the block's result.  ``packed_out``: the caller
         is another planner and takes the result in whatever activation format it was produced in; otherwise
         (the public call) the result is fp32."""
-        Y, out_state = self._forward_seq(X, T, state, out, f32_out=not packed_out and out is None)
+        Y, out_state = self._forward_seq(X, T, state, out, f32_out=not packed_out and out is None, fold=fold)
         if not packed_out and Y.dtype != torch.float32:
             Y = ops.to_f32(Y)
         return Y, out_state
@@ -243,8 +252,83 @@ class BlockGen(nn.Module):
             self._ch32_cache = hit
         return hit
 
-    def _forward_seq(self, X, T, state, out, f32_out=False):
-        """``f32_out``: the result leaves the planner (public call): whatever produces it writes fp32 directly."""
+    # ---- C2f stems: 1x1 convolutions that open the branches of a Dense block --------------------------------
+    def _stem_plan(self):
+        """A Dense block whose branches all START with a plain 1x1 / stride-1 convolution on the block's input (no
+        BatchNorm or neuron directly behind it) - the two ``Conv(half, 1)`` of a C2f block, models/tiny_yolo.py:77-89.
+        Returns ``[(branch index, conv, lo, hi)]``, ``[lo, hi)`` = where that convolution's output lives in the
+        block's concat buffer, when those ranges are adjacent: ONE convolution with the stacked filters then writes
+        all of them and reads the input once (a 1x1 convolution is a matrix product per pixel; stacking output
+        channels changes no arithmetic)."""
+        hit = getattr(self, "_stem_cache", False)
+        if hit is not False:
+            return hit
+        plan = None
+        if self.merge == "dense" and len(self.net) >= 2:
+            plan, c0 = [], 0
+            for bi, branch in enumerate(self.net):
+                s0, s1 = c0, c0 + self.branch_channels[bi]
+                c0 = s1
+                conv = branch[0] if len(branch) else None
+                ok = (isinstance(conv, SodaConv2d) and _conv_eligible(conv) and conv.kernel_size == (1, 1)
+                      and conv.stride == (1, 1))
+                if ok and len(branch) == 1:
+                    lo, hi = s0, s1
+                elif ok and len(branch) == 2 and isinstance(branch[1], BlockGen) and branch[1]._identity_slice():
+                    a, b = branch[1]._identity_slice()
+                    lo, hi = s0 + a, s0 + b
+                    ok = branch[1].out_channels == s1 - s0 and branch[1].out_hw(64, 64) == (64, 64)
+                else:
+                    ok = False
+                if not ok or hi - lo != conv.out_channels or conv.in_channels != self.net[0][0].in_channels:
+                    plan = None
+                    break
+                plan.append((bi, conv, lo, hi))
+            if plan is not None:
+                order = sorted(plan, key=lambda t: t[2])
+                if any(a[3] != b[2] for a, b in zip(order, order[1:])):
+                    plan = None
+                else:
+                    plan = order
+        self._stem_cache = plan
+        return plan
+
+    def _stem_weights(self, plan, fold: Optional[SodaConv2d], in_fmt: int):
+        """Stacked (and, with ``fold``, pre-multiplied) filters of the stem convolutions, packed for ops.pconv.
+        ``fold`` is the 1x1 convolution that feeds this block and nothing else (C2f's entry ``Conv(out, 1)``,
+        models/tiny_yolo.py:79): with no nonlinearity in between, stem(fold(x)) = (W_stem . W_fold) x; the product is
+        formed once in float64 and rounded to fp32, the intermediate tensor is never materialised."""
+        convs = [c for _, c, _, _ in plan] + ([fold] if fold is not None else [])
+        key = tuple((c.weight.data_ptr(), c.weight._version) for c in convs) + (in_fmt, convs[0].weight.device)
+        hit = getattr(self, "_stem_pack", None)
+        if hit is None or hit[0] != key:
+            w = torch.cat([c.weight.detach() for _, c, _, _ in plan], dim=0)
+            if fold is not None:
+                w = (w[:, :, 0, 0].double() @ fold.weight.detach()[:, :, 0, 0].double()).float()[:, :, None, None]
+            hit = (key, ops.pack_pconv(w.contiguous(), 1, None, None, in_fmt))
+            self._stem_pack = hit
+        return hit[1]
+
+    def _run_stem(self, X, dense_buf, fold: Optional[SodaConv2d]):
+        """Runs the fused stem convolution into its slice of ``dense_buf``; returns {branch index: its tensor} or
+        None when this block / input / buffer does not qualify."""
+        plan = self._stem_plan()
+        if plan is None or dense_buf.dtype != torch.int32 or os.environ.get("SODA_STEM_FUSION", "1") == "0":
+            return None
+        cin = fold.in_channels if fold is not None else plan[0][1].in_channels
+        ctot = plan[-1][3] - plan[0][2]
+        Xp = _packed_input(X, (cin, ctot, 1, 1))
+        if Xp is None:
+            return None
+        out = dense_buf[:, plan[0][2]:plan[-1][3]]
+        if not ops.pconv_ok(Xp, (cin, ctot, 1, 1), None, out):
+            return None
+        ops.pconv(Xp, self._stem_weights(plan, fold, ops.fmt_of(Xp)), out=out)
+        return {bi: dense_buf[:, lo:hi] for bi, _, lo, hi in plan}
+
+    def _forward_seq(self, X, T, state, out, f32_out=False, fold=None):
+        """``f32_out``: the result leaves the planner (public call): whatever produces it writes fp32 directly.
+        ``fold``: a 1x1 convolution the caller skipped because this block's stems absorb it (see _stem_weights)."""
         outs = []
         out_state = []
         state = [None] * len(self.net) if state is None else state
@@ -260,6 +344,11 @@ class BlockGen(nn.Module):
                 X.shape[0], self.out_channels, Ho, Wo, X.device,
                 ops.FMT_PAIR if (_packed() and self._ch32() and not f32_out) else ops.FMT_F32,
             )
+        stems = None
+        if dense_buf is not None and _packed():
+            stems = self._run_stem(X, dense_buf, fold)
+        if fold is not None and stems is None:
+            X = _run_conv(fold, None, X, None, _real_fmt(fold.out_channels))   # could not be absorbed: run it after all
         c0 = 0
         for bi, (branch, flags, branch_state) in enumerate(zip(self.net, self.branch_state, state)):
             branch_state = [None] * len(branch) if branch_state is None else list(branch_state)
@@ -274,8 +363,14 @@ class BlockGen(nn.Module):
             fuse_res = None
             if self.merge == "residual" and len(self.net) == 2 and self._is_identity(self.net[1 - bi]):
                 fuse_res = X
-            Y, consumed = self._run_branch(X, T, branch, flags, branch_state, dst, fuse_res, out,
-                                           f32_out=f32_out and self.merge != "dense")
+            if stems is not None:
+                # the branch's opening convolution has already been computed (into its place in the concat buffer)
+                rest_state = branch_state[1:]
+                Y, consumed = self._run_branch(stems[bi], T, branch[1:], flags[1:], rest_state, dst)
+                branch_state = [None] + rest_state
+            else:
+                Y, consumed = self._run_branch(X, T, branch, flags, branch_state, dst, fuse_res, out,
+                                               f32_out=f32_out and self.merge != "dense")
             out_state.append(branch_state)
             if consumed:
                 # the other branch is the identity: its state list is all None
@@ -431,6 +526,24 @@ class BlockGen(nn.Module):
                     idx = lif_idx
                     continue
                 is_last = last == n - 1
+                nxt = branch[last + 1] if not is_last else None
+                if (norm is None and nograd and _packed() and isinstance(nxt, BlockGen) and nxt._stem_plan() is not None
+                        and layer.kernel_size == (1, 1) and layer.stride == (1, 1) and _conv_eligible(layer)
+                        and nxt.net[0][0].in_channels == Cout and os.environ.get("SODA_FOLD_1X1", "1") != "0"):
+                    # C2f entry convolution: its only consumers are the 1x1 stems of the next block, which absorb it
+                    bidx = last + 1
+                    if bidx == n - 1:
+                        o = dst
+                    else:
+                        Hn, Wn = nxt.out_hw(Ho, Wo)
+                        o = self._lookahead_dst(branch, bidx, n, Y.shape[0], nxt.out_channels, Hn, Wn, dst, Y.device,
+                                                prealloc)
+                    Y, branch_state[bidx] = nxt.forward_seq(Y, T, branch_state[bidx], out=o, fold=layer,
+                                                            packed_out=not (f32_out and bidx == n - 1 and o is None))
+                    idx = bidx + 1
+                    if idx == n and o is not None:
+                        return Y, False
+                    continue
                 if is_last:
                     o = dst
                 else:
