@@ -309,6 +309,22 @@ SODA_API int soda_pconv_lif_fwd(const soda_pconv_desc_t* d, const void* x, const
                                 const float* v0, const float* i0, void* y, float* v_out, float* i_out,
                                 unsigned int* status, void* stream);
 
+/* Conv(3x3, stride 1) -> BatchNorm(eval) -> LIF over T steps -> 2x2 sum pooling of the spikes in ONE kernel, for the
+ * small-K blocks of generator nets (reference README.md:57-64: vgg_block(8) / Pool / vgg_block(32) / Pool; layers
+ * models/modules/layer_gen.py:129-136, :211-214, :233, models/modules/common.py:45-49; time loop models/generator.py:184-198).
+ *   x       : Cin = 2: plain NCHW fp32 frames [T*B, 2, H, W] (in_nchw = 1, the binned events);
+ *             Cin = 8: SODA_ACT_HALF pixel-major [T*B, H, W, 8] (in_nchw = 0; the pooled counts of the previous block)
+ *   packed  : soda_conv_pack_weights(kind = SODA_CONV_FP32) of the BatchNorm-folded filter;  shift: [Cout] or NULL
+ *   y       : pooled spike counts {0..4}, element (t, b, py, px, c), in out_fmt (2 bytes per count as SODA_ACT_HALF)
+ *   v0, i0, v_out, i_out : fp32 [B, H, W, Cout] membrane state at FULL resolution (NULL in = initial state)
+ *   H, W even; Cout % 8 == 0.  The full-resolution spike map is never written. */
+SODA_API int soda_conv_lif_pool_supported(int Cin, int Cout, int k, int stride, int H, int W, int in_nchw, int in_fmt);
+SODA_API int soda_conv_lif_pool_fwd(const void* x, int in_fmt, int in_nchw, int64_t in_batch_stride, int64_t in_pix_stride,
+                                    const float* packed, const float* shift, int T, int B, int H, int W, int Cin, int Cout,
+                                    const soda_neuron_params_t* np, const float* v0, const float* i0, void* y, int out_fmt,
+                                    int64_t out_batch_stride, int64_t out_pix_stride, float* v_out, float* i_out,
+                                    void* stream);
+
 /* Format conversion / strided copy of a pixel-major tensor [n_frames][pix_per_frame][C] between any two formats
  * (decode to fp32, re-encode): the boundary between the packed region of a net and fp32 callers, and the copy of a
  * tensor into a concat slice of another format (generator.py:158).  C % 32 == 0 when PAIR is involved, else C % 8. */

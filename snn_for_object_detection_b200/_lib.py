@@ -106,6 +106,9 @@ SIGNATURES = {
     "soda_pconv_fwd": (_i, [C.POINTER(PConvDesc), _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp]),
     "soda_pconv_lif_fwd": (_i, [C.POINTER(PConvDesc), _vp, _vp, _vp, _vp, _vp, _i, C.POINTER(NeuronParams), _vp, _vp,
                                  _vp, _vp, _vp, _vp, _vp]),
+    "soda_conv_lif_pool_supported": (_i, [_i, _i, _i, _i, _i, _i, _i, _i]),
+    "soda_conv_lif_pool_fwd": (_i, [_vp, _i, _i, _i64, _i64, _vp, _vp, _i, _i, _i, _i, _i, _i, C.POINTER(NeuronParams), _vp,
+                                    _vp, _vp, _i, _i64, _i64, _vp, _vp, _vp]),
     "soda_act_convert": (_i, [_vp, _i, _i64, _i64, _vp, _i, _i64, _i64, _i64, _i64, _i, _vp, _vp]),
     "soda_lif_fmt_fwd": (_i, [C.POINTER(NeuronParams), _vp, _vp, _vp, _i, _i64, _i, _vp, _i, _i64, _vp, _i, _i64,
                               _vp, _vp, _vp, _vp]),

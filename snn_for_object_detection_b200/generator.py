@@ -499,8 +499,33 @@ class BlockGen(nn.Module):
                     Y = Yp
                 Cout = layer.out_channels
                 Ho, Wo = ops.conv_out_hw(Y.shape[2], Y.shape[3], layer.kernel_size[0], layer.stride[0])
-                if (norm is not None and type(cell) is LIFCell and nograd and _conv_eligible(layer)
-                        and os.environ.get("SODA_FUSE_LIF", "1") != "0"):
+                fuse_on = os.environ.get("SODA_FUSE_LIF", "1") != "0"
+                if (norm is not None and type(cell) is LIFCell and nograd and _conv_eligible(layer) and fuse_on
+                        and last + 2 < n and isinstance(branch[last + 2], SumPool2d)
+                        and branch[last + 2].kernel_size == 2 and branch[last + 2].stride == 2
+                        and not (last + 2 == n - 1 and residual is not None)):
+                    # Conv, Norm, LIF, Pool("S") block with a small K (README.md:57-64): one kernel, pooled counts out
+                    pc = layer.packed(norm, _lib.SODA_CONV_FP32)
+                    if ops.conv_lif_pool_ok(Y, pc):
+                        lif_idx, pool_idx = last + 1, last + 2
+                        is_last = pool_idx == n - 1
+                        o = dst if is_last else None
+                        if o is not None:
+                            ofmt = ops.fmt_of(o)
+                        elif (not is_last and isinstance(branch[pool_idx + 1], SodaConv2d) and Cout == 8 and _packed()
+                              and branch[pool_idx + 1].kernel_size == (3, 3) and branch[pool_idx + 1].stride == (1, 1)):
+                            ofmt = ops.FMT_HALF      # the next block's fused kernel reads 8-channel fp16 counts
+                        else:
+                            ofmt = self._next_fmt(branch, pool_idx, n, Cout, True, f32_out)
+                        st = branch_state[lif_idx]
+                        v0, i0 = (None, None) if st is None else (st.v, st.i)
+                        Y, v, i = ops.conv_lif_pool(Y, pc, T, cell._const, v0, i0, out=o, out_fmt=ofmt)
+                        branch_state[lif_idx] = LIFFeedForwardState(v, i)
+                        idx = pool_idx + 1
+                        if is_last and o is not None:
+                            return Y, False
+                        continue
+                if (norm is not None and type(cell) is LIFCell and nograd and _conv_eligible(layer) and fuse_on):
                     lif_idx = last + 1
                     is_last = lif_idx == n - 1
                     res = residual if is_last else None

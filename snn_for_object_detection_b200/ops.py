@@ -616,6 +616,53 @@ def pconv_lif(x: torch.Tensor, pc: PackedPConv, T: int, p: "NeuronConst", v0: Op
     return out, v, i
 
 
+def conv_lif_pool_ok(x: torch.Tensor, pc: "PackedConv") -> bool:
+    """The fused Conv(3x3) -> BN -> LIF -> 2x2 sum pool kernel takes the NCHW fp32 event frames (Cin = 2) and fp16
+    pixel-major pooled counts (Cin = 8)."""
+    if pc.kind != _lib.SODA_CONV_FP32 or x.dim() != 4:
+        return False
+    nchw = x.dtype == torch.float32 and x.is_contiguous() and x.shape[1] > 1
+    if not nchw and (x.dtype != torch.float16 or _pm_strides(x) is None):
+        return False
+    return bool(lib.soda_conv_lif_pool_supported(pc.Cin, pc.Cout, pc.k, pc.stride, x.shape[2], x.shape[3], int(nchw),
+                                                 fmt_of(x)))
+
+
+@_prof("conv_lif")
+def conv_lif_pool(x: torch.Tensor, pc: "PackedConv", T: int, p: "NeuronConst", v0=None, i0=None,
+                  out: Optional[torch.Tensor] = None, out_fmt: Optional[int] = None):
+    """``SumPool2x2(LIF_T(conv3x3(x, W*scale) + shift))`` in one kernel; returns ``(pooled counts, v_T, i_T)`` with the
+    state at full resolution.  Reference: the Conv / Norm / LIF / Pool block of README.md:57-64."""
+    _need_cuda(x, v0, i0, out)
+    N, Cin, H, W = x.shape
+    if N % T:
+        raise ValueError("conv_lif_pool: leading dimension is not a multiple of T")
+    B = N // T
+    nchw = x.dtype == torch.float32
+    if out is None:
+        out = empty_act(N, pc.Cout, H // 2, W // 2, x.device, FMT_F32 if out_fmt is None else out_fmt)
+    elif out.shape != (N, pc.Cout, H // 2, W // 2):
+        raise ValueError("conv_lif_pool: out has the wrong shape")
+    so = _pm_strides(out)
+    if so is None:
+        raise ValueError("conv_lif_pool: out must be pixel-major")
+    si = (0, 0) if nchw else _pm_strides(x)
+    v = empty_pixel_major(B, pc.Cout, H, W, x.device)
+    i = torch.empty_like(v)
+    if v0 is not None:
+        v0 = _like_block(v0, v)
+        i0 = _like_block(i0, v)
+    npar = p.c()
+    check(
+        lib.soda_conv_lif_pool_fwd(x.data_ptr(), fmt_of(x), int(nchw), si[0], si[1], pc.packed.data_ptr(), _ptr(pc.shift),
+                                   T, B, H, W, Cin, pc.Cout, C.byref(npar), _ptr(v0), _ptr(i0), out.data_ptr(), fmt_of(out),
+                                   so[0], so[1], v.data_ptr(), i.data_ptr(), _stream()),
+        "soda_conv_lif_pool_fwd",
+    )
+    mark_exact(out, 4)
+    return out, v, i
+
+
 def lif_scan_fmt_ok(x: torch.Tensor, residual: Optional[torch.Tensor], out: Optional[torch.Tensor]) -> bool:
     if x.dim() != 4 or x.dtype != torch.float32 or x.shape[1] % 32 or not x.is_contiguous(memory_format=torch.channels_last):
         return False

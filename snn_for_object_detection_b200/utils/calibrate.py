@@ -41,15 +41,17 @@ def calibrate(model: torch.nn.Module, X: torch.Tensor, gain: float = 5.0) -> Non
     # ... and neither does the packed-activation route (ops.pconv): measure on the fp32 route
     import os
 
-    packed_env = os.environ.get("SODA_PACKED")
+    saved = {k: os.environ.get(k) for k in ("SODA_PACKED", "SODA_FUSE_LIF")}
     os.environ["SODA_PACKED"] = "0"
+    os.environ["SODA_FUSE_LIF"] = "0"
     try:
         model(X)
     finally:
         SodaConv2d.forward = orig
         generator._fused_lif_plan = fused_plan
-        if packed_env is None:
-            del os.environ["SODA_PACKED"]
-        else:
-            os.environ["SODA_PACKED"] = packed_env
+        for k, v in saved.items():
+            if v is None:
+                del os.environ[k]
+            else:
+                os.environ[k] = v
         model.train(was_training)

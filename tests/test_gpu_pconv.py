@@ -193,3 +193,41 @@ def test_lif_fmt_scan_equals_plain_scan(res_fmt, out_fmt):
     _, v1, i1 = ops.lif_scan_fmt(x[:h], 2, out_fmt=F_[out_fmt])
     _, v2, i2 = ops.lif_scan_fmt(x[h:], T - 2, v0=v1, i0=i1, out_fmt=F_[out_fmt])
     assert torch.equal(v2, v_ref) and torch.equal(i2, i_ref)
+
+
+@pytest.mark.parametrize("cin,cout,out_fmt", [(2, 8, "half"), (2, 8, "f32"), (8, 32, "pair"), (8, 32, "half"), (8, 16, "f32")])
+def test_conv_lif_pool_equals_conv_then_scan_then_pool(cin, cout, out_fmt):
+    """Conv(3x3) -> BN -> LIF -> 2x2 sum pool in one kernel (pooled counts in the consumer's format, full-resolution
+    spikes never written) == FP32-pipe convolution, bit-exact LIF scan and pooling kernel run one after the other:
+    pooled counts identical up to borderline spikes (different fp32 summation order; <= 1e-4 of neurons, measured 0),
+    membrane state within 1e-5; also with the state carried across two calls."""
+    pkg = _pkg()
+    ops = pkg.ops
+    F_ = {"f32": ops.FMT_F32, "pair": ops.FMT_PAIR, "half": ops.FMT_HALF}
+    T, B, H, W = 5, 2, 22, 36
+    torch.manual_seed(cin * 100 + cout)
+    if cin == 2:
+        x = (torch.rand(T * B, cin, H, W, device=DEV) < 0.3).float()                      # NCHW event frames
+        xin = x
+    else:
+        x = _cl((torch.rand(T * B, cin, H, W, device=DEV) < 0.3).float() * torch.randint(1, 5, (T * B, cin, H, W), device=DEV))
+        xin = ops.act_convert(x, ops.FMT_HALF)
+    w = torch.randn(cout, cin, 3, 3, device=DEV) * (30.0 / (cin * 9)) ** 0.5
+    scale, shift = torch.rand(cout, device=DEV) + 0.5, torch.randn(cout, device=DEV) * 0.2 + 0.3
+    pc = ops.pack_conv(w, 1, scale, shift, pkg._lib.SODA_CONV_FP32)
+    assert ops.conv_lif_pool_ok(xin, pc)
+    cur = ops.conv2d(x, pc)
+    z, v_ref, i_ref, _, _, _ = ops.lif_scan(cur, T)
+    want = ops.pool2d(z, 2, 2, "S")
+    assert 0.02 < float(z.mean()) < 0.9
+    y, v, i = ops.conv_lif_pool(xin, pc, T, ops.LIF_DEFAULT, out_fmt=F_[out_fmt])
+    got = ops.to_f32(y)
+    assert got.shape == want.shape
+    assert float((got != want).float().mean()) <= 1e-4
+    assert float((v - v_ref).abs().max()) <= 1e-5 * max(1.0, float(v_ref.abs().max())) or \
+        float(((v - v_ref).abs() > 1e-5).float().mean()) <= 1e-4
+    n1 = 2 * B
+    y1, v1, i1 = ops.conv_lif_pool(xin[:n1], pc, 2, ops.LIF_DEFAULT, out_fmt=F_[out_fmt])
+    y2, v2, i2 = ops.conv_lif_pool(xin[n1:], pc, T - 2, ops.LIF_DEFAULT, v0=v1, i0=i1, out_fmt=F_[out_fmt])
+    assert torch.equal(torch.cat([ops.to_f32(y1), ops.to_f32(y2)]), got)
+    assert torch.equal(v2, v) and torch.equal(i2, i)
