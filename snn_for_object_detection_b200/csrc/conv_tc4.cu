@@ -62,7 +62,10 @@ struct Tc4Params {
   int n_sp_items;
   int it_step_sp, it_step_outer;
   int taps, cblocks, kblocks;
-  int mode;                      // 0 = HALO (one A stage per channel slab, `taps` k-blocks), 1 = TAP (one stage per k-block)
+  int mode;                      // 0 = HALO (one A stage per channel slab, `taps` k-blocks), 1 = TAP (one stage per k-block group)
+  int kg;                        // k-blocks per A / B ring stage outside the 3x3 halo mode (1 or 2): every stage hand-off
+                                 // (two barrier round trips + commits) then covers twice the MMAs
+  uint32_t a_tile_bytes;         // one k-block's A tile inside a stage
   int flat;                      // 1x1 stride-1 over the flattened pixel list
   int in_fmt;                    // SODA_ACT_PAIR / SODA_ACT_HALF
   int a_exact;                   // PAIR input whose lo halves are all zero: the a_lo*w_hi product is skipped
@@ -200,7 +203,7 @@ __device__ __forceinline__ void tc4_mma_role(const Tc4Params& p, uint32_t tmem_b
   const uint32_t a_lo0 = (uint32_t)a_desc0, b_lo0 = (uint32_t)b_desc0;
   const bool stat = p.b_stationary != 0;
   const bool lo_pass = PAIR && !p.a_exact;
-  const int stages_per_tile = HALO3 ? p.cblocks : p.kblocks;
+  const int stages_per_tile = HALO3 ? p.cblocks : p.kblocks / p.kg;
   const uint32_t a_stage16 = p.plane_bytes >> 4;
   const uint32_t b_tap16 = (uint32_t)p.cblocks * B_KB16;   // resident weights are stored (tap, cb)
   uint32_t sa = 0, pa = 0, sb = 0, pb = 0, cnt = 0;
@@ -257,15 +260,20 @@ __device__ __forceinline__ void tc4_mma_role(const Tc4Params& p, uint32_t tmem_b
         } else {
           uint32_t b_lo;
           if (stat) {
-            b_lo = b_lo0 + (uint32_t)st * B_KB16;
+            b_lo = b_lo0 + (uint32_t)(st * p.kg) * B_KB16;
           } else {
             mbar_wait_uniform(&b_full[sb], pb);
             tc_fence_after();
-            b_lo = b_lo0 + sb * B_KB16;
+            b_lo = b_lo0 + sb * (B_KB16 * (uint32_t)p.kg);
           }
+          const uint32_t a_tile16 = p.a_tile_bytes >> 4;
           if (elect_one()) {
             _Pragma("unroll") for (int m = 0; m < 2; ++m) if (m < MT)
               tc4_issue_kblock<BN, PAIR>(d_acc[m], a_lo[m], a_hi, b_lo, b_hi, acc0, lo_pass);
+            if (p.kg == 2) {
+              _Pragma("unroll") for (int m = 0; m < 2; ++m) if (m < MT)
+                tc4_issue_kblock<BN, PAIR>(d_acc[m], a_lo[m] + a_tile16, a_hi, b_lo + B_KB16, b_hi, 1u, lo_pass);
+            }
             if (!stat) mma_commit(&b_empty[sb]);
           }
           if (!stat && ++sb == (uint32_t)p.b_stages) sb = 0, pb ^= 1;
@@ -365,7 +373,7 @@ conv_tc4_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__
         const int n_tap = p.mode == 0 ? 1 : p.taps;
         int ky = 0, kx = 0;
         for (int tap = 0; tap < n_tap; ++tap) {
-          for (int cb = 0; cb < p.cblocks; ++cb) {
+          for (int cb = 0; cb < p.cblocks; cb += p.kg) {
             _Pragma("unroll") for (int m = 0; m < 2; ++m) if (m < p.mt) {
               mbar_wait_uniform(&a_empty[s], ph ^ 1);
               if (elect_one()) {
@@ -375,6 +383,9 @@ conv_tc4_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__
                   mbar_expect_tx(&a_full[s], p.a_tx_bytes);
                   tma_load_4d_s(smem_a_u32 + s * p.plane_bytes, &tmA, &a_full[s], cb * rowch, x0[m] + kx, y0[m] + ky,
                                 img);
+                  if (p.kg == 2)
+                    tma_load_4d_s(smem_a_u32 + s * p.plane_bytes + p.a_tile_bytes, &tmA, &a_full[s], (cb + 1) * rowch,
+                                  x0[m] + kx, y0[m] + ky, img);
                 }
               }
               __syncwarp();
@@ -409,23 +420,26 @@ conv_tc4_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__
         }
     } else {
       uint32_t s = 0, ph = 0;
-      const int n_o = p.mode == 0 ? p.cblocks : p.taps;   // HALO walks (cb, tap), TAP walks (tap, cb)
-      const int n_i = p.mode == 0 ? p.taps : p.cblocks;
+      const bool halo3 = p.mode == 0 && p.k == 3;          // halo mode walks (cb, tap); everything else (tap, cb)
+      const int n_o = halo3 ? p.cblocks : p.taps;
+      const int n_i = halo3 ? p.taps : p.cblocks;
       for (int item = blockIdx.x; item < p.n_items; item += gridDim.x) {
         for (int t = 0; t < p.T_inner; ++t) {
           for (int o = 0; o < n_o; ++o)
-            for (int i = 0; i < n_i; ++i) {
-              const int tap = p.mode == 0 ? i : o, cb = p.mode == 0 ? o : i;
+            for (int i = 0; i < n_i; i += p.kg) {   // (kg == 2 only outside the halo mode: i walks the channel slabs)
+              const int tap = halo3 ? i : o, cb = halo3 ? o : i;
               mbar_wait_uniform(&b_empty[s], ph ^ 1);
               if (elect_one() && (p.dbg & 16)) mbar_arrive(&b_full[s]);
               if (elect_one() && !(p.dbg & 16)) {
-                mbar_expect_tx(&b_full[s], p.b_kb_bytes);
-                const uint32_t dst = smem_b_u32 + s * p.b_kb_bytes;
-                if (pair) {
-                  tma_load_3d_s(dst, &tmB, &b_full[s], cb * 64, my_chunk * BN, tap);
-                } else {
-                  tma_load_3d_s(dst, &tmB, &b_full[s], cb * 128, my_chunk * BN, tap);
-                  tma_load_3d_s(dst + B_TILE, &tmB, &b_full[s], cb * 128 + 64, my_chunk * BN, tap);
+                mbar_expect_tx(&b_full[s], p.b_kb_bytes * (uint32_t)p.kg);
+                for (int j = 0; j < p.kg; ++j) {
+                  const uint32_t dst = smem_b_u32 + (s * (uint32_t)p.kg + (uint32_t)j) * p.b_kb_bytes;
+                  if (pair) {
+                    tma_load_3d_s(dst, &tmB, &b_full[s], (cb + j) * 64, my_chunk * BN, tap);
+                  } else {
+                    tma_load_3d_s(dst, &tmB, &b_full[s], (cb + j) * 128, my_chunk * BN, tap);
+                    tma_load_3d_s(dst + B_TILE, &tmB, &b_full[s], (cb + j) * 128 + 64, my_chunk * BN, tap);
+                  }
                 }
               }
               __syncwarp();
@@ -909,8 +923,14 @@ int conv_tc4_dispatch(const soda_pconv_desc_t* d, const void* x, const void* pac
       if (rc) return rc;
     }
   }
-  p.a_tx_bytes = (uint32_t)p.rows * 128u;
-  p.plane_bytes = (p.a_tx_bytes + 1023u) & ~1023u;
+  {
+    static const int env_kg = []() { const char* e = getenv("SODA_TC4_KG"); return e ? atoi(e) : 1; }();   // measured: 2 halves the ring depth where shared memory is tight and loses 15-50 % on the streamed layers; only the fused stride-2 + LIF case gained
+    const bool halo3_ = p.mode == 0 && p.k == 3;
+    p.kg = (!halo3_ && env_kg == 2 && p.cblocks % 2 == 0) ? 2 : 1;
+  }
+  p.a_tile_bytes = ((uint32_t)p.rows * 128u + 1023u) & ~1023u;
+  p.a_tx_bytes = (uint32_t)p.rows * 128u * (uint32_t)p.kg;
+  p.plane_bytes = p.a_tile_bytes * (uint32_t)p.kg;
   {
     const cuuint64_t dims[3] = {(cuuint64_t)(2 * d->Cin), (cuuint64_t)Cout_pad, (cuuint64_t)p.taps};
     const cuuint64_t str[2] = {(cuuint64_t)d->Cin * 4, (cuuint64_t)Cout_pad * d->Cin * 4};
@@ -947,7 +967,7 @@ int conv_tc4_dispatch(const soda_pconv_desc_t* d, const void* x, const void* pac
   const bool halo3 = p.mode == 0 && p.k == 3;
   const int64_t plane = p.plane_bytes;
   static const int env_min_a = []() { const char* e = getenv("SODA_TC4_MIN_A"); return e ? atoi(e) : 0; }();
-  const int min_a = env_min_a > 0 ? env_min_a : (halo3 ? 2 : 4);
+  const int min_a = env_min_a > 0 ? env_min_a : (halo3 || p.kg == 2 ? 2 : 4);
   if (b_total + min_a * plane <= T4_SMEM_LIMIT) {
     p.b_stationary = 1, p.b_stages = 1, p.mt = 1;
     p.b_region_bytes = (uint32_t)b_total;
@@ -958,15 +978,16 @@ int conv_tc4_dispatch(const soda_pconv_desc_t* d, const void* x, const void* pac
     static const int env_mt = []() { const char* e = getenv("SODA_TC4_MT"); return e ? atoi(e) : 0; }();
     const bool want_pair = !is_lif && p.n_spatial > 1 && env_mt != 1;
     p.mt = want_pair ? 2 : 1;
+    const int64_t b_st = (int64_t)b_kb * p.kg;   // one B ring stage
     int bs = 4;
-    while (bs > 2 && (int64_t)bs * b_kb + 2 * plane > T4_SMEM_LIMIT) --bs;
-    int64_t a = (T4_SMEM_LIMIT - (int64_t)bs * b_kb) / plane;
+    while (bs > 2 && (int64_t)bs * b_st + 2 * plane > T4_SMEM_LIMIT) --bs;
+    int64_t a = (T4_SMEM_LIMIT - (int64_t)bs * b_st) / plane;
     if (a < 2) return fail(SODA_ERR_UNSUPPORTED, "pconv: shared-memory plan does not fit");
-    const int a_pref = halo3 ? 4 : 6;
+    const int a_pref = halo3 ? 4 : (p.kg == 2 ? 4 : 6);
     p.a_stages = (int)std::min<int64_t>(std::min<int64_t>(a, T4_MAX_RING), a_pref);
-    p.b_stages = (int)std::min<int64_t>(T4_MAX_RING, (T4_SMEM_LIMIT - (int64_t)p.a_stages * plane) / b_kb);
+    p.b_stages = (int)std::min<int64_t>(T4_MAX_RING, (T4_SMEM_LIMIT - (int64_t)p.a_stages * plane) / b_st);
     if (p.b_stages < 2) return fail(SODA_ERR_UNSUPPORTED, "pconv: shared-memory plan does not fit");
-    p.b_region_bytes = (uint32_t)p.b_stages * b_kb;
+    p.b_region_bytes = (uint32_t)(p.b_stages * b_st);
   }
   p.n_sp_items = (p.n_spatial + p.mt - 1) / p.mt;
   p.n_items = p.nch * p.n_sp_items * p.n_outer;
