@@ -325,6 +325,14 @@ SODA_API int soda_conv_lif_pool_fwd(const void* x, int in_fmt, int in_nchw, int6
                                     int64_t out_batch_stride, int64_t out_pix_stride, float* v_out, float* i_out,
                                     void* stream);
 
+/* Unfolds plain NCHW fp32 frames x [N, C, H, W] (C * 9 <= 32: the binned events, C = 2) for a 3x3 / pad-1 convolution
+ * of the given stride into a pixel-major SODA_ACT_PAIR tensor out [N, Ho, Wo, 32]:
+ *   out(n, oy, ox, (ky*3 + kx)*C + ci) = x(n, ci, oy*stride + ky - 1, ox*stride + kx - 1)   (0 outside the frame / beyond C*9)
+ * so that the detector's first layer (models/tiny_yolo.py:16: Conv(64, 3, 2) on the event frames, K = 18) runs as a 1x1
+ * layer on soda_pconv_lif_fwd.  Occupancy values {0,1} are exact in fp16: lo halves are zero. */
+SODA_API int soda_im2col3_frames(const float* x, int N, int C, int H, int W, int stride, void* out, int64_t out_batch_stride,
+                                 int64_t out_pix_stride, void* stream);
+
 /* Format conversion / strided copy of a pixel-major tensor [n_frames][pix_per_frame][C] between any two formats
  * (decode to fp32, re-encode): the boundary between the packed region of a net and fp32 callers, and the copy of a
  * tensor into a concat slice of another format (generator.py:158).  C % 32 == 0 when PAIR is involved, else C % 8. */

@@ -109,6 +109,7 @@ SIGNATURES = {
     "soda_conv_lif_pool_supported": (_i, [_i, _i, _i, _i, _i, _i, _i, _i]),
     "soda_conv_lif_pool_fwd": (_i, [_vp, _i, _i, _i64, _i64, _vp, _vp, _i, _i, _i, _i, _i, _i, C.POINTER(NeuronParams), _vp,
                                     _vp, _vp, _i, _i64, _i64, _vp, _vp, _vp]),
+    "soda_im2col3_frames": (_i, [_vp, _i, _i, _i, _i, _i, _vp, _i64, _i64, _vp]),
     "soda_act_convert": (_i, [_vp, _i, _i64, _i64, _vp, _i, _i64, _i64, _i64, _i64, _i, _vp, _vp]),
     "soda_lif_fmt_fwd": (_i, [C.POINTER(NeuronParams), _vp, _vp, _vp, _i, _i64, _i, _vp, _i, _i64, _vp, _i, _i64,
                               _vp, _vp, _vp, _vp]),

@@ -155,6 +155,50 @@ lif_fmt_fwd_kernel(NP p, const float* __restrict__ x, const float* __restrict__ 
   if (status != nullptr && over != 0) atomicAdd(status, over);
 }
 
+// im2col of the binned event frames for the detector's first layer (models/tiny_yolo.py:16 -> Conv(64, 3, stride 2) on
+// [T*B, 2, H, W]): K = Cin * 9 = 18 is below one MMA k-block, so the frames are unfolded ONCE into a pixel-major
+// SODA_ACT_PAIR tensor with 32 "channels" per output pixel - channel (ky * 3 + kx) * Cin + ci = x[ci, oy*s+ky-1,
+// ox*s+kx-1], zeros beyond Cin * 9 and in the lo halves (occupancy {0,1} is exact in fp16) - and the convolution
+// becomes a 1x1 layer on the tensor-core kernel.  One thread writes one pixel's 128-byte row.
+template <int C>
+__global__ void __launch_bounds__(256)
+im2col3_frames_kernel(const float* __restrict__ x, int N, int H, int W, int stride, int Ho, int Wo,
+                      uint8_t* __restrict__ out, int64_t out_bs, int64_t out_ps) {
+  pdl_trigger();
+  const int64_t total = (int64_t)N * Ho * Wo;
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (int64_t)gridDim.x * blockDim.x) {
+    const int ox = (int)(i % Wo);
+    const int64_t r = i / Wo;
+    const int oy = (int)(r % Ho);
+    const int64_t n = r / Ho;
+    const float* xf = x + n * (int64_t)C * H * W;
+    float v[32];
+#pragma unroll
+    for (int k = 0; k < 32; ++k) v[k] = 0.0f;
+#pragma unroll
+    for (int ky = 0; ky < 3; ++ky) {
+      const int iy = oy * stride + ky - 1;
+#pragma unroll
+      for (int kx = 0; kx < 3; ++kx) {
+        const int ix = ox * stride + kx - 1;
+        const bool inb = iy >= 0 && iy < H && ix >= 0 && ix < W;
+#pragma unroll
+        for (int ci = 0; ci < C; ++ci)
+          v[(ky * 3 + kx) * C + ci] = inb ? __ldg(xf + ((int64_t)ci * H + iy) * W + ix) : 0.0f;
+      }
+    }
+    uint8_t* dst = out + n * out_bs + ((int64_t)oy * Wo + ox) * out_ps;
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+      uint4 u;
+      u.x = h2_pack(v[8 * j], v[8 * j + 1]), u.y = h2_pack(v[8 * j + 2], v[8 * j + 3]);
+      u.z = h2_pack(v[8 * j + 4], v[8 * j + 5]), u.w = h2_pack(v[8 * j + 6], v[8 * j + 7]);
+      *reinterpret_cast<uint4*>(dst + j * 16) = u;
+      *reinterpret_cast<uint4*>(dst + 64 + j * 16) = make_uint4(0u, 0u, 0u, 0u);
+    }
+  }
+}
+
 static inline int fmt_bytes(int fmt) { return fmt == SODA_ACT_HALF ? 2 : 4; }
 static inline bool fmt_ok(int fmt) { return fmt >= SODA_ACT_F32 && fmt <= SODA_ACT_HALF; }
 // pointer / stride (in elements) alignment a format needs for the vector accesses above
@@ -205,4 +249,23 @@ extern "C" int soda_lif_fmt_fwd(const soda_neuron_params_t* p, const float* x, c
       res_pix_stride * fmt_bytes(res_fmt), reinterpret_cast<uint8_t*>(out), out_fmt, out_pix_stride * fmt_bytes(out_fmt),
       v_out, i_out, status);
   return after_launch("lif_fmt_fwd_kernel");
+}
+
+extern "C" int soda_im2col3_frames(const float* x, int N, int C, int H, int W, int stride, void* out, int64_t out_batch_stride,
+                                   int64_t out_pix_stride, void* stream) {
+  using namespace soda;
+  if (!x || !out) return fail(SODA_ERR_BAD_ARG, "im2col3_frames: null pointer");
+  if (N <= 0 || C <= 0 || H <= 0 || W <= 0 || stride <= 0) return fail(SODA_ERR_BAD_ARG, "im2col3_frames: non-positive size");
+  if (C * 9 > 32) return fail(SODA_ERR_UNSUPPORTED, "im2col3_frames: Cin * 9 must fit one 32-channel group");
+  if (!fmt_aligned(out, SODA_ACT_PAIR, out_batch_stride, out_pix_stride))
+    return fail(SODA_ERR_BAD_ARG, "im2col3_frames: misaligned output");
+  const int Ho = (H + 2 - 3) / stride + 1, Wo = (W + 2 - 3) / stride + 1;
+  const int64_t total = (int64_t)N * Ho * Wo;
+  const unsigned grid = (unsigned)std::min<int64_t>(ceil_div(total, 256), 148 * 32);
+  uint8_t* o8 = reinterpret_cast<uint8_t*>(out);
+  cudaStream_t st = (cudaStream_t)stream;
+  if (C == 1) im2col3_frames_kernel<1><<<grid, 256, 0, st>>>(x, N, H, W, stride, Ho, Wo, o8, out_batch_stride * 4, out_pix_stride * 4);
+  else if (C == 2) im2col3_frames_kernel<2><<<grid, 256, 0, st>>>(x, N, H, W, stride, Ho, Wo, o8, out_batch_stride * 4, out_pix_stride * 4);
+  else im2col3_frames_kernel<3><<<grid, 256, 0, st>>>(x, N, H, W, stride, Ho, Wo, o8, out_batch_stride * 4, out_pix_stride * 4);
+  return after_launch("im2col3_frames_kernel");
 }

@@ -85,7 +85,30 @@ def _copy_into(src: torch.Tensor, dst: torch.Tensor) -> None:
     ops.mark_exact(dst, ops.exact_bound(src))
 
 
-def _conv_eligible(conv: SodaConv2d) -> bool:
+class _ColConv:
+    """The event-frame layer seen as a 1x1 convolution over ops.im2col_frames' 32-channel rows (same interface as
+    the SodaConv2d attributes the planner reads)."""
+
+    in_channels, kernel_size, stride, bias, groups, dilation = 32, (1, 1), (1, 1), None, 1, (1, 1)
+
+    def __init__(self, conv: SodaConv2d):
+        self.conv, self.out_channels = conv, conv.out_channels
+
+    def packed_p(self, norm, in_fmt: int):
+        return self.conv.packed_im2col(norm)
+
+
+def _im2col_route(conv: SodaConv2d, Y: torch.Tensor) -> bool:
+    """K = Cin * 9 <= 32 on plain NCHW fp32 frames (the detector's first layer, models/tiny_yolo.py:16): unfold the
+    frames once and run a 1x1 layer on the tensor-core kernel.  Decided by shapes alone - never by batch size or T - so
+    that sharded, chunked and per-step execution all take the same arithmetic."""
+    return (_packed() and Y.dtype == torch.float32 and Y.dim() == 4 and Y.is_contiguous() and _conv_eligible(conv)
+            and conv.kernel_size == (3, 3) and conv.padding == (1, 1) and Y.shape[1] == conv.in_channels
+            and conv.in_channels * 9 <= 32 and conv.out_channels % 32 == 0 and Y.shape[1] > 1
+            and os.environ.get("SODA_IM2COL_FIRST", "1") != "0")
+
+
+def _conv_eligible(conv) -> bool:
     return conv.bias is None and conv.groups == 1 and conv.dilation == (1, 1)
 
 
@@ -127,6 +150,15 @@ def _run_conv(conv: SodaConv2d, norm, Y: torch.Tensor, out: Optional[torch.Tenso
         shape = (conv.in_channels, conv.out_channels, conv.kernel_size[0], conv.stride[0])
         if ops.pconv_ok(Yp, shape, residual, out):
             return ops.pconv(Yp, conv.packed_p(norm, ops.fmt_of(Yp)), residual=residual, out=out, out_fmt=out_fmt)
+        if isinstance(conv, _ColConv):
+            # destination not addressable by the tensor-core store (misaligned slice): via a temporary
+            tmp = ops.pconv(Yp, conv.packed_p(norm, ops.fmt_of(Yp)), out_fmt=ops.FMT_F32)
+            if residual is not None:
+                tmp = ops.add_n([tmp, ops.to_f32(residual)])
+            if out is None:
+                return tmp if out_fmt == ops.FMT_F32 else ops.act_convert(tmp, out_fmt)
+            _copy_into(tmp, out)
+            return out
     Yf = ops.to_f32(Y)
     rf = None if residual is None else ops.to_f32(residual)
     if out is not None and out.dtype != torch.float32:
@@ -494,9 +526,6 @@ class BlockGen(nn.Module):
                     norm = branch[idx + 1]
                     last = idx + 1
                 cell = branch[last + 1] if last + 1 < n else None
-                Yp = _packed_input(Y, layer)   # one conversion at most; later uses see the packed tensor
-                if Yp is not None:
-                    Y = Yp
                 Cout = layer.out_channels
                 Ho, Wo = ops.conv_out_hw(Y.shape[2], Y.shape[3], layer.kernel_size[0], layer.stride[0])
                 fuse_on = os.environ.get("SODA_FUSE_LIF", "1") != "0"
@@ -525,6 +554,12 @@ class BlockGen(nn.Module):
                         if is_last and o is not None:
                             return Y, False
                         continue
+                if _im2col_route(layer, Y):
+                    Y = ops.im2col_frames(Y, layer.stride[0])   # [N, 32, Ho, Wo] PAIR: the layer is now a 1x1 one
+                    layer = _ColConv(layer)
+                Yp = _packed_input(Y, layer)   # one conversion at most; later uses see the packed tensor
+                if Yp is not None:
+                    Y = Yp
                 if (norm is not None and type(cell) is LIFCell and nograd and _conv_eligible(layer) and fuse_on):
                     lif_idx = last + 1
                     is_last = lif_idx == n - 1

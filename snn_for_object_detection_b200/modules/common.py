@@ -72,6 +72,24 @@ class SodaConv2d(nn.Conv2d):
             self._pack_cache[slot] = hit
         return hit[1]
 
+    def packed_im2col(self, norm: Optional["SodaBatchNorm2d"]) -> "ops.PackedPConv":
+        """The 3x3 filter of a layer on few input channels (Cin * 9 <= 32: the event-frame layer) as the 1x1 filter
+        over ops.im2col_frames' tap-major 32-channel rows, BatchNorm folded, packed for the tensor-core kernel."""
+        key = (self.weight.data_ptr(), self.weight._version, self.weight.device)
+        scale = shift = None
+        if norm is not None:
+            key = key + norm.fold_key()
+        hit = self._pack_cache.get("im2col")
+        if hit is None or hit[0] != key:
+            if norm is not None:
+                scale, shift = norm.fold()
+            co, ci = self.out_channels, self.in_channels
+            w = torch.zeros(co, 32, 1, 1, device=self.weight.device)
+            w[:, : ci * 9, 0, 0] = self.weight.detach().permute(0, 2, 3, 1).reshape(co, ci * 9)   # (ky, kx, ci) order
+            hit = (key, ops.pack_pconv(w, 1, scale, shift, ops.FMT_PAIR))
+            self._pack_cache["im2col"] = hit
+        return hit[1]
+
     def packed_dgrad(self) -> ops.PackedConv:
         """Packed filter of the data-gradient convolution of a stride-1 layer: ``W'[ci, co, ky, kx] =
         W[co, ci, k-1-ky, k-1-kx]`` (tensor-core kind), cached on the weight version."""

@@ -474,6 +474,21 @@ def act_convert(x: torch.Tensor, fmt: int, out: Optional[torch.Tensor] = None) -
     return out
 
 
+def im2col_frames(x: torch.Tensor, stride: int) -> torch.Tensor:
+    """Plain NCHW fp32 frames ``[N, C, H, W]`` (``C * 9 <= 32``) unfolded for a 3x3 / pad-1 convolution into a PAIR
+    tensor ``[N, 32, Ho, Wo]`` (tap-major channels, exact)."""
+    _need_cuda(x)
+    if x.dim() != 4 or x.dtype != torch.float32 or not x.is_contiguous() or x.shape[1] * 9 > 32:
+        raise ValueError("im2col_frames: contiguous NCHW fp32 frames with C * 9 <= 32")
+    N, Cc, H, W = x.shape
+    Ho, Wo = conv_out_hw(H, W, 3, stride)
+    out = empty_act(N, 32, Ho, Wo, x.device, FMT_PAIR)
+    so = _pm_strides(out)
+    check(lib.soda_im2col3_frames(x.data_ptr(), N, Cc, H, W, stride, out.data_ptr(), so[0], so[1], _stream()),
+          "soda_im2col3_frames")
+    return mark_exact(out, exact_bound(x) if exact_bound(x) is not None else 1)
+
+
 def to_f32(x: torch.Tensor) -> torch.Tensor:
     """The fp32 view of an activation tensor of any format (a no-op for fp32)."""
     return x if x.dtype == torch.float32 else act_convert(x, FMT_F32)

@@ -231,3 +231,32 @@ def test_conv_lif_pool_equals_conv_then_scan_then_pool(cin, cout, out_fmt):
     y2, v2, i2 = ops.conv_lif_pool(xin[n1:], pc, T - 2, ops.LIF_DEFAULT, v0=v1, i0=i1, out_fmt=F_[out_fmt])
     assert torch.equal(torch.cat([ops.to_f32(y1), ops.to_f32(y2)]), got)
     assert torch.equal(v2, v) and torch.equal(i2, i)
+
+
+def test_event_frame_layer_as_im2col_plus_1x1_matches_the_direct_kernel():
+    """The detector's first layer (Conv(64, 3, stride 2) + BN + LIF on the binned frames, K = 18) as im2col of the
+    frames + a 1x1 layer on the tensor-core kernel == the direct FP32-pipe kernel: spikes equal up to borderline
+    neurons (<= 1e-4), membranes within 1e-5."""
+    pkg = _pkg()
+    ops = pkg.ops
+    T, B, H, W = 6, 3, 48, 64
+    torch.manual_seed(5)
+    x = (torch.rand(T * B, 2, H, W, device=DEV) < 0.1).float()
+    conv = pkg.modules.common.SodaConv2d(2, 64, 3, stride=2, padding=1, bias=False).to(DEV)
+    torch.nn.init.normal_(conv.weight, std=1.2)
+    norm = pkg.modules.common.SodaBatchNorm2d(64).to(DEV).eval()
+    norm.bias = None
+    norm.weight.data.uniform_(0.5, 2.0)
+    norm.running_mean.uniform_(-0.2, 0.2)
+    col = ops.im2col_frames(x, 2)
+    ref_col = torch.nn.functional.unfold(x, 3, padding=1, stride=2)             # [N, C*9 (ci, ky, kx), L]
+    Ho, Wo = ops.conv_out_hw(H, W, 3, 2)
+    ref_col = ref_col.reshape(T * B, 2, 9, Ho, Wo).permute(0, 2, 1, 3, 4).reshape(T * B, 18, Ho, Wo)
+    got_col = ops.to_f32(col)
+    assert torch.equal(got_col[:, :18], ref_col) and float(got_col[:, 18:].abs().max()) == 0
+    y, v, i = ops.pconv_lif(col, conv.packed_im2col(norm), T, ops.LIF_DEFAULT, out_fmt=ops.FMT_HALF)
+    pc = conv.packed(norm, pkg._lib.SODA_CONV_FP32)
+    y0, v0, i0 = ops.conv_lif(x, pc, T, ops.LIF_DEFAULT)
+    assert 0.02 < float(y0.mean()) < 0.9
+    assert float((ops.to_f32(y) != y0).float().mean()) <= 1e-4
+    assert float(((v - v0).abs() > 1e-5 * max(1.0, float(v0.abs().max()))).float().mean()) <= 1e-4
