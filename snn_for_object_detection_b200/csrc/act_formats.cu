@@ -6,6 +6,7 @@
 // Both kernels are pure HBM streams: one thread owns one pixel's 8-channel piece (a 16- or 32-byte vector in every
 // format), consecutive threads take consecutive pieces, so a warp reads and writes whole 128-byte lines.
 #include <cuda_fp16.h>
+#include <stdlib.h>
 
 #include <algorithm>
 
@@ -95,63 +96,113 @@ act_convert_kernel(const uint8_t* __restrict__ src, int src_fmt, int64_t src_bs,
   if (status != nullptr && over != 0) atomicAdd(status, over);
 }
 
-// One thread: 8 channels of one pixel for all T steps, state in registers; loads of 4 steps are issued before the
-// first of them is consumed so that 8 x 32 bytes per thread are in flight.
+// CH-channel variants of the piece accessors (CH = 4: 16 / 8 bytes per access)
+template <int CH>
+__device__ __forceinline__ void loadp(const uint8_t* px, int fmt, int c, float (&v)[CH]) {
+  if constexpr (CH == 8) {
+    load8(px, fmt, c, v);
+  } else {
+    const uint8_t* q = px + piece_off(fmt, c);
+    if (fmt == SODA_ACT_F32) {
+      const float4 a = __ldg(reinterpret_cast<const float4*>(q));
+      v[0] = a.x, v[1] = a.y, v[2] = a.z, v[3] = a.w;
+    } else {
+      const uint2 h = __ldg(reinterpret_cast<const uint2*>(q));
+      const float2 f0 = h2_unpack(h.x), f1 = h2_unpack(h.y);
+      v[0] = f0.x, v[1] = f0.y, v[2] = f1.x, v[3] = f1.y;
+      if (fmt == SODA_ACT_PAIR) {
+        const uint2 l = __ldg(reinterpret_cast<const uint2*>(q + 64));
+        const float2 g0 = h2_unpack(l.x), g1 = h2_unpack(l.y);
+        v[0] += g0.x, v[1] += g0.y, v[2] += g1.x, v[3] += g1.y;
+      }
+    }
+  }
+}
+template <int CH>
+__device__ __forceinline__ unsigned int storep(uint8_t* px, int fmt, int c, const float (&v)[CH]) {
+  if constexpr (CH == 8) {
+    return store8(px, fmt, c, v);
+  } else {
+    uint8_t* q = px + piece_off(fmt, c);
+    if (fmt == SODA_ACT_F32) {
+      *reinterpret_cast<float4*>(q) = make_float4(v[0], v[1], v[2], v[3]);
+      return 0;
+    }
+    const uint32_t h0 = h2_pack(v[0], v[1]), h1 = h2_pack(v[2], v[3]);
+    *reinterpret_cast<uint2*>(q) = make_uint2(h0, h1);
+    if (fmt == SODA_ACT_PAIR) {
+      const float2 f0 = h2_unpack(h0), f1 = h2_unpack(h1);
+      *reinterpret_cast<uint2*>(q + 64) = make_uint2(h2_pack(v[0] - f0.x, v[1] - f0.y), h2_pack(v[2] - f1.x, v[3] - f1.y));
+    }
+    return (fabsf(v[0]) > 65504.f) + (fabsf(v[1]) > 65504.f) + (fabsf(v[2]) > 65504.f) + (fabsf(v[3]) > 65504.f);
+  }
+}
+
+// One thread: CH channels of one pixel for all T steps, state in registers; the loads of UNR steps are issued before the
+// first of them is consumed.  CH = 8 for large maps (32-byte accesses), CH = 4 where the map alone would not fill the
+// GPU with threads (small maps at small batch: twice the threads, half the registers).
+template <int CH, int UNR>
 __global__ void __launch_bounds__(256)
 lif_fmt_fwd_kernel(NP p, const float* __restrict__ x, const float* __restrict__ v0, const float* __restrict__ i0, int T,
                    int64_t n_pix, int C, const uint8_t* __restrict__ residual, int res_fmt, int64_t res_ps,
                    uint8_t* __restrict__ out, int out_fmt, int64_t out_ps, float* __restrict__ v_out,
                    float* __restrict__ i_out, unsigned int* status) {
   pdl_trigger();
-  const int pieces = C >> 3;
+  const int pieces = C / CH;
   const int64_t total = n_pix * pieces;
   const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
   if (i >= total) return;
-  const int c = (int)(i % pieces) * 8;
+  const int c = (int)(i % pieces) * CH;
   const int64_t q = i / pieces;
   const int64_t soff = q * C + c;
-  float v[8], cur[8];
-  if (v0 != nullptr) {
-    const float4 a = __ldg(reinterpret_cast<const float4*>(v0 + soff)), b = __ldg(reinterpret_cast<const float4*>(v0 + soff + 4));
-    const float4 e = __ldg(reinterpret_cast<const float4*>(i0 + soff)), f = __ldg(reinterpret_cast<const float4*>(i0 + soff + 4));
-    v[0] = a.x, v[1] = a.y, v[2] = a.z, v[3] = a.w, v[4] = b.x, v[5] = b.y, v[6] = b.z, v[7] = b.w;
-    cur[0] = e.x, cur[1] = e.y, cur[2] = e.z, cur[3] = e.w, cur[4] = f.x, cur[5] = f.y, cur[6] = f.z, cur[7] = f.w;
-  } else {
+  float v[CH], cur[CH];
 #pragma unroll
-    for (int k = 0; k < 8; ++k) v[k] = p.v_leak, cur[k] = 0.f;
+  for (int k = 0; k < CH; k += 4) {
+    if (v0 != nullptr) {
+      const float4 a = __ldg(reinterpret_cast<const float4*>(v0 + soff + k));
+      const float4 e = __ldg(reinterpret_cast<const float4*>(i0 + soff + k));
+      v[k] = a.x, v[k + 1] = a.y, v[k + 2] = a.z, v[k + 3] = a.w;
+      cur[k] = e.x, cur[k + 1] = e.y, cur[k + 2] = e.z, cur[k + 3] = e.w;
+    } else {
+      v[k] = v[k + 1] = v[k + 2] = v[k + 3] = p.v_leak;
+      cur[k] = cur[k + 1] = cur[k + 2] = cur[k + 3] = 0.f;
+    }
   }
   const int64_t step = n_pix * C;   // floats between two time steps of x
   unsigned int over = 0;
-  for (int t0 = 0; t0 < T; t0 += 4) {
-    float xin[4][8], rin[4][8];
+  for (int t0 = 0; t0 < T; t0 += UNR) {
+    float xin[UNR][CH], rin[UNR][CH];
 #pragma unroll
-    for (int u = 0; u < 4; ++u) {
+    for (int u = 0; u < UNR; ++u) {
       if (t0 + u < T) {
         const float* xp = x + (int64_t)(t0 + u) * step + soff;
-        const float4 a = __ldg(reinterpret_cast<const float4*>(xp)), b = __ldg(reinterpret_cast<const float4*>(xp + 4));
-        xin[u][0] = a.x, xin[u][1] = a.y, xin[u][2] = a.z, xin[u][3] = a.w;
-        xin[u][4] = b.x, xin[u][5] = b.y, xin[u][6] = b.z, xin[u][7] = b.w;
-        if (residual != nullptr) load8(residual + ((int64_t)(t0 + u) * n_pix + q) * res_ps, res_fmt, c, rin[u]);
+#pragma unroll
+        for (int k = 0; k < CH; k += 4) {
+          const float4 a = __ldg(reinterpret_cast<const float4*>(xp + k));
+          xin[u][k] = a.x, xin[u][k + 1] = a.y, xin[u][k + 2] = a.z, xin[u][k + 3] = a.w;
+        }
+        if (residual != nullptr) loadp<CH>(residual + ((int64_t)(t0 + u) * n_pix + q) * res_ps, res_fmt, c, rin[u]);
       }
     }
 #pragma unroll
-    for (int u = 0; u < 4; ++u) {
+    for (int u = 0; u < UNR; ++u) {
       if (t0 + u < T) {
-        float o[8];
+        float o[CH];
 #pragma unroll
-        for (int k = 0; k < 8; ++k) {
+        for (int k = 0; k < CH; ++k) {
           float z, vd;
           lif_step(p, xin[u][k], v[k], cur[k], z, vd);
           o[k] = residual != nullptr ? z + rin[u][k] : z;
         }
-        over += store8(out + ((int64_t)(t0 + u) * n_pix + q) * out_ps, out_fmt, c, o);
+        over += storep<CH>(out + ((int64_t)(t0 + u) * n_pix + q) * out_ps, out_fmt, c, o);
       }
     }
   }
-  *reinterpret_cast<float4*>(v_out + soff) = make_float4(v[0], v[1], v[2], v[3]);
-  *reinterpret_cast<float4*>(v_out + soff + 4) = make_float4(v[4], v[5], v[6], v[7]);
-  *reinterpret_cast<float4*>(i_out + soff) = make_float4(cur[0], cur[1], cur[2], cur[3]);
-  *reinterpret_cast<float4*>(i_out + soff + 4) = make_float4(cur[4], cur[5], cur[6], cur[7]);
+#pragma unroll
+  for (int k = 0; k < CH; k += 4) {
+    *reinterpret_cast<float4*>(v_out + soff + k) = make_float4(v[k], v[k + 1], v[k + 2], v[k + 3]);
+    *reinterpret_cast<float4*>(i_out + soff + k) = make_float4(cur[k], cur[k + 1], cur[k + 2], cur[k + 3]);
+  }
   if (status != nullptr && over != 0) atomicAdd(status, over);
 }
 
@@ -243,11 +294,21 @@ extern "C" int soda_lif_fmt_fwd(const soda_neuron_params_t* p, const float* x, c
   if ((reinterpret_cast<uintptr_t>(x) & 15) || !fmt_aligned(out, out_fmt, out_pix_stride, out_pix_stride) ||
       (residual != nullptr && !fmt_aligned(residual, res_fmt, res_pix_stride, res_pix_stride)))
     return fail(SODA_ERR_BAD_ARG, "lif_fmt: misaligned pointer or stride");
-  const int64_t total = n_pix * (C / 8);
-  lif_fmt_fwd_kernel<<<(unsigned)ceil_div(total, 256), 256, 0, (cudaStream_t)stream>>>(
-      to_np(p), x, v0, i0, T, n_pix, C, reinterpret_cast<const uint8_t*>(residual), res_fmt,
-      res_pix_stride * fmt_bytes(res_fmt), reinterpret_cast<uint8_t*>(out), out_fmt, out_pix_stride * fmt_bytes(out_fmt),
-      v_out, i_out, status);
+  static const int env_ch = []() { const char* e = getenv("SODA_SCAN_CH"); return e ? atoi(e) : 0; }();
+  const int64_t total8 = n_pix * (C / 8);
+  const bool ch4 = env_ch == 4 || (env_ch != 8 && total8 < 148LL * 1024);   // fewer than one full wave of 8-channel threads
+  const int64_t total = ch4 ? n_pix * (C / 4) : total8;
+  const uint8_t* r8 = reinterpret_cast<const uint8_t*>(residual);
+  uint8_t* o8 = reinterpret_cast<uint8_t*>(out);
+  const int64_t rps = res_pix_stride * fmt_bytes(res_fmt), ops_ = out_pix_stride * fmt_bytes(out_fmt);
+  const unsigned grid = (unsigned)ceil_div(total, 256);
+  cudaStream_t st = (cudaStream_t)stream;
+  if (ch4)
+    lif_fmt_fwd_kernel<4, 4><<<grid, 256, 0, st>>>(to_np(p), x, v0, i0, T, n_pix, C, r8, res_fmt, rps, o8, out_fmt, ops_, v_out,
+                                                   i_out, status);
+  else
+    lif_fmt_fwd_kernel<8, 4><<<grid, 256, 0, st>>>(to_np(p), x, v0, i0, T, n_pix, C, r8, res_fmt, rps, o8, out_fmt, ops_, v_out,
+                                                   i_out, status);
   return after_launch("lif_fmt_fwd_kernel");
 }
 

@@ -186,14 +186,16 @@ __device__ __forceinline__ void tc4_issue_kblock(uint32_t d_main, uint32_t a_lo,
 
 // HALO3: 3x3 stride-1 layers (one A stage = one channel slab with its halo, nine taps = nine descriptor offsets);
 // otherwise one A stage = one k-block (1x1 layers, stride-2 tap tiles).
-template <int BN, int MT, bool PAIR, bool HALO3>
+template <int BN, int MT, bool PAIR, int MODE>
 __device__ __forceinline__ void tc4_mma_role(const Tc4Params& p, uint32_t tmem_base, uint32_t smem_a_u32,
                                              uint32_t smem_b_u32, uint64_t* a_full, uint64_t* a_empty,
                                              uint64_t* b_full, uint64_t* b_empty, uint64_t* acc_full,
                                              uint64_t* acc_empty) {
   constexpr uint32_t NACC = t4_nacc(BN);
   constexpr uint32_t B_KB16 = ((BN * 128) >> 4) * (PAIR ? 1 : 2);   // one weight k-block, in descriptor units
+  constexpr bool HALO3 = MODE == 0;
   constexpr int WW = T4_BW + 2;                                      // halo row pitch in pixels
+  constexpr int PW = T4_BW + 1;                                      // phase-plane row pitch in pixels (stride-2 layers)
   // BN = 32: the two epilogue warps of a lane quarter alternate WORK UNITS (item x m-tile), and a warp must see every
   // phase of a barrier it waits on - so the units of warpgroup e cycle through their own two stages {2e, 2e + 1}
   constexpr bool UNIT_SPLIT = BN == 32;
@@ -203,13 +205,15 @@ __device__ __forceinline__ void tc4_mma_role(const Tc4Params& p, uint32_t tmem_b
   const uint32_t a_lo0 = (uint32_t)a_desc0, b_lo0 = (uint32_t)b_desc0;
   const bool stat = p.b_stationary != 0;
   const bool lo_pass = PAIR && !p.a_exact;
-  const int stages_per_tile = HALO3 ? p.cblocks : p.kblocks / p.kg;
+  const int stages_per_tile = HALO3 ? p.cblocks : (MODE == 2 ? p.cblocks * 4 : p.kblocks / p.kg);
   const uint32_t a_stage16 = p.plane_bytes >> 4;
   const uint32_t b_tap16 = (uint32_t)p.cblocks * B_KB16;   // resident weights are stored (tap, cb)
   uint32_t sa = 0, pa = 0, sb = 0, pb = 0, cnt = 0;
   uint32_t unit = 0, ce0 = 0, ce1 = 0;
   if (stat) mbar_wait_uniform(&b_full[0], 0);
   const long long dbg_t0 = clock64();
+  long long dbg_wa = 0, dbg_wb = 0, dbg_wc = 0;
+  const bool dbg_on = (p.dbg & 32) != 0;
   for (int item = blockIdx.x; item < p.n_items; item += gridDim.x, unit += MT) {
     for (int t = 0; t < p.T_inner; ++t) {
       uint32_t d_acc[2], acc_i[2];
@@ -223,7 +227,7 @@ __device__ __forceinline__ void tc4_mma_role(const Tc4Params& p, uint32_t tmem_b
         } else {
           a = (cnt + m) % NACC, ph = ((cnt + m) / NACC) & 1u;
         }
-        mbar_wait_uniform(&acc_empty[a], ph ^ 1);
+        { const long long w0 = dbg_on ? clock64() : 0; mbar_wait_uniform(&acc_empty[a], ph ^ 1); if (dbg_on) dbg_wc += clock64() - w0; }
         acc_i[m] = a;
         d_acc[m] = tmem_base + a * (2 * BN);   // main; correction accumulator BN columns further
       }
@@ -231,7 +235,7 @@ __device__ __forceinline__ void tc4_mma_role(const Tc4Params& p, uint32_t tmem_b
       for (int st = 0; st < stages_per_tile; ++st) {
         uint32_t s_m[2], a_lo[2];
         _Pragma("unroll") for (int m = 0; m < 2; ++m) if (m < MT) {
-          mbar_wait_uniform(&a_full[sa], pa);
+          { const long long w0 = dbg_on ? clock64() : 0; mbar_wait_uniform(&a_full[sa], pa); if (dbg_on) dbg_wa += clock64() - w0; }
           a_lo[m] = a_lo0 + sa * a_stage16;
           s_m[m] = sa;
           if (++sa == (uint32_t)p.a_stages) sa = 0, pa ^= 1;
@@ -242,7 +246,7 @@ __device__ __forceinline__ void tc4_mma_role(const Tc4Params& p, uint32_t tmem_b
           uint32_t b_lo = b_lo0 + (uint32_t)st * B_KB16;   // resident: k-block (tap 0, slab st)
           _Pragma("unroll") for (int tp = 0; tp < 9; ++tp) {
             if (!stat) {
-              mbar_wait_uniform(&b_full[sb], pb);
+              { const long long w0 = dbg_on ? clock64() : 0; mbar_wait_uniform(&b_full[sb], pb); if (dbg_on) dbg_wb += clock64() - w0; }
               tc_fence_after();
               b_lo = b_lo0 + sb * B_KB16;
             }
@@ -257,12 +261,41 @@ __device__ __forceinline__ void tc4_mma_role(const Tc4Params& p, uint32_t tmem_b
             if (stat) b_lo += b_tap16;
             else if (++sb == (uint32_t)p.b_stages) sb = 0, pb ^= 1;
           }
+        } else if constexpr (MODE == 2) {
+          // stride-2 3x3 layer: stage st = parity plane (st & 3) of channel slab (st >> 2).  A plane holds every
+          // second input row / column of the tile's halo (17 x 9 pixels); the taps that read it are descriptor shifts:
+          //   plane 0 (even rows, even cols): tap (1,1)           plane 1 (even rows, odd cols): (1,0) (1,2)
+          //   plane 2 (odd rows, even cols) : (0,1) (2,1)         plane 3 (odd rows, odd cols) : (0,0) (0,2) (2,0) (2,2)
+          const int pl = st & 3, cb = st >> 2;
+          const int ntap = pl == 0 ? 1 : (pl == 3 ? 4 : 2);
+          for (int j = 0; j < ntap; ++j) {
+            int ky, kx;
+            if (pl == 0) ky = 1, kx = 1;
+            else if (pl == 1) ky = 1, kx = 2 * j;
+            else if (pl == 2) ky = 2 * j, kx = 1;
+            else ky = 2 * (j >> 1), kx = 2 * (j & 1);
+            const uint32_t tap_off = (uint32_t)((ky >> 1) * PW + (kx >> 1)) * 8u;
+            uint32_t b_lo;
+            if (stat) {
+              b_lo = b_lo0 + (uint32_t)((ky * 3 + kx) * p.cblocks + cb) * B_KB16;
+            } else {
+              { const long long w0 = dbg_on ? clock64() : 0; mbar_wait_uniform(&b_full[sb], pb); if (dbg_on) dbg_wb += clock64() - w0; }
+              tc_fence_after();
+              b_lo = b_lo0 + sb * B_KB16;
+            }
+            if (elect_one()) {
+              _Pragma("unroll") for (int m = 0; m < 2; ++m) if (m < MT)
+                tc4_issue_kblock<BN, PAIR>(d_acc[m], a_lo[m] + tap_off, a_hi, b_lo, b_hi, (st == 0 && j == 0) ? 0u : 1u, lo_pass);
+              if (!stat) mma_commit(&b_empty[sb]);
+            }
+            if (!stat && ++sb == (uint32_t)p.b_stages) sb = 0, pb ^= 1;
+          }
         } else {
           uint32_t b_lo;
           if (stat) {
             b_lo = b_lo0 + (uint32_t)(st * p.kg) * B_KB16;
           } else {
-            mbar_wait_uniform(&b_full[sb], pb);
+            { const long long w0 = dbg_on ? clock64() : 0; mbar_wait_uniform(&b_full[sb], pb); if (dbg_on) dbg_wb += clock64() - w0; }
             tc_fence_after();
             b_lo = b_lo0 + sb * (B_KB16 * (uint32_t)p.kg);
           }
@@ -289,7 +322,8 @@ __device__ __forceinline__ void tc4_mma_role(const Tc4Params& p, uint32_t tmem_b
     }
   }
   if ((p.dbg & 32) && blockIdx.x == 0 && (threadIdx.x & 31) == 0)
-    printf("tc4 mma warp: %lld clk total, %u tiles, BN=%d MT=%d\n", clock64() - dbg_t0, cnt, BN, MT);
+    printf("tc4 mma warp: %lld clk total, waits: A %lld B %lld acc %lld; %u tiles, BN=%d MT=%d MODE=%d\n", clock64() - dbg_t0,
+           dbg_wa, dbg_wb, dbg_wc, cnt, BN, MT, MODE);
 }
 
 template <int BN, bool LIF>
@@ -370,6 +404,23 @@ conv_tc4_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__
       }
       for (int t = 0; t < p.T_inner; ++t) {
         const int img = p.flat ? 0 : t * p.Bsz + it.outer;
+        if (p.mode == 2) {
+          // four parity planes per channel slab; x0 / y0 = 2 * (tile origin) - 1 is the ODD start, + 1 the even one
+          for (int cb = 0; cb < p.cblocks; ++cb)
+            for (int pl = 0; pl < 4; ++pl) {
+              _Pragma("unroll") for (int m = 0; m < 2; ++m) if (m < p.mt) {
+                mbar_wait_uniform(&a_empty[s], ph ^ 1);
+                if (elect_one()) {
+                  mbar_expect_tx(&a_full[s], p.a_tx_bytes);
+                  tma_load_4d_s(smem_a_u32 + s * p.plane_bytes, &tmA, &a_full[s], cb * rowch, x0[m] + ((pl & 1) ? 0 : 1),
+                                y0[m] + ((pl & 2) ? 0 : 1), img);
+                }
+                __syncwarp();
+                if (++s == (uint32_t)p.a_stages) s = 0, ph ^= 1;
+              }
+            }
+          continue;
+        }
         const int n_tap = p.mode == 0 ? 1 : p.taps;
         int ky = 0, kx = 0;
         for (int tap = 0; tap < n_tap; ++tap) {
@@ -425,6 +476,27 @@ conv_tc4_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__
       const int n_i = halo3 ? p.taps : p.cblocks;
       for (int item = blockIdx.x; item < p.n_items; item += gridDim.x) {
         for (int t = 0; t < p.T_inner; ++t) {
+          if (p.mode == 2) {
+            // the issuer's order: per channel slab the taps of plane 0, 1, 2, 3
+            for (int cb = 0; cb < p.cblocks; ++cb)
+              for (int j = 0; j < 9; ++j) {
+                const int tap = j == 0 ? 4 : j == 1 ? 3 : j == 2 ? 5 : j == 3 ? 1 : j == 4 ? 7 : j == 5 ? 0 : j == 6 ? 2 : j == 7 ? 6 : 8;
+                mbar_wait_uniform(&b_empty[s], ph ^ 1);
+                if (elect_one()) {
+                  mbar_expect_tx(&b_full[s], p.b_kb_bytes);
+                  const uint32_t dst = smem_b_u32 + s * p.b_kb_bytes;
+                  if (pair) {
+                    tma_load_3d_s(dst, &tmB, &b_full[s], cb * 64, my_chunk * BN, tap);
+                  } else {
+                    tma_load_3d_s(dst, &tmB, &b_full[s], cb * 128, my_chunk * BN, tap);
+                    tma_load_3d_s(dst + B_TILE, &tmB, &b_full[s], cb * 128 + 64, my_chunk * BN, tap);
+                  }
+                }
+                __syncwarp();
+                if (++s == (uint32_t)p.b_stages) s = 0, ph ^= 1;
+              }
+            continue;
+          }
           for (int o = 0; o < n_o; ++o)
             for (int i = 0; i < n_i; i += p.kg) {   // (kg == 2 only outside the halo mode: i walks the channel slabs)
               const int tap = halo3 ? i : o, cb = halo3 ? o : i;
@@ -450,16 +522,18 @@ conv_tc4_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__
     }
   } else if (warp == T4_W_MMA) {
     const uint32_t sa_u32 = smem_u32(smem_a), sb_u32 = smem_u32(smem_b);
-    const bool pair = p.in_fmt == SODA_ACT_PAIR, halo3 = p.mode == 0 && p.k == 3;
-#define TC4_ROLE(MT_, PAIR_, HALO_) \
-    tc4_mma_role<BN, MT_, PAIR_, HALO_>(p, tmem_base, sa_u32, sb_u32, a_full, a_empty, b_full, b_empty, acc_full, acc_empty)
+    const bool pair = p.in_fmt == SODA_ACT_PAIR;
+    const int rmode = p.mode == 2 ? 2 : ((p.mode == 0 && p.k == 3) ? 0 : 1);
+#define TC4_ROLE(MT_, PAIR_, MODE_) \
+    tc4_mma_role<BN, MT_, PAIR_, MODE_>(p, tmem_base, sa_u32, sb_u32, a_full, a_empty, b_full, b_empty, acc_full, acc_empty)
+#define TC4_ROLE_M(MT_, PAIR_) \
+    do { if (rmode == 0) TC4_ROLE(MT_, PAIR_, 0); else if (rmode == 1) TC4_ROLE(MT_, PAIR_, 1); else TC4_ROLE(MT_, PAIR_, 2); } while (0)
     if (p.mt == 2) {
-      if (pair) { if (halo3) TC4_ROLE(2, true, true); else TC4_ROLE(2, true, false); }
-      else      { if (halo3) TC4_ROLE(2, false, true); else TC4_ROLE(2, false, false); }
+      if (pair) TC4_ROLE_M(2, true); else TC4_ROLE_M(2, false);
     } else {
-      if (pair) { if (halo3) TC4_ROLE(1, true, true); else TC4_ROLE(1, true, false); }
-      else      { if (halo3) TC4_ROLE(1, false, true); else TC4_ROLE(1, false, false); }
+      if (pair) TC4_ROLE_M(1, true); else TC4_ROLE_M(1, false);
     }
+#undef TC4_ROLE_M
 #undef TC4_ROLE
   } else if (warp < 8) {
     // ================================ epilogue ================================================
@@ -884,7 +958,12 @@ int conv_tc4_dispatch(const soda_pconv_desc_t* d, const void* x, const void* pac
   const CUtensorMapDataType adt = d->in_fmt == SODA_ACT_PAIR ? CU_TENSOR_MAP_DATA_TYPE_FLOAT32 : CU_TENSOR_MAP_DATA_TYPE_FLOAT16;
   const int64_t HW = (int64_t)d->H * d->W;
   const bool frames_dense = d->N == 1 || d->in_batch_stride == HW * d->in_pix_stride;
-  p.mode = d->stride == 1 ? 0 : 1;
+  {
+    static const int env_phase = []() { const char* e = getenv("SODA_TC4_PHASE"); return e ? atoi(e) : 1; }();
+    // stride 1: halo mode; 3x3 stride 2: parity planes (each input pixel loaded ~1.1 x instead of 2.25 x); else one tap
+    // tile per k-block
+    p.mode = d->stride == 1 ? 0 : ((d->k == 3 && d->stride == 2 && env_phase) ? 2 : 1);
+  }
   const int64_t HWo = (int64_t)p.Ho * p.Wo;
   const bool out_dense = (d->N == 1 || d->out_batch_stride == HWo * d->out_pix_stride) &&
                          (residual == nullptr || d->N == 1 || d->res_batch_stride == HWo * d->res_pix_stride);
@@ -916,6 +995,14 @@ int conv_tc4_dispatch(const soda_pconv_desc_t* d, const void* x, const void* pac
       const cuuint32_t es[4] = {1, 1, 1, 1};
       int rc = encode_map4(&tmA, adt, x, 4, dims, str, box, es);
       if (rc) return rc;
+    } else if (p.mode == 2) {
+      p.WW = T4_BW + 1;
+      p.rows = p.WW * (T4_BH + 1);          // 9 x 17 pixels of one parity plane
+      p.sbo = (uint32_t)p.WW * 128u;
+      const cuuint32_t box[4] = {(cuuint32_t)rowch, (cuuint32_t)(2 * p.WW), (cuuint32_t)(2 * (T4_BH + 1)), 1};
+      const cuuint32_t es[4] = {1, 2, 2, 1};
+      int rc = encode_map4(&tmA, adt, x, 4, dims, str, box, es);
+      if (rc) return rc;
     } else {
       const cuuint32_t box[4] = {(cuuint32_t)rowch, (cuuint32_t)(T4_BW * d->stride), (cuuint32_t)(T4_BH * d->stride), 1};
       const cuuint32_t es[4] = {1, (cuuint32_t)d->stride, (cuuint32_t)d->stride, 1};
@@ -926,7 +1013,7 @@ int conv_tc4_dispatch(const soda_pconv_desc_t* d, const void* x, const void* pac
   {
     static const int env_kg = []() { const char* e = getenv("SODA_TC4_KG"); return e ? atoi(e) : 1; }();   // measured: 2 halves the ring depth where shared memory is tight and loses 15-50 % on the streamed layers; only the fused stride-2 + LIF case gained
     const bool halo3_ = p.mode == 0 && p.k == 3;
-    p.kg = (!halo3_ && env_kg == 2 && p.cblocks % 2 == 0) ? 2 : 1;
+    p.kg = (!halo3_ && p.mode != 2 && env_kg == 2 && p.cblocks % 2 == 0) ? 2 : 1;
   }
   p.a_tile_bytes = ((uint32_t)p.rows * 128u + 1023u) & ~1023u;
   p.a_tx_bytes = (uint32_t)p.rows * 128u * (uint32_t)p.kg;
@@ -967,7 +1054,7 @@ int conv_tc4_dispatch(const soda_pconv_desc_t* d, const void* x, const void* pac
   const bool halo3 = p.mode == 0 && p.k == 3;
   const int64_t plane = p.plane_bytes;
   static const int env_min_a = []() { const char* e = getenv("SODA_TC4_MIN_A"); return e ? atoi(e) : 0; }();
-  const int min_a = env_min_a > 0 ? env_min_a : (halo3 || p.kg == 2 ? 2 : 4);
+  const int min_a = env_min_a > 0 ? env_min_a : (halo3 || p.kg == 2 ? 2 : (p.mode == 2 ? 3 : 4));
   if (b_total + min_a * plane <= T4_SMEM_LIMIT) {
     p.b_stationary = 1, p.b_stages = 1, p.mt = 1;
     p.b_region_bytes = (uint32_t)b_total;
@@ -983,7 +1070,7 @@ int conv_tc4_dispatch(const soda_pconv_desc_t* d, const void* x, const void* pac
     while (bs > 2 && (int64_t)bs * b_st + 2 * plane > T4_SMEM_LIMIT) --bs;
     int64_t a = (T4_SMEM_LIMIT - (int64_t)bs * b_st) / plane;
     if (a < 2) return fail(SODA_ERR_UNSUPPORTED, "pconv: shared-memory plan does not fit");
-    const int a_pref = halo3 ? 4 : (p.kg == 2 ? 4 : 6);
+    const int a_pref = (halo3 || p.mode == 2) ? 4 : (p.kg == 2 ? 4 : 6);
     p.a_stages = (int)std::min<int64_t>(std::min<int64_t>(a, T4_MAX_RING), a_pref);
     p.b_stages = (int)std::min<int64_t>(T4_MAX_RING, (T4_SMEM_LIMIT - (int64_t)p.a_stages * plane) / b_st);
     if (p.b_stages < 2) return fail(SODA_ERR_UNSUPPORTED, "pconv: shared-memory plan does not fit");

@@ -171,6 +171,16 @@ def _run_conv(conv: SodaConv2d, norm, Y: torch.Tensor, out: Optional[torch.Tenso
     return y
 
 
+def conv_forward(conv: SodaConv2d, norm, X: torch.Tensor, out_fmt: int = ops.FMT_F32) -> torch.Tensor:
+    """Conv (+ folded eval BatchNorm) exactly as the inference planner runs it for an input of any format - the
+    packed-activation tensor-core kernel where the layer qualifies, the event-frame im2col route, else the fp32
+    kernels - without any fusion with what follows.  (Used by the per-block parity tests.)"""
+    if _im2col_route(conv, X):
+        X = ops.im2col_frames(X, conv.stride[0])
+        conv = _ColConv(conv)
+    return _run_conv(conv, norm, X, None, out_fmt)
+
+
 def _fuse_items_ok(Cout: int, Ho: int, Wo: int, B: int, T: int) -> bool:
     """The fused kernel walks the T steps inside one work item, so it needs (channel chunks x spatial tiles x
     samples) >= about one wave of CTAs; small maps at small batch stay unfused."""

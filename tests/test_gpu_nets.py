@@ -10,6 +10,7 @@ import torch.nn.functional as F
 
 from helpers import golden, calibrated_tiny_yolo, tiny_yolo_from_golden, vgg_block_from_golden
 from oracle import net_restated as onr
+from snn_for_object_detection_b200 import generator
 
 pytestmark = pytest.mark.gpu
 DEV = "cuda"
@@ -131,7 +132,7 @@ def test_tiny_yolo_every_conv_norm_neuron_block_teacher_forced():
         if x.shape[1] != 2:
             x = x.contiguous(memory_format=torch.channels_last)
         with torch.no_grad():
-            y = conv(x, norm=norm)
+            y = generator.conv_forward(conv, norm, x)     # the planner's route: packed-activation tcgen05 kernel
             cell.forward_seq(y, T, None)
         got, v = cell.get_spikes().cpu(), cell.get_state().v.cpu()
         assert got.shape == outs.shape

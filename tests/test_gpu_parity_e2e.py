@@ -16,6 +16,7 @@ import torch.nn.functional as F
 
 from helpers import ap50, calibrated_tiny_yolo, vgg_cfg
 from oracle import net_restated as onr
+from snn_for_object_detection_b200 import generator
 
 pytestmark = pytest.mark.gpu
 DEV = "cuda"
@@ -203,7 +204,7 @@ def test_every_block_teacher_forced_at_gen1_size():
         if x.shape[1] != 2:
             x = x.contiguous(memory_format=torch.channels_last)
         with torch.no_grad():
-            y = conv(x, norm=norm)
+            y = generator.conv_forward(conv, norm, x)     # the planner's route: packed-activation tcgen05 kernel
             cell.forward_seq(y, T, None)
         got, v = cell.get_spikes().cpu(), cell.get_state().v.cpu()
         if type(cell.module).__name__ == "LIFCell":
