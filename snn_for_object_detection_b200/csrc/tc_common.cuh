@@ -188,6 +188,17 @@ __device__ __forceinline__ uint64_t smem_desc_sw128_sbo(uint32_t saddr, uint32_t
   d |= (uint64_t)2 << 61;
   return d;
 }
+// K-major swizzled descriptor with explicit 8-row-group stride and layout type (2 = SWIZZLE_128B, 4 = SWIZZLE_64B,
+// 6 = SWIZZLE_32B)
+__device__ __forceinline__ uint64_t smem_desc_swz(uint32_t saddr, uint32_t sbo_bytes, uint32_t layout) {
+  uint64_t d = 0;
+  d |= (uint64_t)((saddr & 0x3FFFFu) >> 4);
+  d |= (uint64_t)1 << 16;
+  d |= (uint64_t)(sbo_bytes >> 4) << 32;
+  d |= (uint64_t)1 << 46;
+  d |= (uint64_t)layout << 61;
+  return d;
+}
 // A operand from tensor memory
 __device__ __forceinline__ void mma_tf32_ts(uint32_t tmem_d, uint32_t tmem_a, uint64_t bdesc, uint32_t idesc,
                                             uint32_t accumulate) {
