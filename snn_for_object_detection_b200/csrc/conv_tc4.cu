@@ -83,7 +83,7 @@ struct Tc4Params {
   const uint8_t* residual;
   uint8_t* y;
   unsigned int* status;          // [0] counts values that left fp16's range when encoded (NULL = not counted)
-  int dbg;                       // SODA_TC4_DBG timing experiments (results are garbage when set): 1 = no MMAs, 2 = no stores,
+  int dbg;                       // SODA_TC4_DBG timing experiments (results are garbage when set): 2 = no stores,
                                  // 4 = no epilogue arithmetic / stores, 8 = no A loads, 16 = no (streamed) B loads
   int lif;
   NP np;
@@ -154,33 +154,36 @@ __device__ __forceinline__ void mma_f16_lo(uint32_t tmem_d, uint32_t a_lo, uint3
       : "memory");
 }
 
-// one k-block (one 128-byte A row slab x one filter tap) of one tile: 6 (PAIR) / 8 (HALF) MMAs
+// One k-block (one 128-byte A row slab x one filter tap) of one tile.  The weight k-block in shared memory is
+// [w_hi rows (BN) ; w_lo rows (BN)], so ONE MMA of N = 2*BN multiplies an A slice by both halves and lands in the main |
+// correction accumulator pair (adjacent TMEM columns): the A slice is fetched from shared memory once for two
+// products.  SS-mode MMAs are paced by operand fetch (128 B/clk of shared memory: measured 85 clk for an M128 N128 K16
+// MMA that needs 64 clk of math), so this is what the products cost:
+//   PAIR : a_hi x [w_hi ; w_lo] (N = 2BN) + a_lo x w_hi (N = BN)   2 + 2 MMAs per 32 channels (was 6)
+//   HALF : a    x [w_hi ; w_lo] (N = 2BN)                          4 MMAs per 64 channels (was 8)
 template <int BN, bool PAIR>
 __device__ __forceinline__ void tc4_issue_kblock(uint32_t d_main, uint32_t a_lo, uint32_t a_hi, uint32_t b_lo,
                                                  uint32_t b_hi, uint32_t accum, bool lo_pass) {
-  constexpr uint32_t idesc = idesc_f16(T4_BM, BN);
-  constexpr uint32_t B_TILE16 = (BN * 128) >> 4;
+#ifdef SODA_TC4_NO_MMA   // timing experiment (build with -DSODA_TC4_NO_MMA): the issue loop without tensor work
+  return;
+#endif
+  constexpr uint32_t idesc1 = idesc_f16(T4_BM, BN);
+  constexpr uint32_t idesc2 = idesc_f16(T4_BM, 2 * BN);
   const uint32_t d_corr = d_main + BN;
   if constexpr (PAIR) {
-    // A row = hi[0..15] hi[16..31] lo[0..15] lo[16..31]; B row = w_hi[0..31] | w_lo[0..31]
-    mma_f16_lo(d_main, a_lo, a_hi, b_lo, b_hi, idesc, accum);               // a_hi * w_hi
-    mma_f16_lo(d_main, a_lo + 2, a_hi, b_lo + 2, b_hi, idesc, 1);
-    mma_f16_lo(d_corr, a_lo, a_hi, b_lo + 4, b_hi, idesc, accum);           // a_hi * w_lo
-    mma_f16_lo(d_corr, a_lo + 2, a_hi, b_lo + 6, b_hi, idesc, 1);
+    // A row = hi[0..15] hi[16..31] lo[0..15] lo[16..31] (128 B); B rows of 64 B = 32 channels (SWIZZLE_64B)
+    mma_f16_lo(d_main, a_lo, a_hi, b_lo, b_hi, idesc2, accum);             // a_hi x [w_hi ; w_lo]
+    mma_f16_lo(d_main, a_lo + 2, a_hi, b_lo + 2, b_hi, idesc2, 1);
     if (lo_pass) {
-      mma_f16_lo(d_corr, a_lo + 4, a_hi, b_lo, b_hi, idesc, 1);             // a_lo * w_hi
-      mma_f16_lo(d_corr, a_lo + 6, a_hi, b_lo + 2, b_hi, idesc, 1);
+      mma_f16_lo(d_corr, a_lo + 4, a_hi, b_lo, b_hi, idesc1, 1);           // a_lo x w_hi
+      mma_f16_lo(d_corr, a_lo + 6, a_hi, b_lo + 2, b_hi, idesc1, 1);
     }
   } else {
-    // A row = a[0..63]; B tiles = w_hi[0..63], then w_lo[0..63]
-    mma_f16_lo(d_main, a_lo, a_hi, b_lo, b_hi, idesc, accum);
-    mma_f16_lo(d_main, a_lo + 2, a_hi, b_lo + 2, b_hi, idesc, 1);
-    mma_f16_lo(d_main, a_lo + 4, a_hi, b_lo + 4, b_hi, idesc, 1);
-    mma_f16_lo(d_main, a_lo + 6, a_hi, b_lo + 6, b_hi, idesc, 1);
-    mma_f16_lo(d_corr, a_lo, a_hi, b_lo + B_TILE16, b_hi, idesc, accum);
-    mma_f16_lo(d_corr, a_lo + 2, a_hi, b_lo + B_TILE16 + 2, b_hi, idesc, 1);
-    mma_f16_lo(d_corr, a_lo + 4, a_hi, b_lo + B_TILE16 + 4, b_hi, idesc, 1);
-    mma_f16_lo(d_corr, a_lo + 6, a_hi, b_lo + B_TILE16 + 6, b_hi, idesc, 1);
+    // A row = a[0..63] (128 B); B rows of 128 B = 64 channels (SWIZZLE_128B)
+    mma_f16_lo(d_main, a_lo, a_hi, b_lo, b_hi, idesc2, accum);
+    mma_f16_lo(d_main, a_lo + 2, a_hi, b_lo + 2, b_hi, idesc2, 1);
+    mma_f16_lo(d_main, a_lo + 4, a_hi, b_lo + 4, b_hi, idesc2, 1);
+    mma_f16_lo(d_main, a_lo + 6, a_hi, b_lo + 6, b_hi, idesc2, 1);
   }
 }
 
@@ -200,7 +203,9 @@ __device__ __forceinline__ void tc4_mma_role(const Tc4Params& p, uint32_t tmem_b
   // phase of a barrier it waits on - so the units of warpgroup e cycle through their own two stages {2e, 2e + 1}
   constexpr bool UNIT_SPLIT = BN == 32;
   const uint64_t a_desc0 = smem_desc_sw128_sbo(smem_a_u32, p.sbo);
-  const uint64_t b_desc0 = smem_desc_sw128(smem_b_u32);
+  // weight rows: 64 B (32 channels, SWIZZLE_64B, 8-row groups 512 B apart) for PAIR input, 128 B (64 channels,
+  // SWIZZLE_128B) for HALF input
+  const uint64_t b_desc0 = PAIR ? smem_desc_swz(smem_b_u32, 512, 4) : smem_desc_sw128(smem_b_u32);
   const uint32_t a_hi = (uint32_t)(a_desc0 >> 32), b_hi = (uint32_t)(b_desc0 >> 32);
   const uint32_t a_lo0 = (uint32_t)a_desc0, b_lo0 = (uint32_t)b_desc0;
   const bool stat = p.b_stationary != 0;
@@ -330,7 +335,6 @@ template <int BN, bool LIF>
 __global__ void __launch_bounds__(T4_THREADS, 1)
 conv_tc4_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
                 const __grid_constant__ CUtensorMap tmY, Tc4Params p) {
-  constexpr uint32_t B_TILE = BN * 128;
   constexpr uint32_t NACC = t4_nacc(BN);
   constexpr uint32_t TMEM_COLS = NACC * 2 * BN;
   constexpr bool UNIT_SPLIT = BN == 32;          // the two warps of a lane quarter alternate work units
@@ -460,12 +464,7 @@ conv_tc4_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__
         for (int cb = 0; cb < p.cblocks; ++cb) {
           const uint32_t dst = smem_b_u32 + (uint32_t)(tap * p.cblocks + cb) * p.b_kb_bytes;
           if (elect_one()) {
-            if (pair) {
-              tma_load_3d_s(dst, &tmB, &b_full[0], cb * 64, my_chunk * BN, tap);
-            } else {
-              tma_load_3d_s(dst, &tmB, &b_full[0], cb * 128, my_chunk * BN, tap);
-              tma_load_3d_s(dst + B_TILE, &tmB, &b_full[0], cb * 128 + 64, my_chunk * BN, tap);
-            }
+            tma_load_4d_s(dst, &tmB, &b_full[0], cb * (pair ? 32 : 64), my_chunk * BN, 0, tap);
           }
           __syncwarp();
         }
@@ -485,12 +484,7 @@ conv_tc4_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__
                 if (elect_one()) {
                   mbar_expect_tx(&b_full[s], p.b_kb_bytes);
                   const uint32_t dst = smem_b_u32 + s * p.b_kb_bytes;
-                  if (pair) {
-                    tma_load_3d_s(dst, &tmB, &b_full[s], cb * 64, my_chunk * BN, tap);
-                  } else {
-                    tma_load_3d_s(dst, &tmB, &b_full[s], cb * 128, my_chunk * BN, tap);
-                    tma_load_3d_s(dst + B_TILE, &tmB, &b_full[s], cb * 128 + 64, my_chunk * BN, tap);
-                  }
+                  tma_load_4d_s(dst, &tmB, &b_full[s], cb * (pair ? 32 : 64), my_chunk * BN, 0, tap);
                 }
                 __syncwarp();
                 if (++s == (uint32_t)p.b_stages) s = 0, ph ^= 1;
@@ -506,12 +500,7 @@ conv_tc4_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__
                 mbar_expect_tx(&b_full[s], p.b_kb_bytes * (uint32_t)p.kg);
                 for (int j = 0; j < p.kg; ++j) {
                   const uint32_t dst = smem_b_u32 + (s * (uint32_t)p.kg + (uint32_t)j) * p.b_kb_bytes;
-                  if (pair) {
-                    tma_load_3d_s(dst, &tmB, &b_full[s], (cb + j) * 64, my_chunk * BN, tap);
-                  } else {
-                    tma_load_3d_s(dst, &tmB, &b_full[s], (cb + j) * 128, my_chunk * BN, tap);
-                    tma_load_3d_s(dst + B_TILE, &tmB, &b_full[s], (cb + j) * 128 + 64, my_chunk * BN, tap);
-                  }
+                  tma_load_4d_s(dst, &tmB, &b_full[s], (cb + j) * (pair ? 32 : 64), my_chunk * BN, 0, tap);
                 }
               }
               __syncwarp();
@@ -777,11 +766,11 @@ int64_t conv_tc4_packed_bytes(int Cout, int Cin, int k) {
   return 4LL * k * k * tc4_cout_pad(Cout) * Cin;
 }
 
-// [Cout, Cin, k, k] * scale[co] * mult -> [tap][Cout_pad][2 * Cin] fp16:
-//   PAIR input: per 32 channels  hi[32] | lo[32]      HALF input: per 64 channels  hi[64] | lo[64]
+// [Cout, Cin, k, k] * scale[co] * mult -> fp16 planes [tap][hi | lo][Cout_pad][Cin]: one layout for both input formats
+// (a TMA box {32 or 64 channels, BN rows, 2 planes} is one weight k-block: the w_hi rows, then the w_lo rows)
 __global__ void pack_weights_tc4_kernel(const float* __restrict__ w, const float* __restrict__ scale,
                                         const float* __restrict__ mult, int Cout, int Cin, int taps, int Cout_pad,
-                                        int grp, __half* __restrict__ wp) {
+                                        __half* __restrict__ wp) {
   const int64_t n = (int64_t)taps * Cout_pad * Cin;
   const float mu = mult != nullptr ? __ldg(mult) : 1.0f;
   for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x) {
@@ -797,9 +786,9 @@ __global__ void pack_weights_tc4_kernel(const float* __restrict__ w, const float
     }
     const __half hi = __float2half_rn(v);
     const __half lo = __float2half_rn(v - __half2float(hi));
-    const int64_t base = r * (2 * Cin) + (int64_t)(ci / grp) * (2 * grp) + (ci % grp);
+    const int64_t base = ((int64_t)(tap * 2) * Cout_pad + co) * Cin + ci;
     wp[base] = hi;
-    wp[base + grp] = lo;
+    wp[base + (int64_t)Cout_pad * Cin] = lo;
   }
 }
 
@@ -811,7 +800,7 @@ int conv_tc4_pack(const float* w, const float* scale, const float* mult, int Cou
   if (Cin % grp != 0) return fail(SODA_ERR_UNSUPPORTED, "pconv_pack: Cin must be a multiple of 32 (PAIR) / 64 (HALF)");
   const int64_t n = (int64_t)k * k * tc4_cout_pad(Cout) * Cin;
   pack_weights_tc4_kernel<<<(unsigned)std::min<int64_t>(ceil_div(n, 256), 4096), 256, 0, st>>>(
-      w, scale, mult, Cout, Cin, k * k, tc4_cout_pad(Cout), grp, reinterpret_cast<__half*>(packed));
+      w, scale, mult, Cout, Cin, k * k, tc4_cout_pad(Cout), reinterpret_cast<__half*>(packed));
   return after_launch("pack_weights_tc4_kernel");
 }
 
@@ -1019,11 +1008,13 @@ int conv_tc4_dispatch(const soda_pconv_desc_t* d, const void* x, const void* pac
   p.a_tx_bytes = (uint32_t)p.rows * 128u * (uint32_t)p.kg;
   p.plane_bytes = p.a_tile_bytes * (uint32_t)p.kg;
   {
-    const cuuint64_t dims[3] = {(cuuint64_t)(2 * d->Cin), (cuuint64_t)Cout_pad, (cuuint64_t)p.taps};
-    const cuuint64_t str[2] = {(cuuint64_t)d->Cin * 4, (cuuint64_t)Cout_pad * d->Cin * 4};
-    const cuuint32_t box[3] = {64, (cuuint32_t)BN, 1};
-    const cuuint32_t es[3] = {1, 1, 1};
-    int rc = encode_map4(&tmB, CU_TENSOR_MAP_DATA_TYPE_FLOAT16, packed, 3, dims, str, box, es);
+    // packed weights [tap][hi | lo][Cout_pad][Cin]: one k-block = box {32 | 64 channels, BN rows, both planes}
+    const cuuint64_t dims[4] = {(cuuint64_t)d->Cin, (cuuint64_t)Cout_pad, 2, (cuuint64_t)p.taps};
+    const cuuint64_t str[3] = {(cuuint64_t)d->Cin * 2, (cuuint64_t)Cout_pad * d->Cin * 2, (cuuint64_t)Cout_pad * d->Cin * 4};
+    const cuuint32_t box[4] = {(cuuint32_t)rowch, (cuuint32_t)BN, 2, 1};
+    const cuuint32_t es[4] = {1, 1, 1, 1};
+    int rc = encode_map4(&tmB, CU_TENSOR_MAP_DATA_TYPE_FLOAT16, packed, 4, dims, str, box, es,
+                         d->in_fmt == SODA_ACT_PAIR ? CU_TENSOR_MAP_SWIZZLE_64B : CU_TENSOR_MAP_SWIZZLE_128B);
     if (rc) return rc;
   }
   CUtensorMap tmY;
