@@ -121,8 +121,12 @@ def batchnorm_train(norm, x, T: int = 1):
     B = x.shape[0] // T
     outs = []
     for t in range(T):
-        if norm.momentum is not None and norm.num_batches_tracked is not None:
+        # nn.BatchNorm2d.forward: the counter always advances; momentum=None means the cumulative average 1 / n
+        mom = norm.momentum
+        if norm.running_mean is not None and norm.num_batches_tracked is not None:
             norm.num_batches_tracked.add_(1)
+            if mom is None:
+                mom = 1.0 / float(norm.num_batches_tracked)
         outs.append(F.batch_norm(x[t * B : (t + 1) * B], norm.running_mean, norm.running_var, norm.weight, norm.bias,
-                                 True, 0.0 if norm.momentum is None else norm.momentum, norm.eps))
+                                 True, 0.0 if mom is None else mom, norm.eps))
     return outs[0] if T == 1 else torch.cat(outs)

@@ -811,15 +811,13 @@ static int encode_map3(CUtensorMap* m, const void* base, int rank, const cuuint6
 template <int BN, bool LIF, bool SPK>
 static int launch_tc3_(const CUtensorMap& tmA, const CUtensorMap& tmB, const Tc3Params& p, int grid, size_t smem,
                       cudaStream_t st) {
-  static bool attr_set = false;
-  if (!attr_set) {
+  {   // the opt-in is per device: set on every launch (cheap), not once per process
     cudaError_t e = cudaFuncSetAttribute(conv_tc3_kernel<BN, LIF, SPK>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                          232448);
     if (e != cudaSuccess) {
       set_error("conv_tc: cudaFuncSetAttribute: %s", cudaGetErrorString(e));
       return (int)SODA_ERR_CUDA;
     }
-    attr_set = true;
   }
   static const bool pdl = []() { const char* e = getenv("SODA_PDL"); return !(e && atoi(e) == 0); }();
   if (pdl) {

@@ -254,14 +254,12 @@ extern "C" int soda_multibox_detection(const float* cls_probs, const float* offs
   p.n_pad = 1024;
   while (p.n_pad < A) p.n_pad <<= 1;
   const size_t smem = p.n_pad > DET_SMEM_N ? 16 : (size_t)p.n_pad * 9 + (size_t)((A + 15) / 16 * 16);
-  static bool attr_set = false;
-  if (!attr_set) {
+  {   // the opt-in is per device: set on every launch (cheap), not once per process
     cudaError_t e = cudaFuncSetAttribute(multibox_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024);
     if (e != cudaSuccess) {
       set_error("multibox: cudaFuncSetAttribute: %s", cudaGetErrorString(e));
       return (int)SODA_ERR_CUDA;
     }
-    attr_set = true;
   }
   multibox_kernel<<<B, DET_THREADS, smem, (cudaStream_t)stream>>>(p, cls_probs, offsets, anchors,
                                                                    reinterpret_cast<uint8_t*>(workspace), out);

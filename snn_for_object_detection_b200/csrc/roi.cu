@@ -220,14 +220,12 @@ extern "C" int soda_roi_assign(const float* anchors, const float* labels, int B,
       (reinterpret_cast<uintptr_t>(bbox_mask) & 15))
     return fail(SODA_ERR_BAD_ARG, "roi_assign: anchors and outputs must be 16-byte aligned");
   if (B == 0) return 0;
-  static bool attr_set = false;
-  if (!attr_set) {
+  {   // the opt-in is per device: set on every launch (cheap), not once per process
     cudaError_t e = cudaFuncSetAttribute(roi_assign_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 160 * 1024);
     if (e != cudaSuccess) {
       set_error("roi_assign: cudaFuncSetAttribute: %s", cudaGetErrorString(e));
       return (int)SODA_ERR_CUDA;
     }
-    attr_set = true;
   }
   roi_assign_kernel<<<B, ROI_THREADS, smem, (cudaStream_t)stream>>>(
       reinterpret_cast<const float4*>(anchors), labels, A, G, iou_threshold, reinterpret_cast<float4*>(bbox_offset),

@@ -158,7 +158,9 @@ class STSampleStream:
         self.device = torch.device(device)
         self.alive = [True] * len(self.readers)
         self._stage = [None, None]   # two pinned staging buffers, used alternately
+        self._stage_done = [None, None]   # CUDA event recorded after the H2D copy that last read each buffer
         self._flip = 0
+        self._next_k = 0             # round-robin cursor over the recordings (kept across next_batch calls)
 
     def next_window(self, k: int):
         rd, steps = self.readers[k], self.label_steps[k]
@@ -180,14 +182,30 @@ class STSampleStream:
         return (rec, first_event_time_us, label_step), True
 
     def _pinned(self, n_rec: int) -> torch.Tensor:
-        buf = self._stage[self._flip]
+        """The next staging buffer.  Its previous H2D copy is asynchronous (pinned memory, ``non_blocking``): the host
+        may run several batches ahead of a GPU-bound consumer, so the buffer is only rewritten after the event
+        recorded behind that copy has completed."""
+        k = self._flip
+        ev = self._stage_done[k]
+        if ev is not None:
+            ev.synchronize()
+            self._stage_done[k] = None
+        buf = self._stage[k]
         if buf is None or buf.shape[0] < n_rec:
             buf = torch.empty((max(n_rec, 1) * 5 // 4 + 1, 2), dtype=torch.int32)
             if torch.cuda.is_available():
                 buf = buf.pin_memory()
-            self._stage[self._flip] = buf
+            self._stage[k] = buf
+        self._last = k
         self._flip ^= 1
         return buf
+
+    def _staged(self) -> None:
+        """Call right after the copy out of the buffer handed out last has been enqueued."""
+        if torch.cuda.is_available() and self.device.type == "cuda":
+            ev = torch.cuda.Event()
+            ev.record(torch.cuda.current_stream(self.device))
+            self._stage_done[self._last] = ev
 
     def next_batch(self, batch_size: int):
         """Up to ``batch_size`` accepted windows, visiting the live recordings round-robin (the reference's
@@ -217,6 +235,7 @@ class STSampleStream:
         frames = events_to_frames(buf[: max(int(offs[-1]), 1)], torch.from_numpy(offs), [p[2] for p in picked],
                                   self.step_us, self.num_steps, self.height, self.width, clip_x=True,
                                   device=self.device)
+        self._staged()
         return frames, [p[3] for p in picked], [p[0] for p in picked]
 
 
@@ -241,11 +260,11 @@ class MTSampleStream(STSampleStream):
         """One window from each recording in turn until ``batch_size`` samples: ``(X[T, B, 2, H, W], start_steps,
         recording indices)``."""
         picked = []
-        k = 0
         while len(picked) < batch_size and self.readers:
-            win, _ = self.next_window(k % len(self.readers))
-            picked.append((k % len(self.readers),) + win)
-            k += 1
+            k = self._next_k % len(self.readers)     # the cursor survives the call: every recording gets its turn
+            win, _ = self.next_window(k)             # (datasets.py:305-309 visits every loaded file)
+            picked.append((k,) + win)
+            self._next_k += 1
         counts = [int(p[1].shape[0]) for p in picked]
         offs = np.zeros(len(picked) + 1, dtype=np.int64)
         np.cumsum(counts, out=offs[1:])
@@ -256,4 +275,5 @@ class MTSampleStream(STSampleStream):
         frames = events_to_frames(buf[: max(int(offs[-1]), 1)], torch.from_numpy(offs), [p[2] for p in picked],
                                   self.step_us, self.num_steps, self.height, self.width, clip_x=False,
                                   device=self.device)
+        self._staged()
         return frames, [p[3] for p in picked], [p[0] for p in picked]

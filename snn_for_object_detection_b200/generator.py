@@ -883,8 +883,10 @@ class HeadGen(ModelGen):
         B = Y.shape[0] // T
         outs = []
         for k, net in ((1, self.box_net), (2, self.cls_net)):
-            if T > 1 and not _has_state(net):
-                # stateless prediction nets: only the last step is observable
+            trains_bn = self.training and any(isinstance(m, nn.modules.batchnorm._BatchNorm) for m in net.modules())
+            if T > 1 and not _has_state(net) and not trains_bn:
+                # stateless prediction nets: only the last step is observable (a train-mode BatchNorm inside would
+                # have to see all T steps to update its running statistics as the reference does)
                 o, state[k] = net.forward_seq(Y[(T - 1) * B :], 1, state[k])
             else:
                 o, state[k] = net.forward_seq(Y, T, state[k])

@@ -1,7 +1,8 @@
 """Box decode + greedy per-class NMS (role of the reference's ``utils/box.py:72-153``).
 
-Host-side torch restatement used by ``SODa.predict``; SURVEY.md 8(f)-1 marks the GPU kernel
-version as the next row after the spiking forward.
+Torch restatement of the same algorithm.  ``SODa.predict`` runs the CUDA kernel
+(``ops.multibox_detection`` -> ``soda_multibox_detection``, csrc/detect.cu); this module is
+its cross-check in the tests and the route for anchor sets beyond the kernel's limit (262 143).
 """
 
 from __future__ import annotations

@@ -845,6 +845,64 @@ def test_mt_sample_stream_consecutive_windows_match_reference_golden():
 
 
 @pytest.mark.gpu
+def test_mt_sample_stream_visits_every_recording_and_reuses_staging_buffers_safely():
+    """More recordings than the batch size: the round-robin cursor survives the call (the reference's MT
+    samples_generator visits every loaded file, datasets.py:305-309); and many batches in flight without a host
+    sync (the pinned staging buffers are only rewritten after the copy that read them has finished) all come out
+    equal to the oracle's binning."""
+    from snn_for_object_detection_b200.events import MTSampleStream
+
+    T, H, W, step_us = 3, 16, 24, 16000
+    rng = np.random.default_rng(9)
+    recs = [ob.make_records(rng, 6000, 0, 4 * T * step_us, H, W) for _ in range(3)]
+    st = MTSampleStream([ob.dat_bytes(r, H, W) for r in recs], num_steps=T, time_step_ms=step_us // 1000, height=H, width=W)
+    seen, outs = [], []
+    for _ in range(6):                      # 12 windows, no synchronisation in between
+        X, starts, files = st.next_batch(2)
+        seen += files
+        outs.append((X, starts, files))
+    assert seen == [0, 1, 2, 0, 1, 2, 0, 1, 2, 0, 1, 2]
+    for X, starts, files in outs:
+        for b, (s0, k) in enumerate(zip(starts, files)):
+            rec = recs[k]
+            lo, hi = np.searchsorted(rec[:, 0], [s0 * step_us, (s0 + T) * step_us])
+            ref = ob.bin_batch([rec[lo:hi]], [s0 * step_us], step_us, T, H, W, clip_x=False)
+            assert np.array_equal(X[:, b].cpu().numpy(), ref[:, 0])
+
+
+@pytest.mark.gpu
+def test_folded_batchnorm_cache_follows_the_running_statistics():
+    """eval forward, then a train-mode forward with frozen weights (running statistics move through the CUDA kernel's
+    raw pointers), then an eval forward: the cached Conv+BN fold must be rebuilt (round-1 advice)."""
+    pkg = _pkg()
+    from snn_for_object_detection_b200 import BlockGen
+    from snn_for_object_detection_b200.modules import LIF, Conv, Norm
+
+    torch.manual_seed(2)
+    block = BlockGen(2, [Conv(32, 3), Norm(), LIF()]).to(DEV)
+    block.net[0][1].weight.data.fill_(6.0)       # with the reference's raw initialisation the layer is silent
+    block.net[0][1].running_mean.fill_(-0.3)
+    X = (torch.rand(8, 2, 16, 24, device=DEV) < 0.3).float()
+    block.eval()
+    with torch.no_grad():
+        y0, _ = block.forward_seq(X, 4)
+    block.train()
+    for p in block.parameters():
+        p.requires_grad_(False)
+    with torch.no_grad():
+        block.forward_seq(X * 3.0, 4)        # moves running_mean / running_var only
+    block.eval()
+    with torch.no_grad():
+        y1, _ = block.forward_seq(X, 4)
+    conv, norm = block.net[0][0], block.net[0][1]
+    conv._pack_cache.clear()
+    with torch.no_grad():
+        y2, _ = block.forward_seq(X, 4)      # fresh pack: the truth for the current statistics
+    assert torch.equal(y1, y2)
+    assert float(norm.running_var.mean()) != 1.0 and 0.01 < float(y0.mean()) < 0.9 and not torch.equal(y0, y1)
+
+
+@pytest.mark.gpu
 def test_sync_batchnorm_sums_exchange_equals_full_batch():
     """SyncBatchNorm route (config.yaml:76) on one GPU: the batch is split between two emulated ranks, their
     [T, 2, C] sums are added (what the all-reduce does) and each rank normalises its own frames with the global sums:
