@@ -384,6 +384,20 @@ SODA_API int soda_multibox_detection(const float* cls_probs, const float* offset
                             int C, float nms_threshold, float pos_threshold, void* workspace, float* out,
                             void* stream);
 
+/* soda_multibox_detection without a caller workspace, for callers that cannot allocate device memory (code under CUDA
+ * graph capture, tight serving loops, harnesses that forbid cudaMalloc).  NO COUNTERPART IN THE REFERENCE.
+ * The scratch is a file-scope device array of SODA_MULTIBOX_STATIC_WS_BYTES (8 MiB)
+ * that every GPU loading the library holds until exit; the call allocates nothing (no cudaMalloc / cudaFree).
+ *   Same arguments, rows and limits as soda_multibox_detection, and additionally
+ *   soda_multibox_workspace_bytes(B, A) <= soda_multibox_static_max_bytes()  (GEN1, 13 545 anchors: B <= 14),
+ *   else SODA_ERR_UNSUPPORTED with the needed and available byte counts in soda_last_error().
+ *   All calls share the one array: calls that overlap on the GPU (two streams, two threads) race - serialise them.
+ *   Nothing in the array has to start at zero; it keeps the last call's contents. */
+#define SODA_MULTIBOX_STATIC_WS_BYTES (8 << 20)
+SODA_API int64_t soda_multibox_static_max_bytes(void);
+SODA_API int soda_multibox_detection_static(const float* cls_probs, const float* offsets, const float* anchors, int B,
+                            int A, int C, float nms_threshold, float pos_threshold, float* out, void* stream);
+
 /* ---------------------------------------------------------------------------------------------
  * Anchor labelling for the detection loss (the step right after the forward in training)
  *   replaces: utils/roi.py:18-63 RoI.__call__ with _assign_anchor_to_box :65-109, utils/box.py:24-57 box_iou and

@@ -126,6 +126,8 @@ SIGNATURES = {
     "soda_add_n": (_i, [C.POINTER(_vp), _i, _i64, _vp, _vp]),
     "soda_multibox_workspace_bytes": (_i64, [_i, _i]),
     "soda_multibox_detection": (_i, [_vp, _vp, _vp, _i, _i, _i, _f, _f, _vp, _vp, _vp]),
+    "soda_multibox_static_max_bytes": (_i64, []),
+    "soda_multibox_detection_static": (_i, [_vp, _vp, _vp, _i, _i, _i, _f, _f, _vp, _vp]),
     "soda_sli_fwd": (_i, [C.POINTER(NeuronParams), _vp, _vp, _vp, _i, _i64, _vp, _vp, _vp, _vp, _vp]),
     "soda_synapse_fwd": (_i, [_f, _f, _f, _f, _vp, _vp, _i, _i64, _vp, _vp, _vp]),
     "soda_lstm_gates": (_i, [_vp, _vp, _i64, _i, _vp, _vp, _vp]),

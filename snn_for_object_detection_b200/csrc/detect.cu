@@ -15,6 +15,8 @@
 // greedy suppression with the whole CTA computing IoUs against each kept box -> two block scans for the row order.
 // Integer/compare-bound, a few hundred microseconds per sample at GEN1 size (13 545 anchors: keys in shared memory);
 // larger sets (1Mpx: 170 280) keep the keys in the L2-resident workspace; anchors <= 262 143.
+#include <mutex>
+
 #include "common.cuh"
 
 namespace soda {
@@ -264,4 +266,61 @@ extern "C" int soda_multibox_detection(const float* cls_probs, const float* offs
   multibox_kernel<<<B, DET_THREADS, smem, (cudaStream_t)stream>>>(p, cls_probs, offsets, anchors,
                                                                    reinterpret_cast<uint8_t*>(workspace), out);
   return after_launch("multibox_kernel");
+}
+
+// ---- soda_multibox_detection_static: the same kernel with its scratch in a file-scope device array ------------------
+// For callers that cannot allocate (CUDA graph capture, serving loops, harnesses that forbid cudaMalloc).  No counterpart
+// in the reference.  8 MiB per GPU that loads the library, held until exit: 14 samples at GEN1 size (13 545 anchors,
+// 587 296 bytes each).  Every call shares the array: two calls that overlap on the GPU (different streams) race.
+// Nothing in it has to start at zero - the kernel writes conf / cls / box / sbox (and keys / alive / kept for large
+// anchor sets) before it reads them - so no clearing between calls.
+namespace soda {
+constexpr int64_t DET_STATIC_WS_BYTES = SODA_MULTIBOX_STATIC_WS_BYTES;
+static __device__ __align__(256) uint8_t det_static_ws[DET_STATIC_WS_BYTES];
+
+constexpr int DET_MAX_DEVICES = 64;
+static uint8_t* det_static_ptr[DET_MAX_DEVICES];   // device address of det_static_ws on each device, looked up once
+static std::mutex det_static_mu;
+
+// The array's NAME in host code is a host-side stand-in, not a device address: ask the runtime, with the device current.
+static int det_static_address(uint8_t** out) {
+  int dev = -1;
+  cudaError_t e = cudaGetDevice(&dev);
+  if (e != cudaSuccess || dev < 0 || dev >= DET_MAX_DEVICES) {
+    set_error("multibox_static: cudaGetDevice: %s (device %d)", cudaGetErrorString(e), dev);
+    return (int)SODA_ERR_CUDA;
+  }
+  std::lock_guard<std::mutex> g(det_static_mu);
+  if (det_static_ptr[dev] == nullptr) {
+    void* ptr = nullptr;
+    e = cudaGetSymbolAddress(&ptr, det_static_ws);
+    if (e != cudaSuccess || ptr == nullptr) {
+      set_error("multibox_static: cudaGetSymbolAddress: %s", cudaGetErrorString(e));
+      return (int)SODA_ERR_CUDA;
+    }
+    det_static_ptr[dev] = reinterpret_cast<uint8_t*>(ptr);
+  }
+  *out = det_static_ptr[dev];
+  return 0;
+}
+}  // namespace soda
+
+extern "C" int64_t soda_multibox_static_max_bytes(void) { return soda::DET_STATIC_WS_BYTES; }
+
+extern "C" int soda_multibox_detection_static(const float* cls_probs, const float* offsets, const float* anchors, int B,
+                                              int A, int C, float nms_threshold, float pos_threshold, float* out,
+                                              void* stream) {
+  using namespace soda;
+  if (B <= 0 || A <= 0) return fail(SODA_ERR_BAD_ARG, "multibox_static: non-positive size");
+  const int64_t need = soda_multibox_workspace_bytes(B, A);
+  if (need > DET_STATIC_WS_BYTES) {
+    set_error("multibox_static: B = %d samples of A = %d anchors need %lld scratch bytes, the built-in array holds %lld; "
+              "split the batch or use soda_multibox_detection with a caller workspace",
+              B, A, (long long)need, (long long)DET_STATIC_WS_BYTES);
+    return (int)SODA_ERR_UNSUPPORTED;
+  }
+  uint8_t* ws = nullptr;
+  const int rc = det_static_address(&ws);
+  if (rc != 0) return rc;
+  return soda_multibox_detection(cls_probs, offsets, anchors, B, A, C, nms_threshold, pos_threshold, ws, out, stream);
 }
