@@ -14,8 +14,10 @@
 //     SODA_ACT_HALF : fp16, for values that are exact in it (spikes {0,1}, spike counts <= 2048): 2 bytes per value
 //   so TMA's bytes ARE the MMA operands: no split warps, no second shared-memory plane, no tf32 stream.
 // * Products, all kind::f16 with fp32 accumulation in TMEM:
-//     PAIR : a_hi*w_hi + a_hi*w_lo + a_lo*w_hi      (6 MMAs per 32 channels and tap; a_lo*w_lo ~ 2^-22 is dropped)
-//     HALF : a*w_hi + a*w_lo                         (8 MMAs per 64 channels and tap)
+//     PAIR : a_hi*[w_hi | w_lo] + a_lo*w_hi         (4 MMAs per 32 channels and tap: the weight k-block is N-stacked,
+//                                                    hi rows then lo rows, so one N = 2*BN MMA feeds the adjacent main |
+//                                                    correction accumulators; a_lo*w_lo ~ 2^-22 is dropped)
+//     HALF : a*[w_hi | w_lo]                         (4 MMAs per 64 channels and tap)
 //   Weights are split the same way (fp16 hi | fp16 lo) after multiplication by the folded BatchNorm scale and by a
 //   per-tensor power of two that puts them in fp16's normal range; the epilogue multiplies by its inverse (exact).
 // * One weight k-block is BN x 128 B per 32 channels (was 2 x BN x 128 B): twice as many layers keep their weights
