@@ -548,7 +548,7 @@ conv_tc4_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__
     Tc4Iter it;
     it.init(p);
     for (int item = blockIdx.x; item < p.n_items; item += gridDim.x, it.next(p)) {
-      for (int m = 0; m < p.mt; ++m) {   // (mt == 2 only without LIF: T_inner == 1)
+      for (int m = 0; m < p.mt; ++m) {   // (mt == 2 with LIF only at BN = 32, where tile m belongs to warpgroup m)
         const bool mine = !UNIT_SPLIT || ((unit & 1u) == (uint32_t)e);
         ++unit;
         if (!mine) {
@@ -1048,15 +1048,30 @@ int conv_tc4_dispatch(const soda_pconv_desc_t* d, const void* x, const void* pac
   const int64_t plane = p.plane_bytes;
   static const int env_min_a = []() { const char* e = getenv("SODA_TC4_MIN_A"); return e ? atoi(e) : 0; }();
   const int min_a = env_min_a > 0 ? env_min_a : (halo3 || p.kg == 2 ? 2 : (p.mode == 2 ? 3 : 4));
+  static const int env_mt = []() { const char* e = getenv("SODA_TC4_MT"); return e ? atoi(e) : 0; }();
   if (b_total + min_a * plane <= T4_SMEM_LIMIT) {
     p.b_stationary = 1, p.b_stages = 1, p.mt = 1;
     p.b_region_bytes = (uint32_t)b_total;
     p.a_stages = (int)std::min<int64_t>(T4_MAX_RING, (T4_SMEM_LIMIT - b_total) / plane);
+    // LIF at BN = 32: a unit (tile x all T steps) belongs to ONE epilogue warpgroup, which walks its T steps serially
+    // (the membrane lives in its registers).  Two tiles per item, issued step-interleaved into the two warpgroups' own
+    // accumulator stages, keep both warpgroups busy; with one tile per item they took turns, one always idle.
+    if (is_lif && BN == 32 && p.n_spatial > 1 && env_mt != 1 && env_mt != 3 && p.a_stages >= 4) p.mt = 2;
   } else {
     // streamed weights: an item takes TWO M-tiles that share each weight k-block (two accumulators of the four)
     p.b_stationary = 0;
-    static const int env_mt = []() { const char* e = getenv("SODA_TC4_MT"); return e ? atoi(e) : 0; }();
-    const bool want_pair = !is_lif && p.n_spatial > 1 && env_mt != 1;
+    // Measured per layer (bench.py --per-layer, SODA_TC4_MT=2 against 4): sharing the k-blocks pays only on the
+    // stride-2 3x3 layers (~7 % per tile) and only when pairing does not cost more in wave quantisation / an odd tile
+    // count than that (256 -> 256 on 15 x 19 output: 3 tiles per frame, a quarter of the paired slots empty); 3x3
+    // stride-1 and 1x1 layers run 4 .. 30 % faster unpaired.  (SODA_TC4_MT: 1 never, 2 LIF only, 3 streamed only by
+    // this rule, 4 every streamed layer.)
+    bool want_pair = false;
+    if (!is_lif && p.n_spatial > 1 && env_mt != 1 && env_mt != 2) {
+      const int64_t slots = std::max(1, kNumSMs / p.nch);
+      const int64_t per_chunk_1 = (int64_t)p.n_spatial * p.n_outer, per_chunk_2 = (int64_t)((p.n_spatial + 1) / 2) * p.n_outer;
+      const int64_t rounds_1 = (per_chunk_1 + slots - 1) / slots, rounds_2 = 2 * ((per_chunk_2 + slots - 1) / slots);
+      want_pair = env_mt == 4 || (p.mode == 2 && rounds_2 * 93 < rounds_1 * 100);
+    }
     p.mt = want_pair ? 2 : 1;
     const int64_t b_st = (int64_t)b_kb * p.kg;   // one B ring stage
     int bs = 4;
