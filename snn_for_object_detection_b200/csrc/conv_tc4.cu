@@ -49,6 +49,11 @@ constexpr int T4_BH = 16, T4_BW = 8;
 constexpr int T4_THREADS = 384;             // 12 warps: three whole warpgroups, as setmaxnreg wants
 constexpr int T4_W_PROD_A = 8, T4_W_PROD_B = 9, T4_W_MMA = 10;
 constexpr int T4_MAX_RING = 8;
+#ifdef SODA_TC4_EPI_DBG
+constexpr bool T4_EPI_DBG = true;
+#else
+constexpr bool T4_EPI_DBG = false;
+#endif
 // accumulator stages in TMEM; a stage = main accumulator (hi * hi products) | correction accumulator (hi * lo, lo * hi):
 // the tensor core truncates on every accumulate, an error proportional to the accumulator's magnitude and to the number
 // of MMAs into it - the 2^-11-small corrections, two thirds of the MMAs, must not pay it at the main sum's magnitude
@@ -539,12 +544,18 @@ conv_tc4_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__
     const int row = q * 32 + lane;
     const int64_t hw = (int64_t)p.Ho * p.Wo;
     const float descale = __ldg(p.descale);
+    const f32x2_t descale2 = pk2(descale, descale);
+    [[maybe_unused]] const NP2 np2 = np_pairs(p.np);
     const bool half_out = p.out_fmt == SODA_ACT_HALF;
     // byte address of 16-byte chunk j of this lane's row inside the staging tile (TMA SWIZZLE_128B / SWIZZLE_64B)
     const uint32_t st_row = stage_u32 + (uint32_t)lane * (half_out ? 64u : 128u);
     const uint32_t st_xor = half_out ? (((uint32_t)lane >> 1) & 3u) : ((uint32_t)lane & 7u);
     unsigned int n_over = 0;
     uint32_t local = 0, unit = 0, mine_cnt = 0;
+    const bool edbg = T4_EPI_DBG && (p.dbg & 32) != 0;   // (make CFLAGS=-DSODA_TC4_EPI_DBG: per-warp clock64 counters)
+    const long long e_t0 = clock64();
+    long long e_wacc = 0, e_wst = 0, e_ld = 0;
+    uint32_t e_steps = 0;
     Tc4Iter it;
     it.init(p);
     for (int item = blockIdx.x; item < p.n_items; item += gridDim.x, it.next(p)) {
@@ -577,7 +588,7 @@ conv_tc4_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__
         }
         const int col_base = UNIT_SPLIT ? 0 : e * (BN / 2);
         const int co_base = my_chunk * BN + col_base;
-        float sv[LIF ? 32 : 1], si[LIF ? 32 : 1];
+        f32x2_t sv[LIF ? 16 : 1], si[LIF ? 16 : 1];   // membrane / current of this lane's 32 neurons, two per register pair
         if constexpr (LIF) {
           const int64_t soff = ((int64_t)it.outer * hw + rr) * p.Cout + co_base;
 #pragma unroll
@@ -588,8 +599,8 @@ conv_tc4_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__
               a = __ldg(reinterpret_cast<const float4*>(p.v0 + soff + c));
               b = __ldg(reinterpret_cast<const float4*>(p.i0 + soff + c));
             }
-            sv[c] = a.x, sv[c + 1] = a.y, sv[c + 2] = a.z, sv[c + 3] = a.w;
-            si[c] = b.x, si[c + 1] = b.y, si[c + 2] = b.z, si[c + 3] = b.w;
+            sv[c / 2] = pk2(a.x, a.y), sv[c / 2 + 1] = pk2(a.z, a.w);
+            si[c / 2] = pk2(b.x, b.y), si[c / 2 + 1] = pk2(b.z, b.w);
           }
         }
         for (int t = 0; t < p.T_inner; ++t, ++local, ++mine_cnt) {
@@ -608,7 +619,7 @@ conv_tc4_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__
             for (int j = 0; j < 8; ++j)
               if (j < 4 || p.res_fmt != SODA_ACT_HALF) rp[j] = ldg_u4(rp0 + j * 16);
           }
-          mbar_wait(&acc_full[acc], acc_ph);
+          { const long long w0 = edbg ? clock64() : 0; mbar_wait(&acc_full[acc], acc_ph); if (edbg) e_wacc += clock64() - w0, ++e_steps; }
           tc_fence_after();
           const uint32_t t_row = tmem_base + ((uint32_t)(q * 32) << 16) + acc * (2 * BN) + (uint32_t)col_base;
 #pragma unroll
@@ -619,9 +630,11 @@ conv_tc4_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__
 #pragma unroll
             for (int h = 0; h < 2; ++h) {   // 16 columns of main + correction at a time: 32 transient registers
               uint32_t r[16], rc[16];
+              const long long l0 = edbg ? clock64() : 0;
               tmem_ld_32x16(t_row + g * 32 + h * 16, r);
               tmem_ld_32x16(t_row + BN + g * 32 + h * 16, rc);
               tmem_ld_wait();
+              if (edbg) e_ld += clock64() - l0;
               if (g == NG - 1 && h == 1) {
                 // last TMEM read of this tile: hand the accumulator back before the rest
                 tc_fence_before();
@@ -631,11 +644,14 @@ conv_tc4_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__
               if (p.shift != nullptr && group_live) {
 #pragma unroll
                 for (int j = 0; j < 16; j += 4) {
+                  // fma(main + correction, descale, shift), two columns per FADD2 / FFMA2
                   const float4 sh = __ldg(reinterpret_cast<const float4*>(p.shift + co0 + h * 16 + j));
-                  o[h * 16 + j] = fmaf(__uint_as_float(r[j]) + __uint_as_float(rc[j]), descale, sh.x);
-                  o[h * 16 + j + 1] = fmaf(__uint_as_float(r[j + 1]) + __uint_as_float(rc[j + 1]), descale, sh.y);
-                  o[h * 16 + j + 2] = fmaf(__uint_as_float(r[j + 2]) + __uint_as_float(rc[j + 2]), descale, sh.z);
-                  o[h * 16 + j + 3] = fmaf(__uint_as_float(r[j + 3]) + __uint_as_float(rc[j + 3]), descale, sh.w);
+                  const f32x2_t s0 = add2(pk2(__uint_as_float(r[j]), __uint_as_float(r[j + 1])),
+                                          pk2(__uint_as_float(rc[j]), __uint_as_float(rc[j + 1])));
+                  const f32x2_t s1 = add2(pk2(__uint_as_float(r[j + 2]), __uint_as_float(r[j + 3])),
+                                          pk2(__uint_as_float(rc[j + 2]), __uint_as_float(rc[j + 3])));
+                  upk2(fma2(s0, descale2, pk2(sh.x, sh.y)), o[h * 16 + j], o[h * 16 + j + 1]);
+                  upk2(fma2(s1, descale2, pk2(sh.z, sh.w)), o[h * 16 + j + 2], o[h * 16 + j + 3]);
                 }
               } else {
 #pragma unroll
@@ -645,11 +661,8 @@ conv_tc4_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__
             if (p.dbg & 4) continue;
             if constexpr (LIF) {
 #pragma unroll
-              for (int j = 0; j < 32; ++j) {
-                float z, vd;
-                lif_step(p.np, o[j], sv[j], si[j], z, vd);
-                o[j] = z;
-              }
+              for (int j = 0; j < 16; ++j)
+                lif_step2(np2, pk2(o[2 * j], o[2 * j + 1]), sv[j], si[j], o[2 * j], o[2 * j + 1]);
             }
             if (has_res && group_live) {
               if (g > 0) {
@@ -708,8 +721,10 @@ conv_tc4_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__
               n_over += amax > 65504.f;
             }
             // ---- stage (swizzled) and let TMA store it ----
-            if (lane == 0) bulk_wait_read0();   // this warp's previous store has read the staging tile
-            __syncwarp();
+            { const long long w0 = edbg ? clock64() : 0;
+              if (lane == 0) bulk_wait_read0();   // this warp's previous store has read the staging tile
+              __syncwarp();
+              if (edbg) e_wst += clock64() - w0; }
 #pragma unroll
             for (uint32_t j = 0; j < 8; ++j)
               if (j < 4 || !half_out)
@@ -728,13 +743,19 @@ conv_tc4_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__
             const int64_t soff = ((int64_t)it.outer * hw + rr) * p.Cout + co_base;
 #pragma unroll
             for (int c = 0; c < 32; c += 4) {
-              *reinterpret_cast<float4*>(p.v_out + soff + c) = make_float4(sv[c], sv[c + 1], sv[c + 2], sv[c + 3]);
-              *reinterpret_cast<float4*>(p.i_out + soff + c) = make_float4(si[c], si[c + 1], si[c + 2], si[c + 3]);
+              float4 a, b;
+              upk2(sv[c / 2], a.x, a.y), upk2(sv[c / 2 + 1], a.z, a.w);
+              upk2(si[c / 2], b.x, b.y), upk2(si[c / 2 + 1], b.z, b.w);
+              *reinterpret_cast<float4*>(p.v_out + soff + c) = a;
+              *reinterpret_cast<float4*>(p.i_out + soff + c) = b;
             }
           }
         }
       }  // m
     }
+    if (edbg && blockIdx.x == 0 && lane == 0 && (warp == 0 || warp == 4))
+      printf("tc4 epilogue warp %d: %lld clk total, %u tile-steps, waits: acc_full %lld, tmem ld %lld, staging %lld\n", warp,
+             clock64() - e_t0, e_steps, e_wacc, e_ld, e_wst);
     if (lane == 0) bulk_wait_all();
     if (p.status != nullptr && n_over != 0) atomicAdd(p.status, n_over);
   }
