@@ -273,6 +273,32 @@ def test_full_size_gen1_forward_properties():
     assert torch.isfinite(cls).all() and torch.isfinite(bbox).all()
     assert torch.equal(torch.cat([cls_a, cls_b]), cls) and torch.equal(torch.cat([bbox_a, bbox_b]), bbox)
     assert float(cls.std()) > 0
+    # ---- the planner's routes at this size (the benchmarked configuration), by the launches it makes ----------
+    from snn_for_object_detection_b200 import _lib, ops
+
+    prof = {}
+    ops.PROFILE = prof
+    try:
+        n0 = _lib.launch_count()
+        with torch.no_grad():
+            model(X)
+        n_launch = _lib.launch_count() - n0
+    finally:
+        ops.PROFILE = None
+    conv_tags, lif_tags = prof.get("conv2d_tags", []), prof.get("conv_lif_tags", [])
+    # 48 convolutions of the net -> 38 launches: each C2f block's entry 1x1 is folded into the two stacked stem
+    # convolutions that open its Dense block (5 blocks x 2 launches saved)
+    assert len(conv_tags) + len(lif_tags) == 38, (len(conv_tags), len(lif_tags))
+    # fused Conv -> BN -> LIF where a layer has >= 600 work items: the event-frame layer (as an im2col'd 1x1 layer:
+    # 32 "channels") and the two 32 -> 32 bottlenecks of the first C2f block
+    assert sorted(t.split(" exact")[0] for t in lif_tags) == sorted([
+        "(160, 32, 120, 152)->64 k1 s1 kindP", "(160, 32, 120, 152)->32 k3 s1 kindP", "(160, 32, 120, 152)->32 k3 s1 kindP"]), lif_tags
+    # every other convolution of backbone and neck runs on the packed-activation tensor-core kernel; only the six
+    # box / class convolutions of the head (fp32 LI + tanh input, last time step only) take the fp32-input kernel
+    assert sum("kindP" in t for t in conv_tags) == 29 and sum("kind1" in t and t.startswith("(5, 256") for t in conv_tags) == 6, conv_tags
+    assert len(prof.get("lif_scan", [])) == 16 and len(prof.get("li_scan", [])) == 3
+    assert n_launch <= 62, n_launch   # one step = 59 kernels of this library (+ 3 torch cat copies in the head)
+    assert ops.overflow_count() == 0
 
 
 def _flat_states(state, acc=None):
