@@ -703,22 +703,31 @@ conv_tc4_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__
             }
             // ---- encode this row's 32 channels: 8 (F32 / PAIR) or 4 (HALF) chunks of 16 bytes ----
             uint32_t w[32];
+            // (one uniform branch per format around whole loops: a format test inside the loop gets if-converted and
+            // the PAIR arithmetic is then issued, predicated off, for HALF output as well)
             if (p.out_fmt == SODA_ACT_F32) {
 #pragma unroll
               for (int j = 0; j < 32; ++j) w[j] = __float_as_uint(o[j]);
-            } else {
+            } else if (p.out_fmt == SODA_ACT_PAIR) {
               float amax = 0.f;
 #pragma unroll
               for (int j = 0; j < 16; ++j) {
                 const uint32_t hi = pack_h2(o[2 * j], o[2 * j + 1]);
+                const float2 hf = unpack_h2(hi);
                 w[j] = hi;
-                if (p.out_fmt == SODA_ACT_PAIR) {
-                  const float2 hf = unpack_h2(hi);
-                  w[16 + j] = pack_h2(o[2 * j] - hf.x, o[2 * j + 1] - hf.y);
-                }
+                w[16 + j] = pack_h2(o[2 * j] - hf.x, o[2 * j + 1] - hf.y);
                 amax = fmaxf(amax, fmaxf(fabsf(o[2 * j]), fabsf(o[2 * j + 1])));
               }
               n_over += amax > 65504.f;
+            } else {
+#pragma unroll
+              for (int j = 0; j < 16; ++j) w[j] = pack_h2(o[2 * j], o[2 * j + 1]);
+              if (!(LIF && !has_res)) {   // spikes {0, 1} cannot leave the fp16 range; anything else is checked
+                float amax = 0.f;
+#pragma unroll
+                for (int j = 0; j < 16; ++j) amax = fmaxf(amax, fmaxf(fabsf(o[2 * j]), fabsf(o[2 * j + 1])));
+                n_over += amax > 65504.f;
+              }
             }
             // ---- stage (swizzled) and let TMA store it ----
             { const long long w0 = edbg ? clock64() : 0;
