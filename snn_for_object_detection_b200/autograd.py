@@ -46,8 +46,9 @@ class _ConvFn(torch.autograd.Function):
         if need_x and ctx.stride == 1 and _DGRAD_NATIVE and weight.shape[0] % 32 == 0:
             # dgrad of a stride-1 'same' convolution IS a convolution of gy with the spatially flipped, (Cout, Cin)-
             # transposed filter: it runs on our own forward kernel (tcgen05, fp32-accurate operand scheme)
-            gx = ops.conv2d(gy if gy.is_contiguous(memory_format=torch.channels_last)
-                            else gy.contiguous(memory_format=torch.channels_last), ctx.conv.packed_dgrad())
+            # (a channel slice of a concat gradient is pixel-major addressable: the kernel reads it through its pixel
+            # stride, no copy - ops.conv2d only makes a tensor contiguous when it is not addressable that way)
+            gx = ops.conv2d(gy, ctx.conv.packed_dgrad())
             need_x = False
         if need_x or need_w:
             gx2, gw, _ = torch.ops.aten.convolution_backward(

@@ -49,6 +49,13 @@ def _has_state(block: "BlockGen") -> bool:
     return False
 
 
+class _CatParts(list):
+    """Training route: the pieces of a Dense merge that is the LAST layer of a branch of an enclosing Dense block,
+    handed up unconcatenated.  The reference nests its C2f bottlenecks as Dense-in-Dense (models/tiny_yolo.py:67-75),
+    so ``torch.cat`` at every level copies the innermost tensors once per level (n + 1 levels for n bottlenecks);
+    only the enclosing merge consumes the result, and it concatenates all pieces once."""
+
+
 def _packed() -> bool:
     """Inference keeps inter-layer activations in the tensor core's own operand formats (ops.FMT_PAIR /
     FMT_HALF, rows N1 / N2 of the scope table) unless ``SODA_PACKED=0``; a recorded (training) graph is fp32."""
@@ -274,13 +281,16 @@ class BlockGen(nn.Module):
 
     def forward_seq(
         self, X: torch.Tensor, T: int, state: Optional[ListState] = None, out: Optional[torch.Tensor] = None,
-        packed_out: bool = False, fold: Optional[SodaConv2d] = None,
+        packed_out: bool = False, fold: Optional[SodaConv2d] = None, lazy_cat: bool = False,
     ) -> Tuple[torch.Tensor, ListState]:
         """All T steps of the block; ``X`` is ``[T*B, C, H, W]`` time-major.  ``out``: optional
         pre-allocated (possibly channel-sliced) destination for the block's result.  ``packed_out``: the caller
         is another planner and takes the result in whatever activation format it was produced in; otherwise
         (the public call) the result is fp32."""
-        Y, out_state = self._forward_seq(X, T, state, out, f32_out=not packed_out and out is None, fold=fold)
+        Y, out_state = self._forward_seq(X, T, state, out, f32_out=not packed_out and out is None, fold=fold,
+                                         lazy_cat=lazy_cat)
+        if isinstance(Y, _CatParts):
+            return Y, out_state      # (only ever asked for by an enclosing Dense merge of the training route)
         if not packed_out and Y.dtype != torch.float32:
             Y = ops.to_f32(Y)
         return Y, out_state
@@ -368,7 +378,7 @@ class BlockGen(nn.Module):
         ops.pconv(Xp, self._stem_weights(plan, fold, ops.fmt_of(Xp)), out=out)
         return {bi: dense_buf[:, lo:hi] for bi, _, lo, hi in plan}
 
-    def _forward_seq(self, X, T, state, out, f32_out=False, fold=None):
+    def _forward_seq(self, X, T, state, out, f32_out=False, fold=None, lazy_cat=False):
         """``f32_out``: the result leaves the planner (public call): whatever produces it writes fp32 directly.
         ``fold``: a 1x1 convolution the caller skipped because this block's stems absorb it (see _stem_weights)."""
         outs = []
@@ -412,7 +422,8 @@ class BlockGen(nn.Module):
                 branch_state = [None] + rest_state
             else:
                 Y, consumed = self._run_branch(X, T, branch, flags, branch_state, dst, fuse_res, out,
-                                               f32_out=f32_out and self.merge != "dense")
+                                               f32_out=f32_out and self.merge != "dense",
+                                               lazy_last=recording and self.merge == "dense")
             out_state.append(branch_state)
             if consumed:
                 # the other branch is the identity: its state list is all None
@@ -420,7 +431,15 @@ class BlockGen(nn.Module):
                 return Y, ([branch_state, other] if bi == 0 else [other, branch_state])
             outs.append(Y)
         if self.merge == "dense" and recording:
-            return torch.cat(outs, dim=1), out_state   # models/generator.py:158
+            parts = []
+            for o in outs:
+                if isinstance(o, _CatParts):
+                    parts.extend(o)
+                else:
+                    parts.append(o)
+            if lazy_cat:
+                return _CatParts(parts), out_state
+            return torch.cat(parts, dim=1), out_state   # models/generator.py:158 (nested merges flattened)
         if self.merge == "dense":
             # a concat of spike maps / spike counts is itself one (largest bound): the next Conv may use the
             # bf16-only operand scheme
@@ -516,7 +535,8 @@ class BlockGen(nn.Module):
         return ops.pconv_lif(Y, conv.packed_p(norm, ops.fmt_of(Y)), T, cell._const, v0, i0, residual=res, out=o,
                              out_fmt=ofmt)
 
-    def _run_branch(self, X, T, branch, flags, branch_state, dst, residual=None, residual_dst=None, f32_out=False):
+    def _run_branch(self, X, T, branch, flags, branch_state, dst, residual=None, residual_dst=None, f32_out=False,
+                    lazy_last=False):
         """Runs one branch; fuses Conv+Norm(eval)(+LIF) and LI+Tanh; the branch's last layer writes
         straight into ``dst`` (concat slice / caller's buffer) when it can.  ``residual``: tensor the
         caller wants added to the branch result (then written to ``residual_dst`` if given); returns
@@ -634,7 +654,8 @@ class BlockGen(nn.Module):
                     o = self._lookahead_dst(branch, idx, n, Y.shape[0], layer.out_channels, Ho, Wo, dst, Y.device,
                                             prealloc)
                 Y, branch_state[idx] = layer.forward_seq(Y, T, branch_state[idx], out=o,
-                                                         packed_out=not (f32_out and idx == n - 1 and o is None))
+                                                         packed_out=not (f32_out and idx == n - 1 and o is None),
+                                                         lazy_cat=lazy_last and idx == n - 1 and o is None)
                 idx += 1
                 if idx == n and o is not None:
                     return Y, False
@@ -730,6 +751,8 @@ class BlockGen(nn.Module):
                 if b is not None and not (isinstance(layer, nn.Upsample) and layer.mode != "nearest"):
                     ops.mark_exact(Y, b)
             idx += 1
+        if isinstance(Y, _CatParts):
+            return Y, False
         if dst is not None and dst.data_ptr() != Y.data_ptr():
             _copy_into(Y, dst)
             Y = dst
