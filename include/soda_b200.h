@@ -249,6 +249,14 @@ SODA_API int soda_lif_bwd(const soda_neuron_params_t* p, const float* grad_out, 
                  const float* grad_i_T, const float* v_dec_trace, int T, int64_t n, float* grad_x,
                  float* grad_v0, float* grad_i0, void* stream);
 
+/* The same with grad_out read in place from a channel slice of a wider pixel-major tensor - the gradient of a Dense
+ * concat (models/generator.py:158) as autograd hands it to a branch: element e of step t is channel e % C of pixel
+ * t * (n / C) + e / C, pixels grad_out_pix_stride floats apart (>= C; n % C == 0).  Saves the .contiguous() copy of
+ * every such slice in the training step.  Everything else as soda_lif_bwd. */
+SODA_API int soda_lif_bwd_strided(const soda_neuron_params_t* p, const float* grad_out, int C, int64_t grad_out_pix_stride,
+                 const float* grad_v_T, const float* grad_i_T, const float* v_dec_trace, int T, int64_t n,
+                 float* grad_x, float* grad_v0, float* grad_i0, void* stream);
+
 /* LI backward: out_t = v_t (pre-tanh; tanh' is applied by the caller's grad_out). */
 SODA_API int soda_li_bwd(const soda_neuron_params_t* p, const float* grad_out, const float* grad_v_T,
                 const float* grad_i_T, int T, int64_t n, float* grad_x, float* grad_v0,

@@ -120,6 +120,7 @@ SIGNATURES = {
                                _vp]),
     "soda_li_fwd": (_i, [C.POINTER(NeuronParams), _vp, _vp, _vp, _i, _i64, _i, _vp, _vp, _vp, _vp, _vp]),
     "soda_lif_bwd": (_i, [C.POINTER(NeuronParams), _vp, _vp, _vp, _vp, _i, _i64, _vp, _vp, _vp, _vp]),
+    "soda_lif_bwd_strided": (_i, [C.POINTER(NeuronParams), _vp, _i, _i64, _vp, _vp, _vp, _i, _i64, _vp, _vp, _vp, _vp]),
     "soda_li_bwd": (_i, [C.POINTER(NeuronParams), _vp, _vp, _vp, _i, _i64, _vp, _vp, _vp, _vp]),
     "soda_pool2d_fwd": (_i, [_vp, _i, _i, _i, _i, _i, _i, _i, _i64, _i64, _vp, _i64, _i64, _vp]),
     "soda_channel_affine": (_i, [_vp, _i64, _i, _i64, _vp, _vp, _vp, _i64, _vp]),

@@ -131,10 +131,14 @@ __global__ void __launch_bounds__(256)
 neuron_bwd_kernel(NP p, const float* __restrict__ gout, const float* __restrict__ gvT,
                   const float* __restrict__ giT, const float* __restrict__ v_dec_trace, int T,
                   int64_t n, float* __restrict__ gx, float* __restrict__ gv0,
-                  float* __restrict__ gi0) {
+                  float* __restrict__ gi0, int C, int64_t g_ps) {
   pdl_trigger();   // lets a dependent tensor-core conv start its prologue in this grid's tail
   const int64_t e = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) * V;
   if (e >= n) return;
+  // grad_out may be a channel slice of a wider pixel-major tensor (the gradient of a Dense concat): element e of step t
+  // is channel e % C of pixel t * n / C + e / C, pixels g_ps floats apart.  g_ps == 0: dense [T, n].
+  const int64_t g_step = g_ps ? (n / C) * g_ps : n;
+  const int64_t g_e = g_ps ? (e / C) * g_ps + (e % C) : e;
   float gv[V], gi[V];
   if (gvT != nullptr) {
     vload<V>(gv, gvT + e);
@@ -157,7 +161,7 @@ neuron_bwd_kernel(NP p, const float* __restrict__ gout, const float* __restrict_
     for (int u = 0; u < kUnroll; ++u) {
       if (u < cnt) {
         const int64_t off = (int64_t)(t0 - 1 - u) * n + e;
-        vload<V>(go[u], gout + off);
+        vload<V>(go[u], gout + (int64_t)(t0 - 1 - u) * g_step + g_e);
         if constexpr (kLif) vload<V>(vd[u], v_dec_trace + off);
       }
     }
@@ -359,19 +363,23 @@ static int launch_fwd(const soda_neuron_params_t* q, const float* x, const float
 template <bool kLif>
 static int launch_bwd(const soda_neuron_params_t* q, const float* gout, const float* gvT,
                       const float* giT, const float* v_dec_trace, int T, int64_t n, float* gx,
-                      float* gv0, float* gi0, void* stream, const char* name) {
+                      float* gv0, float* gi0, void* stream, const char* name, int C = 0, int64_t g_ps = 0) {
   if (!q || !gout || !gx || (kLif && !v_dec_trace))
     return fail(SODA_ERR_BAD_ARG, "neuron bwd: null pointer");
   if (T <= 0 || n <= 0) return fail(SODA_ERR_BAD_ARG, "neuron bwd: non-positive size");
+  if (g_ps != 0 && (C <= 0 || n % C != 0 || g_ps < C))
+    return fail(SODA_ERR_BAD_ARG, "neuron bwd: strided grad_out needs C > 0, n % C == 0 and pixel stride >= C");
+  if (g_ps == C) g_ps = 0;   // dense after all
   const NP p = to_np(q);
   cudaStream_t st = (cudaStream_t)stream;
-  const bool vec = (n % 4 == 0) && all_aligned16({gout, gvT, giT, v_dec_trace, gx, gv0, gi0});
+  const bool vec = (n % 4 == 0) && all_aligned16({gout, gvT, giT, v_dec_trace, gx, gv0, gi0}) &&
+                   (g_ps == 0 || (C % 4 == 0 && g_ps % 4 == 0));
   if (vec) {
     neuron_bwd_kernel<4, kLif><<<(unsigned)ceil_div(n / 4, 256), 256, 0, st>>>(
-        p, gout, gvT, giT, v_dec_trace, T, n, gx, gv0, gi0);
+        p, gout, gvT, giT, v_dec_trace, T, n, gx, gv0, gi0, C, g_ps);
   } else {
     neuron_bwd_kernel<1, kLif><<<(unsigned)ceil_div(n, 256), 256, 0, st>>>(
-        p, gout, gvT, giT, v_dec_trace, T, n, gx, gv0, gi0);
+        p, gout, gvT, giT, v_dec_trace, T, n, gx, gv0, gi0, C, g_ps);
   }
   return after_launch(name);
 }
@@ -494,6 +502,15 @@ extern "C" int soda_lif_bwd(const soda_neuron_params_t* p, const float* grad_out
                             void* stream) {
   return soda::launch_bwd<true>(p, grad_out, grad_v_T, grad_i_T, v_dec_trace, T, n, grad_x,
                                 grad_v0, grad_i0, stream, "lif_bwd");
+}
+
+extern "C" int soda_lif_bwd_strided(const soda_neuron_params_t* p, const float* grad_out, int C,
+                                    int64_t grad_out_pix_stride, const float* grad_v_T, const float* grad_i_T,
+                                    const float* v_dec_trace, int T, int64_t n, float* grad_x, float* grad_v0,
+                                    float* grad_i0, void* stream) {
+  if (C <= 0 || grad_out_pix_stride < C) return soda::fail(SODA_ERR_BAD_ARG, "lif_bwd_strided: bad C / pixel stride");
+  return soda::launch_bwd<true>(p, grad_out, grad_v_T, grad_i_T, v_dec_trace, T, n, grad_x, grad_v0, grad_i0,
+                                stream, "lif_bwd_strided", C, grad_out_pix_stride);
 }
 
 extern "C" int soda_li_bwd(const soda_neuron_params_t* p, const float* grad_out,

@@ -1006,10 +1006,20 @@ def lstm_gates(pre: torch.Tensor, c_prev: Optional[torch.Tensor]) -> Tuple[torch
 def lif_scan_bwd(grad_out, grad_vT, grad_iT, v_dec, T: int, p: NeuronConst = LIF_DEFAULT):
     """Fused reverse scan: returns ``(grad_x, grad_v0, grad_i0)``."""
     _need_cuda(grad_out, grad_vT, grad_iT, v_dec)
+    g_ps = 0
     if grad_out.stride() != v_dec.stride():
-        g = torch.empty_like(v_dec)
-        g.copy_(grad_out)
-        grad_out = g
+        # a channel slice of a concat gradient (pixel-major, pixels further apart than its own channels) is read in
+        # place by the kernel; anything else is re-laid out like v_dec first
+        pm = _pm_strides(grad_out) if (grad_out.dim() == 4 and v_dec.dim() == 4 and grad_out.dtype == torch.float32
+                                       and v_dec.is_contiguous(memory_format=torch.channels_last)) else None
+        Cg = grad_out.shape[1] if grad_out.dim() == 4 else 0
+        if (pm is not None and pm[0] == grad_out.shape[2] * grad_out.shape[3] * pm[1] and Cg % 4 == 0 and pm[1] % 4 == 0
+                and grad_out.data_ptr() % 16 == 0):
+            g_ps = pm[1]
+        else:
+            g = torch.empty_like(v_dec)
+            g.copy_(grad_out)
+            grad_out = g
     n = v_dec.numel() // T
     blk = v_dec[: v_dec.shape[0] // T]
     gx = torch.empty_like(v_dec)
@@ -1020,6 +1030,14 @@ def lif_scan_bwd(grad_out, grad_vT, grad_iT, v_dec, T: int, p: NeuronConst = LIF
     if grad_iT is not None:
         grad_iT = _like_block(grad_iT, blk)
     pc = p.c()
+    if g_ps:
+        check(
+            lib.soda_lif_bwd_strided(C.byref(pc), grad_out.data_ptr(), grad_out.shape[1], g_ps, _ptr(grad_vT),
+                                     _ptr(grad_iT), v_dec.data_ptr(), T, n, gx.data_ptr(), gv0.data_ptr(),
+                                     gi0.data_ptr(), _stream()),
+            "soda_lif_bwd_strided",
+        )
+        return gx, gv0, gi0
     check(
         lib.soda_lif_bwd(C.byref(pc), grad_out.data_ptr(), _ptr(grad_vT), _ptr(grad_iT), v_dec.data_ptr(), T, n,
                          gx.data_ptr(), gv0.data_ptr(), gi0.data_ptr(), _stream()),

@@ -391,6 +391,26 @@ def test_conv_lif_direct_event_frames():
         assert torch.equal(torch.cat([za, zb]), z0) and torch.equal(vb, v0) and torch.equal(ib, i0)
 
 
+
+def test_lif_backward_reads_a_concat_gradient_slice_in_place():
+    """soda_lif_bwd_strided: grad_out as a channel slice of a wider pixel-major tensor (the gradient a Dense concat
+    hands to one branch) gives bit-identical gradients to the dense call on a copy of that slice."""
+    ops = _pkg().ops
+    torch.manual_seed(5)
+    T, B, C, H, W, Ct = 6, 2, 32, 9, 13, 96
+    x = torch.randn(T * B, C, H, W, device=DEV).contiguous(memory_format=torch.channels_last) * 2
+    z, v, i, vd, _, _ = ops.lif_scan(x, T, None, None, ops.LIF_DEFAULT, want_v_dec=True)
+    wide = torch.randn(T * B, Ct, H, W, device=DEV).contiguous(memory_format=torch.channels_last)
+    g_slice = wide[:, 32:64]
+    assert not g_slice.is_contiguous(memory_format=torch.channels_last)
+    gv = torch.randn_like(v)
+    gi = torch.randn_like(i)
+    got = ops.lif_scan_bwd(g_slice, gv, gi, vd, T, ops.LIF_DEFAULT)
+    want = ops.lif_scan_bwd(g_slice.contiguous(memory_format=torch.channels_last), gv, gi, vd, T, ops.LIF_DEFAULT)
+    for a, b in zip(got, want):
+        assert torch.equal(a, b)
+    assert float(got[0].abs().max()) > 0
+
 @pytest.mark.parametrize("with_res", [False, True])
 def test_lif_scan_out_residual_and_slice_store(with_res):
     """soda_lif_res_fwd == soda_lif_fwd (+ residual) written into a concat slice."""
