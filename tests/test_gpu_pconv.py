@@ -163,6 +163,33 @@ def test_pconv_lif_equals_pconv_then_scan(shape, out_fmt):
     assert torch.equal(v2, v) and torch.equal(i2, i)
 
 
+@pytest.mark.parametrize("hw", [(13, 19), (16, 8), (40, 23), (5, 3)])
+def test_pconv_lif_two_tiles_per_item_with_an_odd_tile_count(hw):
+    """The fused kernel at 32 output channels takes TWO 16 x 8 tiles per work item (one per epilogue warpgroup, step-
+    interleaved).  Maps with an odd number of tiles (13 x 19: 3; 40 x 23: 9), exactly one tile and a map smaller than a
+    tile: the unpaired last tile is computed, the absent partner neither stored nor carried into the state."""
+    ops = _pkg().ops
+    H, W = hw
+    T, B, C = 4, 3, 32
+    torch.manual_seed(H * 100 + W)
+    x = _cl(torch.randn(T * B, C, H, W, device=DEV))
+    w = torch.randn(C, C, 3, 3, device=DEV) * (6.0 / (C * 9)) ** 0.5
+    scale, shift = torch.rand(C, device=DEV) + 0.5, torch.randn(C, device=DEV) * 0.3
+    xp = ops.act_convert(x, ops.FMT_PAIR)
+    pc = ops.pack_pconv(w, 1, scale, shift, ops.FMT_PAIR)
+    res = ops.act_convert(_cl(torch.randn(T * B, C, H, W, device=DEV)), ops.FMT_PAIR)
+    cur = ops.pconv(xp, pc)
+    z_ref, v_ref, i_ref, _, _, _ = ops.lif_scan(cur, T)
+    assert 0.01 < float(z_ref.mean()) < 0.9
+    wide = ops.empty_act(T * B, C + 64, H, W, DEV, ops.FMT_PAIR)
+    wide.zero_()
+    y, v, i = ops.pconv_lif(xp, pc, T, ops.LIF_DEFAULT, residual=res, out=wide[:, 32:64])
+    want = z_ref + ops.to_f32(res)
+    assert float((ops.to_f32(y) - want).abs().max()) <= 2.0 ** -21 * float(want.abs().max())
+    assert torch.equal(v, v_ref) and torch.equal(i, i_ref)
+    assert float(ops.to_f32(wide[:, :32]).abs().max()) == 0 and float(ops.to_f32(wide[:, 64:]).abs().max()) == 0
+
+
 @pytest.mark.parametrize("res_fmt", [None, "f32", "pair", "half"])
 @pytest.mark.parametrize("out_fmt", ["f32", "pair", "half"])
 def test_lif_fmt_scan_equals_plain_scan(res_fmt, out_fmt):
