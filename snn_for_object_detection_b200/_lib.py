@@ -12,7 +12,7 @@ import ctypes as C
 import os
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, "libsoda_b200.so")
+LIB_PATH = os.path.join(_HERE, os.environ.get("SODA_LIB_NAME", "libsoda_b200.so"))   # (A/B builds of the same ABI)
 
 SODA_CONV_FP32 = 0
 SODA_CONV_TC = 1
