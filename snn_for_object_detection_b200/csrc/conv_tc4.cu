@@ -46,8 +46,6 @@ using namespace tc;
 
 constexpr int T4_BM = 128;
 constexpr int T4_BH = 16, T4_BW = 8;
-constexpr int T4_THREADS = 384;             // 12 warps: three whole warpgroups, as setmaxnreg wants
-constexpr int T4_W_PROD_A = 8, T4_W_PROD_B = 9, T4_W_MMA = 10;
 constexpr int T4_MAX_RING = 8;
 #ifdef SODA_TC4_EPI_DBG
 constexpr bool T4_EPI_DBG = true;
@@ -338,10 +336,224 @@ __device__ __forceinline__ void tc4_mma_role(const Tc4Params& p, uint32_t tmem_b
            dbg_wa, dbg_wb, dbg_wc, cnt, BN, MT, MODE);
 }
 
-template <int BN, bool LIF>
-__global__ void __launch_bounds__(T4_THREADS, 1)
+// ---- the 16-warp epilogue of the fused Conv -> BN -> LIF kernel (NE = 16) ---------------------------------------
+// Warp w: TMEM lane quarter q = w & 3 (32 pixels), column half h = (w >> 2) & 1, group g = w >> 3.
+//   BN = 64: all warps work on the same tile; g = its 32-channel group, the warp owns channels g*32 + h*16 .. + 16.
+//   BN = 32: g = the work unit's owner (units alternate, each with its own accumulator stages {2g, 2g+1}), the warp owns
+//            channels h*16 .. + 16 of the unit's single group.
+// The two warps (h = 0, 1) of a (q, g) pair fill ONE 32-pixel x 32-channel staging tile and the h = 0 warp hands it to
+// TMA; two named barriers per step (tile free -> both write -> tile complete) keep the pair in step.
+__device__ __forceinline__ void pair_sync(int id) { asm volatile("bar.sync %0, 64;" ::"r"(id) : "memory"); }
+
+template <int BN>
+__device__ __forceinline__ void tc4_lif16_epilogue(const Tc4Params& p, const CUtensorMap& tmY, uint32_t tmem_base,
+                                                   uint64_t* acc_full, uint64_t* acc_empty, uint8_t* epi_base,
+                                                   int my_chunk, int warp, int lane) {
+  constexpr uint32_t NACC = t4_nacc(BN);
+  constexpr bool UNIT_SPLIT = BN == 32;
+  static_assert(BN == 32 || BN == 64, "fused LIF: 32 or 64 output channels per CTA");
+  const int q = warp & 3, h = (warp >> 2) & 1, g = warp >> 3;
+  const int pair = q + 4 * g;
+  const uint32_t stage_u32 = smem_u32(epi_base) + (uint32_t)pair * T4_EPI_BYTES;
+  const int row = q * 32 + lane;
+  const int64_t hw = (int64_t)p.Ho * p.Wo;
+  const float descale = __ldg(p.descale);
+  const f32x2_t descale2 = pk2(descale, descale);
+  const NP2 np2 = np_pairs(p.np);
+  const bool half_out = p.out_fmt == SODA_ACT_HALF;
+  const uint32_t st_row = stage_u32 + (uint32_t)lane * (half_out ? 64u : 128u);
+  const uint32_t st_xor = half_out ? (((uint32_t)lane >> 1) & 3u) : ((uint32_t)lane & 7u);
+  const int col_base = UNIT_SPLIT ? h * 16 : g * 32 + h * 16;
+  const int co_grp = my_chunk * BN + (UNIT_SPLIT ? 0 : g * 32);   // first channel of the pair's 32-channel group
+  const int co_base = my_chunk * BN + col_base;                    // first of this warp's 16 channels
+  const bool group_live = co_grp < p.Cout;                          // Cout % 32 == 0: a group is whole or absent
+  f32x2_t sh2[8];
+#pragma unroll
+  for (int j = 0; j < 8; ++j) sh2[j] = pk2(0.f, 0.f);
+  if (p.shift != nullptr && group_live) {
+#pragma unroll
+    for (int j = 0; j < 16; j += 4) {
+      const float4 v = __ldg(reinterpret_cast<const float4*>(p.shift + co_base + j));
+      sh2[j / 2] = pk2(v.x, v.y), sh2[j / 2 + 1] = pk2(v.z, v.w);
+    }
+  }
+  unsigned int n_over = 0;
+  uint32_t local = 0, unit = 0, mine_cnt = 0;
+  Tc4Iter it;
+  it.init(p);
+  for (int item = blockIdx.x; item < p.n_items; item += gridDim.x, it.next(p)) {
+    for (int m = 0; m < p.mt; ++m) {
+      const bool mine = !UNIT_SPLIT || ((unit & 1u) == (uint32_t)g);
+      ++unit;
+      if (!mine) {
+        local += (uint32_t)p.T_inner;
+        continue;
+      }
+      const int spt = it.sp * p.mt + m;
+      const int ty = spt / p.tiles_x, tx = spt - ty * p.tiles_x;
+      const int oy = ty * T4_BH + (row >> 3), ox = tx * T4_BW + (row & 7);
+      const bool valid = oy < p.Ho && ox < p.Wo;
+      const int64_t rr = (int64_t)oy * p.Wo + ox;
+      const int64_t frame0 = it.outer;
+      const int sx = tx * T4_BW, sy = ty * T4_BH + q * 4;
+      const int64_t soff = ((int64_t)it.outer * hw + rr) * p.Cout + co_base;
+      f32x2_t sv[8], si[8];
+#pragma unroll
+      for (int c = 0; c < 16; c += 4) {
+        float4 a = make_float4(p.np.v_leak, p.np.v_leak, p.np.v_leak, p.np.v_leak);
+        float4 b = make_float4(0.f, 0.f, 0.f, 0.f);
+        if (valid && p.v0 != nullptr && group_live) {
+          a = __ldg(reinterpret_cast<const float4*>(p.v0 + soff + c));
+          b = __ldg(reinterpret_cast<const float4*>(p.i0 + soff + c));
+        }
+        sv[c / 2] = pk2(a.x, a.y), sv[c / 2 + 1] = pk2(a.z, a.w);
+        si[c / 2] = pk2(b.x, b.y), si[c / 2 + 1] = pk2(b.z, b.w);
+      }
+      for (int t = 0; t < p.T_inner; ++t, ++local, ++mine_cnt) {
+        const uint32_t acc = UNIT_SPLIT ? 2u * (uint32_t)g + (mine_cnt & 1u) : local % NACC;
+        const uint32_t acc_ph = UNIT_SPLIT ? (mine_cnt >> 1) & 1u : (local / NACC) & 1u;
+        const int64_t frame = frame0 + (int64_t)t * p.Bsz;
+        const bool has_res = p.residual != nullptr && valid && group_live;
+        // this warp's 16 residual channels, fetched ahead of the accumulator wait: F32 64 B, HALF 32 B, PAIR 32 B of the
+        // group's hi half + 32 B of its lo half (64 B further)
+        uint4 rp[4];
+        if (has_res) {
+          const uint8_t* rg = p.residual + frame * p.res_bs + rr * p.res_ps;
+          if (p.res_fmt == SODA_ACT_F32) {
+            const uint8_t* r0 = rg + (int64_t)co_base * 4;
+#pragma unroll
+            for (int j = 0; j < 4; ++j) rp[j] = ldg_u4(r0 + j * 16);
+          } else if (p.res_fmt == SODA_ACT_PAIR) {
+            const uint8_t* r0 = rg + (int64_t)co_grp * 4 + h * 32;
+            rp[0] = ldg_u4(r0), rp[1] = ldg_u4(r0 + 16), rp[2] = ldg_u4(r0 + 64), rp[3] = ldg_u4(r0 + 80);
+          } else {
+            const uint8_t* r0 = rg + (int64_t)co_base * 2;
+            rp[0] = ldg_u4(r0), rp[1] = ldg_u4(r0 + 16);
+          }
+        }
+        mbar_wait(&acc_full[acc], acc_ph);
+        tc_fence_after();
+        const uint32_t t_row = tmem_base + ((uint32_t)(q * 32) << 16) + acc * (2 * BN) + (uint32_t)col_base;
+        float o[16];
+        {
+          uint32_t r[16], rc[16];
+          tmem_ld_32x16(t_row, r);
+          tmem_ld_32x16(t_row + BN, rc);
+          tmem_ld_wait();
+          tc_fence_before();
+          __syncwarp();
+          if (lane == 0) mbar_arrive(&acc_empty[acc]);
+          if (p.shift != nullptr) {
+#pragma unroll
+            for (int j = 0; j < 16; j += 2) {
+              const f32x2_t sum = add2(pk2(__uint_as_float(r[j]), __uint_as_float(r[j + 1])),
+                                       pk2(__uint_as_float(rc[j]), __uint_as_float(rc[j + 1])));
+              upk2(fma2(sum, descale2, sh2[j / 2]), o[j], o[j + 1]);
+            }
+          } else {
+#pragma unroll
+            for (int j = 0; j < 16; ++j) o[j] = __fmul_rn(__uint_as_float(r[j]) + __uint_as_float(rc[j]), descale);
+          }
+        }
+#pragma unroll
+        for (int j = 0; j < 8; ++j) lif_step2(np2, pk2(o[2 * j], o[2 * j + 1]), sv[j], si[j], o[2 * j], o[2 * j + 1]);
+        if (has_res) {
+          if (p.res_fmt == SODA_ACT_F32) {
+#pragma unroll
+            for (int j = 0; j < 4; ++j) {
+              o[4 * j] += __uint_as_float(rp[j].x), o[4 * j + 1] += __uint_as_float(rp[j].y);
+              o[4 * j + 2] += __uint_as_float(rp[j].z), o[4 * j + 3] += __uint_as_float(rp[j].w);
+            }
+          } else if (p.res_fmt == SODA_ACT_PAIR) {
+#pragma unroll
+            for (int j = 0; j < 2; ++j) {
+              const uint32_t hw4[4] = {rp[j].x, rp[j].y, rp[j].z, rp[j].w};
+              const uint32_t lw4[4] = {rp[j + 2].x, rp[j + 2].y, rp[j + 2].z, rp[j + 2].w};
+#pragma unroll
+              for (int w = 0; w < 4; ++w) {
+                const float2 a = unpack_h2(hw4[w]), b = unpack_h2(lw4[w]);
+                o[8 * j + 2 * w] += a.x + b.x;
+                o[8 * j + 2 * w + 1] += a.y + b.y;
+              }
+            }
+          } else {
+#pragma unroll
+            for (int j = 0; j < 2; ++j) {
+              const uint32_t hw4[4] = {rp[j].x, rp[j].y, rp[j].z, rp[j].w};
+#pragma unroll
+              for (int w = 0; w < 4; ++w) {
+                const float2 a = unpack_h2(hw4[w]);
+                o[8 * j + 2 * w] += a.x, o[8 * j + 2 * w + 1] += a.y;
+              }
+            }
+          }
+        }
+        // ---- the pair's staging tile: free (the leader's previous store has read it) -> both write -> complete ----
+        if (h == 0 && lane == 0) bulk_wait_read0();
+        pair_sync(1 + pair);
+        if (p.out_fmt == SODA_ACT_F32) {
+#pragma unroll
+          for (uint32_t j = 0; j < 4; ++j)
+            sts128(st_row + (((uint32_t)h * 4u + j) ^ st_xor) * 16u, o[4 * j], o[4 * j + 1], o[4 * j + 2], o[4 * j + 3]);
+        } else {
+          uint32_t whi[8];
+#pragma unroll
+          for (int j = 0; j < 8; ++j) whi[j] = pack_h2(o[2 * j], o[2 * j + 1]);
+          if (p.residual != nullptr) {   // spikes {0, 1} alone cannot leave the fp16 range; spike + residual is checked
+            float amax = 0.f;
+#pragma unroll
+            for (int j = 0; j < 8; ++j) amax = fmaxf(amax, fmaxf(fabsf(o[2 * j]), fabsf(o[2 * j + 1])));
+            n_over += amax > 65504.f;
+          }
+#pragma unroll
+          for (uint32_t j = 0; j < 2; ++j)
+            sts128(st_row + (((uint32_t)h * 2u + j) ^ st_xor) * 16u, __uint_as_float(whi[4 * j]), __uint_as_float(whi[4 * j + 1]),
+                   __uint_as_float(whi[4 * j + 2]), __uint_as_float(whi[4 * j + 3]));
+          if (p.out_fmt == SODA_ACT_PAIR) {
+            uint32_t wlo[8];
+#pragma unroll
+            for (int j = 0; j < 8; ++j) {
+              const float2 hf = unpack_h2(whi[j]);
+              wlo[j] = pack_h2(o[2 * j] - hf.x, o[2 * j + 1] - hf.y);
+            }
+#pragma unroll
+            for (uint32_t j = 0; j < 2; ++j)
+              sts128(st_row + ((4u + (uint32_t)h * 2u + j) ^ st_xor) * 16u, __uint_as_float(wlo[4 * j]),
+                     __uint_as_float(wlo[4 * j + 1]), __uint_as_float(wlo[4 * j + 2]), __uint_as_float(wlo[4 * j + 3]));
+          }
+        }
+        fence_proxy_async_smem();
+        pair_sync(1 + pair);
+        if (h == 0 && lane == 0 && group_live) {
+          tma_store_4d(&tmY, stage_u32, co_grp, sx, sy, (int)frame);
+          bulk_commit();
+        }
+      }
+      if (valid && group_live) {
+#pragma unroll
+        for (int c = 0; c < 16; c += 4) {
+          float4 a, b;
+          upk2(sv[c / 2], a.x, a.y), upk2(sv[c / 2 + 1], a.z, a.w);
+          upk2(si[c / 2], b.x, b.y), upk2(si[c / 2 + 1], b.z, b.w);
+          *reinterpret_cast<float4*>(p.v_out + soff + c) = a;
+          *reinterpret_cast<float4*>(p.i_out + soff + c) = b;
+        }
+      }
+    }
+  }
+  if (h == 0 && lane == 0) bulk_wait_all();
+  if (p.status != nullptr && n_over != 0) atomicAdd(p.status, n_over);
+}
+
+// NE = epilogue warps.  8: two per TMEM lane quarter, 32 output channels each.  16 (fused LIF only, SODA_TC4_LIF16=1):
+// four per quarter, 16 channels each - the LIF epilogue is instruction-bound (~700 warp-instructions per warp and time
+// step), and two warps per scheduler cannot hide its fixed latencies; four can.  Role warps follow the epilogue warps.
+template <int BN, bool LIF, int NE = 8>
+__global__ void __launch_bounds__((NE + 4) * 32, 1)
 conv_tc4_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
                 const __grid_constant__ CUtensorMap tmY, Tc4Params p) {
+  static_assert(NE == 8 || (NE == 16 && LIF), "16 epilogue warps: fused LIF variants only");
+  constexpr int T4_W_PROD_A = NE, T4_W_PROD_B = NE + 1, T4_W_MMA = NE + 2;
   constexpr uint32_t NACC = t4_nacc(BN);
   constexpr uint32_t TMEM_COLS = NACC * 2 * BN;
   constexpr bool UNIT_SPLIT = BN == 32;          // the two warps of a lane quarter alternate work units
@@ -378,7 +590,7 @@ conv_tc4_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__
     }
     for (int a = 0; a < 4; ++a) {
       mbar_init(&acc_full[a], 1);
-      mbar_init(&acc_empty[a], UNIT_SPLIT ? 4 : 8);   // one arrival per epilogue warp that reads the stage
+      mbar_init(&acc_empty[a], (UNIT_SPLIT ? 4 : 8) * (NE / 8));   // one arrival per epilogue warp that reads the stage
     }
     fence_barrier_init();
   }
@@ -531,7 +743,10 @@ conv_tc4_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__
     }
 #undef TC4_ROLE_M
 #undef TC4_ROLE
-  } else if (warp < 8) {
+  } else if (warp < NE) {
+    if constexpr (NE == 16) {
+      tc4_lif16_epilogue<BN>(p, tmY, tmem_base, acc_full, acc_empty, epi_base, my_chunk, warp, lane);
+    } else {
     // ================================ epilogue ================================================
     // Two warps per TMEM lane quarter.  BN >= 64: warpgroup e owns columns [e*BN/2, (e+1)*BN/2) of every tile;
     // BN = 32: the warpgroups alternate work units.  Per 32-channel group a warp reads main + correction accumulator,
@@ -767,6 +982,7 @@ conv_tc4_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__
              clock64() - e_t0, e_steps, e_wacc, e_ld, e_wst);
     if (lane == 0) bulk_wait_all();
     if (p.status != nullptr && n_over != 0) atomicAdd(p.status, n_over);
+    }   // NE == 8
   }
 
   tc_fence_before();
@@ -867,11 +1083,12 @@ static int encode_map4(CUtensorMap* m, CUtensorMapDataType dt, const void* base,
   return 0;
 }
 
-template <int BN, bool LIF>
+template <int BN, bool LIF, int NE = 8>
 static int launch_tc4(const CUtensorMap& tmA, const CUtensorMap& tmB, const CUtensorMap& tmY, const Tc4Params& p, int grid,
                       size_t smem, cudaStream_t st) {
+  constexpr int T4_THREADS = (NE + 4) * 32;
   // the opt-in is per device: set it on every launch (cheap), not once per process
-  cudaError_t e = cudaFuncSetAttribute(conv_tc4_kernel<BN, LIF>, cudaFuncAttributeMaxDynamicSharedMemorySize, 232448);
+  cudaError_t e = cudaFuncSetAttribute(conv_tc4_kernel<BN, LIF, NE>, cudaFuncAttributeMaxDynamicSharedMemorySize, 232448);
   if (e != cudaSuccess) {
     set_error("pconv: cudaFuncSetAttribute: %s", cudaGetErrorString(e));
     return (int)SODA_ERR_CUDA;
@@ -886,9 +1103,9 @@ static int launch_tc4(const CUtensorMap& tmA, const CUtensorMap& tmB, const CUte
     at[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
     at[0].val.programmaticStreamSerializationAllowed = 1;
     cfg.attrs = at, cfg.numAttrs = 1;
-    cudaLaunchKernelEx(&cfg, conv_tc4_kernel<BN, LIF>, tmA, tmB, tmY, p);
+    cudaLaunchKernelEx(&cfg, conv_tc4_kernel<BN, LIF, NE>, tmA, tmB, tmY, p);
   } else {
-    conv_tc4_kernel<BN, LIF><<<grid, T4_THREADS, smem, st>>>(tmA, tmB, tmY, p);
+    conv_tc4_kernel<BN, LIF, NE><<<grid, T4_THREADS, smem, st>>>(tmA, tmB, tmY, p);
   }
   return after_launch("conv_tc4_kernel");
 }
@@ -1132,6 +1349,12 @@ int conv_tc4_dispatch(const soda_pconv_desc_t* d, const void* x, const void* pac
   const size_t smem = (size_t)p.b_region_bytes + (size_t)p.a_stages * p.plane_bytes + 1024 + 8 * T4_EPI_BYTES + 1024;
   cudaStream_t st = (cudaStream_t)stream;
   if (is_lif) {
+    // 16 epilogue warps by default (measured on the step: fused-LIF kernels 1.02 -> 0.79 ms); SODA_TC4_LIF16=0: 8
+    static const int lif16 = []() { const char* e = getenv("SODA_TC4_LIF16"); return e ? atoi(e) : 1; }();
+    if (lif16) {
+      if (BN == 32) return launch_tc4<32, true, 16>(tmA, tmB, tmY, p, grid, smem, st);
+      return launch_tc4<64, true, 16>(tmA, tmB, tmY, p, grid, smem, st);
+    }
     if (BN == 32) return launch_tc4<32, true>(tmA, tmB, tmY, p, grid, smem, st);
     return launch_tc4<64, true>(tmA, tmB, tmY, p, grid, smem, st);
   }
