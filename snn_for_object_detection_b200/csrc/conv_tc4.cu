@@ -28,7 +28,9 @@
 // "im2col by descriptor" (one 18 x 10 halo tile per 32-channel slab, the nine taps are nine descriptors into it),
 // the persistent item loop, the weight-stationary / streamed plans and programmatic dependent launch are those of
 // conv_tc3.cu.  12 warps: w0-7 epilogue (two per TMEM lane quarter), w8 A producer (TMA), w9 B producer (TMA),
-// w10 MMA issuer + TMEM owner, w11 idle (setmaxnreg moves registers between whole warpgroups).
+// w10 MMA issuer + TMEM owner, w11 idle.  The fused Conv -> BN -> LIF instantiations run 20 warps: w0-15 epilogue (four
+// per lane quarter, 16 channels each - their neuron arithmetic is instruction-bound and needs the schedulers full),
+// w16 / w17 producers, w18 issuer.
 #include <stdlib.h>
 #include <string.h>
 
