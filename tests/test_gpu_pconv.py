@@ -121,7 +121,8 @@ def test_pconv_against_fp64(case):
 
 
 @pytest.mark.parametrize("shape", [(32, 32, 3, 1, "pair"), (64, 64, 3, 1, "pair"), (64, 128, 3, 2, "pair"),
-                                   (128, 128, 1, 1, "half"), (2 * 32, 64, 3, 2, "half")])
+                                   (128, 128, 1, 1, "half"), (2 * 32, 64, 3, 2, "half"),
+                                   (64, 96, 3, 1, "pair")])   # 96 channels: the second 64-channel chunk has one absent group
 @pytest.mark.parametrize("out_fmt", ["f32", "pair", "half"])
 def test_pconv_lif_equals_pconv_then_scan(shape, out_fmt):
     """Fused Conv -> BN -> LIF (+ residual) over T steps with the state in registers == the same convolution written
