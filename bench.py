@@ -348,6 +348,12 @@ def run_gpu_arm(args, cfg_id, cfg):
         copied = [torch.cuda.Event() for _ in range(2)]
         consumed = [torch.cuda.Event() for _ in range(2)]
         copy_stream = torch.cuda.Stream()
+        # results leave through a second stream: the compute stream only makes a device copy of the step's outputs
+        # (microseconds), the PCIe read-back of that copy overlaps the next step instead of holding the compute stream
+        d2h_stream = torch.cuda.Stream()
+        out_stage = [[torch.empty_like(o) for o in g_outs] for _ in range(2)]
+        out_ready = [torch.cuda.Event() for _ in range(2)]
+        out_read = [torch.cuda.Event() for _ in range(2)]
         e2e_k = [0]
 
         def step_e2e():
@@ -363,15 +369,22 @@ def run_gpu_arm(args, cfg_id, cfg):
                 ev_static.copy_(stage[k])
                 consumed[k].record(main)
                 run_chunk()
-                for o, h in zip(g_outs, host_out[c]):
-                    h.copy_(o, non_blocking=True)
+                main.wait_event(out_read[k])                     # the read-back two steps ago has drained this copy
+                for o, d in zip(g_outs, out_stage[k]):
+                    d.copy_(o, non_blocking=True)
+                out_ready[k].record(main)
+                with torch.cuda.stream(d2h_stream):
+                    d2h_stream.wait_event(out_ready[k])
+                    for d, h in zip(out_stage[k], host_out[c]):
+                        h.copy_(d, non_blocking=True)
+                    out_read[k].record(d2h_stream)
 
         def barrier():
             if world > 1:
                 dist.barrier()
             torch.cuda.synchronize()
 
-        def timed(fn, steps, warmup):
+        def timed(fn, steps, warmup, finish=None):
             for _ in range(warmup):
                 fn()
             barrier()
@@ -381,6 +394,8 @@ def run_gpu_arm(args, cfg_id, cfg):
             e0.record()
             for _ in range(steps):
                 fn()
+            if finish is not None:
+                finish()          # work the steps left on other streams belongs to the timed region
             e1.record()
             barrier()
             clocks = sampler.stop()
@@ -391,10 +406,15 @@ def run_gpu_arm(args, cfg_id, cfg):
                 ms = float(t.item())
             return ms, clocks
 
-        for ev in consumed:
+        for ev in consumed + out_read:
             ev.record()
         ms_dev, clocks = timed(step_device, args.steps, args.warmup)
-        ms_e2e, _ = timed(step_e2e, args.steps, args.warmup)
+        def e2e_drain():
+            main = torch.cuda.current_stream()
+            for ev in out_read:
+                main.wait_event(ev)      # the last results have reached host memory before the closing event
+
+        ms_e2e, _ = timed(step_e2e, args.steps, args.warmup, finish=e2e_drain)
 
         # ---- per-kernel-family device time of one eager chunk (CUDA events on the launch stream) -------------
         # The GPU is parked on a spin kernel while the host enqueues the whole pass, so that each (start, end)
